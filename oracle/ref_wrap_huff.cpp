@@ -1,0 +1,79 @@
+// TEST INFRASTRUCTURE ONLY -- never linked into the product library.
+//
+// C-ABI wrapper around the UNMODIFIED reference Huffman stage
+//   include/mgard-x/Lossless/ParallelHuffman/Huffman.hpp:553-632
+// (SERIAL back-end, Q=uint64, S=int64, H=uint64 exactly as instantiated by
+//  CompressionLowLevel/Compressor.h:47-48).  Compiled by oracle/Makefile into
+// oracle/_ref/libmgardx_ref.so.
+#include <cstdint>
+#include <cstring>
+#include <vector>
+
+#include "mgard-x/RuntimeX/RuntimeX.h"
+
+#include "mgard-x/Lossless/ParallelHuffman/Huffman.hpp"
+
+using namespace mgard_x;
+
+extern "C" {
+
+// codes: shifted quantised integers (dictionary range is [0, dict)); values
+// outside become outliers.  Returns the serialized "MGXHUFF" container.
+int ref_huffman_compress(const int64_t *codes, uint64_t n, uint32_t dict,
+                         uint32_t chunk, uint8_t *out, uint64_t cap,
+                         uint64_t *out_bytes) {
+  using Dev = SERIAL;
+  try {
+    DeviceRuntime<Dev>::Initialize();
+    log::level = log::ERR;
+    Huffman<QUANTIZED_UNSIGNED_INT, QUANTIZED_INT, HUFFMAN_CODE, Dev> huffman;
+    huffman.Resize((SIZE)n, (int)dict, (int)chunk, 1.0, 0);
+    DeviceRuntime<Dev>::SyncQueue(0);
+    Array<1, QUANTIZED_INT, Dev> data({(SIZE)n});
+    data.load(codes);
+    Array<1, Byte, Dev> compressed;
+    huffman.Compress(data, compressed, 0.0f, 0);
+    huffman.Serialize(compressed, 0);
+    DeviceRuntime<Dev>::SyncQueue(0);
+    *out_bytes = compressed.shape(0);
+    if (compressed.shape(0) > cap)
+      return 2;
+    std::memcpy(out, compressed.hostCopy(false, 0), compressed.shape(0));
+    return 0;
+  } catch (...) {
+    return 1;
+  }
+}
+
+int ref_huffman_decompress(const uint8_t *in, uint64_t bytes, uint64_t n,
+                           uint32_t dict, uint32_t chunk, int64_t *codes) {
+  using Dev = SERIAL;
+  try {
+    DeviceRuntime<Dev>::Initialize();
+    log::level = log::ERR;
+    Huffman<QUANTIZED_UNSIGNED_INT, QUANTIZED_INT, HUFFMAN_CODE, Dev> huffman;
+    huffman.Resize((SIZE)n, (int)dict, (int)chunk, 1.0, 0);
+    DeviceRuntime<Dev>::SyncQueue(0);
+    Array<1, Byte, Dev> compressed({(SIZE)bytes});
+    compressed.load(in);
+    Array<1, QUANTIZED_INT, Dev> data({(SIZE)n});
+    huffman.Deserialize(compressed, 0);
+    huffman.Decompress(compressed, data, 0);
+    DeviceRuntime<Dev>::SyncQueue(0);
+    std::memcpy(codes, data.hostCopy(false, 0), n * sizeof(int64_t));
+    return 0;
+  } catch (...) {
+    return 1;
+  }
+}
+
+// zstd is referenced unconditionally by Lossless/Zstd.hpp and Lossless/CPU.hpp
+// but never called on the Huffman path; stub the five symbols so the oracle has
+// no run-time dependency outside libstdc++/libgomp.
+size_t ZSTD_compress(void *, size_t, const void *, size_t, int) { return 0; }
+size_t ZSTD_decompress(void *, size_t, const void *, size_t) { return 0; }
+size_t ZSTD_compressBound(size_t n) { return n; }
+unsigned ZSTD_isError(size_t) { return 1; }
+const char *ZSTD_getErrorName(size_t) { return "zstd stubbed out in oracle"; }
+
+} // extern "C"
