@@ -1,0 +1,225 @@
+"""ctypes loaders for the two CPU oracles (TEST INFRASTRUCTURE ONLY).
+
+* ``ref``  -- oracle/_ref/libmgardx_ref.so: the reference's own SERIAL/OPENMP
+  MGARD-X low-level path compiled from /root/reference by oracle/Makefile.
+* ``port`` -- oracle/libmgx_oracle.so: the plain-C restatement (mgx_oracle.c).
+
+Nothing under mgard_b200/ imports this module.
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+REF_SO = os.path.join(ORACLE_DIR, "_ref", "libmgardx_ref.so")
+PORT_SO = os.path.join(ORACLE_DIR, "libmgx_oracle.so")
+
+c_u64 = ctypes.c_uint64
+c_dbl = ctypes.c_double
+c_vp = ctypes.c_void_p
+
+
+def _vp(a):
+    return a.ctypes.data_as(c_vp)
+
+
+def _shape(shape):
+    return (c_u64 * len(shape))(*[int(s) for s in shape])
+
+
+def _suffix(D, dtype):
+    return "%d%s" % (D, "f" if np.dtype(dtype) == np.float32 else "d")
+
+
+def _psuffix(dtype):
+    return "f32" if np.dtype(dtype) == np.float32 else "f64"
+
+
+def build_port():
+    if not os.path.exists(PORT_SO) or os.path.getmtime(PORT_SO) < max(
+        os.path.getmtime(os.path.join(ORACLE_DIR, f))
+        for f in ("mgx_oracle.c", "mgx_oracle_core.inc",
+                  "mgx_oracle_huffman.inc", "mgx_oracle.h")):
+        subprocess.check_call(["make", "-C", ORACLE_DIR, "port"],
+                              stdout=subprocess.DEVNULL)
+
+
+_ref = None
+_port = None
+
+
+def have_ref():
+    return os.path.exists(REF_SO)
+
+
+def ref():
+    global _ref
+    if _ref is None:
+        _ref = ctypes.CDLL(REF_SO)
+    return _ref
+
+
+def port():
+    global _port
+    if _port is None:
+        build_port()
+        _port = ctypes.CDLL(PORT_SO)
+        for t in ("f32", "f64"):
+            getattr(_port, "mgxo_norm_" + t).restype = c_dbl
+    return _port
+
+
+class Oracle:
+    """Uniform python face over either library."""
+
+    def __init__(self, kind):
+        assert kind in ("ref", "port")
+        self.kind = kind
+        self.lib = ref() if kind == "ref" else port()
+
+    # -- stage: decomposition ------------------------------------------------
+    def decompose(self, u, orthogonal):
+        v = np.ascontiguousarray(u).copy()
+        D = v.ndim
+        if self.kind == "ref":
+            fn = getattr(self.lib, "ref_decompose_" + _suffix(D, v.dtype))
+            rc = fn(_shape(v.shape), _vp(v), int(orthogonal))
+        else:
+            fn = getattr(self.lib, "mgxo_decompose_" + _psuffix(v.dtype))
+            rc = fn(D, _shape(v.shape), _vp(v), int(orthogonal))
+        assert rc == 0
+        return v
+
+    def recompose(self, c, orthogonal):
+        v = np.ascontiguousarray(c).copy()
+        D = v.ndim
+        if self.kind == "ref":
+            fn = getattr(self.lib, "ref_recompose_" + _suffix(D, v.dtype))
+            rc = fn(_shape(v.shape), _vp(v), int(orthogonal))
+        else:
+            fn = getattr(self.lib, "mgxo_recompose_" + _psuffix(v.dtype))
+            rc = fn(D, _shape(v.shape), _vp(v), int(orthogonal))
+        assert rc == 0
+        return v
+
+    # -- stage: quantization -------------------------------------------------
+    def quantize(self, c, rel, tol, s, norm, dict_size=8192):
+        c = np.ascontiguousarray(c)
+        D = c.ndim
+        codes = np.zeros(c.shape, np.int64)
+        if self.kind == "ref":
+            fn = getattr(self.lib, "ref_quantize_" + _suffix(D, c.dtype))
+            rc = fn(_shape(c.shape), _vp(c), int(rel), c_dbl(tol), c_dbl(s),
+                    c_dbl(norm), dict_size, _vp(codes))
+        else:
+            fn = getattr(self.lib, "mgxo_quantize_" + _psuffix(c.dtype))
+            rc = fn(D, _shape(c.shape), _vp(c), int(rel), c_dbl(tol), c_dbl(s),
+                    c_dbl(norm), dict_size, _vp(codes))
+        assert rc == 0
+        return codes
+
+    def dequantize(self, codes, dtype, rel, tol, s, norm, dict_size=8192):
+        codes = np.ascontiguousarray(codes, np.int64)
+        D = codes.ndim
+        c = np.zeros(codes.shape, dtype)
+        if self.kind == "ref":
+            fn = getattr(self.lib, "ref_dequantize_" + _suffix(D, dtype))
+            rc = fn(_shape(c.shape), _vp(codes), int(rel), c_dbl(tol),
+                    c_dbl(s), c_dbl(norm), dict_size, _vp(c))
+        else:
+            fn = getattr(self.lib, "mgxo_dequantize_" + _psuffix(dtype))
+            rc = fn(D, _shape(c.shape), _vp(codes), int(rel), c_dbl(tol),
+                    c_dbl(s), c_dbl(norm), dict_size, _vp(c))
+        assert rc == 0
+        return c
+
+    # -- stage: Huffman ------------------------------------------------------
+    def huffman_compress(self, codes, dict_size=8192, chunk=1024):
+        codes = np.ascontiguousarray(codes, np.int64).ravel()
+        n = codes.size
+        cap = 64 + 16 * (n // chunk + 1) + 8 * (128 + dict_size) + 24 * n + 4096
+        out = np.zeros(cap, np.uint8)
+        nb = c_u64(0)
+        name = ("ref_huffman_compress" if self.kind == "ref" else
+                "mgxo_huffman_compress")
+        rc = getattr(self.lib, name)(_vp(codes), c_u64(n), dict_size, chunk,
+                                     _vp(out), c_u64(cap), ctypes.byref(nb))
+        assert rc == 0, rc
+        return out[:nb.value].copy()
+
+    def huffman_decompress(self, blob, n, dict_size=8192, chunk=1024):
+        blob = np.ascontiguousarray(blob, np.uint8)
+        codes = np.zeros(n, np.int64)
+        if self.kind == "ref":
+            rc = self.lib.ref_huffman_decompress(_vp(blob), c_u64(blob.size),
+                                                 c_u64(n), dict_size, chunk,
+                                                 _vp(codes))
+        else:
+            rc = self.lib.mgxo_huffman_decompress(_vp(blob), c_u64(blob.size),
+                                                  c_u64(n), _vp(codes))
+        assert rc == 0, rc
+        return codes
+
+    # -- whole path ----------------------------------------------------------
+    def compress(self, u, rel, tol, s, norm=0.0, dict_size=8192, chunk=1024,
+                 backend=0):
+        u = np.ascontiguousarray(u)
+        D = u.ndim
+        cap = u.nbytes * 3 + (1 << 20)
+        out = np.zeros(cap, np.uint8)
+        nb = c_u64(0)
+        nrm = c_dbl(norm)
+        if self.kind == "ref":
+            fn = getattr(self.lib, "ref_compress_" + _suffix(D, u.dtype))
+            rc = fn(backend, _shape(u.shape), _vp(u), int(rel), c_dbl(tol),
+                    c_dbl(s), ctypes.byref(nrm), dict_size, chunk, _vp(out),
+                    c_u64(cap), ctypes.byref(nb))
+        else:
+            fn = getattr(self.lib, "mgxo_compress_" + _psuffix(u.dtype))
+            rc = fn(D, _shape(u.shape), _vp(u), int(rel), c_dbl(tol), c_dbl(s),
+                    ctypes.byref(nrm), dict_size, chunk, _vp(out), c_u64(cap),
+                    ctypes.byref(nb))
+        assert rc == 0, rc
+        return out[:nb.value].copy(), nrm.value
+
+    def decompress(self, blob, shape, dtype, rel, tol, s, norm,
+                   dict_size=8192, chunk=1024, backend=0):
+        blob = np.ascontiguousarray(blob, np.uint8)
+        out = np.zeros(shape, dtype)
+        D = out.ndim
+        if self.kind == "ref":
+            fn = getattr(self.lib, "ref_decompress_" + _suffix(D, dtype))
+            rc = fn(backend, _shape(shape), _vp(blob), c_u64(blob.size),
+                    int(rel), c_dbl(tol), c_dbl(s), c_dbl(norm), dict_size,
+                    chunk, _vp(out))
+        else:
+            fn = getattr(self.lib, "mgxo_decompress_" + _psuffix(dtype))
+            rc = fn(D, _shape(shape), _vp(blob), c_u64(blob.size), int(rel),
+                    c_dbl(tol), c_dbl(s), c_dbl(norm), dict_size, _vp(out))
+        assert rc == 0, rc
+        return out
+
+
+def smooth_field(shape, dtype, seed=42, noise=1e-6):
+    """The reference's own test generator (tests/mgard-x/src/
+    test_Compressor.cpp.in:27-43) plus a higher-frequency term and a small
+    integer-hash noise -- closed form, libm-only."""
+    idx = np.indices(shape, dtype=np.float64)
+    D = len(shape)
+    v = np.ones(shape, np.float64)
+    ph = np.zeros(shape, np.float64)
+    for d in range(D):
+        v *= np.sin(2.0 * np.pi * idx[d] / shape[d] + 0.5 * d)
+        ph += (d + 1) * idx[d] / shape[d]
+    for k in range(1, 5):
+        v += 0.05 * 2.0 ** (-k) * np.sin(2.0 * np.pi * (2 * k + 1) * ph)
+    lin = np.arange(int(np.prod(shape)), dtype=np.uint64).reshape(shape)
+    h = (lin + np.uint64(seed)) * np.uint64(0x9E3779B97F4A7C15)
+    h ^= h >> np.uint64(31)
+    h *= np.uint64(0xBF58476D1CE4E5B9)
+    h ^= h >> np.uint64(29)
+    v += noise * ((h >> np.uint64(11)).astype(np.float64) / 2.0 ** 53 - 0.5)
+    return v.astype(dtype)
