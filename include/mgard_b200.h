@@ -1,0 +1,122 @@
+/* mgard_b200 -- C ABI of the B200-native MGARD-X compression hot path.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no C++/torch types.
+ * Every entry point names the reference interface (file:line under the
+ * reference tree) it stands in for.  All `d_*` pointers are DEVICE pointers on
+ * the context's GPU; work is enqueued on the context's CUDA stream and every
+ * call that returns a value through a host pointer synchronises that stream
+ * before returning (the reference's API is synchronous at return as well,
+ * CompressionHighLevel.hpp:47-286).
+ *
+ * There is no CPU fallback: every function fails with MGX_BACKEND_UNAVAILABLE
+ * when no CUDA device can be used.
+ */
+#ifndef MGARD_B200_H
+#define MGARD_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* mirrors mgard_x::compress_status_type, include/mgard-x/Utilities/Types.h:76-83 */
+enum mgx_status {
+  MGX_SUCCESS = 0,
+  MGX_FAILURE = 1,
+  MGX_OUTPUT_TOO_LARGE = 2,
+  MGX_TOO_MANY_DIMENSIONS = 3,
+  MGX_BAD_DATA_TYPE = 4,
+  MGX_BACKEND_UNAVAILABLE = 5
+};
+
+/* mirrors mgard_x::data_type, Types.h:60 */
+enum mgx_dtype { MGX_F32 = 0, MGX_F64 = 1 };
+
+typedef struct mgx_ctx mgx_ctx;
+
+/* Context = one (device, stream) pair with its workspaces and cached hierarchy
+ * tables; replaces DeviceRuntime<Dev>::Initialize + the process-global
+ * CompressorCache (CompressionLowLevel/CompressorCache.hpp:25-147).
+ * cuda_stream may be NULL (a private stream is created). */
+int mgx_create(mgx_ctx **ctx, int device, void *cuda_stream);
+void mgx_destroy(mgx_ctx *ctx);
+const char *mgx_last_error(const mgx_ctx *ctx);
+const char *mgx_version(void);
+
+/* Hierarchy<D,T,Dev>(shape, config) + Compressor::Adapt
+ * (Hierarchy/Hierarchy.hpp:814-837, CompressionLowLevel/Compressor.hpp:60-84).
+ * shape is slowest -> fastest; dict_size/chunk_size are Config::huff_dict_size /
+ * huff_block_size (Config/Config.h:17-18); max_level = Config::max_larget_level
+ * (UINT64_MAX = unlimited). */
+int mgx_plan(mgx_ctx *ctx, int D, const uint64_t *shape, int dtype,
+             uint32_t dict_size, uint32_t chunk_size, uint64_t max_level);
+/* l_target and the (l_target+1) x D level shapes (Hierarchy.hpp:277-309). */
+int mgx_levels(const mgx_ctx *ctx, int *l_target, uint64_t *level_shapes);
+/* bytes a caller must provide to mgx_compress / mgx_huff_encode in the worst
+ * case (every code an outlier). */
+uint64_t mgx_max_compressed_bytes(const mgx_ctx *ctx);
+
+/* norm_calculator (CompressionLowLevel/NormCalculator.hpp:13-80), split so a
+ * multi-GPU caller can all-reduce the partial: linf != 0 -> max|u|, else
+ * sum u^2 (fp64 accumulation).  mgx_finish_norm applies the sqrt / N /
+ * zero->epsilon rules of NormCalculator.hpp:49-71 to a (reduced) partial. */
+int mgx_norm_partial(mgx_ctx *ctx, const void *d_in, int linf, double *partial);
+double mgx_finish_norm(int dtype, int linf, double partial, uint64_t total_elems,
+                       int normalize_coordinates);
+
+/* DataRefactor::Decompose / Recompose, in place, reordered level-blocked layout
+ * (DataRefactoring/DataRefactor.hpp:73-130,
+ *  MultiDimension/DataRefactoring.hpp:24-317). */
+int mgx_decompose(mgx_ctx *ctx, void *d_data, int orthogonal);
+int mgx_recompose(mgx_ctx *ctx, void *d_data, int orthogonal);
+
+/* LinearQuantizer::Quantize / Dequantize with the dictionary shift folded in
+ * (Quantization/LinearQuantization.hpp:19-145, 315-420).  s = +inf -> L-inf,
+ * 0 -> L2, else s-norm; rel != 0 multiplies tol by norm. */
+int mgx_quantize(mgx_ctx *ctx, const void *d_coeff, int rel, double tol,
+                 double s, double norm, int64_t *d_codes);
+int mgx_dequantize(mgx_ctx *ctx, const int64_t *d_codes, int rel, double tol,
+                   double s, double norm, void *d_coeff);
+
+/* Huffman::Compress + Serialize / Deserialize + Decompress: the "MGXHUFF"
+ * container (Lossless/ParallelHuffman/Huffman.hpp:157-632). */
+int mgx_huff_encode(mgx_ctx *ctx, const int64_t *d_codes, uint64_t n,
+                    uint8_t *d_out, uint64_t cap, uint64_t *out_bytes);
+int mgx_huff_decode(mgx_ctx *ctx, const uint8_t *d_in, uint64_t bytes,
+                    int64_t *d_codes, uint64_t n);
+/* GetCodebook (ParallelHuffman/GetCodebook.hpp:23-145) on its own: d_freq[dict]
+ * -> d_codebook[dict] (len<<56|code) and d_decodebook[128+dict]
+ * (first[64] | entry[64] | keys[dict]).  Returns the longest code length
+ * through max_len. */
+int mgx_huff_codebook(mgx_ctx *ctx, const uint32_t *d_freq, uint64_t *d_codebook,
+                      uint64_t *d_decodebook, int *max_len);
+
+/* Compressor<D,T,Dev>::Compress / Decompress
+ * (CompressionLowLevel/Compressor.hpp:204-286): norm -> decompose -> quantize
+ * -> Huffman -> serialize, fused where the basis allows it.  d_in is NOT
+ * modified.  REL: if *norm_inout > 0 it is used as the (already global) norm,
+ * otherwise the norm of d_in is computed and returned. */
+int mgx_compress(mgx_ctx *ctx, const void *d_in, int rel, double tol, double s,
+                 double *norm_inout, uint8_t *d_out, uint64_t cap,
+                 uint64_t *out_bytes);
+int mgx_decompress(mgx_ctx *ctx, const uint8_t *d_in, uint64_t bytes, int rel,
+                   double tol, double s, double norm, void *d_out);
+
+/* Same two calls with HOST buffers: pinned staging + H2D / D2H inside
+ * (the host-pointer branch of general_compress_pipeline,
+ *  CompressionHighLevel.hpp:141-183, GPUPipelines.hpp:89-205). */
+int mgx_compress_host(mgx_ctx *ctx, const void *h_in, int rel, double tol,
+                      double s, double *norm_inout, uint8_t *h_out,
+                      uint64_t cap, uint64_t *out_bytes);
+int mgx_decompress_host(mgx_ctx *ctx, const uint8_t *h_in, uint64_t bytes,
+                        int rel, double tol, double s, double norm,
+                        void *h_out);
+
+/* kernels launched by this context since creation (bench.py's gpu_launches) */
+uint64_t mgx_launch_count(const mgx_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

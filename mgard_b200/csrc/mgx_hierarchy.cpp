@@ -1,0 +1,151 @@
+// Host-side hierarchy tables.  Mirrors what Hierarchy<D,T,Dev>::init computes on
+// the host in the reference (include/mgard-x/Hierarchy/Hierarchy.hpp:22-268 and
+// 277-496): level shapes, per-level spacing `dist`, interpolation `ratio`,
+// Thomas factors `am/bm` and level volumes, all in the data precision T so the
+// kernels see bit-identical constants.  Must be compiled with
+// -ffp-contract=off (the build passes it to the host compiler).
+#include <cmath>
+#include <cstring>
+
+#include "mgx_internal.h"
+
+// Hierarchy.hpp:277-309 -- per dim n -> n/2+1 while n > 2; l_target =
+// min_d(#levels) - 1; level_shape[l][d] = shape_level[d][l_target - l].
+int mgx_build_levels(int D, const uint64_t *shape, uint64_t max_level,
+                     MgxLevels *lv) {
+  if (D < 1)
+    return MGX_FAILURE;
+  if (D > MGX_MAX_D)
+    return MGX_TOO_MANY_DIMENSIONS;
+  std::vector<std::vector<uint64_t>> sl(D);
+  size_t nlevel = SIZE_MAX;
+  for (int d = 0; d < D; d++) {
+    uint64_t n = shape[d];
+    if (n < 3)
+      return MGX_FAILURE; // check_shape: no dimension smaller than 3
+    while (n > 2) {
+      sl[d].push_back(n);
+      n = n / 2 + 1;
+    }
+    sl[d].push_back(2);
+    nlevel = std::min(nlevel, sl[d].size());
+  }
+  uint64_t L = nlevel - 1;
+  if (max_level < L)
+    L = max_level;
+  if (L >= MGX_MAX_L)
+    return MGX_FAILURE;
+  lv->D = D;
+  lv->L = (int)L;
+  int pad = MGX_MAX_D - D;
+  lv->N = 1;
+  for (int d = 0; d < MGX_MAX_D; d++)
+    lv->shape[d] = d < pad ? 1 : shape[d - pad];
+  uint64_t st = 1;
+  for (int d = MGX_MAX_D - 1; d >= 0; d--) {
+    lv->stride[d] = st;
+    st *= lv->shape[d];
+  }
+  lv->N = st;
+  for (uint64_t l = 0; l <= L; l++)
+    for (int d = 0; d < MGX_MAX_D; d++)
+      lv->n[l][d] = d < pad ? 1 : sl[d - pad][L - l];
+  return MGX_SUCCESS;
+}
+
+template <typename T>
+void mgx_build_tables(const MgxLevels &lv, MgxHostTables<T> *tb) {
+  const int L = lv.L;
+  const int pad = MGX_MAX_D - lv.D;
+  tb->buf.clear();
+  tb->ratios_half = true;
+  std::memset(&tb->off, 0, sizeof(tb->off));
+  std::vector<std::vector<T>> dist((L + 1) * MGX_MAX_D);
+  auto D_ = [&](int l, int d) -> std::vector<T> & {
+    return dist[l * MGX_MAX_D + d];
+  };
+  T vol[MGX_MAX_L][MGX_MAX_D], volr[MGX_MAX_L][MGX_MAX_D];
+  for (int d = pad; d < MGX_MAX_D; d++) {
+    // create_uniform_coords (normalize_coordinates) + coord_to_dist,
+    // Hierarchy.hpp:762-782, 22-61
+    uint64_t n = lv.shape[d];
+    std::vector<T> coord(n);
+    for (uint64_t i = 0; i < n; i++)
+      coord[i] = (T)i / (n - 1);
+    D_(L, d).assign(n, (T)0);
+    for (uint64_t i = 0; i + 1 < n; i++)
+      D_(L, d)[i] = coord[i + 1] - coord[i];
+    // reduce_dist, uniform branch, Hierarchy.hpp:115-126
+    for (int l = L - 1; l >= 0; l--) {
+      uint64_t dof = lv.n[l + 1][d], dof2 = lv.n[l][d];
+      T total = 0;
+      for (uint64_t i = 0; i + 1 < dof; i++)
+        total += D_(l + 1, d)[i];
+      D_(l, d).assign(dof2, (T)0);
+      for (uint64_t i = 0; i + 1 < dof2; i++)
+        D_(l, d)[i] = total / (dof2 - 1);
+    }
+  }
+  for (int l = 0; l <= L; l++)
+    for (int d = pad; d < MGX_MAX_D; d++) {
+      uint64_t dof = lv.n[l][d];
+      const std::vector<T> &hd = D_(l, d);
+      tb->off.dist[l][d] = (uint32_t)tb->buf.size();
+      tb->buf.insert(tb->buf.end(), hd.begin(), hd.end());
+      // dist_to_ratio, Hierarchy.hpp:63-84
+      tb->off.ratio[l][d] = (uint32_t)tb->buf.size();
+      for (uint64_t i = 0; i < dof; i++) {
+        T r = 0;
+        if (i + 2 < dof) {
+          r = hd[i] / (hd[i + 1] + hd[i]);
+          if (r != (T)0.5)
+            tb->ratios_half = false;
+        }
+        tb->buf.push_back(r);
+      }
+      // calc_volume, Hierarchy.hpp:194-268
+      T total = 0;
+      for (uint64_t i = 0; i + 1 < dof; i++)
+        total += hd[i];
+      T v = total / (dof - 1);
+      vol[l][d] = v;
+      volr[l][d] = (T)(1.0 / v);
+      // calc_am_bm, Hierarchy.hpp:141-192 (bm stored shifted by one, bm[0]=1)
+      std::vector<T> am(dof + 1, (T)0), bm(dof + 1, (T)0), hb(dof + 1, (T)0);
+      hb[0] = 2 * hd[0] / 6;
+      for (uint64_t i = 1; i + 1 < dof; i++) {
+        T a_j = hd[i - 1] / 6;
+        T w = a_j / hb[i - 1];
+        hb[i] = 2 * (hd[i - 1] + hd[i]) / 6 - w * a_j;
+        am[i] = a_j;
+      }
+      {
+        T a_j = hd[dof - 2] / 6;
+        T w = a_j / hb[dof - 2];
+        hb[dof - 1] = 2 * hd[dof - 2] / 6 - w * a_j;
+        am[dof - 1] = a_j;
+      }
+      bm[0] = 1;
+      for (uint64_t i = 0; i < dof; i++)
+        bm[i + 1] = hb[i];
+      tb->off.am[l][d] = (uint32_t)tb->buf.size();
+      tb->buf.insert(tb->buf.end(), am.begin(), am.end());
+      tb->off.bm[l][d] = (uint32_t)tb->buf.size();
+      tb->buf.insert(tb->buf.end(), bm.begin(), bm.end());
+    }
+  // lwqzk volume factor, Quantization/LinearQuantization.hpp:74-90: product
+  // over d = D-1 .. 0 starting from 1, then sqrt in T
+  for (int l = 0; l <= L; l++) {
+    T a = 1, b = 1;
+    for (int d = MGX_MAX_D - 1; d >= pad; d--) {
+      a *= vol[l][d];
+      b *= volr[l][d];
+    }
+    tb->vol[l] = std::sqrt(a);
+    tb->volr[l] = std::sqrt(b);
+  }
+}
+
+template void mgx_build_tables<float>(const MgxLevels &, MgxHostTables<float> *);
+template void mgx_build_tables<double>(const MgxLevels &,
+                                       MgxHostTables<double> *);

@@ -1,0 +1,666 @@
+// Huffman stage on the GPU (sm_100a): symbol staging, histogram, fused
+// encode + bit-pack with a decoupled look-back scan, container assembly,
+// table-driven decode.
+//
+// reference: Lossless/ParallelHuffman/Huffman.hpp:157-632 (stage sequencing and
+// the "MGXHUFF" container), OutlierSeparator.hpp:17-120, Histogram.hpp,
+// ParallelDeflate.hpp:19-357 (group bits -> scans -> pack), Decode.hpp:14-206.
+//
+// Differences in *how* (never in the bytes produced):
+//  * dictionary symbols travel as uint16 (the reference keeps int64);
+//  * per-chunk word offsets come from a single-pass decoupled look-back scan
+//    fused into the bit-count kernel instead of two device-wide scans;
+//  * one warp packs one chunk into shared memory and writes it out coalesced
+//    (the reference packs 32 symbols per thread straight to global memory with
+//    atomicOr on shared words);
+//  * decoding uses a 2^12-entry prefix table in shared memory with the
+//    canonical first[]/entry[] search only for longer codes.
+#include <algorithm>
+#include <cub/device/device_radix_sort.cuh>
+
+#include "mgx_device.cuh"
+#include "mgx_internal.h"
+
+size_t mgx_codebook_ws_bytes(int dict, int P);
+cudaError_t mgx_launch_codebook(const uint32_t *d_freq, int dict, int P,
+                                uint64_t *d_codebook, uint64_t *d_decodebook,
+                                unsigned char *gws, int use_smem, size_t smem,
+                                uint64_t *d_scalars, cudaStream_t stream);
+
+namespace {
+
+typedef unsigned long long u64;
+
+// ---- int64 codes <-> 16-bit symbols -------------------------------------------
+// OutlierSeparator (SEPARATE) + Histogram in one pass over the int64 codes.
+__global__ void __launch_bounds__(256)
+    k_codes_to_symbols(const long long *__restrict__ codes, uint64_t n,
+                       uint32_t dict, uint16_t *__restrict__ sym,
+                       uint32_t *__restrict__ g_freq, u64 *__restrict__ out_count,
+                       u64 *__restrict__ out_idx, long long *__restrict__ out_val,
+                       u64 out_cap) {
+  extern __shared__ uint32_t s_hist[];
+  for (uint32_t i = threadIdx.x; i < dict; i += blockDim.x)
+    s_hist[i] = 0;
+  __syncthreads();
+  const uint64_t step = (uint64_t)gridDim.x * blockDim.x;
+  const uint64_t rounds = (n + step - 1) / step;
+  for (uint64_t k = 0; k < rounds; k++) {
+    uint64_t it = k * step + blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+    bool valid = it < n;
+    uint32_t sv = 0;
+    if (valid) {
+      long long q = codes[it];
+      if (q < 0 || q >= (long long)dict) {
+        u64 slot = atomicAdd(out_count, 1ull);
+        if (slot < out_cap) {
+          out_idx[slot] = it;
+          out_val[slot] = q;
+        }
+        q = 0;
+      }
+      sv = (uint32_t)q;
+      sym[it] = (uint16_t)sv;
+    }
+    mgx_hist_add(s_hist, sv, valid);
+  }
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < dict; i += blockDim.x) {
+    uint32_t v = s_hist[i];
+    if (v)
+      atomicAdd(&g_freq[i], v);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+    k_symbols_to_codes(const uint16_t *__restrict__ sym, uint64_t n,
+                       long long *__restrict__ codes) {
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n;
+       i += (uint64_t)gridDim.x * blockDim.x)
+    codes[i] = (long long)sym[i];
+}
+
+// OutlierSeparator (RESTORE), OutlierSeparator.hpp:45-51
+__global__ void __launch_bounds__(256)
+    k_restore_outliers(const u64 *__restrict__ idx,
+                       const long long *__restrict__ val, uint64_t n_out,
+                       long long *__restrict__ codes) {
+  for (uint64_t j = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; j < n_out;
+       j += (uint64_t)gridDim.x * blockDim.x)
+    codes[idx[j]] = val[j];
+}
+
+} // namespace
+
+int mgxk_histogram_reset(mgx_ctx *ctx) {
+  MGX_CUDA(cudaMemsetAsync(ctx->d_freq, 0, (size_t)ctx->dict * 4, ctx->stream));
+  MGX_CUDA(cudaMemsetAsync(ctx->d_scalars, 0, MGX_SC_COUNT * 8, ctx->stream));
+  return MGX_SUCCESS;
+}
+
+int mgxk_codes_to_symbols(mgx_ctx *ctx, const int64_t *d_codes, uint64_t n) {
+  size_t smem = (size_t)ctx->dict * 4;
+  MGX_CUDA(cudaFuncSetAttribute(k_codes_to_symbols,
+                                cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)smem));
+  unsigned grid = mgx_grid_for(n, 256 * 16, ctx->num_sms * 4);
+  k_codes_to_symbols<<<grid, 256, smem, ctx->stream>>>(
+      (const long long *)d_codes, n, ctx->dict, ctx->d_sym, ctx->d_freq,
+      (u64 *)(ctx->d_scalars + MGX_SC_OUTLIERS), (u64 *)ctx->d_out_idx,
+      (long long *)ctx->d_out_val, ctx->out_cap);
+  ctx->launches++;
+  MGX_CUDA(cudaGetLastError());
+  return MGX_SUCCESS;
+}
+
+int mgxk_symbols_to_codes(mgx_ctx *ctx, uint64_t n, int64_t *d_codes,
+                          const uint64_t *d_oidx, const int64_t *d_oval,
+                          uint64_t n_out) {
+  k_symbols_to_codes<<<mgx_grid_for(n, 256, ctx->num_sms * 16), 256, 0,
+                       ctx->stream>>>(ctx->d_sym, n, (long long *)d_codes);
+  ctx->launches++;
+  if (n_out) {
+    k_restore_outliers<<<mgx_grid_for(n_out, 256, ctx->num_sms * 4), 256, 0,
+                         ctx->stream>>>((const u64 *)d_oidx,
+                                        (const long long *)d_oval, n_out,
+                                        (long long *)d_codes);
+    ctx->launches++;
+  }
+  MGX_CUDA(cudaGetLastError());
+  return MGX_SUCCESS;
+}
+
+// GetCodebook, GetCodebook.hpp:23-145 (see mgx_codebook.cu)
+int mgxk_codebook(mgx_ctx *ctx, const uint32_t *d_freq, uint64_t *d_codebook,
+                  uint64_t *d_decodebook) {
+  int dict = (int)ctx->dict;
+  if (dict > 16384) {
+    ctx->err = "dictionary sizes above 16384 are not supported";
+    return MGX_FAILURE;
+  }
+  int P = 1;
+  while (P < dict)
+    P <<= 1;
+  size_t ws = mgx_codebook_ws_bytes(dict, P);
+  int use_smem = ws <= 200 * 1024;
+  static void *gws = nullptr; // L2-resident fallback workspace (large dicts)
+  static size_t gws_bytes = 0;
+  if (!use_smem && gws_bytes < ws) {
+    if (gws)
+      cudaFree(gws);
+    MGX_CUDA(cudaMalloc(&gws, ws));
+    gws_bytes = ws;
+  }
+  size_t smem = use_smem ? ws : 0;
+  MGX_CUDA(mgx_launch_codebook(d_freq, dict, P, d_codebook, d_decodebook,
+                               (unsigned char *)gws, use_smem, smem,
+                               ctx->d_scalars, ctx->stream));
+  ctx->launches++;
+  MGX_CUDA(cudaGetLastError());
+  return MGX_SUCCESS;
+}
+
+// ============================ encode ==========================================
+namespace {
+
+constexpr int ENC_WARPS = 8; // chunks per tile (one warp each)
+constexpr u64 FLAG_AGG = 1ull << 62, FLAG_INC = 2ull << 62,
+              VAL_MASK = (1ull << 62) - 1;
+
+// Pass 1 (DeflateGroupBits + both ScanSumExtended + DeflateChunkMeta,
+// ParallelDeflate.hpp:39-175, Huffman.hpp:243-274): per-chunk bit length,
+// ceil(bits/64) words, and the exclusive scan of the word counts through a
+// decoupled look-back over tiles of ENC_WARPS chunks.  Grid is persistent and
+// fully resident, tiles are taken round-robin, so a tile's predecessors are
+// always owned by running CTAs.
+__global__ void __launch_bounds__(ENC_WARPS * 32)
+    k_chunk_bits(const uint16_t *__restrict__ sym, uint64_t n, uint32_t chunk,
+                 uint32_t dict, const u64 *__restrict__ codebook,
+                 u64 *__restrict__ chunk_bits, u64 *__restrict__ chunk_off,
+                 u64 *__restrict__ tile_state, uint64_t nchunk, uint64_t ntiles,
+                 u64 *__restrict__ scalars) {
+  extern __shared__ uint8_t s_len[]; // code length per symbol
+  __shared__ u64 s_words[ENC_WARPS];
+  __shared__ u64 s_prefix;
+  for (uint32_t i = threadIdx.x; i < dict; i += blockDim.x)
+    s_len[i] = (uint8_t)(codebook[i] >> 56);
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const uint64_t c = tile * ENC_WARPS + warp;
+    u64 bits = 0;
+    if (c < nchunk) {
+      const uint64_t b = c * chunk;
+      const uint64_t e = min(b + (uint64_t)chunk, n);
+      for (uint64_t i = b + lane; i < e; i += 32)
+        bits += s_len[sym[i]];
+      for (int o = 16; o > 0; o >>= 1)
+        bits += __shfl_xor_sync(0xffffffffu, bits, o);
+    }
+    const u64 words = (bits + 63) >> 6;
+    if (lane == 0) {
+      s_words[warp] = words;
+      if (c < nchunk)
+        chunk_bits[c] = bits;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      u64 agg = 0;
+      for (int w = 0; w < ENC_WARPS; w++)
+        agg += s_words[w];
+      u64 prefix = 0;
+      if (tile > 0) {
+        volatile u64 *vs = tile_state;
+        __threadfence();
+        vs[tile] = FLAG_AGG | agg;
+        int64_t p = (int64_t)tile - 1;
+        while (true) {
+          u64 v = vs[p];
+          if (v & FLAG_INC) {
+            prefix += v & VAL_MASK;
+            break;
+          }
+          if (v & FLAG_AGG) {
+            prefix += v & VAL_MASK;
+            --p;
+          }
+        }
+      }
+      __threadfence();
+      ((volatile u64 *)tile_state)[tile] = FLAG_INC | (prefix + agg);
+      s_prefix = prefix;
+      if (tile == ntiles - 1) {
+        chunk_off[nchunk] = prefix + agg;
+        scalars[MGX_SC_DDATA] = prefix + agg;
+      }
+    }
+    __syncthreads();
+    if (lane == 0 && c < nchunk) {
+      u64 off = s_prefix;
+      for (int w = 0; w < warp; w++)
+        off += s_words[w];
+      chunk_off[c] = off;
+    }
+    __syncthreads();
+  }
+}
+
+// Pass 2 (DeflatePack, ParallelDeflate.hpp:177-266): one warp packs one chunk,
+// MSB first, into a zeroed shared-memory image of the chunk's words, then
+// streams it to its final place in the container.  Lane l owns the contiguous
+// run of ceil(chunk/32) symbols the reference calls a "group".
+__global__ void __launch_bounds__(ENC_WARPS * 32)
+    k_pack(const uint16_t *__restrict__ sym, uint64_t n, uint32_t chunk,
+           const u64 *__restrict__ codebook, const u64 *__restrict__ chunk_off,
+           u64 *__restrict__ packed, uint64_t nchunk, uint32_t words_cap) {
+  extern __shared__ __align__(16) u64 s_out[]; // ENC_WARPS * words_cap
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  u64 *out = s_out + (size_t)warp * words_cap;
+  const uint32_t G = (chunk + 31) / 32;
+  const uint64_t nwarps = (uint64_t)gridDim.x * ENC_WARPS;
+  for (uint64_t c = (uint64_t)blockIdx.x * ENC_WARPS + warp; c < nchunk;
+       c += nwarps) {
+    const uint64_t cb = c * chunk;
+    const uint64_t ce = min(cb + (uint64_t)chunk, n);
+    const uint64_t gb = min(cb + (uint64_t)lane * G, ce);
+    const uint64_t ge = min(gb + G, ce);
+    const u64 w0 = chunk_off[c], w1 = chunk_off[c + 1];
+    const uint32_t nwords = (uint32_t)(w1 - w0);
+    for (uint32_t i = lane; i < nwords; i += 32)
+      out[i] = 0;
+    // group bit count -> exclusive warp scan -> my first bit
+    uint32_t gbits = 0;
+    for (uint64_t i = gb; i < ge; i++)
+      gbits += (uint32_t)(__ldg(&codebook[sym[i]]) >> 56);
+    uint32_t incl = gbits;
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o)
+        incl += t;
+    }
+    uint32_t bit = incl - gbits;
+    __syncwarp();
+    // append my codes; words I do not fully own are merged with atomicOr
+    u64 acc = 0;
+    uint32_t word = bit >> 6, fill = bit & 63; // bits already used in `word`
+    bool first_word = true;
+    const bool left_shared = fill != 0;
+    for (uint64_t i = gb; i < ge; i++) {
+      u64 cw = __ldg(&codebook[sym[i]]);
+      uint32_t len = (uint32_t)(cw >> 56);
+      cw &= 0x00ffffffffffffffull;
+      uint32_t room = 64 - fill;
+      if (len < room) {
+        acc |= cw << (room - len);
+        fill += len;
+      } else {
+        uint32_t r = len - room; // bits spilling into the next word
+        acc |= cw >> r;
+        if (first_word && left_shared)
+          atomicOr(&out[word], acc);
+        else
+          out[word] = acc;
+        first_word = false;
+        ++word;
+        acc = r ? (cw << (64 - r)) : 0;
+        fill = r;
+      }
+    }
+    if (fill != 0 && (gb < ge))
+      atomicOr(&out[word], acc);
+    __syncwarp();
+    u64 *dst = packed + w0;
+    for (uint32_t i = lane; i < nwords; i += 32)
+      dst[i] = out[i];
+    __syncwarp();
+  }
+}
+
+// scalar header fields of the container (Huffman.hpp:344-395)
+struct HuffHeader {
+  uint64_t n, nchunk, dbs;
+  int32_t dict, chunk;
+  uint64_t off_bits, off_offs, off_dbs, off_db, off_ddata, off_packed;
+};
+
+__global__ void k_write_header(uint8_t *out, HuffHeader h,
+                               const u64 *__restrict__ scalars) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    const char sig[8] = {'M', 'G', 'X', 'H', 'U', 'F', 'F', 0};
+    for (int i = 0; i < 8; i++)
+      out[i] = (uint8_t)sig[i];
+    *(u64 *)(out + 8) = h.n;
+    *(int32_t *)(out + 16) = h.dict;
+    *(int32_t *)(out + 20) = h.chunk;
+    *(u64 *)(out + 24) = 2 * h.nchunk;
+    *(u64 *)(out + h.off_dbs) = h.dbs;
+    *(u64 *)(out + h.off_ddata) = scalars[MGX_SC_DDATA];
+  }
+}
+
+__global__ void k_write_outlier_count(uint8_t *out, u64 off, u64 count) {
+  if (threadIdx.x == 0 && blockIdx.x == 0)
+    *(u64 *)(out + off) = count;
+}
+
+} // namespace
+
+uint64_t mgx_container_fixed_bytes(uint64_t n, uint32_t dict, uint32_t chunk) {
+  uint64_t nchunk = (n - 1) / chunk + 1;
+  return 32 + 16 * nchunk + 8 + 8ull * (128 + dict) + 8;
+}
+
+// Huffman::CompressPrimary + Serialize, Huffman.hpp:157-434: symbols (d_sym),
+// histogram (d_freq) and outliers are already in the context.
+int mgxk_encode_container(mgx_ctx *ctx, uint64_t n, uint8_t *d_out, uint64_t cap,
+                          uint64_t *out_bytes) {
+  const uint32_t chunk = ctx->chunk, dict = ctx->dict;
+  const uint64_t nchunk = (n - 1) / chunk + 1;
+  const uint64_t ntiles = (nchunk + ENC_WARPS - 1) / ENC_WARPS;
+  HuffHeader h;
+  h.n = n;
+  h.nchunk = nchunk;
+  h.dict = (int32_t)dict;
+  h.chunk = (int32_t)chunk;
+  h.dbs = 8ull * (128 + dict);
+  h.off_bits = 32;
+  h.off_offs = 32 + 8 * nchunk;
+  h.off_dbs = 32 + 16 * nchunk;
+  h.off_db = h.off_dbs + 8;
+  h.off_ddata = h.off_db + h.dbs;
+  h.off_packed = h.off_ddata + 8;
+  if (h.off_packed + 8 > cap) {
+    *out_bytes = h.off_packed + 8;
+    return MGX_OUTPUT_TOO_LARGE;
+  }
+  if (((uintptr_t)d_out & 7) != 0) {
+    ctx->err = "output buffer must be 8-byte aligned";
+    return MGX_FAILURE;
+  }
+  int rc = mgxk_codebook(ctx, ctx->d_freq, ctx->d_codebook, ctx->d_decodebook);
+  if (rc)
+    return rc;
+  // pass 1: sizes + offsets
+  MGX_CUDA(cudaMemsetAsync(ctx->d_scan_state, 0, ntiles * 8, ctx->stream));
+  int occ = 1;
+  MGX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+      &occ, k_chunk_bits, ENC_WARPS * 32, dict));
+  unsigned grid1 = (unsigned)std::min<uint64_t>(
+      ntiles, (uint64_t)std::max(occ, 1) * ctx->num_sms);
+  k_chunk_bits<<<grid1, ENC_WARPS * 32, dict, ctx->stream>>>(
+      ctx->d_sym, n, chunk, dict, (const u64 *)ctx->d_codebook,
+      (u64 *)ctx->d_chunk_bits, (u64 *)ctx->d_chunk_off,
+      (u64 *)ctx->d_scan_state, nchunk, ntiles, (u64 *)ctx->d_scalars);
+  ctx->launches++;
+  // one host round trip: packed size, longest code, outlier count, error flags
+  MGX_CUDA(cudaMemcpyAsync(ctx->h_scalars, ctx->d_scalars, MGX_SC_COUNT * 8,
+                           cudaMemcpyDeviceToHost, ctx->stream));
+  MGX_CUDA(cudaStreamSynchronize(ctx->stream));
+  if (ctx->h_scalars[MGX_SC_ERR] & 2) {
+    ctx->err = "longest Huffman codeword exceeds 56 bits"; // GetCodebook.hpp:111
+    return MGX_FAILURE;
+  }
+  if (ctx->h_scalars[MGX_SC_ERR]) {
+    ctx->err = "codebook construction failed";
+    return MGX_FAILURE;
+  }
+  const uint64_t ddata = ctx->h_scalars[MGX_SC_DDATA];
+  const uint64_t n_out = ctx->h_scalars[MGX_SC_OUTLIERS];
+  const uint32_t maxlen = (uint32_t)ctx->h_scalars[MGX_SC_MAXLEN];
+  if (n_out > ctx->out_cap) {
+    ctx->err = "outlier workspace overflow";
+    return MGX_FAILURE + 100; // caller grows the workspace and retries
+  }
+  const uint64_t off_outc = h.off_packed + 8 * ddata;
+  const uint64_t total = off_outc + 8 + 16 * n_out;
+  *out_bytes = total;
+  if (total > cap)
+    return MGX_OUTPUT_TOO_LARGE;
+  // metadata sections
+  k_write_header<<<1, 32, 0, ctx->stream>>>(d_out, h, (const u64 *)ctx->d_scalars);
+  ctx->launches++;
+  MGX_CUDA(cudaMemcpyAsync(d_out + h.off_bits, ctx->d_chunk_bits, 8 * nchunk,
+                           cudaMemcpyDeviceToDevice, ctx->stream));
+  MGX_CUDA(cudaMemcpyAsync(d_out + h.off_offs, ctx->d_chunk_off, 8 * nchunk,
+                           cudaMemcpyDeviceToDevice, ctx->stream));
+  MGX_CUDA(cudaMemcpyAsync(d_out + h.off_db, ctx->d_decodebook, h.dbs,
+                           cudaMemcpyDeviceToDevice, ctx->stream));
+  // pass 2: pack
+  uint32_t words_cap = (uint32_t)(((uint64_t)chunk * maxlen + 63) / 64 + 1);
+  size_t smem = (size_t)ENC_WARPS * words_cap * 8;
+  if (smem > 200 * 1024) {
+    ctx->err = "huff_block_size too large for the shared-memory packer";
+    return MGX_FAILURE;
+  }
+  MGX_CUDA(cudaFuncSetAttribute(
+      k_pack, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  MGX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_pack,
+                                                         ENC_WARPS * 32, smem));
+  unsigned grid2 = (unsigned)std::min<uint64_t>(
+      ntiles, (uint64_t)std::max(occ, 1) * ctx->num_sms);
+  k_pack<<<grid2, ENC_WARPS * 32, smem, ctx->stream>>>(
+      ctx->d_sym, n, chunk, (const u64 *)ctx->d_codebook,
+      (const u64 *)ctx->d_chunk_off, (u64 *)(d_out + h.off_packed), nchunk,
+      words_cap);
+  ctx->launches++;
+  // outliers in ascending index order (the SERIAL reference's order)
+  k_write_outlier_count<<<1, 32, 0, ctx->stream>>>(d_out, off_outc, n_out);
+  ctx->launches++;
+  if (n_out) {
+    size_t tmp = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, tmp, (const u64 *)ctx->d_out_idx,
+                                    (u64 *)(d_out + off_outc + 8),
+                                    (const long long *)ctx->d_out_val,
+                                    (long long *)(d_out + off_outc + 8 + 8 * n_out),
+                                    (int)n_out, 0, 64, ctx->stream);
+    if (tmp > ctx->sort_tmp_bytes) {
+      if (ctx->d_sort_tmp)
+        cudaFree(ctx->d_sort_tmp);
+      MGX_CUDA(cudaMalloc(&ctx->d_sort_tmp, tmp));
+      ctx->sort_tmp_bytes = tmp;
+    }
+    cub::DeviceRadixSort::SortPairs(ctx->d_sort_tmp, tmp,
+                                    (const u64 *)ctx->d_out_idx,
+                                    (u64 *)(d_out + off_outc + 8),
+                                    (const long long *)ctx->d_out_val,
+                                    (long long *)(d_out + off_outc + 8 + 8 * n_out),
+                                    (int)n_out, 0, 64, ctx->stream);
+    ctx->launches += 4;
+  }
+  MGX_CUDA(cudaGetLastError());
+  return MGX_SUCCESS;
+}
+
+// ============================ decode ==========================================
+namespace {
+
+constexpr int LUT_BITS = 12;
+
+// Prefix table for codes of up to LUT_BITS bits: entry = symbol | len << 16
+// (len 0 = longer code, fall back to the canonical search).  Built from the
+// container's own first[] / entry[] / keys[] tables (Decode.hpp:60-66): at
+// length l the codes are first[l] + j, j = 0 .. entry[l+1]-entry[l]-1, and
+// decode to keys[entry[l] + j].
+__global__ void __launch_bounds__(256)
+    k_build_lut(const u64 *__restrict__ db, uint32_t dict,
+                uint32_t *__restrict__ lut) {
+  const u64 *first = db, *entry = db + 64, *keys = db + 128;
+  for (uint32_t i = threadIdx.x; i < (1u << LUT_BITS); i += blockDim.x)
+    lut[i] = 0;
+  __syncthreads();
+  for (int l = 1; l <= LUT_BITS; l++) {
+    u64 f = first[l];
+    if (f == ~0ull)
+      continue;
+    u64 e0 = entry[l];
+    u64 cnt = entry[l + 1] - e0; // number of codes of exactly this length
+    u64 span = 1ull << (LUT_BITS - l);
+    for (u64 j = threadIdx.x; j < cnt * span; j += blockDim.x) {
+      u64 code = f + j / span;
+      u64 r = e0 + (code - f);
+      if (r < dict)
+        lut[(code << (LUT_BITS - l)) + (j % span)] =
+            (uint32_t)keys[r] | ((uint32_t)l << 16);
+    }
+  }
+}
+
+// DecodeFunctor, Decode.hpp:14-130: one thread per chunk, but table driven and
+// with 16-byte symbol stores.
+__global__ void __launch_bounds__(128)
+    k_decode(const u64 *__restrict__ packed, const u64 *__restrict__ meta,
+             uint64_t nchunk, uint32_t chunk, uint64_t n,
+             const u64 *__restrict__ db, const uint32_t *__restrict__ g_lut,
+             uint16_t *__restrict__ sym) {
+  __shared__ uint32_t lut[1 << LUT_BITS];
+  __shared__ u64 s_first[64], s_entry[64];
+  for (uint32_t i = threadIdx.x; i < (1u << LUT_BITS); i += blockDim.x)
+    lut[i] = g_lut[i];
+  if (threadIdx.x < 64) {
+    s_first[threadIdx.x] = db[threadIdx.x];
+    s_entry[threadIdx.x] = db[64 + threadIdx.x];
+  }
+  __syncthreads();
+  const u64 *keys = db + 128;
+  for (uint64_t c = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; c < nchunk;
+       c += (uint64_t)gridDim.x * blockDim.x) {
+    const u64 *w = packed + meta[nchunk + c];
+    const uint64_t total = meta[c];
+    const uint64_t base = c * chunk;
+    const uint32_t count = (uint32_t)min((uint64_t)chunk, n - base);
+    uint16_t *dst = sym + base;
+    // 128-bit window: `hi` holds the next bits MSB-aligned, `lo` the refill
+    uint64_t pos = 0;      // bits consumed
+    uint32_t widx = 0;     // next word to load
+    u64 cur = w[0], nxt = (total > 64) ? w[1] : 0;
+    widx = 2;
+    uint32_t used = 0;     // bits of `cur` already consumed
+    uint32_t k = 0;
+    uint16_t stage[8];
+    const bool aligned16 = ((base * 2) & 15) == 0;
+    while (k < count && pos < total) {
+      // peek 64 bits starting at the cursor
+      u64 window = used ? ((cur << used) | (nxt >> (64 - used))) : cur;
+      uint32_t e = lut[(uint32_t)(window >> (64 - LUT_BITS))];
+      uint32_t len = e >> 16, s = e & 0xffff;
+      if (len == 0) { // long code: canonical search from LUT_BITS+1 upwards
+        uint32_t l = LUT_BITS;
+        u64 v = window >> (64 - LUT_BITS);
+        do {
+          ++l;
+          v = window >> (64 - l);
+        } while (v < s_first[l] && l < 63);
+        s = (uint32_t)keys[s_entry[l] + v - s_first[l]];
+        len = l;
+      }
+      stage[k & 7] = (uint16_t)s;
+      ++k;
+      if ((k & 7) == 0) {
+        if (aligned16) {
+          uint4 pk;
+          pk.x = stage[0] | ((uint32_t)stage[1] << 16);
+          pk.y = stage[2] | ((uint32_t)stage[3] << 16);
+          pk.z = stage[4] | ((uint32_t)stage[5] << 16);
+          pk.w = stage[6] | ((uint32_t)stage[7] << 16);
+          *reinterpret_cast<uint4 *>(dst + k - 8) = pk;
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; j++)
+            dst[k - 8 + j] = stage[j];
+        }
+      }
+      pos += len;
+      used += len;
+      if (used >= 64) {
+        used -= 64;
+        cur = nxt;
+        nxt = ((uint64_t)widx * 64 < total) ? w[widx] : 0;
+        ++widx;
+      }
+    }
+    for (uint32_t j = k & ~7u; j < k; j++)
+      dst[j] = stage[j & 7];
+  }
+}
+
+struct ParsedHeader {
+  uint64_t n, nchunk, dbs, ddata, n_out;
+  int32_t dict, chunk;
+  uint64_t off_meta, off_db, off_packed, off_oidx, off_oval;
+};
+
+} // namespace
+
+// Huffman::Deserialize + DecompressPrimary, Huffman.hpp:453-551.  Symbols land
+// in ctx->d_sym; the outlier sections are returned as views into d_in.
+int mgxk_decode_container(mgx_ctx *ctx, const uint8_t *d_in, uint64_t bytes,
+                          uint64_t n, const uint64_t **d_oidx,
+                          const int64_t **d_oval, uint64_t *n_out) {
+  if (bytes < 40 || ((uintptr_t)d_in & 7) != 0) {
+    ctx->err = "bad Huffman container (size/alignment)";
+    return MGX_FAILURE;
+  }
+  // fixed part of the header
+  uint8_t *hs = (uint8_t *)ctx->h_scalars;
+  MGX_CUDA(cudaMemcpyAsync(hs, d_in, 32, cudaMemcpyDeviceToHost, ctx->stream));
+  MGX_CUDA(cudaStreamSynchronize(ctx->stream));
+  if (memcmp(hs, "MGXHUFF", 7) != 0) {
+    ctx->err = "Huffman signature mismatch."; // Huffman.hpp:459-461
+    return MGX_FAILURE;
+  }
+  ParsedHeader p;
+  memcpy(&p.n, hs + 8, 8);
+  memcpy(&p.dict, hs + 16, 4);
+  memcpy(&p.chunk, hs + 20, 4);
+  uint64_t huffmeta;
+  memcpy(&huffmeta, hs + 24, 8);
+  if (p.n != n || p.chunk <= 0 || p.dict <= 0 || p.dict > 65536) {
+    ctx->err = "Huffman container does not match the plan";
+    return MGX_FAILURE;
+  }
+  p.nchunk = (p.n - 1) / (uint64_t)p.chunk + 1;
+  if (huffmeta != 2 * p.nchunk)
+    return MGX_FAILURE;
+  p.off_meta = 32;
+  uint64_t off_dbs = 32 + 16 * p.nchunk;
+  if (off_dbs + 8 > bytes)
+    return MGX_FAILURE;
+  MGX_CUDA(cudaMemcpyAsync(hs, d_in + off_dbs, 8, cudaMemcpyDeviceToHost,
+                           ctx->stream));
+  MGX_CUDA(cudaStreamSynchronize(ctx->stream));
+  memcpy(&p.dbs, hs, 8);
+  p.off_db = off_dbs + 8;
+  if (p.dbs != 8ull * (128 + (uint64_t)p.dict) || p.off_db + p.dbs + 8 > bytes)
+    return MGX_FAILURE;
+  MGX_CUDA(cudaMemcpyAsync(hs, d_in + p.off_db + p.dbs, 8,
+                           cudaMemcpyDeviceToHost, ctx->stream));
+  MGX_CUDA(cudaStreamSynchronize(ctx->stream));
+  memcpy(&p.ddata, hs, 8);
+  p.off_packed = p.off_db + p.dbs + 8;
+  uint64_t off_outc = p.off_packed + 8 * p.ddata;
+  if (off_outc + 8 > bytes)
+    return MGX_FAILURE;
+  MGX_CUDA(cudaMemcpyAsync(hs, d_in + off_outc, 8, cudaMemcpyDeviceToHost,
+                           ctx->stream));
+  MGX_CUDA(cudaStreamSynchronize(ctx->stream));
+  memcpy(&p.n_out, hs, 8);
+  p.off_oidx = off_outc + 8;
+  p.off_oval = p.off_oidx + 8 * p.n_out;
+  if (p.off_oval + 8 * p.n_out > bytes)
+    return MGX_FAILURE;
+  *n_out = p.n_out;
+  *d_oidx = (const uint64_t *)(d_in + p.off_oidx);
+  *d_oval = (const int64_t *)(d_in + p.off_oval);
+
+  const u64 *db = (const u64 *)(d_in + p.off_db);
+  k_build_lut<<<1, 256, 0, ctx->stream>>>(db, (uint32_t)p.dict,
+                                          (uint32_t *)ctx->d_lut);
+  k_decode<<<mgx_grid_for(p.nchunk, 128, ctx->num_sms * 16), 128, 0,
+             ctx->stream>>>((const u64 *)(d_in + p.off_packed),
+                            (const u64 *)(d_in + p.off_meta), p.nchunk,
+                            (uint32_t)p.chunk, p.n, db,
+                            (const uint32_t *)ctx->d_lut, ctx->d_sym);
+  ctx->launches += 2;
+  MGX_CUDA(cudaGetLastError());
+  return MGX_SUCCESS;
+}
