@@ -103,6 +103,14 @@ int mgx_compress(mgx_ctx *ctx, const void *d_in, int rel, double tol, double s,
 int mgx_decompress(mgx_ctx *ctx, const uint8_t *d_in, uint64_t bytes, int rel,
                    double tol, double s, double norm, void *d_out);
 
+/* The fused fast path of mgx_compress on its own (L-inf, D <= 3): Decompose with
+ * the hierarchical basis + Quantize in ONE pass over d_in
+ * (DataRefactoring.hpp:77-114 with orthogonal_projection == false, then
+ * LinearQuantization.hpp:19-145), returned as the reference's int64 codes so
+ * it can be compared with mgx_decompose + mgx_quantize and with the oracle. */
+int mgx_hier_quantize(mgx_ctx *ctx, const void *d_in, int rel, double tol,
+                      double norm, int64_t *d_codes);
+
 /* Same two calls with HOST buffers: pinned staging + H2D / D2H inside
  * (the host-pointer branch of general_compress_pipeline,
  *  CompressionHighLevel.hpp:141-183, GPUPipelines.hpp:89-205). */

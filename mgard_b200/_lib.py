@@ -42,6 +42,7 @@ SIGNATURES = {
                              ctypes.POINTER(c_u64)]),
     "mgx_decompress": (c_int, [c_vp, c_vp, c_u64, c_int, c_dbl, c_dbl, c_dbl,
                                c_vp]),
+    "mgx_hier_quantize": (c_int, [c_vp, c_vp, c_int, c_dbl, c_dbl, c_vp]),
     "mgx_compress_host": (c_int, [c_vp, c_vp, c_int, c_dbl, c_dbl,
                                   ctypes.POINTER(c_dbl), c_vp, c_u64,
                                   ctypes.POINTER(c_u64)]),

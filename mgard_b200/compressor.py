@@ -183,6 +183,16 @@ class Compressor:
                                             out.data_ptr()))
         return out
 
+    def DecomposeQuantizeFused(self, data, ebtype, tol, norm):
+        """hierarchical Decompose + Quantize in one pass (L-inf, D <= 3)."""
+        data = self._dev(data, self.tdtype)
+        codes = torch.empty(self.hierarchy.shape, dtype=torch.int64,
+                            device=self.device)
+        self._check(self.lib.mgx_hier_quantize(self._ctx, data.data_ptr(),
+                                               int(ebtype == REL), tol, norm,
+                                               codes.data_ptr()))
+        return codes
+
     def HuffmanCodebook(self, freq):
         freq = self._dev(freq, torch.int32)  # uint32 bit pattern
         d = self.config.huff_dict_size

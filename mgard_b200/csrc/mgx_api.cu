@@ -365,6 +365,35 @@ int mgx_huff_decode(mgx_ctx *ctx, const uint8_t *d_in, uint64_t bytes,
   return MGX_SUCCESS;
 }
 
+int mgx_hier_quantize(mgx_ctx *ctx, const void *d_in, int rel, double tol,
+                      double norm, int64_t *d_codes) {
+  MGX_CHECK_PLAN();
+  int rc = mgxk_histogram_reset(ctx);
+  if (!rc)
+    rc = mgxk_hier_forward(ctx, d_in, rel, tol, false, norm);
+  if (rc)
+    return rc;
+  MGX_CUDA(cudaMemcpyAsync(ctx->h_scalars, ctx->d_scalars, MGX_SC_COUNT * 8,
+                           cudaMemcpyDeviceToHost, ctx->stream));
+  MGX_CUDA(cudaStreamSynchronize(ctx->stream));
+  uint64_t n_out = ctx->h_scalars[MGX_SC_OUTLIERS];
+  if (n_out > ctx->out_cap) {
+    rc = grow_outliers(ctx, n_out);
+    if (!rc)
+      rc = mgxk_histogram_reset(ctx);
+    if (!rc)
+      rc = mgxk_hier_forward(ctx, d_in, rel, tol, false, norm);
+    if (rc)
+      return rc;
+  }
+  rc = mgxk_symbols_to_codes(ctx, ctx->lv.N, d_codes, ctx->d_out_idx,
+                             ctx->d_out_val, n_out);
+  if (rc)
+    return rc;
+  MGX_CUDA(cudaStreamSynchronize(ctx->stream));
+  return MGX_SUCCESS;
+}
+
 // Compressor::Compress, Compressor.hpp:204-251
 int mgx_compress(mgx_ctx *ctx, const void *d_in, int rel, double tol, double s,
                  double *norm_inout, uint8_t *d_out, uint64_t cap,

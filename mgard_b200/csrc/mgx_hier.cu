@@ -82,6 +82,18 @@ __device__ __forceinline__ AxisInfo axis_info(uint32_t i, uint32_t n, int L,
   return a;
 }
 
+__device__ __forceinline__ uint32_t final_pos(const AxisInfo &a, uint32_t i,
+                                              uint32_t n, int l, int L,
+                                              const uint32_t *nl, int ax) {
+  if (l == 0 || a.lvl == l)
+    return a.pos;
+  if (n == 1)
+    return 0;
+  if (i == n - 1)
+    return nl[(l - 1) * 3 + ax] - 1;
+  return i >> (L - l + 1);
+}
+
 template <typename T>
 __global__ void __launch_bounds__(HIER_THREADS)
     k_hier_forward(const T *__restrict__ u, uint16_t *__restrict__ sym,
@@ -180,8 +192,15 @@ __global__ void __launch_bounds__(HIER_THREADS)
           c = sub_rn(c, h0);
         }
         long long q = mgx_quantize(c, a.qv, (T)1, a.shift);
-        const uint64_t opos =
-            (uint64_t)az.pos * sz + (uint64_t)ay.pos * sy + ax.pos;
+        // reordered position: a level-l coefficient keeps, along the axes in
+        // which it is a level-l COARSE node, its index in the level-(l-1)
+        // grid (coarser levels only permute the [0, n_{l-1}) box, which this
+        // element is outside of); along its odd axes it sits in the
+        // coefficient block [n_{l-1}, n_l).
+        const uint32_t px = final_pos(ax, gx, nx, l, a.L, nl, 2);
+        const uint32_t py = final_pos(ay, gy, ny, l, a.L, nl, 1);
+        const uint32_t pz = final_pos(az, gz, nz, l, a.L, nl, 0);
+        const uint64_t opos = (uint64_t)pz * sz + (uint64_t)py * sy + px;
         if (q < 0 || q >= (long long)a.dict) {
           unsigned long long slot = atomicAdd(out_count, 1ull);
           if (slot < out_cap) {

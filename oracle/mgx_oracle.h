@@ -62,6 +62,9 @@ int mgxo_codebook(const uint32_t *freq, uint32_t dict, uint64_t *codebook,
 
 /* Huffman::Compress + Serialize / Deserialize + Decompress
  * (Huffman.hpp:157-632): the "MGXHUFF" container. */
+/* reference defect hooks, see mgx_oracle_huffman.inc */
+void mgxo_set_oob_value(uint32_t v);
+uint64_t mgxo_oob_reads(void);
 int mgxo_huffman_compress(const int64_t *codes, uint64_t n, uint32_t dict,
                           uint32_t chunk, uint8_t *out, uint64_t cap,
                           uint64_t *out_bytes);

@@ -69,6 +69,8 @@ def port():
         _port = ctypes.CDLL(PORT_SO)
         for t in ("f32", "f64"):
             getattr(_port, "mgxo_norm_" + t).restype = c_dbl
+        _port.mgxo_oob_reads.restype = c_u64
+        _port.mgxo_set_oob_value.argtypes = [ctypes.c_uint32]
     return _port
 
 
@@ -223,3 +225,50 @@ def smooth_field(shape, dtype, seed=42, noise=1e-6):
     h ^= h >> np.uint64(29)
     v += noise * ((h >> np.uint64(11)).astype(np.float64) / 2.0 ** 53 - 0.5)
     return v.astype(dtype)
+
+
+def fresh(kind, method, *args, **kwargs):
+    """Run Oracle(kind).method(*args) in a NEW process.
+
+    The reference's GenerateCL reads one element past its frequency array
+    (see oracle/mgx_oracle_huffman.inc); what it finds there depends on the
+    heap's history, so bit-exact comparisons against the compiled reference
+    are only reproducible from a fresh process (fresh heap => 0)."""
+    import pickle
+    import sys
+    import tempfile
+    with tempfile.TemporaryDirectory() as td:
+        pin, pout = os.path.join(td, "in.pkl"), os.path.join(td, "out.pkl")
+        with open(pin, "wb") as f:
+            pickle.dump((kind, method, args, kwargs), f)
+        code = ("import pickle,sys; sys.path.insert(0,%r); import oracle_lib as o;"
+                "k,m,a,kw=pickle.load(open(%r,'rb'));"
+                "r=getattr(o.Oracle(k),m)(*a,**kw);"
+                "pickle.dump(r,open(%r,'wb'))" % (os.path.dirname(__file__), pin, pout))
+        subprocess.check_call([sys.executable, "-c", code])
+        with open(pout, "rb") as f:
+            return pickle.load(f)
+
+
+def same_container(a, b):
+    """byte equality except byte 7 (uninitialised pad after the 7-byte
+    signature in the reference's Serialize)."""
+    return a.size == b.size and np.array_equal(np.delete(a, 7), np.delete(b, 7))
+
+
+def ref_allowed_outputs(method, *args, **kwargs):
+    """Outputs of the restatement for the outcomes the reference's
+    out-of-bounds read allows (stand-in value 0 = the defined behaviour, and
+    UINT32_MAX = 'garbage larger than any frequency'); one element if the
+    read is never hit for this input."""
+    p = Oracle("port")
+    p.lib.mgxo_set_oob_value(0)
+    p.lib.mgxo_oob_reads()
+    outs = [getattr(p, method)(*args, **kwargs)]
+    if p.lib.mgxo_oob_reads() > 0:
+        p.lib.mgxo_set_oob_value(0xFFFFFFFF)
+        try:
+            outs.append(getattr(p, method)(*args, **kwargs))
+        finally:
+            p.lib.mgxo_set_oob_value(0)
+    return outs

@@ -141,8 +141,14 @@ E2E = [((65, 65, 65), np.float32, INF, 1, 1e-3), ((129, 129), np.float64, 0.0, 1
 @pytest.mark.parametrize("shape,dtype,s,rel,tol", E2E)
 def test_compress_decompress_vs_oracle(shape, dtype, s, rel, tol):
     u = smooth_field(shape, dtype)
-    o = oracles()[-1]
+    o = Oracle("port")
     want, norm = o.compress(u, rel, tol, s)
+    if oracle_lib.have_ref():
+        # the reference itself, from a fresh process (see oracle_lib.fresh)
+        rwant, rnorm = oracle_lib.fresh("ref", "compress", u, rel, tol, s)
+        allowed = oracle_lib.ref_allowed_outputs("compress", u, rel, tol, s)
+        assert rnorm == norm
+        assert any(oracle_lib.same_container(rwant, a[0]) for a in allowed)
     comp, tdt = make(shape, dtype)
     eb = mg.REL if rel else mg.ABS
     # L2 norms accumulate in fp64 on the GPU (T on the SERIAL reference): hand
@@ -189,3 +195,26 @@ def test_error_paths():
     bad = torch.zeros(4096, dtype=torch.uint8, device="cuda")
     with pytest.raises(mg.MgardError):
         comp.Decompress(bad, mg.REL, 1e-3, INF, 1.0)  # signature mismatch
+
+
+FUSED = [((33,), np.float32), ((4097,), np.float64), ((40,), np.float32),
+         ((17, 17), np.float64), ((129, 129), np.float32), ((20, 11), np.float64),
+         ((513, 513), np.float32), ((9, 9, 9), np.float32), ((33, 33, 33), np.float64),
+         ((20, 11, 6), np.float32), ((65, 65, 65), np.float32), ((65, 70, 130), np.float32),
+         ((100, 257, 70), np.float64)]
+
+
+@pytest.mark.parametrize("shape,dtype", FUSED)
+@pytest.mark.parametrize("rel,tol", [(1, 1e-3), (0, 1e-4), (1, 1e-6)])
+def test_fused_hierarchical_forward(shape, dtype, rel, tol):
+    """one-pass coefficients+quantise == oracle Decompose(hier) + Quantize"""
+    u = smooth_field(shape, dtype)
+    o = oracles()[-1]
+    norm = float(np.abs(u).max())
+    want = o.quantize(o.decompose(u, 0), rel, tol, INF, norm)
+    comp, _ = make(shape, dtype)
+    got = comp.DecomposeQuantizeFused(torch.from_numpy(u).cuda(),
+                                      mg.REL if rel else mg.ABS, tol, norm).cpu().numpy()
+    bad = np.argwhere(got != want)
+    assert len(bad) == 0, "%d codes differ, first %s: got %s want %s" % (
+        len(bad), bad[:5].tolist(), got[tuple(bad[0])], want[tuple(bad[0])])
