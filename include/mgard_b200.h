@@ -124,6 +124,27 @@ int mgx_decompress_host(mgx_ctx *ctx, const uint8_t *h_in, uint64_t bytes,
 /* kernels launched by this context since creation (bench.py's gpu_launches) */
 uint64_t mgx_launch_count(const mgx_ctx *ctx);
 
+/* Stage timing with CUDA events on the context's stream (what the reference
+ * prints through its Timer / log::time calls, Compressor.hpp:125-248,
+ * Huffman.hpp:186-330).  Ticks are recorded by mgx_compress / mgx_decompress
+ * while timing is on; mgx_elapsed_ms reads the last call's ticks. */
+enum mgx_tick_id {
+  MGX_TICK_C_BEGIN = 0,    /* mgx_compress entered                          */
+  MGX_TICK_C_NORM = 1,     /* after CalculateNorm (if it ran)               */
+  MGX_TICK_C_REFACTOR = 2, /* after Decompose + Quantize (+ histogram)      */
+  MGX_TICK_C_CODEBOOK = 3, /* after GetCodebook                             */
+  MGX_TICK_C_SIZES = 4,    /* after chunk bit counts + offset scan          */
+  MGX_TICK_C_PACK = 5,     /* after bit packing                             */
+  MGX_TICK_C_END = 6,      /* container complete                            */
+  MGX_TICK_D_BEGIN = 8,    /* mgx_decompress entered                        */
+  MGX_TICK_D_DECODE = 9,   /* after Huffman decode                          */
+  MGX_TICK_D_DEQUANT = 10, /* after Dequantize (+ outlier restore)          */
+  MGX_TICK_D_END = 11,     /* after Recompose                               */
+  MGX_TICK_COUNT = 16
+};
+int mgx_set_timing(mgx_ctx *ctx, int on);
+int mgx_elapsed_ms(mgx_ctx *ctx, int from_tick, int to_tick, float *ms);
+
 #ifdef __cplusplus
 }
 #endif

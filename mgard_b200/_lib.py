@@ -49,6 +49,9 @@ SIGNATURES = {
     "mgx_decompress_host": (c_int, [c_vp, c_vp, c_u64, c_int, c_dbl, c_dbl,
                                     c_dbl, c_vp]),
     "mgx_launch_count": (c_u64, [c_vp]),
+    "mgx_set_timing": (c_int, [c_vp, c_int]),
+    "mgx_elapsed_ms": (c_int, [c_vp, c_int, c_int,
+                               ctypes.POINTER(ctypes.c_float)]),
 }
 
 _lib = None

@@ -141,6 +141,19 @@ class Compressor:
     def launch_count(self):
         return int(self.lib.mgx_launch_count(self._ctx))
 
+    TICKS = {"c_begin": 0, "c_norm": 1, "c_refactor": 2, "c_codebook": 3,
+             "c_sizes": 4, "c_pack": 5, "c_end": 6, "d_begin": 8,
+             "d_decode": 9, "d_dequant": 10, "d_end": 11}
+
+    def set_timing(self, on=True):
+        self._check(self.lib.mgx_set_timing(self._ctx, int(on)))
+
+    def elapsed_ms(self, a, b):
+        ms = ctypes.c_float()
+        self._check(self.lib.mgx_elapsed_ms(self._ctx, self.TICKS[a],
+                                            self.TICKS[b], ctypes.byref(ms)))
+        return ms.value
+
     # ---- stages (Compressor.h:60-85) --------------------------------------
     def CalculateNorm(self, data, s):
         data = self._dev(data, self.tdtype)
@@ -151,6 +164,21 @@ class Compressor:
         return float(self.lib.mgx_finish_norm(
             self.hierarchy.dtype_code, linf, part.value, self.N,
             1 if self.config.normalize_coordinates else 0))
+
+    def NormPartial(self, data, s):
+        """local part of the norm (max |u| for s=inf, else sum u^2); combine
+        partials of all subdomains (max / sum) and pass to FinishNorm."""
+        data = self._dev(data, self.tdtype)
+        part = ctypes.c_double()
+        self._check(self.lib.mgx_norm_partial(
+            self._ctx, data.data_ptr(), 1 if math.isinf(s) else 0,
+            ctypes.byref(part)))
+        return part.value
+
+    def FinishNorm(self, partial, s, total_elems):
+        return float(self.lib.mgx_finish_norm(
+            self.hierarchy.dtype_code, 1 if math.isinf(s) else 0, partial,
+            int(total_elems), 1 if self.config.normalize_coordinates else 0))
 
     def Decompose(self, data, orthogonal_projection):
         """in place on a device tensor (reordered level-blocked layout)."""

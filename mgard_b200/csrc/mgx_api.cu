@@ -123,6 +123,9 @@ void mgx_destroy(mgx_ctx *ctx) {
     return;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
+  for (int i = 0; i < MGX_TICK_COUNT; i++)
+    if (ctx->ev[i])
+      cudaEventDestroy(ctx->ev[i]);
   release_plan(ctx);
   free_dev(ctx->d_scalars);
   free_dev(ctx->d_sort_tmp);
@@ -142,6 +145,28 @@ const char *mgx_last_error(const mgx_ctx *ctx) {
 }
 
 uint64_t mgx_launch_count(const mgx_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+int mgx_set_timing(mgx_ctx *ctx, int on) {
+  if (!ctx)
+    return MGX_FAILURE;
+  if (on && !ctx->ev[0])
+    for (int i = 0; i < MGX_TICK_COUNT; i++)
+      MGX_CUDA(cudaEventCreate(&ctx->ev[i]));
+  ctx->timing = on != 0;
+  for (int i = 0; i < MGX_TICK_COUNT; i++)
+    ctx->ev_set[i] = false;
+  return MGX_SUCCESS;
+}
+
+int mgx_elapsed_ms(mgx_ctx *ctx, int from_tick, int to_tick, float *ms) {
+  if (!ctx || from_tick < 0 || to_tick < 0 || from_tick >= MGX_TICK_COUNT ||
+      to_tick >= MGX_TICK_COUNT || !ctx->ev_set[from_tick] ||
+      !ctx->ev_set[to_tick])
+    return MGX_FAILURE;
+  MGX_CUDA(cudaEventSynchronize(ctx->ev[to_tick]));
+  MGX_CUDA(cudaEventElapsedTime(ms, ctx->ev[from_tick], ctx->ev[to_tick]));
+  return MGX_SUCCESS;
+}
 
 int mgx_plan(mgx_ctx *ctx, int D, const uint64_t *shape, int dtype,
              uint32_t dict_size, uint32_t chunk_size, uint64_t max_level) {
@@ -326,6 +351,7 @@ int mgx_huff_encode(mgx_ctx *ctx, const int64_t *d_codes, uint64_t n,
     ctx->err = "mgx_huff_encode: n must equal the planned element count";
     return MGX_FAILURE;
   }
+  mgx_tick(ctx, MGX_TICK_C_NORM);
   for (int attempt = 0; attempt < 2; attempt++) {
     int rc = mgxk_histogram_reset(ctx);
     if (!rc)
@@ -342,6 +368,7 @@ int mgx_huff_encode(mgx_ctx *ctx, const int64_t *d_codes, uint64_t n,
       return rc > MGX_BACKEND_UNAVAILABLE ? MGX_FAILURE : rc;
     break;
   }
+  mgx_tick(ctx, MGX_TICK_C_END);
   MGX_CUDA(cudaStreamSynchronize(ctx->stream));
   return MGX_SUCCESS;
 }
@@ -403,6 +430,7 @@ int mgx_compress(mgx_ctx *ctx, const void *d_in, int rel, double tol, double s,
   const bool orth = need_orthogonal(ctx, s);
   const uint64_t N = ctx->lv.N;
   double norm = norm_inout ? *norm_inout : 0.0;
+  mgx_tick(ctx, MGX_TICK_C_BEGIN);
   if (rel && !(norm > 0)) { // CalculateNorm, Compressor.hpp:122-130
     double partial;
     int rc = mgx_norm_partial(ctx, d_in, linf, &partial);
@@ -412,6 +440,7 @@ int mgx_compress(mgx_ctx *ctx, const void *d_in, int rel, double tol, double s,
     if (norm_inout)
       *norm_inout = norm;
   }
+  mgx_tick(ctx, MGX_TICK_C_NORM);
   for (int attempt = 0; attempt < 2; attempt++) {
     int rc = mgxk_histogram_reset(ctx);
     if (rc)
@@ -429,6 +458,7 @@ int mgx_compress(mgx_ctx *ctx, const void *d_in, int rel, double tol, double s,
       if (!rc)
         rc = mgxk_quantize_sym(ctx, ctx->d_v, rel, tol, s, nullptr, norm);
     }
+    mgx_tick(ctx, MGX_TICK_C_REFACTOR);
     if (!rc)
       rc = mgxk_encode_container(ctx, N, d_out, cap, out_bytes);
     if (rc == MGX_FAILURE + 100 && attempt == 0) {
@@ -441,6 +471,7 @@ int mgx_compress(mgx_ctx *ctx, const void *d_in, int rel, double tol, double s,
       return rc > MGX_BACKEND_UNAVAILABLE ? MGX_FAILURE : rc;
     break;
   }
+  mgx_tick(ctx, MGX_TICK_C_END);
   MGX_CUDA(cudaStreamSynchronize(ctx->stream));
   return MGX_SUCCESS;
 }
@@ -454,14 +485,18 @@ int mgx_decompress(mgx_ctx *ctx, const uint8_t *d_in, uint64_t bytes, int rel,
   const uint64_t *oidx;
   const int64_t *oval;
   uint64_t n_out;
+  mgx_tick(ctx, MGX_TICK_D_BEGIN);
   int rc = mgxk_decode_container(ctx, d_in, bytes, N, &oidx, &oval, &n_out);
   if (rc)
     return rc;
+  mgx_tick(ctx, MGX_TICK_D_DECODE);
   rc = mgxk_dequantize_sym_out(ctx, rel, tol, s, norm, d_out, oidx, oval, n_out);
+  mgx_tick(ctx, MGX_TICK_D_DEQUANT);
   if (!rc)
     rc = mgxk_recompose(ctx, d_out, orth ? 1 : 0);
   if (rc)
     return rc;
+  mgx_tick(ctx, MGX_TICK_D_END);
   MGX_CUDA(cudaStreamSynchronize(ctx->stream));
   return MGX_SUCCESS;
 }

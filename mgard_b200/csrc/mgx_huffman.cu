@@ -380,6 +380,7 @@ int mgxk_encode_container(mgx_ctx *ctx, uint64_t n, uint8_t *d_out, uint64_t cap
   int rc = mgxk_codebook(ctx, ctx->d_freq, ctx->d_codebook, ctx->d_decodebook);
   if (rc)
     return rc;
+  mgx_tick(ctx, MGX_TICK_C_CODEBOOK);
   // pass 1: sizes + offsets
   MGX_CUDA(cudaMemsetAsync(ctx->d_scan_state, 0, ntiles * 8, ctx->stream));
   int occ = 1;
@@ -392,6 +393,7 @@ int mgxk_encode_container(mgx_ctx *ctx, uint64_t n, uint8_t *d_out, uint64_t cap
       (u64 *)ctx->d_chunk_bits, (u64 *)ctx->d_chunk_off,
       (u64 *)ctx->d_scan_state, nchunk, ntiles, (u64 *)ctx->d_scalars);
   ctx->launches++;
+  mgx_tick(ctx, MGX_TICK_C_SIZES);
   // one host round trip: packed size, longest code, outlier count, error flags
   MGX_CUDA(cudaMemcpyAsync(ctx->h_scalars, ctx->d_scalars, MGX_SC_COUNT * 8,
                            cudaMemcpyDeviceToHost, ctx->stream));
@@ -443,6 +445,7 @@ int mgxk_encode_container(mgx_ctx *ctx, uint64_t n, uint8_t *d_out, uint64_t cap
       (const u64 *)ctx->d_chunk_off, (u64 *)(d_out + h.off_packed), nchunk,
       words_cap);
   ctx->launches++;
+  mgx_tick(ctx, MGX_TICK_C_PACK);
   // outliers in ascending index order (the SERIAL reference's order)
   k_write_outlier_count<<<1, 32, 0, ctx->stream>>>(d_out, off_outc, n_out);
   ctx->launches++;

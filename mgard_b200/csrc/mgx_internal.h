@@ -85,7 +85,19 @@ struct mgx_ctx {
   size_t h_stage_bytes = 0;
   void *d_stage_in = nullptr, *d_stage_out = nullptr;
   size_t d_stage_in_bytes = 0, d_stage_out_bytes = 0;
+
+  // optional stage timing (mgx_set_timing): events on ctx->stream
+  bool timing = false;
+  cudaEvent_t ev[MGX_TICK_COUNT] = {};
+  bool ev_set[MGX_TICK_COUNT] = {};
 };
+
+static inline void mgx_tick(mgx_ctx *c, int id) {
+  if (c->timing) {
+    cudaEventRecord(c->ev[id], c->stream);
+    c->ev_set[id] = true;
+  }
+}
 
 // indices into d_scalars / h_scalars (uint64 each; doubles are bit-cast)
 enum {
