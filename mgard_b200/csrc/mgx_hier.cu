@@ -16,7 +16,18 @@
 // staged in shared memory with coalesced row loads; because tile origins are
 // multiples of the tile size, all neighbours at distance <= T/2 are inside the
 // staged tile, and the few coarser nodes (< 1/512 of the grid) gather from
-// global memory / L2 instead.  TMA (cp.async.bulk.tensor) is not usable here:
+// global memory / L2 instead.
+//
+// Interior tiles run a structured schedule instead of a per-element gather:
+// pass p (stride h = 2^p) visits the sub-grid of multiples of h row by row,
+// one thread per (even, odd) pair of neighbouring sub-grid nodes along x.  The
+// odd node is always a level-(L-p) coefficient, the even one is a coefficient
+// iff its row has an odd y or z sub-index -- a per-row (warp-uniform in pass 0)
+// property -- and both share the same neighbour-row loads.  Only nodes that are
+// multiples of the tile edge on every axis (1/512 in 3-D) fall through to the
+// generic per-element path, as do the tiles that touch the last node of an
+// axis (where the reference's "even indices + last node" coarsening is not a
+// plain stride).  TMA (cp.async.bulk.tensor) is not usable here:
 // the 2^k+1 row pitch (e.g. 1025 * 4 B) is not a multiple of 16 bytes.
 #include <algorithm>
 #include <cmath>
@@ -27,21 +38,34 @@
 
 namespace {
 
-constexpr int TZ = 8, TY = 8, TX = 64;
-constexpr int HZ = TZ + 1, HY = TY + 1, HX = TX + 1;
 constexpr int HIER_THREADS = 256;
+constexpr int HIER_WARPS = HIER_THREADS / 32;
 
 template <typename T> struct HierArgs {
   uint32_t n[3];                // nz, ny, nx (padded with 1)
   uint32_t nl[MGX_MAX_L][3];    // level sizes per axis
   uint32_t roff[MGX_MAX_L][3];  // ratio table offsets per level and axis
   int L;
-  int half;                     // all ratios exactly 0.5
   T qv;                         // quantiser reciprocal (all levels equal, L-inf)
-  long long shift;
+  int shift;                    // dict / 2
   uint32_t dict;
   uint32_t tiles[3];
   uint64_t ntiles;
+};
+
+// Tile geometry: 2^LZ x 2^LY x 2^LX nodes; an axis with extent 1 is "flat"
+// (no halo, never interpolated).  PASSES = strides 1, 2, .. handled in-tile.
+template <int LZ_, int LY_, int LX_> struct TileShape {
+  static constexpr int LZ = LZ_, LY = LY_, LX = LX_;
+  static constexpr int TZ = 1 << LZ, TY = 1 << LY, TX = 1 << LX;
+  static constexpr bool RZ = LZ > 0, RY = LY > 0; // real (non-flat) axes
+  static constexpr int HZ = RZ ? TZ + 1 : 1, HY = RY ? TY + 1 : 1;
+  static constexpr int PX = TX + 2; // even pitch: (even, odd) pairs stay aligned
+  static constexpr int ROWS = HZ * HY;
+  static constexpr int PASSES =
+      RZ ? (LZ < LY ? (LZ < LX ? LZ : LX) : (LY < LX ? LY : LX))
+         : (RY ? (LY < LX ? LY : LX) : LX);
+  static constexpr size_t tile_elems = (size_t)ROWS * PX;
 };
 
 struct AxisInfo {
@@ -82,6 +106,10 @@ __device__ __forceinline__ AxisInfo axis_info(uint32_t i, uint32_t n, int L,
   return a;
 }
 
+// Reordered position: a level-l coefficient keeps, along the axes in which it
+// is a level-l COARSE node, its index in the level-(l-1) grid (coarser levels
+// only permute the [0, n_{l-1}) box, which this element is outside of); along
+// its odd axes it sits in the coefficient block [n_{l-1}, n_l).
 __device__ __forceinline__ uint32_t final_pos(const AxisInfo &a, uint32_t i,
                                               uint32_t n, int l, int L,
                                               const uint32_t *nl, int ax) {
@@ -94,7 +122,208 @@ __device__ __forceinline__ uint32_t final_pos(const AxisInfo &a, uint32_t i,
   return i >> (L - l + 1);
 }
 
-template <typename T>
+__device__ __noinline__ void hier_outlier(unsigned long long *out_count,
+                                          unsigned long long *out_idx,
+                                          long long *out_val,
+                                          unsigned long long out_cap,
+                                          uint64_t opos, long long q) {
+  unsigned long long slot = atomicAdd(out_count, 1ull);
+  if (slot < out_cap) {
+    out_idx[slot] = opos;
+    out_val[slot] = q;
+  }
+}
+
+// Per-thread sink: quantise (lwqzk, LinearQuantization.hpp:96-111), separate
+// outliers (OutlierSeparator.hpp:17-44), count the symbol, store it.
+template <typename T> struct Sink {
+  uint16_t *sym;
+  uint32_t *s_hist;
+  unsigned long long *out_count, *out_idx;
+  long long *out_val;
+  unsigned long long out_cap;
+  T qv;
+  int shift;
+  uint32_t dict;
+  uint32_t centre_hits; // symbols equal to dict/2 are counted in a register
+
+  __device__ __forceinline__ void put(T c, uint64_t opos) {
+    const T r = add_rn((T)0.5, fabs(mul_rn(c, qv)));
+    uint32_t sv;
+    if (r < (T)1.0e9) {
+      int q = (int)r;
+      q = (c < (T)0 ? -q : q) + shift;
+      sv = (uint32_t)q;
+      if (sv >= dict) { // q < 0 wraps to a huge unsigned value
+        outlier(opos, (long long)q);
+        sv = 0;
+      }
+    } else {
+      long long q = (long long)r;
+      q = (c < (T)0 ? -q : q) + (long long)shift;
+      outlier(opos, q);
+      sv = 0;
+    }
+    sym[opos] = (uint16_t)sv;
+    if (sv == (uint32_t)shift)
+      centre_hits++;
+    else
+      atomicAdd(&s_hist[sv], 1u);
+  }
+  __device__ __forceinline__ void outlier(uint64_t opos, long long q) {
+    hier_outlier(out_count, out_idx, out_val, out_cap, opos, q);
+  }
+};
+
+// Generic per-element path (any index, any size): gathers the 2^k neighbours
+// from the staged tile when they are inside it, else from global memory.
+template <typename T, bool HALF, class TS>
+__device__ __forceinline__ void
+element_generic(const T *__restrict__ u, const T *tile, const T *__restrict__ tables,
+                const HierArgs<T> &a, uint32_t gx, uint32_t gy, uint32_t gz,
+                uint32_t x0, uint32_t y0, uint32_t z0, uint32_t ex, uint32_t ey,
+                uint32_t ez, Sink<T> &sink) {
+  const uint32_t nz = a.n[0], ny = a.n[1], nx = a.n[2];
+  const uint64_t sy = nx, sz = (uint64_t)nx * ny;
+  const uint32_t *nl = &a.nl[0][0];
+  const AxisInfo ax = axis_info(gx, nx, a.L, nl, 2);
+  const AxisInfo ay = axis_info(gy, ny, a.L, nl, 1);
+  const AxisInfo az = axis_info(gz, nz, a.L, nl, 0);
+  const int l = max(ax.lvl, max(ay.lvl, az.lvl));
+  const bool ix = l > 0 && ax.lvl == l, iy = l > 0 && ay.lvl == l,
+             iz = l > 0 && az.lvl == l;
+  const uint32_t xl = ix ? ax.lo : gx, xh = ix ? ax.hi : gx;
+  const uint32_t yl = iy ? ay.lo : gy, yh = iy ? ay.hi : gy;
+  const uint32_t zl = iz ? az.lo : gz, zh = iz ? az.hi : gz;
+  T c = tile[((gz - z0) * TS::HY + (gy - y0)) * TS::PX + (gx - x0)];
+  if (l > 0) {
+    T v[8];
+    const bool in_tile = xl >= x0 && xh < x0 + ex && yl >= y0 && yh < y0 + ey &&
+                         zl >= z0 && zh < z0 + ez;
+    if (in_tile) {
+      const uint32_t a0 = (zl - z0) * TS::HY, a1 = (zh - z0) * TS::HY;
+      const uint32_t b0 = yl - y0, b1 = yh - y0, c0 = xl - x0, c1 = xh - x0;
+      v[0] = tile[(a0 + b0) * TS::PX + c0];
+      v[1] = tile[(a0 + b0) * TS::PX + c1];
+      v[2] = tile[(a0 + b1) * TS::PX + c0];
+      v[3] = tile[(a0 + b1) * TS::PX + c1];
+      v[4] = tile[(a1 + b0) * TS::PX + c0];
+      v[5] = tile[(a1 + b0) * TS::PX + c1];
+      v[6] = tile[(a1 + b1) * TS::PX + c0];
+      v[7] = tile[(a1 + b1) * TS::PX + c1];
+    } else {
+      const uint64_t a0 = zl * sz, a1 = zh * sz, b0 = yl * sy, b1 = yh * sy;
+      v[0] = __ldg(u + a0 + b0 + xl);
+      v[1] = __ldg(u + a0 + b0 + xh);
+      v[2] = __ldg(u + a0 + b1 + xl);
+      v[3] = __ldg(u + a0 + b1 + xh);
+      v[4] = __ldg(u + a1 + b0 + xl);
+      v[5] = __ldg(u + a1 + b0 + xh);
+      v[6] = __ldg(u + a1 + b1 + xl);
+      v[7] = __ldg(u + a1 + b1 + xh);
+    }
+    // interpolate along f (x), then c (y), then r (z) -- the order of
+    // GridProcessingKernel3D.hpp:732-877; ratio index = left neighbour
+    T tx_ = (T)0.5, ty_ = (T)0.5, tz_ = (T)0.5;
+    if (!HALF) {
+      if (ix) tx_ = tables[a.roff[l][2] + ax.j - 1];
+      if (iy) ty_ = tables[a.roff[l][1] + ay.j - 1];
+      if (iz) tz_ = tables[a.roff[l][0] + az.j - 1];
+    }
+    T f0 = ix ? mgx_lerp(v[0], v[1], tx_) : v[0];
+    T f1 = ix ? mgx_lerp(v[2], v[3], tx_) : v[2];
+    T f2 = ix ? mgx_lerp(v[4], v[5], tx_) : v[4];
+    T f3 = ix ? mgx_lerp(v[6], v[7], tx_) : v[6];
+    T g0 = iy ? mgx_lerp(f0, f1, ty_) : f0;
+    T g1 = iy ? mgx_lerp(f2, f3, ty_) : f2;
+    T h0 = iz ? mgx_lerp(g0, g1, tz_) : g0;
+    c = sub_rn(c, h0);
+  }
+  const uint32_t px = final_pos(ax, gx, nx, l, a.L, nl, 2);
+  const uint32_t py = final_pos(ay, gy, ny, l, a.L, nl, 1);
+  const uint32_t pz = final_pos(az, gz, nz, l, a.L, nl, 0);
+  sink.put(c, (uint64_t)pz * sz + (uint64_t)py * sy + px);
+}
+
+// One structured pass over an interior tile: stride h = 2^P, coefficients of
+// level l = L - P.  Thread <-> (even, odd) pair of sub-grid nodes along x.
+template <typename T, bool HALF, class TS, int P>
+__device__ __forceinline__ void
+tile_pass(const T *tile, const T *__restrict__ tables, const HierArgs<T> &a,
+          uint32_t x0, uint32_t y0, uint32_t z0, Sink<T> &sink) {
+  constexpr int H = 1 << P;
+  constexpr int PPR_SH = TS::LX - P - 1;               // pairs per row
+  constexpr int RY_SH = TS::RY ? TS::LY - P : 0;       // sub-rows along y
+  constexpr int RZ_SH = TS::RZ ? TS::LZ - P : 0;       // sub-rows along z
+  constexpr int NPAIRS = 1 << (PPR_SH + RY_SH + RZ_SH);
+  const int l = a.L - P;
+  const uint32_t ncx = a.nl[l - 1][2], ncy = a.nl[l - 1][1], ncz = a.nl[l - 1][0];
+  const uint64_t sy = a.n[2], sz = (uint64_t)a.n[2] * a.n[1];
+  const uint32_t xb = x0 >> (P + 1);
+  for (int id = threadIdx.x; id < NPAIRS; id += HIER_THREADS) {
+    const int k = id & ((1 << PPR_SH) - 1);
+    const int row = id >> PPR_SH;
+    const int ys = row & ((1 << RY_SH) - 1);
+    const int zs = row >> RY_SH;
+    const int iy = TS::RY ? (ys & 1) : 0, iz = TS::RZ ? (zs & 1) : 0;
+    const int ly = ys << P, lz = zs << P, lxe = k << (P + 1);
+    const uint32_t jy = (y0 + ly) >> P, jz = (z0 + lz) >> P;
+    T tx = (T)0.5, ty = (T)0.5, tz = (T)0.5;
+    if (!HALF) {
+      tx = tables[a.roff[l][2] + ((x0 + lxe) >> P)];
+      if (iy) ty = tables[a.roff[l][1] + jy - 1];
+      if (iz) tz = tables[a.roff[l][0] + jz - 1];
+    }
+    const int yl = ly - (iy << P), yh = ly + (iy << P);
+    const int zl = lz - (iz << P), zh = lz + (iz << P);
+    const T *pO = tile + (lz * TS::HY + ly) * TS::PX + lxe;
+    const T own_e = pO[0], own_o = pO[H];
+    const T *pA = tile + (zl * TS::HY + yl) * TS::PX + lxe;
+    T gE0 = pA[0];
+    T gO0 = mgx_lerp(gE0, pA[2 * H], tx);
+    if (iy) {
+      const T *pB = tile + (zl * TS::HY + yh) * TS::PX + lxe;
+      const T eB = pB[0];
+      const T fB = mgx_lerp(eB, pB[2 * H], tx);
+      gE0 = mgx_lerp(gE0, eB, ty);
+      gO0 = mgx_lerp(gO0, fB, ty);
+    }
+    T hE = gE0, hO = gO0;
+    if (iz) {
+      const T *pC = tile + (zh * TS::HY + yl) * TS::PX + lxe;
+      T gE1 = pC[0];
+      T gO1 = mgx_lerp(gE1, pC[2 * H], tx);
+      if (iy) {
+        const T *pD = tile + (zh * TS::HY + yh) * TS::PX + lxe;
+        const T eD = pD[0];
+        const T fD = mgx_lerp(eD, pD[2 * H], tx);
+        gE1 = mgx_lerp(gE1, eD, ty);
+        gO1 = mgx_lerp(gO1, fD, ty);
+      }
+      hE = mgx_lerp(gE0, gE1, tz);
+      hO = mgx_lerp(gO0, gO1, tz);
+    }
+    // reordered positions: j odd -> coefficient block, j even -> j / 2
+    const uint32_t py = (iy ? ncy : 0u) + (jy >> 1);
+    const uint32_t pz = (iz ? ncz : 0u) + (jz >> 1);
+    const uint64_t rowpos = (uint64_t)pz * sz + (uint64_t)py * sy + xb + k;
+    sink.put(sub_rn(own_o, hO), rowpos + ncx);
+    if (iy | iz)
+      sink.put(sub_rn(own_e, hE), rowpos);
+  }
+}
+
+template <typename T, bool HALF, class TS, int P>
+__device__ __forceinline__ void
+run_passes(const T *tile, const T *__restrict__ tables, const HierArgs<T> &a,
+           uint32_t x0, uint32_t y0, uint32_t z0, Sink<T> &sink) {
+  if constexpr (P < TS::PASSES) {
+    tile_pass<T, HALF, TS, P>(tile, tables, a, x0, y0, z0, sink);
+    run_passes<T, HALF, TS, P + 1>(tile, tables, a, x0, y0, z0, sink);
+  }
+}
+
+template <typename T, bool HALF, class TS>
 __global__ void __launch_bounds__(HIER_THREADS)
     k_hier_forward(const T *__restrict__ u, uint16_t *__restrict__ sym,
                    uint32_t *__restrict__ g_freq,
@@ -105,122 +334,151 @@ __global__ void __launch_bounds__(HIER_THREADS)
                    const __grid_constant__ HierArgs<T> a) {
   extern __shared__ __align__(16) unsigned char smem[];
   T *tile = (T *)smem;
-  uint32_t *s_hist = (uint32_t *)(smem + sizeof(T) * HZ * HY * HX);
+  uint32_t *s_hist = (uint32_t *)(smem + sizeof(T) * TS::tile_elems);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   for (uint32_t i = tid; i < a.dict; i += HIER_THREADS)
     s_hist[i] = 0;
   const uint32_t nz = a.n[0], ny = a.n[1], nx = a.n[2];
   const uint64_t sy = nx, sz = (uint64_t)nx * ny;
-  const uint32_t *nl = &a.nl[0][0];
+  Sink<T> sink{sym, s_hist, out_count, out_idx, out_val, out_cap,
+               a.qv, a.shift, a.dict, 0u};
 
   for (uint64_t t = blockIdx.x; t < a.ntiles; t += gridDim.x) {
     const uint32_t tx = (uint32_t)(t % a.tiles[2]);
     const uint32_t ty = (uint32_t)((t / a.tiles[2]) % a.tiles[1]);
     const uint32_t tzz = (uint32_t)(t / ((uint64_t)a.tiles[2] * a.tiles[1]));
-    const uint32_t z0 = tzz * TZ, y0 = ty * TY, x0 = tx * TX;
-    const uint32_t ez = min((uint32_t)HZ, nz - z0), ey = min((uint32_t)HY, ny - y0),
-                   ex = min((uint32_t)HX, nx - x0);
+    const uint32_t z0 = tzz * TS::TZ, y0 = ty * TS::TY, x0 = tx * TS::TX;
+    // interior tile: the +1 halo exists on every real axis and no node of the
+    // tile is the last node of its axis
+    const bool regular = a.L >= TS::PASSES && x0 + TS::TX <= nx - 1 &&
+                         (!TS::RY || y0 + TS::TY <= ny - 1) &&
+                         (!TS::RZ || z0 + TS::TZ <= nz - 1);
+    const T *src0 = u + (uint64_t)z0 * sz + (uint64_t)y0 * sy + x0;
     __syncthreads(); // previous tile fully consumed (also orders the hist init)
-    // stage the tile: one warp per (z,y) row, coalesced along x
-    for (uint32_t r = warp; r < ez * ey; r += HIER_THREADS / 32) {
-      uint32_t rz = r / ey, ry = r % ey;
-      const T *src = u + (uint64_t)(z0 + rz) * sz + (uint64_t)(y0 + ry) * sy + x0;
-      T *dst = tile + (rz * HY + ry) * HX;
-      for (uint32_t x = lane; x < ex; x += 32)
-        dst[x] = src[x];
-    }
-    __syncthreads();
-    for (int k = 0; k < (TZ * TY * TX) / HIER_THREADS; k++) {
-      const int id = k * HIER_THREADS + tid;
-      const uint32_t lx = id % TX, ly = (id / TX) % TY, lz = id / (TX * TY);
-      const uint32_t gx = x0 + lx, gy = y0 + ly, gz = z0 + lz;
-      const bool valid = gx < nx && gy < ny && gz < nz;
-      uint32_t sv = 0;
-      if (valid) {
-        const AxisInfo ax = axis_info(gx, nx, a.L, nl, 2);
-        const AxisInfo ay = axis_info(gy, ny, a.L, nl, 1);
-        const AxisInfo az = axis_info(gz, nz, a.L, nl, 0);
-        const int l = max(ax.lvl, max(ay.lvl, az.lvl));
-        const bool ix = l > 0 && ax.lvl == l, iy = l > 0 && ay.lvl == l,
-                   iz = l > 0 && az.lvl == l;
-        const uint32_t xl = ix ? ax.lo : gx, xh = ix ? ax.hi : gx;
-        const uint32_t yl = iy ? ay.lo : gy, yh = iy ? ay.hi : gy;
-        const uint32_t zl = iz ? az.lo : gz, zh = iz ? az.hi : gz;
-        T c = tile[(lz * HY + ly) * HX + lx];
-        if (l > 0) {
-          T v[8];
-          const bool in_tile = xl >= x0 && xh < x0 + ex && yl >= y0 &&
-                               yh < y0 + ey && zl >= z0 && zh < z0 + ez;
-          if (in_tile) {
-            const uint32_t a0 = (zl - z0) * HY, a1 = (zh - z0) * HY;
-            const uint32_t b0 = yl - y0, b1 = yh - y0, c0 = xl - x0,
-                           c1 = xh - x0;
-            v[0] = tile[(a0 + b0) * HX + c0];
-            v[1] = tile[(a0 + b0) * HX + c1];
-            v[2] = tile[(a0 + b1) * HX + c0];
-            v[3] = tile[(a0 + b1) * HX + c1];
-            v[4] = tile[(a1 + b0) * HX + c0];
-            v[5] = tile[(a1 + b0) * HX + c1];
-            v[6] = tile[(a1 + b1) * HX + c0];
-            v[7] = tile[(a1 + b1) * HX + c1];
-          } else {
-            const uint64_t a0 = zl * sz, a1 = zh * sz, b0 = yl * sy, b1 = yh * sy;
-            v[0] = __ldg(u + a0 + b0 + xl);
-            v[1] = __ldg(u + a0 + b0 + xh);
-            v[2] = __ldg(u + a0 + b1 + xl);
-            v[3] = __ldg(u + a0 + b1 + xh);
-            v[4] = __ldg(u + a1 + b0 + xl);
-            v[5] = __ldg(u + a1 + b0 + xh);
-            v[6] = __ldg(u + a1 + b1 + xl);
-            v[7] = __ldg(u + a1 + b1 + xh);
-          }
-          // interpolate along f (x), then c (y), then r (z) -- the order of
-          // GridProcessingKernel3D.hpp:732-877; ratio index = left neighbour
-          T tx_ = (T)0.5, ty_ = (T)0.5, tz_ = (T)0.5;
-          if (!a.half) {
-            if (ix) tx_ = tables[a.roff[l][2] + ax.j - 1];
-            if (iy) ty_ = tables[a.roff[l][1] + ay.j - 1];
-            if (iz) tz_ = tables[a.roff[l][0] + az.j - 1];
-          }
-          T f0 = ix ? mgx_lerp(v[0], v[1], tx_) : v[0];
-          T f1 = ix ? mgx_lerp(v[2], v[3], tx_) : v[2];
-          T f2 = ix ? mgx_lerp(v[4], v[5], tx_) : v[4];
-          T f3 = ix ? mgx_lerp(v[6], v[7], tx_) : v[6];
-          T g0 = iy ? mgx_lerp(f0, f1, ty_) : f0;
-          T g1 = iy ? mgx_lerp(f2, f3, ty_) : f2;
-          T h0 = iz ? mgx_lerp(g0, g1, tz_) : g0;
-          c = sub_rn(c, h0);
+    if (regular) {
+      // stage ROWS rows of TX + 1 nodes: one warp per row, all loads of a
+      // thread issued before the first shared store
+      constexpr int RPW = (TS::ROWS + HIER_WARPS - 1) / HIER_WARPS;
+      constexpr int XPL = TS::TX / 32;
+      if constexpr (TS::ROWS >= HIER_WARPS && RPW * XPL <= 32) {
+        T v[RPW][XPL];
+#pragma unroll
+        for (int i = 0; i < RPW; i++) {
+          const int r = warp + i * HIER_WARPS;
+          const int rz = r / TS::HY, ry = r - rz * TS::HY;
+          const T *src = src0 + rz * sz + ry * sy;
+#pragma unroll
+          for (int j = 0; j < XPL; j++)
+            if (r < TS::ROWS)
+              v[i][j] = src[lane + 32 * j];
         }
-        long long q = mgx_quantize(c, a.qv, (T)1, a.shift);
-        // reordered position: a level-l coefficient keeps, along the axes in
-        // which it is a level-l COARSE node, its index in the level-(l-1)
-        // grid (coarser levels only permute the [0, n_{l-1}) box, which this
-        // element is outside of); along its odd axes it sits in the
-        // coefficient block [n_{l-1}, n_l).
-        const uint32_t px = final_pos(ax, gx, nx, l, a.L, nl, 2);
-        const uint32_t py = final_pos(ay, gy, ny, l, a.L, nl, 1);
-        const uint32_t pz = final_pos(az, gz, nz, l, a.L, nl, 0);
-        const uint64_t opos = (uint64_t)pz * sz + (uint64_t)py * sy + px;
-        if (q < 0 || q >= (long long)a.dict) {
-          unsigned long long slot = atomicAdd(out_count, 1ull);
-          if (slot < out_cap) {
-            out_idx[slot] = opos;
-            out_val[slot] = q;
-          }
-          q = 0;
+#pragma unroll
+        for (int i = 0; i < RPW; i++) {
+          const int r = warp + i * HIER_WARPS;
+#pragma unroll
+          for (int j = 0; j < XPL; j++)
+            if (r < TS::ROWS)
+              tile[r * TS::PX + lane + 32 * j] = v[i][j];
         }
-        sv = (uint32_t)q;
-        sym[opos] = (uint16_t)sv;
+      } else {
+        for (int r = 0; r < TS::ROWS; r++) {
+          const int rz = r / TS::HY, ry = r - rz * TS::HY;
+          const T *src = src0 + rz * sz + ry * sy;
+#pragma unroll 4
+          for (int x = tid; x < TS::TX; x += HIER_THREADS)
+            tile[r * TS::PX + x] = src[x];
+        }
       }
-      mgx_hist_add(s_hist, sv, valid);
+      for (int r = tid; r < TS::ROWS; r += HIER_THREADS) { // halo column
+        const int rz = r / TS::HY, ry = r - rz * TS::HY;
+        tile[r * TS::PX + TS::TX] = src0[rz * sz + ry * sy + TS::TX];
+      }
+      __syncthreads();
+      run_passes<T, HALF, TS, 0>(tile, tables, a, x0, y0, z0, sink);
+      // nodes that are multiples of 2^PASSES on every axis: coarser levels
+      constexpr int CX = TS::TX >> TS::PASSES,
+                    CY = TS::RY ? (TS::TY >> TS::PASSES) : 1,
+                    CZ = TS::RZ ? (TS::TZ >> TS::PASSES) : 1;
+      for (int id = tid; id < CX * CY * CZ; id += HIER_THREADS) {
+        const uint32_t lx = (id % CX) << TS::PASSES,
+                       ly = ((id / CX) % CY) << TS::PASSES,
+                       lz = (id / (CX * CY)) << TS::PASSES;
+        element_generic<T, HALF, TS>(u, tile, tables, a, x0 + lx, y0 + ly, z0 + lz,
+                                     x0, y0, z0, TS::TX + 1, TS::HY, TS::HZ, sink);
+      }
+    } else {
+      const uint32_t ez = min((uint32_t)TS::HZ, nz - z0),
+                     ey = min((uint32_t)TS::HY, ny - y0),
+                     ex = min((uint32_t)TS::TX + 1, nx - x0);
+      for (uint32_t r = warp; r < ez * ey; r += HIER_WARPS) {
+        const uint32_t rz = r / ey, ry = r % ey;
+        const T *src = src0 + rz * sz + ry * sy;
+        T *dst = tile + (rz * TS::HY + ry) * TS::PX;
+        for (uint32_t x = lane; x < ex; x += 32)
+          dst[x] = src[x];
+      }
+      __syncthreads();
+      const uint32_t vz = min((uint32_t)TS::TZ, nz - z0),
+                     vy = min((uint32_t)TS::TY, ny - y0),
+                     vx = min((uint32_t)TS::TX, nx - x0);
+      const uint32_t cnt = vz * vy * vx;
+      for (uint32_t id = tid; id < cnt; id += HIER_THREADS) {
+        const uint32_t lx = id % vx, ly = (id / vx) % vy, lz = id / (vx * vy);
+        element_generic<T, HALF, TS>(u, tile, tables, a, x0 + lx, y0 + ly, z0 + lz,
+                                     x0, y0, z0, ex, ey, ez, sink);
+      }
     }
   }
+  // flush the register-held centre count, then the CTA histogram
+  uint32_t hits = sink.centre_hits;
+  for (int o = 16; o > 0; o >>= 1)
+    hits += __shfl_xor_sync(0xffffffffu, hits, o);
+  if (lane == 0 && hits)
+    atomicAdd(&s_hist[a.shift], hits);
   __syncthreads();
   for (uint32_t i = tid; i < a.dict; i += HIER_THREADS) {
     uint32_t v = s_hist[i];
     if (v)
       atomicAdd(&g_freq[i], v);
   }
+}
+
+typedef TileShape<3, 3, 6> Tile3D;  // 8 x 8 x 64
+typedef TileShape<0, 5, 7> Tile2D;  // 32 x 128
+typedef TileShape<0, 0, 10> Tile1D; // 1024
+
+template <typename T, bool HALF, class TS>
+int launch_forward(mgx_ctx *ctx, const void *d_in, HierArgs<T> &a) {
+  const int tdim[3] = {TS::TZ, TS::TY, TS::TX};
+  for (int d = 0; d < 3; d++)
+    a.tiles[d] = (a.n[d] + tdim[d] - 1) / tdim[d];
+  a.ntiles = (uint64_t)a.tiles[0] * a.tiles[1] * a.tiles[2];
+  size_t smem = sizeof(T) * TS::tile_elems + (size_t)ctx->dict * 4;
+  auto kern = k_hier_forward<T, HALF, TS>;
+  MGX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)smem));
+  int occ = 1;
+  MGX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, HIER_THREADS,
+                                                         smem));
+  unsigned grid = (unsigned)std::min<uint64_t>(
+      a.ntiles, (uint64_t)std::max(occ, 1) * ctx->num_sms);
+  kern<<<grid, HIER_THREADS, smem, ctx->stream>>>(
+      (const T *)d_in, ctx->d_sym, ctx->d_freq,
+      (unsigned long long *)(ctx->d_scalars + MGX_SC_OUTLIERS),
+      (unsigned long long *)ctx->d_out_idx, (long long *)ctx->d_out_val,
+      ctx->out_cap, (const T *)ctx->d_tables, a);
+  ctx->launches++;
+  MGX_CUDA(cudaGetLastError());
+  return MGX_SUCCESS;
+}
+
+template <typename T, bool HALF>
+int launch_forward_shape(mgx_ctx *ctx, const void *d_in, HierArgs<T> &a) {
+  if (a.n[0] > 1)
+    return launch_forward<T, HALF, Tile3D>(ctx, d_in, a);
+  if (a.n[1] > 1)
+    return launch_forward<T, HALF, Tile2D>(ctx, d_in, a);
+  return launch_forward<T, HALF, Tile1D>(ctx, d_in, a);
 }
 
 template <typename T>
@@ -230,18 +488,14 @@ int hier_forward_t(mgx_ctx *ctx, const void *d_in, int rel, double tol_d,
   const MgxHostTables<T> &tb = *reinterpret_cast<const MgxHostTables<T> *>(
       mgx_is_f32(ctx) ? (const void *)&ctx->tbf : (const void *)&ctx->tbd);
   HierArgs<T> a;
-  for (int d = 0; d < 3; d++) {
+  for (int d = 0; d < 3; d++)
     a.n[d] = (uint32_t)lv.shape[2 + d];
-    a.tiles[d] = (a.n[d] + (d == 0 ? TZ : d == 1 ? TY : TX) - 1) /
-                 (d == 0 ? TZ : d == 1 ? TY : TX);
-  }
   for (int l = 0; l <= lv.L; l++)
     for (int d = 0; d < 3; d++) {
       a.nl[l][d] = (uint32_t)lv.n[l][2 + d];
       a.roff[l][d] = tb.off.ratio[l][2 + d];
     }
   a.L = lv.L;
-  a.half = tb.ratios_half;
   // CalcQuantizers, LinearQuantization.hpp:234-261 (hierarchical branch)
   T tol = (T)tol_d, norm = (T)norm_d;
   double abs_tol = tol;
@@ -250,26 +504,10 @@ int hier_forward_t(mgx_ctx *ctx, const void *d_in, int rel, double tol_d,
   abs_tol *= 2;
   T qv = (T)((abs_tol) / (uint64_t)(lv.L + 1));
   a.qv = 1.0f / qv;
-  a.shift = (long long)(ctx->dict / 2);
+  a.shift = (int)(ctx->dict / 2);
   a.dict = ctx->dict;
-  a.ntiles = (uint64_t)a.tiles[0] * a.tiles[1] * a.tiles[2];
-  size_t smem = sizeof(T) * HZ * HY * HX + (size_t)ctx->dict * 4;
-  MGX_CUDA(cudaFuncSetAttribute(k_hier_forward<T>,
-                                cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)smem));
-  int occ = 1;
-  MGX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(
-      &occ, k_hier_forward<T>, HIER_THREADS, smem));
-  unsigned grid = (unsigned)std::min<uint64_t>(
-      a.ntiles, (uint64_t)std::max(occ, 1) * ctx->num_sms);
-  k_hier_forward<T><<<grid, HIER_THREADS, smem, ctx->stream>>>(
-      (const T *)d_in, ctx->d_sym, ctx->d_freq,
-      (unsigned long long *)(ctx->d_scalars + MGX_SC_OUTLIERS),
-      (unsigned long long *)ctx->d_out_idx, (long long *)ctx->d_out_val,
-      ctx->out_cap, (const T *)ctx->d_tables, a);
-  ctx->launches++;
-  MGX_CUDA(cudaGetLastError());
-  return MGX_SUCCESS;
+  return tb.ratios_half ? launch_forward_shape<T, true>(ctx, d_in, a)
+                        : launch_forward_shape<T, false>(ctx, d_in, a);
 }
 
 } // namespace
