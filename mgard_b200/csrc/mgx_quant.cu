@@ -7,6 +7,8 @@
 #include <cmath>
 #include <limits>
 
+#include <type_traits>
+
 #include "mgx_device.cuh"
 #include "mgx_internal.h"
 
@@ -19,15 +21,46 @@ namespace {
 template <typename T, bool LINF>
 __global__ void __launch_bounds__(512)
     k_norm(const T *__restrict__ v, uint64_t n, unsigned long long *out) {
+  // 16-byte loads, four in flight per thread; |max| of floats is exact in T,
+  // sums of squares accumulate in double
+  constexpr int VEC = 16 / sizeof(T);
+  typedef typename std::conditional<sizeof(T) == 4, float4, double2>::type V;
   double acc = 0.0;
-  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n;
-       i += (uint64_t)gridDim.x * blockDim.x) {
-    double x = (double)v[i];
-    if (LINF)
-      acc = fmax(acc, fabs(x));
-    else
-      acc += x * x;
+  T tmax = 0;
+  const uint64_t nvec = (((uintptr_t)v & 15) == 0) ? n / VEC : 0;
+  const V *vv = reinterpret_cast<const V *>(v);
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+  auto take = [&](const V &q) {
+    const T *e = reinterpret_cast<const T *>(&q);
+#pragma unroll
+    for (int k = 0; k < VEC; k++) {
+      if (LINF)
+        tmax = fmax(tmax, fabs(e[k]));
+      else
+        acc += (double)e[k] * (double)e[k];
+    }
+  };
+  for (; i + 3 * stride < nvec; i += 4 * stride) {
+    const V a = vv[i], b = vv[i + stride], c = vv[i + 2 * stride],
+            d = vv[i + 3 * stride];
+    take(a);
+    take(b);
+    take(c);
+    take(d);
   }
+  for (; i < nvec; i += stride)
+    take(vv[i]);
+  for (uint64_t j = nvec * VEC + blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+       j < n; j += stride) {
+    const T x = v[j];
+    if (LINF)
+      tmax = fmax(tmax, fabs(x));
+    else
+      acc += (double)x * (double)x;
+  }
+  if (LINF)
+    acc = (double)tmax;
   for (int o = 16; o > 0; o >>= 1) {
     double other = __shfl_xor_sync(0xffffffffu, acc, o);
     acc = LINF ? fmax(acc, other) : acc + other;
