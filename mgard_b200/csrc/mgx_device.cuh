@@ -18,8 +18,9 @@ __device__ __forceinline__ double div_rn(double a, double b) { return __ddiv_rn(
 
 // lerp, reference Coefficient/GPKFunctor.h:13-25 (non-FMA branch):
 //   r = v0 + v0 * t * -1;  r = r + t * v1;
+// (x * -1 is an exact negation, so v0 + (v0*t)*-1 == v0 - v0*t bit for bit.)
 template <typename T> __device__ __forceinline__ T mgx_lerp(T v0, T v1, T t) {
-  T r = add_rn(v0, mul_rn(mul_rn(v0, t), (T)-1));
+  T r = sub_rn(v0, mul_rn(v0, t));
   return add_rn(r, mul_rn(t, v1));
 }
 

@@ -32,6 +32,7 @@
 #include <algorithm>
 #include <cmath>
 #include <limits>
+#include <type_traits>
 
 #include "mgx_device.cuh"
 #include "mgx_internal.h"
@@ -148,23 +149,24 @@ template <typename T> struct Sink {
   uint32_t centre_hits; // symbols equal to dict/2 are counted in a register
 
   __device__ __forceinline__ void put(T c, uint64_t opos) {
+    put_at(c, sym + opos, sym);
+  }
+  // (int) conversion saturates, so anything that does not fit an int lands
+  // outside [0, dict) after the shift and is redone in 64 bits below.
+  __device__ __forceinline__ void put_at(T c, uint16_t *dst, uint16_t *base) {
     const T r = add_rn((T)0.5, fabs(mul_rn(c, qv)));
-    uint32_t sv;
-    if (r < (T)1.0e9) {
-      int q = (int)r;
-      q = (c < (T)0 ? -q : q) + shift;
-      sv = (uint32_t)q;
-      if (sv >= dict) { // q < 0 wraps to a huge unsigned value
-        outlier(opos, (long long)q);
-        sv = 0;
-      }
-    } else {
+    uint32_t sv = (uint32_t)((int)copysign(r, c) + shift);
+    if (sv >= dict) {
       long long q = (long long)r;
       q = (c < (T)0 ? -q : q) + (long long)shift;
-      outlier(opos, q);
-      sv = 0;
+      if (q < 0 || q >= (long long)dict) {
+        outlier((uint64_t)(dst - base), q);
+        sv = 0;
+      } else {
+        sv = (uint32_t)q;
+      }
     }
-    sym[opos] = (uint16_t)sv;
+    *dst = (uint16_t)sv;
     if (sv == (uint32_t)shift)
       centre_hits++;
     else
@@ -313,12 +315,131 @@ tile_pass(const T *tile, const T *__restrict__ tables, const HierArgs<T> &a,
   }
 }
 
+// Pass 0 (stride 1, the finest level: 7/8 of all nodes in 3-D) as a march
+// along z.  A thread owns one (even, odd) x pair and one (even, odd) y pair of
+// rows and walks the z planes of its half of the tile.  On an even plane Z it
+// forms, from the two even rows y = 2a, 2a+2,
+//     f0 = lerp_x(u[2k], u[2k+2]) on row 2a      gE = lerp_y(u[2k] rows)
+//     f2 = ... on row 2a+2                        gO = lerp_y(f0, f2)
+// which are the interpolants of the three coefficients of that plane; the four
+// coefficients of the odd plane Z+1 interpolate {u[2k], f0, gE, gO} of planes Z
+// and Z+2 along z.  Same operations in the same order (x, then y, then z) as
+// the per-element gather, with a third of the shared-memory loads and half of
+// the lerps, and every address a compile-time offset from one base pointer.
+template <typename T> struct PlaneP {
+  T e0, f0, gE, gO;
+};
+
+template <typename T, bool HALF, class TS>
+__device__ __forceinline__ void
+pass0_march3d(const T *tile, const T *__restrict__ tables, const HierArgs<T> &a,
+              uint32_t x0, uint32_t y0, uint32_t z0, Sink<T> &sink) {
+  static_assert(TS::TX == 64 && TS::TY == 8 && TS::TZ == 8 && HIER_THREADS == 256,
+                "thread mapping below assumes an 8 x 8 x 64 tile");
+  constexpr int SY = TS::PX, SZ = TS::HY * TS::PX;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int ya = warp & 3, zh = warp >> 2; // y pair, z half
+  const int l = a.L;
+  const uint64_t sy = a.n[2], sz = (uint64_t)a.n[2] * a.n[1];
+  const uint64_t oX = a.nl[l - 1][2], oY = (uint64_t)a.nl[l - 1][1] * sy,
+                 oZ = (uint64_t)a.nl[l - 1][0] * sz;
+  T tx = (T)0.5, ty = (T)0.5;
+  if (!HALF) {
+    tx = tables[a.roff[l][2] + x0 + 2 * lane];
+    ty = tables[a.roff[l][1] + y0 + 2 * ya];
+  }
+  const T *p = tile + (4 * zh) * SZ + (2 * ya) * SY + 2 * lane;
+  uint16_t *o = sink.sym + ((uint64_t)((z0 >> 1) + 2 * zh) * sz +
+                            (uint64_t)((y0 >> 1) + ya) * sy + (x0 >> 1) + lane);
+  typedef typename std::conditional<sizeof(T) == 4, float2, double2>::type V2;
+  auto plane = [&](const T *q, PlaneP<T> &P, T &o0) {
+    const V2 own = *reinterpret_cast<const V2 *>(q);
+    const T r0 = q[2], e2 = q[2 * SY], r2 = q[2 * SY + 2];
+    P.e0 = own.x;
+    o0 = own.y;
+    P.f0 = mgx_lerp(own.x, r0, tx);
+    const T f2 = mgx_lerp(e2, r2, tx);
+    P.gE = mgx_lerp(own.x, e2, ty);
+    P.gO = mgx_lerp(P.f0, f2, ty);
+  };
+  PlaneP<T> A, B;
+  T oA, oB;
+  plane(p, A, oA);
+#pragma unroll
+  for (int b = 0; b < 2; b++) {
+    const T *q = p + (2 * b) * SZ;
+    uint16_t *ob = o + (uint64_t)b * sz;
+    // even plane Z = 4 zh + 2 b: rows 2a (odd x only) and 2a + 1
+    const V2 r1 = *reinterpret_cast<const V2 *>(q + SY);
+    sink.put_at(sub_rn(oA, A.f0), ob + oX, sink.sym);
+    sink.put_at(sub_rn(r1.x, A.gE), ob + oY, sink.sym);
+    sink.put_at(sub_rn(r1.y, A.gO), ob + oX + oY, sink.sym);
+    // odd plane Z + 1 between A = P(Z) and B = P(Z + 2)
+    plane(q + 2 * SZ, B, oB);
+    T tz = (T)0.5;
+    if (!HALF)
+      tz = tables[a.roff[l][0] + z0 + 4 * zh + 2 * b];
+    const V2 s0 = *reinterpret_cast<const V2 *>(q + SZ);
+    const V2 s1 = *reinterpret_cast<const V2 *>(q + SZ + SY);
+    sink.put_at(sub_rn(s0.x, mgx_lerp(A.e0, B.e0, tz)), ob + oZ, sink.sym);
+    sink.put_at(sub_rn(s0.y, mgx_lerp(A.f0, B.f0, tz)), ob + oZ + oX, sink.sym);
+    sink.put_at(sub_rn(s1.x, mgx_lerp(A.gE, B.gE, tz)), ob + oZ + oY, sink.sym);
+    sink.put_at(sub_rn(s1.y, mgx_lerp(A.gO, B.gO, tz)), ob + oZ + oX + oY, sink.sym);
+    A = B;
+    oA = oB;
+  }
+}
+
+// 2-D analogue: march along y; even rows carry {u[2k], f}, odd rows interpolate
+// them along y.
+template <typename T, bool HALF, class TS>
+__device__ __forceinline__ void
+pass0_march2d(const T *tile, const T *__restrict__ tables, const HierArgs<T> &a,
+              uint32_t x0, uint32_t y0, Sink<T> &sink) {
+  static_assert(TS::TX == 128 && TS::TY == 32 && !TS::RZ && HIER_THREADS == 256,
+                "thread mapping below assumes a 32 x 128 tile");
+  constexpr int SY = TS::PX;
+  const int k = threadIdx.x & 63, yq = threadIdx.x >> 6; // x pair, y quarter
+  const int l = a.L;
+  const uint64_t sy = a.n[2];
+  const uint64_t oX = a.nl[l - 1][2], oY = (uint64_t)a.nl[l - 1][1] * sy;
+  T tx = (T)0.5;
+  if (!HALF)
+    tx = tables[a.roff[l][2] + x0 + 2 * k];
+  const T *p = tile + (8 * yq) * SY + 2 * k;
+  uint16_t *o = sink.sym + ((uint64_t)((y0 >> 1) + 4 * yq) * sy + (x0 >> 1) + k);
+  typedef typename std::conditional<sizeof(T) == 4, float2, double2>::type V2;
+  V2 ownA = *reinterpret_cast<const V2 *>(p);
+  T fA = mgx_lerp(ownA.x, p[2], tx);
+#pragma unroll
+  for (int b = 0; b < 4; b++) {
+    const T *q = p + (2 * b) * SY;
+    uint16_t *ob = o + (uint64_t)b * sy;
+    sink.put_at(sub_rn(ownA.y, fA), ob + oX, sink.sym);
+    const V2 ownB = *reinterpret_cast<const V2 *>(q + 2 * SY);
+    const T fB = mgx_lerp(ownB.x, q[2 * SY + 2], tx);
+    T ty = (T)0.5;
+    if (!HALF)
+      ty = tables[a.roff[l][1] + y0 + 8 * yq + 2 * b];
+    const V2 s = *reinterpret_cast<const V2 *>(q + SY);
+    sink.put_at(sub_rn(s.x, mgx_lerp(ownA.x, ownB.x, ty)), ob + oY, sink.sym);
+    sink.put_at(sub_rn(s.y, mgx_lerp(fA, fB, ty)), ob + oY + oX, sink.sym);
+    ownA = ownB;
+    fA = fB;
+  }
+}
+
 template <typename T, bool HALF, class TS, int P>
 __device__ __forceinline__ void
 run_passes(const T *tile, const T *__restrict__ tables, const HierArgs<T> &a,
            uint32_t x0, uint32_t y0, uint32_t z0, Sink<T> &sink) {
   if constexpr (P < TS::PASSES) {
-    tile_pass<T, HALF, TS, P>(tile, tables, a, x0, y0, z0, sink);
+    if constexpr (P == 0 && TS::RZ)
+      pass0_march3d<T, HALF, TS>(tile, tables, a, x0, y0, z0, sink);
+    else if constexpr (P == 0 && TS::RY)
+      pass0_march2d<T, HALF, TS>(tile, tables, a, x0, y0, sink);
+    else
+      tile_pass<T, HALF, TS, P>(tile, tables, a, x0, y0, z0, sink);
     run_passes<T, HALF, TS, P + 1>(tile, tables, a, x0, y0, z0, sink);
   }
 }
