@@ -444,6 +444,21 @@ run_passes(const T *tile, const T *__restrict__ tables, const HierArgs<T> &a,
   }
 }
 
+// 4- or 8-byte asynchronous global -> shared copy (LDGSTS); rows of a 2^k+1
+// grid are only element-aligned, so wider copies / TMA boxes are not possible.
+template <typename T>
+__device__ __forceinline__ void cp_async_elem(T *smem_dst, const T *gsrc) {
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], %2;\n" ::"r"(d), "l"(gsrc),
+               "n"(sizeof(T)));
+}
+__device__ __forceinline__ void cp_async_commit() {
+  asm volatile("cp.async.commit_group;\n" ::);
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+  asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+}
+
 template <typename T, bool HALF, class TS>
 __global__ void __launch_bounds__(HIER_THREADS)
     k_hier_forward(const T *__restrict__ u, uint16_t *__restrict__ sym,
@@ -454,8 +469,8 @@ __global__ void __launch_bounds__(HIER_THREADS)
                    const T *__restrict__ tables,
                    const __grid_constant__ HierArgs<T> a) {
   extern __shared__ __align__(16) unsigned char smem[];
-  T *tile = (T *)smem;
-  uint32_t *s_hist = (uint32_t *)(smem + sizeof(T) * TS::tile_elems);
+  T *const buf0 = (T *)smem;
+  uint32_t *s_hist = (uint32_t *)(smem + 2 * sizeof(T) * TS::tile_elems);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   for (uint32_t i = tid; i < a.dict; i += HIER_THREADS)
     s_hist[i] = 0;
@@ -464,57 +479,65 @@ __global__ void __launch_bounds__(HIER_THREADS)
   Sink<T> sink{sym, s_hist, out_count, out_idx, out_val, out_cap,
                a.qv, a.shift, a.dict, 0u};
 
-  for (uint64_t t = blockIdx.x; t < a.ntiles; t += gridDim.x) {
-    const uint32_t tx = (uint32_t)(t % a.tiles[2]);
-    const uint32_t ty = (uint32_t)((t / a.tiles[2]) % a.tiles[1]);
-    const uint32_t tzz = (uint32_t)(t / ((uint64_t)a.tiles[2] * a.tiles[1]));
-    const uint32_t z0 = tzz * TS::TZ, y0 = ty * TS::TY, x0 = tx * TS::TX;
+  // tile walk t = blockIdx.x + i * gridDim.x, kept as mixed-radix digits
+  const uint32_t T2 = a.tiles[2], T1 = a.tiles[1], T0 = a.tiles[0];
+  uint32_t cx = blockIdx.x % T2, cy = (blockIdx.x / T2) % T1,
+           cz = blockIdx.x / (T2 * T1);
+  const uint32_t dx = gridDim.x % T2, dy = (gridDim.x / T2) % T1,
+                 dz = gridDim.x / (T2 * T1);
+
+  // stage the (TZ+1) x (TY+1) x (TX+1) box of a tile (clipped to the grid):
+  // one warp per row, element-wide asynchronous copies
+  auto issue = [&](T *buf, uint32_t tx, uint32_t ty, uint32_t tz) {
+    const uint32_t z0 = tz * TS::TZ, y0 = ty * TS::TY, x0 = tx * TS::TX;
+    const uint32_t ez = min((uint32_t)TS::HZ, nz - z0),
+                   ey = min((uint32_t)TS::HY, ny - y0),
+                   ex = min((uint32_t)TS::TX + 1, nx - x0);
+    const T *src0 = u + (uint64_t)z0 * sz + (uint64_t)y0 * sy + x0;
+    constexpr int RPW = (TS::ROWS + HIER_WARPS - 1) / HIER_WARPS;
+#pragma unroll 4
+    for (int i = 0; i < RPW; i++) {
+      const uint32_t r = warp + i * HIER_WARPS;
+      const uint32_t rz = r / TS::HY, ry = r - rz * TS::HY;
+      if (r < (uint32_t)TS::ROWS && rz < ez && ry < ey) {
+        const T *src = src0 + rz * sz + ry * sy;
+        T *dst = buf + r * TS::PX;
+#pragma unroll
+        for (uint32_t x = lane; x < (uint32_t)TS::TX + 1; x += 32)
+          if (x < ex)
+            cp_async_elem(dst + x, src + x);
+      }
+    }
+    cp_async_commit();
+  };
+
+  bool have = cz < T0;
+  if (have)
+    issue(buf0, cx, cy, cz);
+  for (int it = 0; have; it ^= 1) {
+    // next tile of this CTA
+    uint32_t nx_ = cx + dx, ny_ = cy + dy, nz_ = cz + dz;
+    if (nx_ >= T2) {
+      nx_ -= T2;
+      ++ny_;
+    }
+    if (ny_ >= T1) {
+      ny_ -= T1;
+      ++nz_;
+    }
+    const bool have_next = nz_ < T0;
+    cp_async_wait_all();
+    __syncthreads(); // tile `it` landed; tile `it ^ 1` fully consumed
+    if (have_next)
+      issue(buf0 + (it ^ 1) * TS::tile_elems, nx_, ny_, nz_);
+    const T *tile = buf0 + it * TS::tile_elems;
+    const uint32_t z0 = cz * TS::TZ, y0 = cy * TS::TY, x0 = cx * TS::TX;
     // interior tile: the +1 halo exists on every real axis and no node of the
     // tile is the last node of its axis
     const bool regular = a.L >= TS::PASSES && x0 + TS::TX <= nx - 1 &&
                          (!TS::RY || y0 + TS::TY <= ny - 1) &&
                          (!TS::RZ || z0 + TS::TZ <= nz - 1);
-    const T *src0 = u + (uint64_t)z0 * sz + (uint64_t)y0 * sy + x0;
-    __syncthreads(); // previous tile fully consumed (also orders the hist init)
     if (regular) {
-      // stage ROWS rows of TX + 1 nodes: one warp per row, all loads of a
-      // thread issued before the first shared store
-      constexpr int RPW = (TS::ROWS + HIER_WARPS - 1) / HIER_WARPS;
-      constexpr int XPL = TS::TX / 32;
-      if constexpr (TS::ROWS >= HIER_WARPS && RPW * XPL <= 32) {
-        T v[RPW][XPL];
-#pragma unroll
-        for (int i = 0; i < RPW; i++) {
-          const int r = warp + i * HIER_WARPS;
-          const int rz = r / TS::HY, ry = r - rz * TS::HY;
-          const T *src = src0 + rz * sz + ry * sy;
-#pragma unroll
-          for (int j = 0; j < XPL; j++)
-            if (r < TS::ROWS)
-              v[i][j] = src[lane + 32 * j];
-        }
-#pragma unroll
-        for (int i = 0; i < RPW; i++) {
-          const int r = warp + i * HIER_WARPS;
-#pragma unroll
-          for (int j = 0; j < XPL; j++)
-            if (r < TS::ROWS)
-              tile[r * TS::PX + lane + 32 * j] = v[i][j];
-        }
-      } else {
-        for (int r = 0; r < TS::ROWS; r++) {
-          const int rz = r / TS::HY, ry = r - rz * TS::HY;
-          const T *src = src0 + rz * sz + ry * sy;
-#pragma unroll 4
-          for (int x = tid; x < TS::TX; x += HIER_THREADS)
-            tile[r * TS::PX + x] = src[x];
-        }
-      }
-      for (int r = tid; r < TS::ROWS; r += HIER_THREADS) { // halo column
-        const int rz = r / TS::HY, ry = r - rz * TS::HY;
-        tile[r * TS::PX + TS::TX] = src0[rz * sz + ry * sy + TS::TX];
-      }
-      __syncthreads();
       run_passes<T, HALF, TS, 0>(tile, tables, a, x0, y0, z0, sink);
       // nodes that are multiples of 2^PASSES on every axis: coarser levels
       constexpr int CX = TS::TX >> TS::PASSES,
@@ -531,14 +554,6 @@ __global__ void __launch_bounds__(HIER_THREADS)
       const uint32_t ez = min((uint32_t)TS::HZ, nz - z0),
                      ey = min((uint32_t)TS::HY, ny - y0),
                      ex = min((uint32_t)TS::TX + 1, nx - x0);
-      for (uint32_t r = warp; r < ez * ey; r += HIER_WARPS) {
-        const uint32_t rz = r / ey, ry = r % ey;
-        const T *src = src0 + rz * sz + ry * sy;
-        T *dst = tile + (rz * TS::HY + ry) * TS::PX;
-        for (uint32_t x = lane; x < ex; x += 32)
-          dst[x] = src[x];
-      }
-      __syncthreads();
       const uint32_t vz = min((uint32_t)TS::TZ, nz - z0),
                      vy = min((uint32_t)TS::TY, ny - y0),
                      vx = min((uint32_t)TS::TX, nx - x0);
@@ -549,6 +564,10 @@ __global__ void __launch_bounds__(HIER_THREADS)
                                      x0, y0, z0, ex, ey, ez, sink);
       }
     }
+    cx = nx_;
+    cy = ny_;
+    cz = nz_;
+    have = have_next;
   }
   // flush the register-held centre count, then the CTA histogram
   uint32_t hits = sink.centre_hits;
@@ -574,7 +593,7 @@ int launch_forward(mgx_ctx *ctx, const void *d_in, HierArgs<T> &a) {
   for (int d = 0; d < 3; d++)
     a.tiles[d] = (a.n[d] + tdim[d] - 1) / tdim[d];
   a.ntiles = (uint64_t)a.tiles[0] * a.tiles[1] * a.tiles[2];
-  size_t smem = sizeof(T) * TS::tile_elems + (size_t)ctx->dict * 4;
+  size_t smem = 2 * sizeof(T) * TS::tile_elems + (size_t)ctx->dict * 4;
   auto kern = k_hier_forward<T, HALF, TS>;
   MGX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)smem));
