@@ -52,6 +52,12 @@ template <typename T> struct HierArgs {
   uint32_t dict;
   uint32_t tiles[3];
   uint64_t ntiles;
+  uint64_t oct[8][3];            // pass p: byte offsets of the odd x / y / z blocks
+  uint16_t *sym;                 // output symbols (reordered layout)
+  unsigned long long *out_count; // outlier list
+  unsigned long long *out_idx;
+  long long *out_val;
+  unsigned long long out_cap;
 };
 
 // Tile geometry: 2^LZ x 2^LY x 2^LX nodes; an axis with extent 1 is "flat"
@@ -123,57 +129,75 @@ __device__ __forceinline__ uint32_t final_pos(const AxisInfo &a, uint32_t i,
   return i >> (L - l + 1);
 }
 
-__device__ __noinline__ void hier_outlier(unsigned long long *out_count,
-                                          unsigned long long *out_idx,
-                                          long long *out_val,
-                                          unsigned long long out_cap,
-                                          uint64_t opos, long long q) {
-  unsigned long long slot = atomicAdd(out_count, 1ull);
-  if (slot < out_cap) {
-    out_idx[slot] = opos;
-    out_val[slot] = q;
+// Rare path of the quantiser: the int conversion saturated or the symbol is
+// outside the dictionary.  Redo it in 64 bits and, if it really is an outlier,
+// append (position, value) to the list and return symbol 0
+// (OutlierSeparator.hpp:17-44).
+template <typename T>
+__device__ __noinline__ uint32_t hier_slow_symbol(T c, T r, const HierArgs<T> &a,
+                                                  uint64_t opos) {
+  long long q = (long long)r;
+  q = (c < (T)0 ? -q : q) + (long long)a.shift;
+  if (q >= 0 && q < (long long)a.dict)
+    return (uint32_t)q;
+  unsigned long long slot = atomicAdd(a.out_count, 1ull);
+  if (slot < a.out_cap) {
+    a.out_idx[slot] = opos;
+    a.out_val[slot] = q;
   }
+  return 0;
 }
 
 // Per-thread sink: quantise (lwqzk, LinearQuantization.hpp:96-111), separate
-// outliers (OutlierSeparator.hpp:17-44), count the symbol, store it.
+// outliers, count the symbol, store it.  Symbols equal to dict/2 (a zero
+// coefficient, by far the most frequent one on smooth data) are counted in a
+// register, everything else with a shared-memory reduction.
 template <typename T> struct Sink {
-  uint16_t *sym;
-  uint32_t *s_hist;
-  unsigned long long *out_count, *out_idx;
-  long long *out_val;
-  unsigned long long out_cap;
-  T qv;
-  int shift;
-  uint32_t dict;
-  uint32_t centre_hits; // symbols equal to dict/2 are counted in a register
+  const HierArgs<T> &a;
+  uint32_t hist_saddr; // shared-window address of the CTA histogram
 
-  __device__ __forceinline__ void put(T c, uint64_t opos) {
-    put_at(c, sym + opos, sym);
+  // candidate symbol; the (int) conversion saturates, so anything that does
+  // not fit an int lands outside [0, dict) after the shift
+  __device__ __forceinline__ uint32_t quant(T c) const {
+    const T r = add_rn((T)0.5, fabs(mul_rn(c, a.qv)));
+    return (uint32_t)((int)copysign(r, c) + a.shift);
   }
-  // (int) conversion saturates, so anything that does not fit an int lands
-  // outside [0, dict) after the shift and is redone in 64 bits below.
-  __device__ __forceinline__ void put_at(T c, uint16_t *dst, uint16_t *base) {
-    const T r = add_rn((T)0.5, fabs(mul_rn(c, qv)));
-    uint32_t sv = (uint32_t)((int)copysign(r, c) + shift);
-    if (sv >= dict) {
-      long long q = (long long)r;
-      q = (c < (T)0 ? -q : q) + (long long)shift;
-      if (q < 0 || q >= (long long)dict) {
-        outlier((uint64_t)(dst - base), q);
-        sv = 0;
-      } else {
-        sv = (uint32_t)q;
-      }
+  __device__ __forceinline__ uint32_t fix(uint32_t sv, T c, uint16_t *dst) const {
+    if (sv >= a.dict) {
+      const T r = add_rn((T)0.5, fabs(mul_rn(c, a.qv)));
+      sv = hier_slow_symbol<T>(c, r, a, (uint64_t)(dst - a.sym));
     }
-    *dst = (uint16_t)sv;
-    if (sv == (uint32_t)shift)
-      centre_hits++;
-    else
-      atomicAdd(&s_hist[sv], 1u);
+    return sv;
   }
-  __device__ __forceinline__ void outlier(uint64_t opos, long long q) {
-    hier_outlier(out_count, out_idx, out_val, out_cap, opos, q);
+  // store + count (ATOMS.POPC.INC merges lanes that hit the same bin)
+  __device__ __forceinline__ void store(uint32_t sv, uint16_t *dst) const {
+    *dst = (uint16_t)sv;
+    asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(hist_saddr + sv * 4u));
+  }
+  __device__ __forceinline__ void put_at(T c, uint16_t *dst) const {
+    store(fix(quant(c), c, dst), dst);
+  }
+  __device__ __forceinline__ void put(T c, uint64_t opos) const {
+    put_at(c, a.sym + opos);
+  }
+  // N coefficients at once: one range test for the whole group
+  template <int N>
+  __device__ __forceinline__ void put_group(const T (&c)[N],
+                                            uint16_t *const (&dst)[N]) const {
+    uint32_t sv[N], worst = 0;
+#pragma unroll
+    for (int i = 0; i < N; i++) {
+      sv[i] = quant(c[i]);
+      worst = max(worst, sv[i]);
+    }
+    if (__builtin_expect(worst >= a.dict, 0)) {
+#pragma unroll
+      for (int i = 0; i < N; i++)
+        sv[i] = fix(sv[i], c[i], dst[i]);
+    }
+#pragma unroll
+    for (int i = 0; i < N; i++)
+      store(sv[i], dst[i]);
   }
 };
 
@@ -184,7 +208,7 @@ __device__ __forceinline__ void
 element_generic(const T *__restrict__ u, const T *tile, const T *__restrict__ tables,
                 const HierArgs<T> &a, uint32_t gx, uint32_t gy, uint32_t gz,
                 uint32_t x0, uint32_t y0, uint32_t z0, uint32_t ex, uint32_t ey,
-                uint32_t ez, Sink<T> &sink) {
+                uint32_t ez, const Sink<T> &sink) {
   const uint32_t nz = a.n[0], ny = a.n[1], nx = a.n[2];
   const uint64_t sy = nx, sz = (uint64_t)nx * ny;
   const uint32_t *nl = &a.nl[0][0];
@@ -252,7 +276,7 @@ element_generic(const T *__restrict__ u, const T *tile, const T *__restrict__ ta
 template <typename T, bool HALF, class TS, int P>
 __device__ __forceinline__ void
 tile_pass(const T *tile, const T *__restrict__ tables, const HierArgs<T> &a,
-          uint32_t x0, uint32_t y0, uint32_t z0, Sink<T> &sink) {
+          uint32_t x0, uint32_t y0, uint32_t z0, const Sink<T> &sink) {
   constexpr int H = 1 << P;
   constexpr int PPR_SH = TS::LX - P - 1;               // pairs per row
   constexpr int RY_SH = TS::RY ? TS::LY - P : 0;       // sub-rows along y
@@ -330,61 +354,92 @@ template <typename T> struct PlaneP {
   T e0, f0, gE, gO;
 };
 
-template <typename T, bool HALF, class TS>
+__device__ __forceinline__ uint16_t *byte_off(uint16_t *p, uint64_t bytes) {
+  return (uint16_t *)((char *)p + bytes);
+}
+
+// The same schedule serves every in-tile stride H = 2^P on the sub-grid of
+// multiples of H (fewer threads are busy in the coarser passes).
+template <typename T, bool HALF, class TS, int P>
 __device__ __forceinline__ void
-pass0_march3d(const T *tile, const T *__restrict__ tables, const HierArgs<T> &a,
-              uint32_t x0, uint32_t y0, uint32_t z0, Sink<T> &sink) {
+march3d(const T *tile, const T *__restrict__ tables, const HierArgs<T> &a,
+        uint32_t x0, uint32_t y0, uint32_t z0, const Sink<T> &sink) {
   static_assert(TS::TX == 64 && TS::TY == 8 && TS::TZ == 8 && HIER_THREADS == 256,
                 "thread mapping below assumes an 8 x 8 x 64 tile");
-  constexpr int SY = TS::PX, SZ = TS::HY * TS::PX;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int ya = warp & 3, zh = warp >> 2; // y pair, z half
-  const int l = a.L;
+  constexpr int H = 1 << P;
+  constexpr int SX = H, SY = H * TS::PX, SZ = H * TS::HY * TS::PX;
+  constexpr int NK = 32 >> P, NA = 4 >> P, NB = 4 >> P; // x pairs, y pairs, z pairs
+  constexpr int BPT = P == 0 ? 2 : 1;                   // z pairs per thread
+  constexpr int ACTIVE = NK * NA * NB / BPT;
+  // coarser passes run on their own warps so that no warp carries them all
+  constexpr int FIRST = P == 0 ? 0 : P == 1 ? 64 : 128;
+  const int tid = (int)threadIdx.x - FIRST;
+  if (ACTIVE < HIER_THREADS && (tid < 0 || tid >= ACTIVE))
+    return;
+  const int k = tid % NK, ya = (tid / NK) % NA, zb = (tid / (NK * NA)) * BPT;
+  const int l = a.L - P;
   const uint64_t sy = a.n[2], sz = (uint64_t)a.n[2] * a.n[1];
-  const uint64_t oX = a.nl[l - 1][2], oY = (uint64_t)a.nl[l - 1][1] * sy,
-                 oZ = (uint64_t)a.nl[l - 1][0] * sz;
+  const uint64_t oX = a.oct[P][0], oY = a.oct[P][1], oZ = a.oct[P][2];
   T tx = (T)0.5, ty = (T)0.5;
   if (!HALF) {
-    tx = tables[a.roff[l][2] + x0 + 2 * lane];
-    ty = tables[a.roff[l][1] + y0 + 2 * ya];
+    tx = tables[a.roff[l][2] + (x0 >> P) + 2 * k];
+    ty = tables[a.roff[l][1] + (y0 >> P) + 2 * ya];
   }
-  const T *p = tile + (4 * zh) * SZ + (2 * ya) * SY + 2 * lane;
-  uint16_t *o = sink.sym + ((uint64_t)((z0 >> 1) + 2 * zh) * sz +
-                            (uint64_t)((y0 >> 1) + ya) * sy + (x0 >> 1) + lane);
+  const T *p = tile + (2 * zb) * SZ + (2 * ya) * SY + (2 * k) * SX;
+  uint16_t *o = a.sym + ((uint64_t)((z0 >> (P + 1)) + zb) * sz +
+                         (uint64_t)((y0 >> (P + 1)) + ya) * sy + (x0 >> (P + 1)) + k);
   typedef typename std::conditional<sizeof(T) == 4, float2, double2>::type V2;
-  auto plane = [&](const T *q, PlaneP<T> &P, T &o0) {
-    const V2 own = *reinterpret_cast<const V2 *>(q);
-    const T r0 = q[2], e2 = q[2 * SY], r2 = q[2 * SY + 2];
-    P.e0 = own.x;
+  auto pair = [&](const T *q) -> V2 { // (even, odd) x nodes of a row
+    if constexpr (P == 0) {
+      return *reinterpret_cast<const V2 *>(q);
+    } else {
+      V2 v;
+      v.x = q[0];
+      v.y = q[SX];
+      return v;
+    }
+  };
+  auto plane = [&](const T *q, PlaneP<T> &Q, T &o0) {
+    const V2 own = pair(q);
+    const T r0 = q[2 * SX], e2 = q[2 * SY], r2 = q[2 * SY + 2 * SX];
+    Q.e0 = own.x;
     o0 = own.y;
-    P.f0 = mgx_lerp(own.x, r0, tx);
+    Q.f0 = mgx_lerp(own.x, r0, tx);
     const T f2 = mgx_lerp(e2, r2, tx);
-    P.gE = mgx_lerp(own.x, e2, ty);
-    P.gO = mgx_lerp(P.f0, f2, ty);
+    Q.gE = mgx_lerp(own.x, e2, ty);
+    Q.gO = mgx_lerp(Q.f0, f2, ty);
   };
   PlaneP<T> A, B;
   T oA, oB;
   plane(p, A, oA);
 #pragma unroll
-  for (int b = 0; b < 2; b++) {
+  for (int b = 0; b < BPT; b++) {
     const T *q = p + (2 * b) * SZ;
     uint16_t *ob = o + (uint64_t)b * sz;
-    // even plane Z = 4 zh + 2 b: rows 2a (odd x only) and 2a + 1
-    const V2 r1 = *reinterpret_cast<const V2 *>(q + SY);
-    sink.put_at(sub_rn(oA, A.f0), ob + oX, sink.sym);
-    sink.put_at(sub_rn(r1.x, A.gE), ob + oY, sink.sym);
-    sink.put_at(sub_rn(r1.y, A.gO), ob + oX + oY, sink.sym);
-    // odd plane Z + 1 between A = P(Z) and B = P(Z + 2)
+    const V2 r1 = pair(q + SY);
     plane(q + 2 * SZ, B, oB);
     T tz = (T)0.5;
     if (!HALF)
-      tz = tables[a.roff[l][0] + z0 + 4 * zh + 2 * b];
-    const V2 s0 = *reinterpret_cast<const V2 *>(q + SZ);
-    const V2 s1 = *reinterpret_cast<const V2 *>(q + SZ + SY);
-    sink.put_at(sub_rn(s0.x, mgx_lerp(A.e0, B.e0, tz)), ob + oZ, sink.sym);
-    sink.put_at(sub_rn(s0.y, mgx_lerp(A.f0, B.f0, tz)), ob + oZ + oX, sink.sym);
-    sink.put_at(sub_rn(s1.x, mgx_lerp(A.gE, B.gE, tz)), ob + oZ + oY, sink.sym);
-    sink.put_at(sub_rn(s1.y, mgx_lerp(A.gO, B.gO, tz)), ob + oZ + oX + oY, sink.sym);
+      tz = tables[a.roff[l][0] + (z0 >> P) + 2 * (zb + b)];
+    const V2 s0 = pair(q + SZ);
+    const V2 s1 = pair(q + SZ + SY);
+    // even plane: rows 2a (odd x only) and 2a + 1; odd plane between
+    // A = P(Z) and B = P(Z + 2H): all four nodes
+    const T c[7] = {sub_rn(oA, A.f0),
+                    sub_rn(r1.x, A.gE),
+                    sub_rn(r1.y, A.gO),
+                    sub_rn(s0.x, mgx_lerp(A.e0, B.e0, tz)),
+                    sub_rn(s0.y, mgx_lerp(A.f0, B.f0, tz)),
+                    sub_rn(s1.x, mgx_lerp(A.gE, B.gE, tz)),
+                    sub_rn(s1.y, mgx_lerp(A.gO, B.gO, tz))};
+    uint16_t *const dst[7] = {byte_off(ob, oX),
+                              byte_off(ob, oY),
+                              byte_off(ob, oX + oY),
+                              byte_off(ob, oZ),
+                              byte_off(ob, oZ + oX),
+                              byte_off(ob, oZ + oY),
+                              byte_off(ob, oZ + oX + oY)};
+    sink.template put_group<7>(c, dst);
     A = B;
     oA = oB;
   }
@@ -395,19 +450,19 @@ pass0_march3d(const T *tile, const T *__restrict__ tables, const HierArgs<T> &a,
 template <typename T, bool HALF, class TS>
 __device__ __forceinline__ void
 pass0_march2d(const T *tile, const T *__restrict__ tables, const HierArgs<T> &a,
-              uint32_t x0, uint32_t y0, Sink<T> &sink) {
+              uint32_t x0, uint32_t y0, const Sink<T> &sink) {
   static_assert(TS::TX == 128 && TS::TY == 32 && !TS::RZ && HIER_THREADS == 256,
                 "thread mapping below assumes a 32 x 128 tile");
   constexpr int SY = TS::PX;
   const int k = threadIdx.x & 63, yq = threadIdx.x >> 6; // x pair, y quarter
   const int l = a.L;
   const uint64_t sy = a.n[2];
-  const uint64_t oX = a.nl[l - 1][2], oY = (uint64_t)a.nl[l - 1][1] * sy;
+  const uint64_t oX = a.oct[0][0] / 2, oY = a.oct[0][1] / 2; // elements
   T tx = (T)0.5;
   if (!HALF)
     tx = tables[a.roff[l][2] + x0 + 2 * k];
   const T *p = tile + (8 * yq) * SY + 2 * k;
-  uint16_t *o = sink.sym + ((uint64_t)((y0 >> 1) + 4 * yq) * sy + (x0 >> 1) + k);
+  uint16_t *o = a.sym + ((uint64_t)((y0 >> 1) + 4 * yq) * sy + (x0 >> 1) + k);
   typedef typename std::conditional<sizeof(T) == 4, float2, double2>::type V2;
   V2 ownA = *reinterpret_cast<const V2 *>(p);
   T fA = mgx_lerp(ownA.x, p[2], tx);
@@ -415,15 +470,15 @@ pass0_march2d(const T *tile, const T *__restrict__ tables, const HierArgs<T> &a,
   for (int b = 0; b < 4; b++) {
     const T *q = p + (2 * b) * SY;
     uint16_t *ob = o + (uint64_t)b * sy;
-    sink.put_at(sub_rn(ownA.y, fA), ob + oX, sink.sym);
+    sink.put_at(sub_rn(ownA.y, fA), ob + oX);
     const V2 ownB = *reinterpret_cast<const V2 *>(q + 2 * SY);
     const T fB = mgx_lerp(ownB.x, q[2 * SY + 2], tx);
     T ty = (T)0.5;
     if (!HALF)
       ty = tables[a.roff[l][1] + y0 + 8 * yq + 2 * b];
     const V2 s = *reinterpret_cast<const V2 *>(q + SY);
-    sink.put_at(sub_rn(s.x, mgx_lerp(ownA.x, ownB.x, ty)), ob + oY, sink.sym);
-    sink.put_at(sub_rn(s.y, mgx_lerp(fA, fB, ty)), ob + oY + oX, sink.sym);
+    sink.put_at(sub_rn(s.x, mgx_lerp(ownA.x, ownB.x, ty)), ob + oY);
+    sink.put_at(sub_rn(s.y, mgx_lerp(fA, fB, ty)), ob + oY + oX);
     ownA = ownB;
     fA = fB;
   }
@@ -432,10 +487,10 @@ pass0_march2d(const T *tile, const T *__restrict__ tables, const HierArgs<T> &a,
 template <typename T, bool HALF, class TS, int P>
 __device__ __forceinline__ void
 run_passes(const T *tile, const T *__restrict__ tables, const HierArgs<T> &a,
-           uint32_t x0, uint32_t y0, uint32_t z0, Sink<T> &sink) {
+           uint32_t x0, uint32_t y0, uint32_t z0, const Sink<T> &sink) {
   if constexpr (P < TS::PASSES) {
-    if constexpr (P == 0 && TS::RZ)
-      pass0_march3d<T, HALF, TS>(tile, tables, a, x0, y0, z0, sink);
+    if constexpr (TS::RZ)
+      march3d<T, HALF, TS, P>(tile, tables, a, x0, y0, z0, sink);
     else if constexpr (P == 0 && TS::RY)
       pass0_march2d<T, HALF, TS>(tile, tables, a, x0, y0, sink);
     else
@@ -460,12 +515,8 @@ __device__ __forceinline__ void cp_async_wait_all() {
 }
 
 template <typename T, bool HALF, class TS>
-__global__ void __launch_bounds__(HIER_THREADS)
-    k_hier_forward(const T *__restrict__ u, uint16_t *__restrict__ sym,
-                   uint32_t *__restrict__ g_freq,
-                   unsigned long long *__restrict__ out_count,
-                   unsigned long long *__restrict__ out_idx,
-                   long long *__restrict__ out_val, unsigned long long out_cap,
+__global__ void __launch_bounds__(HIER_THREADS, 3)
+    k_hier_forward(const T *__restrict__ u, uint32_t *__restrict__ g_freq,
                    const T *__restrict__ tables,
                    const __grid_constant__ HierArgs<T> a) {
   extern __shared__ __align__(16) unsigned char smem[];
@@ -476,8 +527,7 @@ __global__ void __launch_bounds__(HIER_THREADS)
     s_hist[i] = 0;
   const uint32_t nz = a.n[0], ny = a.n[1], nx = a.n[2];
   const uint64_t sy = nx, sz = (uint64_t)nx * ny;
-  Sink<T> sink{sym, s_hist, out_count, out_idx, out_val, out_cap,
-               a.qv, a.shift, a.dict, 0u};
+  const Sink<T> sink{a, (uint32_t)__cvta_generic_to_shared(s_hist)};
 
   // tile walk t = blockIdx.x + i * gridDim.x, kept as mixed-radix digits
   const uint32_t T2 = a.tiles[2], T1 = a.tiles[1], T0 = a.tiles[0];
@@ -490,22 +540,42 @@ __global__ void __launch_bounds__(HIER_THREADS)
   // one warp per row, element-wide asynchronous copies
   auto issue = [&](T *buf, uint32_t tx, uint32_t ty, uint32_t tz) {
     const uint32_t z0 = tz * TS::TZ, y0 = ty * TS::TY, x0 = tx * TS::TX;
-    const uint32_t ez = min((uint32_t)TS::HZ, nz - z0),
-                   ey = min((uint32_t)TS::HY, ny - y0),
-                   ex = min((uint32_t)TS::TX + 1, nx - x0);
     const T *src0 = u + (uint64_t)z0 * sz + (uint64_t)y0 * sy + x0;
-    constexpr int RPW = (TS::ROWS + HIER_WARPS - 1) / HIER_WARPS;
-#pragma unroll 4
-    for (int i = 0; i < RPW; i++) {
-      const uint32_t r = warp + i * HIER_WARPS;
-      const uint32_t rz = r / TS::HY, ry = r - rz * TS::HY;
-      if (r < (uint32_t)TS::ROWS && rz < ez && ry < ey) {
-        const T *src = src0 + rz * sz + ry * sy;
-        T *dst = buf + r * TS::PX;
+    const bool full = x0 + TS::TX <= nx - 1 && (!TS::RY || y0 + TS::TY <= ny - 1) &&
+                      (!TS::RZ || z0 + TS::TZ <= nz - 1);
+    auto row = [&](T *dst, const T *src) {
 #pragma unroll
-        for (uint32_t x = lane; x < (uint32_t)TS::TX + 1; x += 32)
-          if (x < ex)
+      for (int x = 0; x < TS::TX; x += 32)
+        cp_async_elem(dst + x + lane, src + x + lane);
+      if (lane == 0)
+        cp_async_elem(dst + TS::TX, src + TS::TX);
+    };
+    if (full && TS::RZ && TS::TY == HIER_WARPS) {
+      // warp w: row y = w of every plane, then row y = TY of plane w
+      const T *src = src0 + warp * sy;
+      T *dst = buf + warp * TS::PX;
+#pragma unroll
+      for (int rz = 0; rz < TS::HZ; rz++)
+        row(dst + rz * TS::HY * TS::PX, src + rz * sz);
+      row(buf + (warp * TS::HY + TS::TY) * TS::PX, src0 + warp * sz + TS::TY * sy);
+      if (warp == 0)
+        row(buf + (TS::TZ * TS::HY + TS::TY) * TS::PX,
+            src0 + TS::TZ * sz + TS::TY * sy);
+    } else if (full && !TS::RZ) {
+      for (int r = warp; r < TS::ROWS; r += HIER_WARPS)
+        row(buf + r * TS::PX, src0 + r * sy);
+    } else {
+      const uint32_t ez = min((uint32_t)TS::HZ, nz - z0),
+                     ey = min((uint32_t)TS::HY, ny - y0),
+                     ex = min((uint32_t)TS::TX + 1, nx - x0);
+      for (uint32_t r = warp; r < (uint32_t)TS::ROWS; r += HIER_WARPS) {
+        const uint32_t rz = r / TS::HY, ry = r - rz * TS::HY;
+        if (rz < ez && ry < ey) {
+          const T *src = src0 + rz * sz + ry * sy;
+          T *dst = buf + r * TS::PX;
+          for (uint32_t x = lane; x < ex; x += 32)
             cp_async_elem(dst + x, src + x);
+        }
       }
     }
     cp_async_commit();
@@ -543,7 +613,9 @@ __global__ void __launch_bounds__(HIER_THREADS)
       constexpr int CX = TS::TX >> TS::PASSES,
                     CY = TS::RY ? (TS::TY >> TS::PASSES) : 1,
                     CZ = TS::RZ ? (TS::TZ >> TS::PASSES) : 1;
-      for (int id = tid; id < CX * CY * CZ; id += HIER_THREADS) {
+      constexpr int DEEP_FIRST = TS::RZ ? 160 : 0; // a warp with no coarse pass
+      for (int id = tid - DEEP_FIRST; id >= 0 && id < CX * CY * CZ;
+           id += HIER_THREADS) {
         const uint32_t lx = (id % CX) << TS::PASSES,
                        ly = ((id / CX) % CY) << TS::PASSES,
                        lz = (id / (CX * CY)) << TS::PASSES;
@@ -569,12 +641,7 @@ __global__ void __launch_bounds__(HIER_THREADS)
     cz = nz_;
     have = have_next;
   }
-  // flush the register-held centre count, then the CTA histogram
-  uint32_t hits = sink.centre_hits;
-  for (int o = 16; o > 0; o >>= 1)
-    hits += __shfl_xor_sync(0xffffffffu, hits, o);
-  if (lane == 0 && hits)
-    atomicAdd(&s_hist[a.shift], hits);
+  // flush the CTA histogram
   __syncthreads();
   for (uint32_t i = tid; i < a.dict; i += HIER_THREADS) {
     uint32_t v = s_hist[i];
@@ -602,11 +669,24 @@ int launch_forward(mgx_ctx *ctx, const void *d_in, HierArgs<T> &a) {
                                                          smem));
   unsigned grid = (unsigned)std::min<uint64_t>(
       a.ntiles, (uint64_t)std::max(occ, 1) * ctx->num_sms);
+  for (int p = 0; p < 8; p++) {
+    const int l = a.L - p;
+    const uint64_t sy = a.n[2], sz = (uint64_t)a.n[2] * a.n[1];
+    for (int d = 0; d < 3; d++)
+      a.oct[p][d] = 0;
+    if (l >= 1) {
+      a.oct[p][0] = 2ull * a.nl[l - 1][2];
+      a.oct[p][1] = 2ull * a.nl[l - 1][1] * sy;
+      a.oct[p][2] = 2ull * a.nl[l - 1][0] * sz;
+    }
+  }
+  a.sym = ctx->d_sym;
+  a.out_count = (unsigned long long *)(ctx->d_scalars + MGX_SC_OUTLIERS);
+  a.out_idx = (unsigned long long *)ctx->d_out_idx;
+  a.out_val = (long long *)ctx->d_out_val;
+  a.out_cap = ctx->out_cap;
   kern<<<grid, HIER_THREADS, smem, ctx->stream>>>(
-      (const T *)d_in, ctx->d_sym, ctx->d_freq,
-      (unsigned long long *)(ctx->d_scalars + MGX_SC_OUTLIERS),
-      (unsigned long long *)ctx->d_out_idx, (long long *)ctx->d_out_val,
-      ctx->out_cap, (const T *)ctx->d_tables, a);
+      (const T *)d_in, ctx->d_freq, (const T *)ctx->d_tables, a);
   ctx->launches++;
   MGX_CUDA(cudaGetLastError());
   return MGX_SUCCESS;
