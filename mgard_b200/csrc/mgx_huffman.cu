@@ -318,17 +318,21 @@ __global__ void __launch_bounds__(ENC_WARPS * 32)
 
 // ---- single-pass encoder ---------------------------------------------------
 // DeflateGroupBits + scans + DeflateChunkMeta + DeflatePack in ONE pass over the
-// symbols (2 B read per symbol, packed words written once):
-//  * warp w of a CTA owns chunk tile*ENC_WARPS + w; a lane holds R runs of 8
-//    consecutive symbols, fetched with 16-byte loads;
-//  * run bit offsets come from warp scans of the run lengths (u8 length table in
-//    shared memory), the chunk's global word offset from a decoupled look-back
-//    over tiles, run by a ninth warp while the other eight pack;
+// symbols (2 B read per symbol, packed words written once).  Everything is
+// warp-granular -- no CTA barrier inside the loop:
+//  * a warp owns one chunk at a time (round-robin over a persistent, fully
+//    resident grid); a lane holds R runs of 8 consecutive symbols, fetched
+//    with 16-byte loads;
+//  * code lengths (and, when the longest code has at most 26 bits, the codes
+//    themselves) come from a packed table in shared memory; run bit offsets
+//    from warp scans;
+//  * the chunk's word offset comes from a decoupled look-back over CHUNKS,
+//    32 predecessors per probe, overlapped with the packing;
 //  * codes are appended MSB first into a zeroed shared-memory image of the
-//    chunk (32-bit units, atomicOr where two runs share a unit) which is then
-//    streamed to its final place in the container.  Chunks whose image would
-//    not fit (more than ENC_CAP_BITS bits per symbol on average) are packed
-//    straight into global memory instead.
+//    chunk (32-bit units, atomicOr because neighbouring runs share units) which
+//    is then streamed to its final place in the container.  A chunk whose image
+//    would not fit (more than ENC_CAP_BITS bits per symbol on average) is
+//    packed straight into global memory instead.
 constexpr int ENC_CAP_BITS = 24;
 constexpr u64 CODE_MASK = 0x00ffffffffffffffull;
 
@@ -343,9 +347,7 @@ struct BitSink {
     fill = bit & 31;
   }
   __device__ __forceinline__ void put32(u64 code, uint32_t len) { // len <= 32
-    if (len == 0)
-      return;
-    acc |= code << (64 - fill - len);
+    acc |= code << (64 - fill - len); // (a shift by 64 yields 0 on the GPU)
     fill += len;
     if (fill >= 32) {
       atomicOr(&dst[unit ^ 1], (uint32_t)(acc >> 32));
@@ -360,7 +362,7 @@ struct BitSink {
     if (len > 32) {
       put32(code >> 32, len - 32);
       put32(code & 0xffffffffull, 32);
-    } else {
+    } else if (len) {
       put32(code, len);
     }
   }
@@ -375,160 +377,154 @@ __device__ __forceinline__ uint32_t sym_of(const uint4 &v, int e) {
   return (e & 1) ? (w >> 16) : (w & 0xffffu);
 }
 
-template <int R>
+// NARROW: s_tab[s] = len << 26 | code (longest code <= 26 bits);
+// otherwise s_tab holds lengths only and codes come from the global codebook.
+template <int R, bool NARROW, bool FULL>
 __device__ __forceinline__ void
 pack_runs(uint32_t *dst, const uint4 (&v)[R], const int (&cnt)[R],
-          const uint32_t (&start)[R], const u64 *__restrict__ codebook) {
+          const uint32_t (&start)[R], const uint32_t *s_tab,
+          const u64 *__restrict__ codebook) {
   BitSink bs;
 #pragma unroll
   for (int j = 0; j < R; j++) {
     bs.begin(dst, start[j]);
 #pragma unroll
-    for (int e = 0; e < 8; e++)
-      if (e < cnt[j])
-        bs.put(__ldg(&codebook[sym_of(v[j], e)]));
+    for (int e = 0; e < 8; e++) {
+      if (FULL || e < cnt[j]) {
+        const uint32_t s = sym_of(v[j], e);
+        if (NARROW) {
+          const uint32_t t = s_tab[s];
+          bs.put32(t & 0x3ffffffu, t >> 26);
+        } else {
+          bs.put(__ldg(&codebook[s]));
+        }
+      }
+    }
     bs.end();
   }
 }
 
 template <int R>
-__global__ void __launch_bounds__((ENC_WARPS + 1) * 32)
+__global__ void __launch_bounds__(ENC_WARPS * 32, 3)
     k_encode(const uint16_t *__restrict__ sym, uint64_t n, uint32_t dict,
              const u64 *__restrict__ codebook, u64 *__restrict__ chunk_bits,
              u64 *__restrict__ chunk_off, u64 *__restrict__ packed,
-             uint64_t cap_words, u64 *__restrict__ tile_state, uint64_t nchunk,
-             uint64_t ntiles, u64 *__restrict__ scalars) {
+             uint64_t cap_words, u64 *__restrict__ state, uint64_t nchunk,
+             u64 *__restrict__ scalars) {
   constexpr int CHUNK = 256 * R;
   constexpr int UNITS = CHUNK * ENC_CAP_BITS / 32; // per-warp image, u32 units
   extern __shared__ __align__(16) unsigned char enc_smem[];
   uint32_t *s_img = (uint32_t *)enc_smem;
-  uint8_t *s_len = (uint8_t *)(s_img + ENC_WARPS * UNITS);
-  __shared__ u64 s_words[2][ENC_WARPS];
-  __shared__ u64 s_prefix[2];
-  for (uint32_t i = threadIdx.x; i < dict; i += blockDim.x)
-    s_len[i] = (uint8_t)(codebook[i] >> 56);
+  uint32_t *s_tab = s_img + ENC_WARPS * UNITS; // dict entries
+  // longest code, left on the device by the codebook kernel
+  const bool narrow = scalars[MGX_SC_MAXLEN] <= 26;
+  for (uint32_t i = threadIdx.x; i < dict; i += blockDim.x) {
+    const u64 cw = codebook[i];
+    const uint32_t len = (uint32_t)(cw >> 56);
+    s_tab[i] = narrow ? (len << 26 | (uint32_t)(cw & 0x3ffffffu)) : len << 26;
+  }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  uint32_t *img = s_img + (warp < ENC_WARPS ? warp : 0) * UNITS;
-  int it = 0;
-  for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, it ^= 1) {
-    const uint64_t c = tile * ENC_WARPS + warp;
-    const bool have = warp < ENC_WARPS && c < nchunk;
+  uint32_t *img = s_img + warp * UNITS;
+  volatile u64 *vs = state;
+  const uint64_t nwarps = (uint64_t)gridDim.x * ENC_WARPS;
+  for (uint64_t c = (uint64_t)blockIdx.x * ENC_WARPS + warp; c < nchunk;
+       c += nwarps) {
+    const uint64_t base = c * CHUNK;
+    const bool full = base + CHUNK <= n;
     uint4 v[R];
     int cnt[R];
     uint32_t start[R];
 #pragma unroll
     for (int j = 0; j < R; j++) {
-      v[j] = make_uint4(0, 0, 0, 0);
-      cnt[j] = 0;
-      start[j] = 0;
+      const uint64_t idx = base + (uint64_t)(j * 32 + lane) * 8;
+      cnt[j] = full ? 8 : idx >= n ? 0 : (n - idx >= 8 ? 8 : (int)(n - idx));
+      v[j] = cnt[j] > 0 ? *(const uint4 *)(sym + idx) : make_uint4(0, 0, 0, 0);
     }
-    uint32_t words = 0;
-    u64 bits = 0;
-    if (warp < ENC_WARPS) {
-      if (have) {
-        const uint64_t base = c * CHUNK;
+    uint32_t carry = 0;
 #pragma unroll
-        for (int j = 0; j < R; j++) {
-          const uint64_t idx = base + (uint64_t)(j * 32 + lane) * 8;
-          cnt[j] = idx >= n ? 0 : (n - idx >= 8 ? 8 : (int)(n - idx));
-          v[j] = cnt[j] > 0 ? *(const uint4 *)(sym + idx) : make_uint4(0, 0, 0, 0);
-        }
-        uint32_t carry = 0;
+    for (int j = 0; j < R; j++) {
+      uint32_t rb = 0;
 #pragma unroll
-        for (int j = 0; j < R; j++) {
-          uint32_t rb = 0;
+      for (int e = 0; e < 8; e++)
+        if (full || e < cnt[j])
+          rb += s_tab[sym_of(v[j], e)] >> 26;
+      uint32_t incl = rb;
 #pragma unroll
-          for (int e = 0; e < 8; e++)
-            if (e < cnt[j])
-              rb += s_len[sym_of(v[j], e)];
-          uint32_t incl = rb;
-#pragma unroll
-          for (int o = 1; o < 32; o <<= 1) {
-            uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o)
-              incl += t;
-          }
-          start[j] = carry + incl - rb;
-          carry += __shfl_sync(0xffffffffu, incl, 31);
-        }
-        bits = carry;
-        words = (uint32_t)((bits + 63) >> 6);
-        if (2 * words <= (uint32_t)UNITS)
-          for (uint32_t i = lane; i < 2 * words; i += 32)
-            img[i] = 0;
+      for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o)
+          incl += t;
       }
-      if (lane == 0) {
-        s_words[it][warp] = words;
-        if (have)
-          chunk_bits[c] = bits;
-      }
+      start[j] = carry + incl - rb;
+      carry += __shfl_sync(0xffffffffu, incl, 31);
     }
-    __syncthreads();
-    if (warp == ENC_WARPS) {
-      // decoupled look-back over tiles, 32 predecessors per probe
-      u64 agg = lane < ENC_WARPS ? s_words[it][lane] : 0;
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1)
-        agg += __shfl_xor_sync(0xffffffffu, agg, o);
-      u64 prefix = 0;
-      if (tile > 0) {
-        volatile u64 *vs = tile_state;
-        if (lane == 0)
-          vs[tile] = FLAG_AGG | agg;
-        int64_t p = (int64_t)tile - 1;
-        while (true) {
-          const int64_t idx = p - lane;
-          u64 x = 2ull << 62; // before tile 0: inclusive prefix 0
-          if (idx >= 0)
-            x = vs[idx];
-          const bool ready = (x & (FLAG_AGG | FLAG_INC)) != 0;
-          if (__ballot_sync(0xffffffffu, ready) != 0xffffffffu)
-            continue;
-          const unsigned inc = __ballot_sync(0xffffffffu, (x & FLAG_INC) != 0);
-          const int stop = inc ? __ffs(inc) - 1 : 31; // nearest inclusive prefix
-          u64 part = lane <= stop ? (x & VAL_MASK) : 0;
-#pragma unroll
-          for (int o = 16; o > 0; o >>= 1)
-            part += __shfl_xor_sync(0xffffffffu, part, o);
-          prefix += part;
-          if (inc)
-            break;
-          p -= 32;
-        }
-      }
-      if (lane == 0) {
-        ((volatile u64 *)tile_state)[tile] = FLAG_INC | (prefix + agg);
-        s_prefix[it] = prefix;
-        if (tile == ntiles - 1)
-          scalars[MGX_SC_DDATA] = prefix + agg;
-      }
-    } else if (have && 2 * words <= (uint32_t)UNITS) {
+    const u64 bits = carry;
+    const uint32_t words = (uint32_t)((bits + 63) >> 6);
+    const bool fits = 2 * words <= (uint32_t)UNITS;
+    if (lane == 0) {
+      chunk_bits[c] = bits;
+      if (c > 0)
+        vs[c] = FLAG_AGG | words;
+    }
+    if (fits) {
+      for (uint32_t i = lane; i < 2 * words; i += 32)
+        img[i] = 0;
       __syncwarp();
-      pack_runs<R>(img, v, cnt, start, codebook);
+      if (narrow && full)
+        pack_runs<R, true, true>(img, v, cnt, start, s_tab, codebook);
+      else if (narrow)
+        pack_runs<R, true, false>(img, v, cnt, start, s_tab, codebook);
+      else
+        pack_runs<R, false, false>(img, v, cnt, start, s_tab, codebook);
     }
-    __syncthreads();
-    if (have) {
-      u64 off = s_prefix[it];
-      for (int w = 0; w < warp; w++)
-        off += s_words[it][w];
+    // decoupled look-back over chunks, 32 predecessors per probe
+    u64 prefix = 0;
+    if (c > 0) {
+      int64_t p = (int64_t)c - 1;
+      while (true) {
+        const int64_t idx = p - lane;
+        u64 x = 2ull << 62; // before chunk 0: inclusive prefix 0
+        if (idx >= 0)
+          x = vs[idx];
+        const bool ready = (x >> 62) != 0;
+        if (__ballot_sync(0xffffffffu, ready) != 0xffffffffu)
+          continue;
+        const unsigned inc = __ballot_sync(0xffffffffu, (x >> 63) != 0);
+        const int stop = inc ? __ffs(inc) - 1 : 31; // nearest inclusive prefix
+        u64 part = lane <= stop ? (x & VAL_MASK) : 0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+          part += __shfl_xor_sync(0xffffffffu, part, o);
+        prefix += part;
+        if (inc)
+          break;
+        p -= 32;
+      }
+    }
+    const u64 off = prefix;
+    if (lane == 0) {
+      vs[c] = FLAG_INC | (prefix + words);
+      chunk_off[c] = off;
+      if (c == nchunk - 1)
+        scalars[MGX_SC_DDATA] = prefix + words;
+    }
+    if (off + words > cap_words) {
       if (lane == 0)
-        chunk_off[c] = off;
-      if (off + words > cap_words) {
-        if (lane == 0)
-          atomicOr((unsigned long long *)&scalars[MGX_SC_ERR], 8ull);
-      } else if (2 * words <= (uint32_t)UNITS) {
-        const u64 *src = (const u64 *)img;
-        for (uint32_t i = lane; i < words; i += 32)
-          packed[off + i] = src[i];
-      } else {
-        for (uint32_t i = lane; i < words; i += 32)
-          packed[off + i] = 0;
-        __syncwarp();
-        pack_runs<R>((uint32_t *)(packed + off), v, cnt, start, codebook);
-      }
+        atomicOr((unsigned long long *)&scalars[MGX_SC_ERR], 8ull);
+    } else if (fits) {
       __syncwarp();
+      const u64 *src = (const u64 *)img;
+      for (uint32_t i = lane; i < words; i += 32)
+        packed[off + i] = src[i];
+    } else {
+      for (uint32_t i = lane; i < words; i += 32)
+        packed[off + i] = 0;
+      __syncwarp();
+      pack_runs<R, false, false>((uint32_t *)(packed + off), v, cnt, start, s_tab,
+                                 codebook);
     }
+    __syncwarp();
   }
 }
 
@@ -597,7 +593,7 @@ int mgxk_encode_container(mgx_ctx *ctx, uint64_t n, uint8_t *d_out, uint64_t cap
   if (rc)
     return rc;
   mgx_tick(ctx, MGX_TICK_C_CODEBOOK);
-  MGX_CUDA(cudaMemsetAsync(ctx->d_scan_state, 0, ntiles * 8, ctx->stream));
+  MGX_CUDA(cudaMemsetAsync(ctx->d_scan_state, 0, (nchunk + 1) * 8, ctx->stream));
   const bool single_pass =
       chunk == 256 || chunk == 512 || chunk == 1024 || chunk == 2048;
   int occ = 1;
@@ -607,18 +603,19 @@ int mgxk_encode_container(mgx_ctx *ctx, uint64_t n, uint8_t *d_out, uint64_t cap
     const int R = (int)(chunk / 256);
     auto kern = R == 1 ? k_encode<1> : R == 2 ? k_encode<2> : R == 4 ? k_encode<4>
                                                                      : k_encode<8>;
-    size_t smem = (size_t)ENC_WARPS * (chunk * ENC_CAP_BITS / 32) * 4 + dict;
+    size_t smem = (size_t)ENC_WARPS * (chunk * ENC_CAP_BITS / 32) * 4 + dict * 4;
     MGX_CUDA(cudaFuncSetAttribute(
         kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     MGX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(
-        &occ, kern, (ENC_WARPS + 1) * 32, smem));
+        &occ, kern, ENC_WARPS * 32, smem));
+    const uint64_t want = (nchunk + ENC_WARPS - 1) / ENC_WARPS;
     unsigned grid = (unsigned)std::min<uint64_t>(
-        ntiles, (uint64_t)std::max(occ, 1) * ctx->num_sms);
-    kern<<<grid, (ENC_WARPS + 1) * 32, smem, ctx->stream>>>(
+        want, (uint64_t)std::max(occ, 1) * ctx->num_sms);
+    kern<<<grid, ENC_WARPS * 32, smem, ctx->stream>>>(
         ctx->d_sym, n, dict, (const u64 *)ctx->d_codebook,
         (u64 *)(d_out + h.off_bits), (u64 *)(d_out + h.off_offs),
         (u64 *)(d_out + h.off_packed), (cap - h.off_packed) / 8,
-        (u64 *)ctx->d_scan_state, nchunk, ntiles, (u64 *)ctx->d_scalars);
+        (u64 *)ctx->d_scan_state, nchunk, (u64 *)ctx->d_scalars);
     ctx->launches++;
     mgx_tick(ctx, MGX_TICK_C_SIZES);
     mgx_tick(ctx, MGX_TICK_C_PACK);
