@@ -333,7 +333,7 @@ __global__ void __launch_bounds__(ENC_WARPS * 32)
 //    is then streamed to its final place in the container.  A chunk whose image
 //    would not fit (more than ENC_CAP_BITS bits per symbol on average) is
 //    packed straight into global memory instead.
-constexpr int ENC_CAP_BITS = 24;
+constexpr int ENC_CAP_BITS = 16;
 constexpr u64 CODE_MASK = 0x00ffffffffffffffull;
 
 struct BitSink {
@@ -377,9 +377,9 @@ __device__ __forceinline__ uint32_t sym_of(const uint4 &v, int e) {
   return (e & 1) ? (w >> 16) : (w & 0xffffu);
 }
 
-// NARROW: s_tab[s] = len << 26 | code (longest code <= 26 bits);
-// otherwise s_tab holds lengths only and codes come from the global codebook.
-template <int R, bool NARROW, bool FULL>
+// s_tab[s] = len << 26 | (code & 0x3ffffff); codes longer than 26 bits (rare
+// symbols only) are fetched from the global codebook instead.
+template <int R, bool FULL>
 __device__ __forceinline__ void
 pack_runs(uint32_t *dst, const uint4 (&v)[R], const int (&cnt)[R],
           const uint32_t (&start)[R], const uint32_t *s_tab,
@@ -392,53 +392,146 @@ pack_runs(uint32_t *dst, const uint4 (&v)[R], const int (&cnt)[R],
     for (int e = 0; e < 8; e++) {
       if (FULL || e < cnt[j]) {
         const uint32_t s = sym_of(v[j], e);
-        if (NARROW) {
-          const uint32_t t = s_tab[s];
-          bs.put32(t & 0x3ffffffu, t >> 26);
-        } else {
+        const uint32_t t = s_tab[s];
+        if (__builtin_expect(t >= (27u << 26), 0))
           bs.put(__ldg(&codebook[s]));
-        }
+        else
+          bs.put32(t & 0x3ffffffu, t >> 26);
       }
     }
     bs.end();
   }
 }
 
+// Tiles of ENC_WARPS chunks, one per packer warp, plus a ninth "scanner" warp.
+// Nobody meets at a CTA barrier: a packer adds its word count to the tile's
+// slot in shared memory and goes on packing; the scanner waits for the eight
+// arrivals, publishes the tile aggregate and runs the decoupled look-back over
+// tiles (32 predecessors per probe).  Packers are one tile ahead of the scan:
+// they stream tile i-1 out of its shared-memory image after packing tile i, so
+// the latency of the look-back chain (which couples all resident CTAs) is
+// hidden behind a full tile of work.
+constexpr int ENC_SLOTS = 4;
+
 template <int R>
-__global__ void __launch_bounds__(ENC_WARPS * 32, 3)
+__global__ void __launch_bounds__((ENC_WARPS + 1) * 32, 3)
     k_encode(const uint16_t *__restrict__ sym, uint64_t n, uint32_t dict,
              const u64 *__restrict__ codebook, u64 *__restrict__ chunk_bits,
              u64 *__restrict__ chunk_off, u64 *__restrict__ packed,
              uint64_t cap_words, u64 *__restrict__ state, uint64_t nchunk,
-             u64 *__restrict__ scalars) {
+             uint64_t ntiles, u64 *__restrict__ scalars) {
   constexpr int CHUNK = 256 * R;
   constexpr int UNITS = CHUNK * ENC_CAP_BITS / 32; // per-warp image, u32 units
   extern __shared__ __align__(16) unsigned char enc_smem[];
-  uint32_t *s_img = (uint32_t *)enc_smem;
-  uint32_t *s_tab = s_img + ENC_WARPS * UNITS; // dict entries
-  // longest code, left on the device by the codebook kernel
-  const bool narrow = scalars[MGX_SC_MAXLEN] <= 26;
+  uint32_t *s_img = (uint32_t *)enc_smem;           // [2][ENC_WARPS][UNITS]
+  uint32_t *s_tab = s_img + 2 * ENC_WARPS * UNITS;  // dict entries
+  __shared__ uint32_t s_words[ENC_SLOTS][ENC_WARPS];
+  __shared__ uint32_t s_arrived[ENC_SLOTS];
+  __shared__ u64 s_prefix[ENC_SLOTS];
+  __shared__ uint32_t s_epoch[ENC_SLOTS];
   for (uint32_t i = threadIdx.x; i < dict; i += blockDim.x) {
     const u64 cw = codebook[i];
-    const uint32_t len = (uint32_t)(cw >> 56);
-    s_tab[i] = narrow ? (len << 26 | (uint32_t)(cw & 0x3ffffffu)) : len << 26;
+    s_tab[i] = (uint32_t)(cw >> 56) << 26 | (uint32_t)(cw & 0x3ffffffu);
+  }
+  if (threadIdx.x < ENC_SLOTS) {
+    s_arrived[threadIdx.x] = 0;
+    s_epoch[threadIdx.x] = 0;
   }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  uint32_t *img = s_img + warp * UNITS;
   volatile u64 *vs = state;
-  const uint64_t nwarps = (uint64_t)gridDim.x * ENC_WARPS;
-  for (uint64_t c = (uint64_t)blockIdx.x * ENC_WARPS + warp; c < nchunk;
-       c += nwarps) {
+  volatile uint32_t *v_arrived = s_arrived, *v_epoch = s_epoch;
+  volatile u64 *v_prefix = s_prefix;
+
+  if (warp == ENC_WARPS) { // ---- scanner ----------------------------------------
+    uint32_t iter = 0;
+    for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++iter) {
+      const int slot = iter & (ENC_SLOTS - 1);
+      while (v_arrived[slot] != ENC_WARPS)
+        ;
+      __threadfence_block();
+      u64 agg = lane < ENC_WARPS ? ((volatile uint32_t *)s_words[slot])[lane] : 0;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1)
+        agg += __shfl_xor_sync(0xffffffffu, agg, o);
+      u64 prefix = 0;
+      if (tile > 0) {
+        if (lane == 0)
+          vs[tile] = FLAG_AGG | agg;
+        int64_t p = (int64_t)tile - 1;
+        while (true) {
+          const int64_t idx = p - lane;
+          u64 x = 2ull << 62; // before tile 0: inclusive prefix 0
+          if (idx >= 0)
+            x = vs[idx];
+          const unsigned inc = __ballot_sync(0xffffffffu, (x >> 63) != 0);
+          const int stop = inc ? __ffs(inc) - 1 : 31; // nearest inclusive prefix
+          const unsigned need = stop == 31 ? 0xffffffffu : ((2u << stop) - 1u);
+          const unsigned ready = __ballot_sync(0xffffffffu, (x >> 62) != 0);
+          if ((ready & need) != need)
+            continue;
+          u64 part = lane <= stop ? (x & VAL_MASK) : 0;
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1)
+            part += __shfl_xor_sync(0xffffffffu, part, o);
+          prefix += part;
+          if (inc)
+            break;
+          p -= 32;
+        }
+      }
+      if (lane == 0) {
+        vs[tile] = FLAG_INC | (prefix + agg);
+        if (tile == ntiles - 1)
+          scalars[MGX_SC_DDATA] = prefix + agg;
+        v_prefix[slot] = prefix;
+        v_arrived[slot] = 0;
+        __threadfence_block();
+        v_epoch[slot] = iter + 1;
+      }
+      __syncwarp();
+    }
+    return;
+  }
+
+  // ---- packers -------------------------------------------------------------------
+  // stream a finished tile out of its image once the scanner has its prefix
+  auto finish = [&](uint32_t it, uint64_t c, uint32_t words) {
+    const int slot = it & (ENC_SLOTS - 1);
+    while (v_epoch[slot] != it + 1)
+      ;
+    __threadfence_block();
+    u64 off = v_prefix[slot];
+    for (int w = 0; w < warp; w++)
+      off += ((volatile uint32_t *)s_words[slot])[w];
+    if (lane == 0)
+      chunk_off[c] = off;
+    if (off + words > cap_words) {
+      if (lane == 0)
+        atomicOr((unsigned long long *)&scalars[MGX_SC_ERR], 8ull);
+      return ~0ull;
+    }
+    return off;
+  };
+  uint32_t iter = 0;
+  bool pend = false; // a packed tile waits in the other image
+  uint64_t pend_c = 0;
+  uint32_t pend_words = 0;
+  for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++iter) {
+    const int slot = iter & (ENC_SLOTS - 1);
+    uint32_t *img = s_img + ((iter & 1) * ENC_WARPS + warp) * UNITS;
+    const uint64_t c = tile * ENC_WARPS + warp;
+    const bool have = c < nchunk;
     const uint64_t base = c * CHUNK;
-    const bool full = base + CHUNK <= n;
+    const bool full = have && base + CHUNK <= n;
     uint4 v[R];
     int cnt[R];
     uint32_t start[R];
 #pragma unroll
     for (int j = 0; j < R; j++) {
       const uint64_t idx = base + (uint64_t)(j * 32 + lane) * 8;
-      cnt[j] = full ? 8 : idx >= n ? 0 : (n - idx >= 8 ? 8 : (int)(n - idx));
+      cnt[j] = full ? 8
+                    : (!have || idx >= n) ? 0 : (n - idx >= 8 ? 8 : (int)(n - idx));
       v[j] = cnt[j] > 0 ? *(const uint4 *)(sym + idx) : make_uint4(0, 0, 0, 0);
     }
     uint32_t carry = 0;
@@ -463,68 +556,56 @@ __global__ void __launch_bounds__(ENC_WARPS * 32, 3)
     const uint32_t words = (uint32_t)((bits + 63) >> 6);
     const bool fits = 2 * words <= (uint32_t)UNITS;
     if (lane == 0) {
-      chunk_bits[c] = bits;
-      if (c > 0)
-        vs[c] = FLAG_AGG | words;
+      if (have)
+        chunk_bits[c] = bits;
+      ((volatile uint32_t *)s_words[slot])[warp] = words;
+      __threadfence_block();
+      atomicAdd(&s_arrived[slot], 1u);
     }
-    if (fits) {
+    if (have && fits) {
       for (uint32_t i = lane; i < 2 * words; i += 32)
         img[i] = 0;
       __syncwarp();
-      if (narrow && full)
-        pack_runs<R, true, true>(img, v, cnt, start, s_tab, codebook);
-      else if (narrow)
-        pack_runs<R, true, false>(img, v, cnt, start, s_tab, codebook);
+      if (full)
+        pack_runs<R, true>(img, v, cnt, start, s_tab, codebook);
       else
-        pack_runs<R, false, false>(img, v, cnt, start, s_tab, codebook);
+        pack_runs<R, false>(img, v, cnt, start, s_tab, codebook);
+      __syncwarp();
     }
-    // decoupled look-back over chunks, 32 predecessors per probe
-    u64 prefix = 0;
-    if (c > 0) {
-      int64_t p = (int64_t)c - 1;
-      while (true) {
-        const int64_t idx = p - lane;
-        u64 x = 2ull << 62; // before chunk 0: inclusive prefix 0
-        if (idx >= 0)
-          x = vs[idx];
-        const bool ready = (x >> 62) != 0;
-        if (__ballot_sync(0xffffffffu, ready) != 0xffffffffu)
-          continue;
-        const unsigned inc = __ballot_sync(0xffffffffu, (x >> 63) != 0);
-        const int stop = inc ? __ffs(inc) - 1 : 31; // nearest inclusive prefix
-        u64 part = lane <= stop ? (x & VAL_MASK) : 0;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1)
-          part += __shfl_xor_sync(0xffffffffu, part, o);
-        prefix += part;
-        if (inc)
-          break;
-        p -= 32;
+    if (pend) { // previous tile: its prefix has had a whole tile of time
+      const u64 off = finish(iter - 1, pend_c, pend_words);
+      if (off != ~0ull) {
+        const u64 *src = (const u64 *)(s_img +
+                                       (((iter - 1) & 1) * ENC_WARPS + warp) * UNITS);
+        for (uint32_t i = lane; i < pend_words; i += 32)
+          packed[off + i] = src[i];
+      }
+      pend = false;
+    }
+    if (have && fits) {
+      pend = true;
+      pend_c = c;
+      pend_words = words;
+    } else if (have) { // oversized chunk: pack straight into the container
+      const u64 off = finish(iter, c, words);
+      if (off != ~0ull) {
+        for (uint32_t i = lane; i < words; i += 32)
+          packed[off + i] = 0;
+        __syncwarp();
+        pack_runs<R, false>((uint32_t *)(packed + off), v, cnt, start, s_tab,
+                            codebook);
       }
     }
-    const u64 off = prefix;
-    if (lane == 0) {
-      vs[c] = FLAG_INC | (prefix + words);
-      chunk_off[c] = off;
-      if (c == nchunk - 1)
-        scalars[MGX_SC_DDATA] = prefix + words;
-    }
-    if (off + words > cap_words) {
-      if (lane == 0)
-        atomicOr((unsigned long long *)&scalars[MGX_SC_ERR], 8ull);
-    } else if (fits) {
-      __syncwarp();
-      const u64 *src = (const u64 *)img;
-      for (uint32_t i = lane; i < words; i += 32)
-        packed[off + i] = src[i];
-    } else {
-      for (uint32_t i = lane; i < words; i += 32)
-        packed[off + i] = 0;
-      __syncwarp();
-      pack_runs<R, false, false>((uint32_t *)(packed + off), v, cnt, start, s_tab,
-                                 codebook);
-    }
     __syncwarp();
+  }
+  if (pend) {
+    const u64 off = finish(iter - 1, pend_c, pend_words);
+    if (off != ~0ull) {
+      const u64 *src =
+          (const u64 *)(s_img + (((iter - 1) & 1) * ENC_WARPS + warp) * UNITS);
+      for (uint32_t i = lane; i < pend_words; i += 32)
+        packed[off + i] = src[i];
+    }
   }
 }
 
@@ -603,19 +684,18 @@ int mgxk_encode_container(mgx_ctx *ctx, uint64_t n, uint8_t *d_out, uint64_t cap
     const int R = (int)(chunk / 256);
     auto kern = R == 1 ? k_encode<1> : R == 2 ? k_encode<2> : R == 4 ? k_encode<4>
                                                                      : k_encode<8>;
-    size_t smem = (size_t)ENC_WARPS * (chunk * ENC_CAP_BITS / 32) * 4 + dict * 4;
+    size_t smem = 2 * (size_t)ENC_WARPS * (chunk * ENC_CAP_BITS / 32) * 4 + dict * 4;
     MGX_CUDA(cudaFuncSetAttribute(
         kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     MGX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(
-        &occ, kern, ENC_WARPS * 32, smem));
-    const uint64_t want = (nchunk + ENC_WARPS - 1) / ENC_WARPS;
+        &occ, kern, (ENC_WARPS + 1) * 32, smem));
     unsigned grid = (unsigned)std::min<uint64_t>(
-        want, (uint64_t)std::max(occ, 1) * ctx->num_sms);
-    kern<<<grid, ENC_WARPS * 32, smem, ctx->stream>>>(
+        ntiles, (uint64_t)std::max(occ, 1) * ctx->num_sms);
+    kern<<<grid, (ENC_WARPS + 1) * 32, smem, ctx->stream>>>(
         ctx->d_sym, n, dict, (const u64 *)ctx->d_codebook,
         (u64 *)(d_out + h.off_bits), (u64 *)(d_out + h.off_offs),
         (u64 *)(d_out + h.off_packed), (cap - h.off_packed) / 8,
-        (u64 *)ctx->d_scan_state, nchunk, (u64 *)ctx->d_scalars);
+        (u64 *)ctx->d_scan_state, nchunk, ntiles, (u64 *)ctx->d_scalars);
     ctx->launches++;
     mgx_tick(ctx, MGX_TICK_C_SIZES);
     mgx_tick(ctx, MGX_TICK_C_PACK);
