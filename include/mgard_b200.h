@@ -121,6 +121,32 @@ int mgx_decompress_host(mgx_ctx *ctx, const uint8_t *h_in, uint64_t bytes,
                         int rel, double tol, double s, double norm,
                         void *h_out);
 
+/* ---- host-only helpers (no context, no GPU) -------------------------------- */
+
+/* Level structure of a shape without planning it: l_target and the
+ * (l_target+1) x D level shapes (Hierarchy.hpp:277-309).  level_shapes may be
+ * NULL.  Returns MGX_TOO_MANY_DIMENSIONS for D > 5. */
+int mgx_hierarchy_levels(int D, const uint64_t *shape, uint64_t max_level,
+                         int *l_target, uint64_t *level_shapes);
+
+/* MaxDim domain decomposition (DomainDecomposer.hpp:192-223): split the largest
+ * dimension (first one on ties) into slabs of *size rows, halving the slab
+ * (round up) until there are at least min_subdomains of them.  The reference
+ * halves until a slab fits the device; with one slab per GPU the stop rule is
+ * the GPU count.  *num = ceil(shape[dim] / size) (the last slab is the
+ * leftover, DomainDecomposer.hpp:118-133). */
+int mgx_max_dim_decomposition(int D, const uint64_t *shape,
+                              uint64_t min_subdomains, int *dim, uint64_t *size,
+                              uint64_t *num);
+/* shape and offset (along dim) of subdomain id */
+int mgx_subdomain_shape(int D, const uint64_t *shape, int dim, uint64_t size,
+                        uint64_t id, uint64_t *sub_shape, uint64_t *offset);
+/* calc_local_abs_tol (ErrorToleranceCalculator.hpp:126-147), evaluated in the
+ * data type's arithmetic like the reference: every subdomain is then compressed
+ * with an ABS bound of this value. */
+double mgx_local_abs_tol(int dtype, int rel, double norm, double tol, double s,
+                         uint64_t num_subdomains);
+
 /* kernels launched by this context since creation (bench.py's gpu_launches) */
 uint64_t mgx_launch_count(const mgx_ctx *ctx);
 

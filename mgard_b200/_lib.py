@@ -48,6 +48,17 @@ SIGNATURES = {
                                   ctypes.POINTER(c_u64)]),
     "mgx_decompress_host": (c_int, [c_vp, c_vp, c_u64, c_int, c_dbl, c_dbl,
                                     c_dbl, c_vp]),
+    "mgx_hierarchy_levels": (c_int, [c_int, ctypes.POINTER(c_u64), c_u64,
+                                     ctypes.POINTER(c_int),
+                                     ctypes.POINTER(c_u64)]),
+    "mgx_max_dim_decomposition": (c_int, [c_int, ctypes.POINTER(c_u64), c_u64,
+                                          ctypes.POINTER(c_int),
+                                          ctypes.POINTER(c_u64),
+                                          ctypes.POINTER(c_u64)]),
+    "mgx_subdomain_shape": (c_int, [c_int, ctypes.POINTER(c_u64), c_int, c_u64,
+                                    c_u64, ctypes.POINTER(c_u64),
+                                    ctypes.POINTER(c_u64)]),
+    "mgx_local_abs_tol": (c_dbl, [c_int, c_int, c_dbl, c_dbl, c_dbl, c_u64]),
     "mgx_launch_count": (c_u64, [c_vp]),
     "mgx_set_timing": (c_int, [c_vp, c_int]),
     "mgx_elapsed_ms": (c_int, [c_vp, c_int, c_int,

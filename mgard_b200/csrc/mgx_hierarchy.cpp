@@ -149,3 +149,95 @@ void mgx_build_tables(const MgxLevels &lv, MgxHostTables<T> *tb) {
 template void mgx_build_tables<float>(const MgxLevels &, MgxHostTables<float> *);
 template void mgx_build_tables<double>(const MgxLevels &,
                                        MgxHostTables<double> *);
+
+// ---- host-only entry points of the C ABI ---------------------------------------
+#include <cmath>
+#include <limits>
+
+template <typename T>
+static T local_abs_tol_t(int rel, T norm, T tol, T s, uint64_t num_subdomain) {
+  if (rel) {
+    if (s == std::numeric_limits<T>::infinity())
+      return tol * norm;
+    return std::sqrt((tol * norm) * (tol * norm) / num_subdomain);
+  }
+  if (s == std::numeric_limits<T>::infinity())
+    return tol;
+  return std::sqrt((tol * tol) / num_subdomain);
+}
+
+extern "C" {
+
+int mgx_hierarchy_levels(int D, const uint64_t *shape, uint64_t max_level,
+                         int *l_target, uint64_t *level_shapes) {
+  if (D > MGX_MAX_D)
+    return MGX_TOO_MANY_DIMENSIONS;
+  if (D < 1 || !shape)
+    return MGX_FAILURE;
+  MgxLevels lv;
+  int rc = mgx_build_levels(D, shape, max_level, &lv);
+  if (rc)
+    return rc;
+  const int pad = MGX_MAX_D - D;
+  if (l_target)
+    *l_target = lv.L;
+  if (level_shapes)
+    for (int l = 0; l <= lv.L; l++)
+      for (int d = 0; d < D; d++)
+        level_shapes[l * D + d] = lv.n[l][d + pad];
+  return MGX_SUCCESS;
+}
+
+int mgx_max_dim_decomposition(int D, const uint64_t *shape,
+                              uint64_t min_subdomains, int *dim, uint64_t *size,
+                              uint64_t *num) {
+  if (D > MGX_MAX_D)
+    return MGX_TOO_MANY_DIMENSIONS;
+  if (D < 1 || !shape || !dim || !size || !num)
+    return MGX_FAILURE;
+  uint64_t best = 0;
+  int bd = 0;
+  for (int d = 0; d < D; d++)
+    if (shape[d] > best) {
+      best = shape[d];
+      bd = d;
+    }
+  uint64_t sz = best, n = 1;
+  while (n < min_subdomains && sz > 1) {
+    sz = (sz - 1) / 2 + 1; // divide by 2 and round up
+    n = (best - 1) / sz + 1;
+  }
+  *dim = bd;
+  *size = sz;
+  *num = n;
+  return MGX_SUCCESS;
+}
+
+int mgx_subdomain_shape(int D, const uint64_t *shape, int dim, uint64_t size,
+                        uint64_t id, uint64_t *sub_shape, uint64_t *offset) {
+  if (D < 1 || D > MGX_MAX_D || !shape || dim < 0 || dim >= D || size == 0)
+    return MGX_FAILURE;
+  const uint64_t num = (shape[dim] - 1) / size + 1;
+  if (id >= num)
+    return MGX_FAILURE;
+  for (int d = 0; d < D; d++)
+    sub_shape[d] = shape[d];
+  // full slabs first, then the leftover (DomainDecomposer.hpp:125-133)
+  if (id < shape[dim] / size)
+    sub_shape[dim] = size;
+  else
+    sub_shape[dim] = shape[dim] % size;
+  if (offset)
+    *offset = id * size;
+  return MGX_SUCCESS;
+}
+
+double mgx_local_abs_tol(int dtype, int rel, double norm, double tol, double s,
+                         uint64_t num_subdomains) {
+  if (dtype == MGX_F32)
+    return (double)local_abs_tol_t<float>(rel, (float)norm, (float)tol, (float)s,
+                                          num_subdomains);
+  return local_abs_tol_t<double>(rel, norm, tol, s, num_subdomains);
+}
+
+} // extern "C"
