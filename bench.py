@@ -271,6 +271,9 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    # torchrun pins OMP_NUM_THREADS=1 for its workers; the CPU arm is meant to
+    # use every host core it can (set before the OpenMP runtime is loaded)
+    os.environ["OMP_NUM_THREADS"] = str(len(os.sched_getaffinity(0)))
     import torch
     edge, tol = args.edge, args.tol
     calib = cpu_run(synth_field(edge, "cpu", crop=129).numpy(), tol, 1)
@@ -348,15 +351,18 @@ def run_ours(args):
     red = torch.zeros(1, dtype=torch.float64, device=dev)
     state = {}
 
+    from mgard_b200.sharding import ShardedCompressor
+    sharded = ShardedCompressor(comp, 0, n_elems * world, world, device=dev)
+
     def compress_step():
         if world == 1:
             blob, norm = comp.Compress(field, mg.REL, tol, mg.INF, 0.0, out=out)
+            state["ltol"] = None
         else:
-            # global value range: local |max| partial -> NCCL allreduce(MAX)
-            red[0] = comp.NormPartial(field, mg.INF)
-            dist.all_reduce(red, op=dist.ReduceOp.MAX)
-            norm = comp.FinishNorm(float(red.item()), mg.INF, n_elems * world)
-            blob, norm = comp.Compress(field, mg.REL, tol, mg.INF, norm, out=out)
+            # one subdomain per GPU: local |max| -> NCCL all-reduce(MAX) -> ABS
+            # bound tol * global norm (calc_local_abs_tol)
+            blob, norm, ltol = sharded.Compress(field, mg.REL, tol, mg.INF, out=out)
+            state["ltol"] = ltol
         state["blob"], state["norm"] = blob, norm
 
     def timed(fn, steps):
@@ -406,7 +412,10 @@ def run_ours(args):
     back = torch.empty(shape, dtype=torch.float32, device=dev)
 
     def decompress_step():
-        comp.Decompress(blob_keep, mg.REL, tol, mg.INF, norm, out=back)
+        if world == 1:
+            comp.Decompress(blob_keep, mg.REL, tol, mg.INF, norm, out=back)
+        else:
+            sharded.Decompress(blob_keep, state["ltol"], mg.INF, out=back)
 
     for _ in range(W):
         decompress_step()
@@ -439,14 +448,16 @@ def run_ours(args):
         h_out = torch.empty(in_bytes // 2 + (8 << 20), dtype=torch.uint8, pin_memory=True)
         h_back = torch.empty(shape, dtype=torch.float32, pin_memory=True)
         a_in, a_out, a_back = h_in.numpy(), h_out.numpy(), h_back.numpy()
-        gnorm = norm if world > 1 else 0.0
+        # multi-GPU: the global norm is an input of the host-pointer call (the
+        # reference computes it in a separate pass over the subdomains too)
+        eb_h, tol_h = (mg.REL, tol) if world == 1 else (mg.ABS, state["ltol"])
 
         def e2e_step():
-            b, _ = comp.CompressHost(a_in, mg.REL, tol, mg.INF, gnorm, out=a_out)
+            b, _ = comp.CompressHost(a_in, eb_h, tol_h, mg.INF, 0.0, out=a_out)
             state["hblob"] = b
 
         def e2e_dstep():
-            comp.DecompressHost(state["hblob"], mg.REL, tol, mg.INF, norm, out=a_back)
+            comp.DecompressHost(state["hblob"], eb_h, tol_h, mg.INF, norm, out=a_back)
 
         for _ in range(max(W, 1)):
             e2e_step()
