@@ -221,11 +221,12 @@ element_generic(const T *__restrict__ u, const T *tile, const T *__restrict__ ta
   const uint32_t xl = ix ? ax.lo : gx, xh = ix ? ax.hi : gx;
   const uint32_t yl = iy ? ay.lo : gy, yh = iy ? ay.hi : gy;
   const uint32_t zl = iz ? az.lo : gz, zh = iz ? az.hi : gz;
-  T c = tile[((gz - z0) * TS::HY + (gy - y0)) * TS::PX + (gx - x0)];
+  T c = tile ? tile[((gz - z0) * TS::HY + (gy - y0)) * TS::PX + (gx - x0)]
+             : __ldg(u + gz * sz + gy * sy + gx);
   if (l > 0) {
     T v[8];
-    const bool in_tile = xl >= x0 && xh < x0 + ex && yl >= y0 && yh < y0 + ey &&
-                         zl >= z0 && zh < z0 + ez;
+    const bool in_tile = tile && xl >= x0 && xh < x0 + ex && yl >= y0 &&
+                         yh < y0 + ey && zl >= z0 && zh < z0 + ez;
     if (in_tile) {
       const uint32_t a0 = (zl - z0) * TS::HY, a1 = (zh - z0) * TS::HY;
       const uint32_t b0 = yl - y0, b1 = yh - y0, c0 = xl - x0, c1 = xh - x0;
@@ -609,19 +610,8 @@ __global__ void __launch_bounds__(HIER_THREADS, 3)
                          (!TS::RZ || z0 + TS::TZ <= nz - 1);
     if (regular) {
       run_passes<T, HALF, TS, 0>(tile, tables, a, x0, y0, z0, sink);
-      // nodes that are multiples of 2^PASSES on every axis: coarser levels
-      constexpr int CX = TS::TX >> TS::PASSES,
-                    CY = TS::RY ? (TS::TY >> TS::PASSES) : 1,
-                    CZ = TS::RZ ? (TS::TZ >> TS::PASSES) : 1;
-      constexpr int DEEP_FIRST = TS::RZ ? 160 : 0; // a warp with no coarse pass
-      for (int id = tid - DEEP_FIRST; id >= 0 && id < CX * CY * CZ;
-           id += HIER_THREADS) {
-        const uint32_t lx = (id % CX) << TS::PASSES,
-                       ly = ((id / CX) % CY) << TS::PASSES,
-                       lz = (id / (CX * CY)) << TS::PASSES;
-        element_generic<T, HALF, TS>(u, tile, tables, a, x0 + lx, y0 + ly, z0 + lz,
-                                     x0, y0, z0, TS::TX + 1, TS::HY, TS::HZ, sink);
-      }
+      // (nodes that are multiples of 2^PASSES on every axis belong to coarser
+      //  levels whose neighbours lie outside the tile: k_hier_deep)
     } else {
       const uint32_t ez = min((uint32_t)TS::HZ, nz - z0),
                      ey = min((uint32_t)TS::HY, ny - y0),
@@ -644,6 +634,53 @@ __global__ void __launch_bounds__(HIER_THREADS, 3)
   // flush the CTA histogram
   __syncthreads();
   for (uint32_t i = tid; i < a.dict; i += HIER_THREADS) {
+    uint32_t v = s_hist[i];
+    if (v)
+      atomicAdd(&g_freq[i], v);
+  }
+}
+
+// The nodes the structured passes leave out: multiples of 2^PASSES on every
+// axis inside interior tiles (1/512 of a 3-D grid).  Their neighbours are up to
+// half the grid away, so they gather straight from global memory / L2; keeping
+// them out of the tile loop keeps that latency off every tile's critical path.
+template <typename T, bool HALF, class TS>
+__global__ void __launch_bounds__(HIER_THREADS)
+    k_hier_deep(const T *__restrict__ u, uint32_t *__restrict__ g_freq,
+                const T *__restrict__ tables,
+                const __grid_constant__ HierArgs<T> a) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  uint32_t *s_hist = (uint32_t *)smem;
+  for (uint32_t i = threadIdx.x; i < a.dict; i += HIER_THREADS)
+    s_hist[i] = 0;
+  __syncthreads();
+  const Sink<T> sink{a, (uint32_t)__cvta_generic_to_shared(s_hist)};
+  constexpr int CX = TS::TX >> TS::PASSES,
+                CY = TS::RY ? (TS::TY >> TS::PASSES) : 1,
+                CZ = TS::RZ ? (TS::TZ >> TS::PASSES) : 1;
+  constexpr int PER_TILE = CX * CY * CZ;
+  const uint32_t nz = a.n[0], ny = a.n[1], nx = a.n[2];
+  const uint64_t total = a.ntiles * PER_TILE;
+  for (uint64_t i = blockIdx.x * (uint64_t)HIER_THREADS + threadIdx.x; i < total;
+       i += (uint64_t)gridDim.x * HIER_THREADS) {
+    const uint64_t t = i / PER_TILE;
+    const int id = (int)(i % PER_TILE);
+    const uint32_t tx = (uint32_t)(t % a.tiles[2]);
+    const uint32_t ty = (uint32_t)((t / a.tiles[2]) % a.tiles[1]);
+    const uint32_t tz = (uint32_t)(t / ((uint64_t)a.tiles[2] * a.tiles[1]));
+    const uint32_t z0 = tz * TS::TZ, y0 = ty * TS::TY, x0 = tx * TS::TX;
+    const bool regular = a.L >= TS::PASSES && x0 + TS::TX <= nx - 1 &&
+                         (!TS::RY || y0 + TS::TY <= ny - 1) &&
+                         (!TS::RZ || z0 + TS::TZ <= nz - 1);
+    if (!regular)
+      continue; // boundary tiles handled all their nodes generically
+    const uint32_t lx = (id % CX) << TS::PASSES, ly = ((id / CX) % CY) << TS::PASSES,
+                   lz = (id / (CX * CY)) << TS::PASSES;
+    element_generic<T, HALF, TS>(u, (const T *)nullptr, tables, a, x0 + lx, y0 + ly,
+                                 z0 + lz, x0, y0, z0, 0, 0, 0, sink);
+  }
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < a.dict; i += HIER_THREADS) {
     uint32_t v = s_hist[i];
     if (v)
       atomicAdd(&g_freq[i], v);
@@ -688,6 +725,20 @@ int launch_forward(mgx_ctx *ctx, const void *d_in, HierArgs<T> &a) {
   kern<<<grid, HIER_THREADS, smem, ctx->stream>>>(
       (const T *)d_in, ctx->d_freq, (const T *)ctx->d_tables, a);
   ctx->launches++;
+  if (a.L >= TS::PASSES) {
+    constexpr int PER_TILE = (TS::TX >> TS::PASSES) *
+                             (TS::RY ? (TS::TY >> TS::PASSES) : 1) *
+                             (TS::RZ ? (TS::TZ >> TS::PASSES) : 1);
+    auto deep = k_hier_deep<T, HALF, TS>;
+    const size_t hsmem = (size_t)ctx->dict * 4;
+    MGX_CUDA(cudaFuncSetAttribute(deep, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)hsmem));
+    const uint64_t work = a.ntiles * PER_TILE;
+    unsigned dgrid = mgx_grid_for(work, HIER_THREADS * 4, ctx->num_sms * 4);
+    deep<<<dgrid, HIER_THREADS, hsmem, ctx->stream>>>(
+        (const T *)d_in, ctx->d_freq, (const T *)ctx->d_tables, a);
+    ctx->launches++;
+  }
   MGX_CUDA(cudaGetLastError());
   return MGX_SUCCESS;
 }
