@@ -34,6 +34,9 @@ void release_plan(mgx_ctx *ctx) {
   free_dev(ctx->d_out_idx);
   free_dev(ctx->d_out_val);
   free_dev(ctx->d_lut);
+  free_dev(ctx->d_coarse0);
+  free_dev(ctx->d_coarse1);
+  ctx->coarse_bytes = 0;
   ctx->out_cap = 0;
   ctx->planned = false;
 }
@@ -490,10 +493,17 @@ int mgx_decompress(mgx_ctx *ctx, const uint8_t *d_in, uint64_t bytes, int rel,
   if (rc)
     return rc;
   mgx_tick(ctx, MGX_TICK_D_DECODE);
-  rc = mgxk_dequantize_sym_out(ctx, rel, tol, s, norm, d_out, oidx, oval, n_out);
-  mgx_tick(ctx, MGX_TICK_D_DEQUANT);
-  if (!rc)
-    rc = mgxk_recompose(ctx, d_out, orth ? 1 : 0);
+  rc = MGX_FAILURE + 101;
+  if (!orth) // fused dequantise + recompose (hierarchical basis)
+    rc = mgxk_hier_inverse(ctx, rel, tol, norm, d_out, oidx, oval, n_out);
+  if (rc == MGX_FAILURE + 101) {
+    rc = mgxk_dequantize_sym_out(ctx, rel, tol, s, norm, d_out, oidx, oval, n_out);
+    mgx_tick(ctx, MGX_TICK_D_DEQUANT);
+    if (!rc)
+      rc = mgxk_recompose(ctx, d_out, orth ? 1 : 0);
+  } else {
+    mgx_tick(ctx, MGX_TICK_D_DEQUANT);
+  }
   if (rc)
     return rc;
   mgx_tick(ctx, MGX_TICK_D_END);

@@ -53,7 +53,11 @@ template <typename T> struct HierArgs {
   uint32_t tiles[3];
   uint64_t ntiles;
   uint64_t oct[8][3];            // pass p: byte offsets of the odd x / y / z blocks
-  uint16_t *sym;                 // output symbols (reordered layout)
+  T dq;                          // dequantisation step (inverse)
+  const T *coarse;               // inverse: nodal values of the level-(L-PASSES) grid
+  uint32_t cdim[3];              // its shape
+  unsigned long long n_out;      // inverse: number of outliers (sorted by index)
+  uint16_t *sym;                 // symbols (reordered layout)
   unsigned long long *out_count; // outlier list
   unsigned long long *out_idx;
   long long *out_val;
@@ -687,6 +691,317 @@ __global__ void __launch_bounds__(HIER_THREADS)
   }
 }
 
+// ================================ inverse =====================================
+// Dequantize + recompose for the hierarchical basis in one pass over the symbols
+// (2 B read + 4 B written per fp32 node instead of the reference's level-by-level
+// CopyND / GpkRev3D chain, CoefficientsRestore3D.hpp, DataRefactoring.hpp:179-317).
+//
+// u(x) = c(x) + lerp_r(lerp_c(lerp_f(u at the level-l neighbours))) needs the
+// RECONSTRUCTED coarser nodes, so levels are sequential.  The level-(L-PASSES)
+// grid (1/512 of a 3-D field) is reconstructed first by the level kernels on a
+// compact array (mgxk_recompose_compact); a tile then holds its extended box
+// (+1 halo plane per axis) in shared memory, fills in that coarse lattice, runs
+// the strides 2^(PASSES-1) .. 2 over the whole extended lattice (halo nodes of
+// those strides are recomputed by every tile that needs them; the stride-1 halo
+// nodes are never needed), and finally the stride-1 nodes of its interior, which
+// go straight to global memory.
+
+// value of an outlier (symbol 0 that is in the sorted outlier list), or code 0
+template <typename T>
+__device__ __noinline__ long long hier_outlier_code(const HierArgs<T> &a,
+                                                    uint64_t opos) {
+  unsigned long long lo = 0, hi = a.n_out;
+  while (lo < hi) {
+    const unsigned long long mid = (lo + hi) >> 1;
+    if (a.out_idx[mid] < opos)
+      lo = mid + 1;
+    else
+      hi = mid;
+  }
+  if (lo < a.n_out && a.out_idx[lo] == opos)
+    return a.out_val[lo];
+  return 0;
+}
+
+// lwqzk dequantise (LinearQuantization.hpp:113-126), volume factor 1
+template <typename T>
+__device__ __forceinline__ T coef_of(const HierArgs<T> &a, uint32_t s,
+                                     const uint16_t *at) {
+  if (__builtin_expect(s == 0 && a.n_out != 0, 0)) {
+    const long long q = hier_outlier_code<T>(a, (uint64_t)(at - a.sym));
+    return mul_rn(a.dq, (T)(q - (long long)a.shift));
+  }
+  return mul_rn(a.dq, (T)((int)s - a.shift));
+}
+
+// position of node index i in the level-(L-P) grid (i is a node of that grid)
+__device__ __forceinline__ uint32_t coarse_index(uint32_t i, uint32_t n, int P,
+                                                 uint32_t cn) {
+  return (n > 1 && i == n - 1) ? cn - 1 : (i >> P);
+}
+
+// One node of level `want` inside the staged (extended) tile.
+template <typename T, bool HALF, class TS>
+__device__ __forceinline__ void
+inv_node(T *tile, const T *__restrict__ tables, const HierArgs<T> &a, uint32_t gx,
+         uint32_t gy, uint32_t gz, uint32_t x0, uint32_t y0, uint32_t z0, int want) {
+  const uint32_t nz = a.n[0], ny = a.n[1], nx = a.n[2];
+  const uint64_t sy = nx, sz = (uint64_t)nx * ny;
+  const uint32_t *nl = &a.nl[0][0];
+  const AxisInfo ax = axis_info(gx, nx, a.L, nl, 2);
+  const AxisInfo ay = axis_info(gy, ny, a.L, nl, 1);
+  const AxisInfo az = axis_info(gz, nz, a.L, nl, 0);
+  const int l = max(ax.lvl, max(ay.lvl, az.lvl));
+  if (l != want)
+    return;
+  const bool ix = ax.lvl == l, iy = ay.lvl == l, iz = az.lvl == l;
+  const uint32_t xl = (ix ? ax.lo : gx) - x0, xh = (ix ? ax.hi : gx) - x0;
+  const uint32_t yl = (iy ? ay.lo : gy) - y0, yh = (iy ? ay.hi : gy) - y0;
+  const uint32_t zl = (iz ? az.lo : gz) - z0, zh = (iz ? az.hi : gz) - z0;
+  const uint32_t a0 = zl * TS::HY, a1 = zh * TS::HY;
+  const T v0 = tile[(a0 + yl) * TS::PX + xl], v1 = tile[(a0 + yl) * TS::PX + xh];
+  const T v2 = tile[(a0 + yh) * TS::PX + xl], v3 = tile[(a0 + yh) * TS::PX + xh];
+  const T v4 = tile[(a1 + yl) * TS::PX + xl], v5 = tile[(a1 + yl) * TS::PX + xh];
+  const T v6 = tile[(a1 + yh) * TS::PX + xl], v7 = tile[(a1 + yh) * TS::PX + xh];
+  T tx_ = (T)0.5, ty_ = (T)0.5, tz_ = (T)0.5;
+  if (!HALF) {
+    if (ix) tx_ = tables[a.roff[l][2] + ax.j - 1];
+    if (iy) ty_ = tables[a.roff[l][1] + ay.j - 1];
+    if (iz) tz_ = tables[a.roff[l][0] + az.j - 1];
+  }
+  const T f0 = ix ? mgx_lerp(v0, v1, tx_) : v0;
+  const T f1 = ix ? mgx_lerp(v2, v3, tx_) : v2;
+  const T f2 = ix ? mgx_lerp(v4, v5, tx_) : v4;
+  const T f3 = ix ? mgx_lerp(v6, v7, tx_) : v6;
+  const T g0 = iy ? mgx_lerp(f0, f1, ty_) : f0;
+  const T g1 = iy ? mgx_lerp(f2, f3, ty_) : f2;
+  const T h0 = iz ? mgx_lerp(g0, g1, tz_) : g0;
+  const uint32_t px = final_pos(ax, gx, nx, l, a.L, nl, 2);
+  const uint32_t py = final_pos(ay, gy, ny, l, a.L, nl, 1);
+  const uint32_t pz = final_pos(az, gz, nz, l, a.L, nl, 0);
+  const uint16_t *at = a.sym + ((uint64_t)pz * sz + (uint64_t)py * sy + px);
+  const T c = coef_of<T>(a, (uint32_t)__ldg(at), at);
+  tile[((gz - z0) * TS::HY + (gy - y0)) * TS::PX + (gx - x0)] = add_rn(c, h0);
+}
+
+// passes PASSES-1 .. 1 of an interior tile over its extended lattice
+template <typename T, bool HALF, class TS, int P>
+__device__ __forceinline__ void
+inv_coarse_passes(T *tile, const T *__restrict__ tables, const HierArgs<T> &a,
+                  uint32_t x0, uint32_t y0, uint32_t z0) {
+  if constexpr (P >= 1) {
+    constexpr int NX = (TS::TX >> P) + 1, NY = TS::RY ? (TS::TY >> P) + 1 : 1,
+                  NZ = TS::RZ ? (TS::TZ >> P) + 1 : 1;
+    __syncthreads();
+    for (int id = threadIdx.x; id < NX * NY * NZ; id += HIER_THREADS) {
+      const int i = id % NX, j = (id / NX) % NY, k = id / (NX * NY);
+      if (((i | j | k) & 1) == 0)
+        continue; // node of a coarser lattice
+      inv_node<T, HALF, TS>(tile, tables, a, x0 + (i << P), y0 + (j << P),
+                            z0 + (k << P), x0, y0, z0, a.L - P);
+    }
+    inv_coarse_passes<T, HALF, TS, P - 1>(tile, tables, a, x0, y0, z0);
+  }
+}
+
+template <typename T, bool HALF, class TS>
+__global__ void __launch_bounds__(HIER_THREADS, 3)
+    k_hier_inverse(T *__restrict__ out, const T *__restrict__ tables,
+                   const __grid_constant__ HierArgs<T> a) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  T *tile = (T *)smem;
+  const int tid = threadIdx.x;
+  const uint32_t nz = a.n[0], ny = a.n[1], nx = a.n[2];
+  const uint64_t sy = nx, sz = (uint64_t)nx * ny;
+  constexpr int P = TS::PASSES;
+  const uint32_t T2 = a.tiles[2], T1 = a.tiles[1], T0 = a.tiles[0];
+  uint32_t cx = blockIdx.x % T2, cy = (blockIdx.x / T2) % T1,
+           cz = blockIdx.x / (T2 * T1);
+  const uint32_t dx = gridDim.x % T2, dy = (gridDim.x / T2) % T1,
+                 dz = gridDim.x / (T2 * T1);
+  while (cz < T0) {
+    const uint32_t z0 = cz * TS::TZ, y0 = cy * TS::TY, x0 = cx * TS::TX;
+    const bool regular = x0 + TS::TX <= nx - 1 &&
+                         (!TS::RY || y0 + TS::TY <= ny - 1) &&
+                         (!TS::RZ || z0 + TS::TZ <= nz - 1);
+    __syncthreads(); // previous tile no longer read
+    if (regular) {
+      // stride-1 symbols of this thread's blocks, fetched before anything else
+      uint16_t sv[2][7];
+      const uint16_t *ob0 = nullptr;
+      uint64_t oX = 0, oY = 0, oZ = 0;
+      int k = 0, ya = 0, zb = 0;
+      if constexpr (TS::RZ) {
+        k = tid & 31;
+        ya = (tid >> 5) & 3;
+        zb = (tid >> 7) * 2;
+        oX = a.oct[0][0];
+        oY = a.oct[0][1];
+        oZ = a.oct[0][2];
+        ob0 = a.sym + ((uint64_t)((z0 >> 1) + zb) * sz +
+                       (uint64_t)((y0 >> 1) + ya) * sy + (x0 >> 1) + k);
+#pragma unroll
+        for (int b = 0; b < 2; b++) {
+          const uint16_t *ob = ob0 + (uint64_t)b * sz;
+          sv[b][0] = __ldg(byte_off((uint16_t *)ob, oX));
+          sv[b][1] = __ldg(byte_off((uint16_t *)ob, oY));
+          sv[b][2] = __ldg(byte_off((uint16_t *)ob, oX + oY));
+          sv[b][3] = __ldg(byte_off((uint16_t *)ob, oZ));
+          sv[b][4] = __ldg(byte_off((uint16_t *)ob, oZ + oX));
+          sv[b][5] = __ldg(byte_off((uint16_t *)ob, oZ + oY));
+          sv[b][6] = __ldg(byte_off((uint16_t *)ob, oZ + oX + oY));
+        }
+      }
+      // coarse lattice (stride 2^P) of the extended tile
+      constexpr int CX = (TS::TX >> P) + 1, CY = TS::RY ? (TS::TY >> P) + 1 : 1,
+                    CZ = TS::RZ ? (TS::TZ >> P) + 1 : 1;
+      for (int id = tid; id < CX * CY * CZ; id += HIER_THREADS) {
+        const int i = id % CX, j = (id / CX) % CY, kk = id / (CX * CY);
+        const uint32_t gx = x0 + (i << P), gy = y0 + (j << P), gz = z0 + (kk << P);
+        const uint32_t ci = coarse_index(gx, nx, P, a.cdim[2]),
+                       cj = coarse_index(gy, ny, P, a.cdim[1]),
+                       ck = coarse_index(gz, nz, P, a.cdim[0]);
+        tile[(((kk << P) * TS::HY) + (j << P)) * TS::PX + (i << P)] =
+            a.coarse[((uint64_t)ck * a.cdim[1] + cj) * a.cdim[2] + ci];
+      }
+      inv_coarse_passes<T, HALF, TS, P - 1>(tile, tables, a, x0, y0, z0);
+      __syncthreads();
+      if constexpr (TS::RZ) {
+        // stride 1: the forward march run backwards (x, then y, then z lerps of
+        // the reconstructed even lattice), results straight to global memory
+        constexpr int SY = TS::PX, SZ = TS::HY * TS::PX;
+        const int l = a.L;
+        T tx = (T)0.5, ty = (T)0.5;
+        if (!HALF) {
+          tx = tables[a.roff[l][2] + x0 + 2 * k];
+          ty = tables[a.roff[l][1] + y0 + 2 * ya];
+        }
+        const T *p = tile + (2 * zb) * SZ + (2 * ya) * SY + 2 * k;
+        T *g = out + ((uint64_t)(z0 + 2 * zb) * sz + (uint64_t)(y0 + 2 * ya) * sy +
+                      x0 + 2 * k);
+        auto plane = [&](const T *q, PlaneP<T> &Q) {
+          const T e0 = q[0], r0 = q[2], e2 = q[2 * SY], r2 = q[2 * SY + 2];
+          Q.e0 = e0;
+          Q.f0 = mgx_lerp(e0, r0, tx);
+          const T f2 = mgx_lerp(e2, r2, tx);
+          Q.gE = mgx_lerp(e0, e2, ty);
+          Q.gO = mgx_lerp(Q.f0, f2, ty);
+        };
+        PlaneP<T> A, B;
+        plane(p, A);
+#pragma unroll
+        for (int b = 0; b < 2; b++) {
+          const T *q = p + (2 * b) * SZ;
+          const uint16_t *ob = ob0 + (uint64_t)b * sz;
+          T *gb = g + (uint64_t)(2 * b) * sz;
+          plane(q + 2 * SZ, B);
+          T tz = (T)0.5;
+          if (!HALF)
+            tz = tables[a.roff[l][0] + z0 + 2 * (zb + b)];
+          gb[0] = A.e0;
+          gb[1] = add_rn(coef_of<T>(a, sv[b][0], byte_off((uint16_t *)ob, oX)), A.f0);
+          gb[sy] = add_rn(coef_of<T>(a, sv[b][1], byte_off((uint16_t *)ob, oY)), A.gE);
+          gb[sy + 1] =
+              add_rn(coef_of<T>(a, sv[b][2], byte_off((uint16_t *)ob, oX + oY)), A.gO);
+          gb[sz] = add_rn(coef_of<T>(a, sv[b][3], byte_off((uint16_t *)ob, oZ)),
+                          mgx_lerp(A.e0, B.e0, tz));
+          gb[sz + 1] = add_rn(coef_of<T>(a, sv[b][4], byte_off((uint16_t *)ob, oZ + oX)),
+                              mgx_lerp(A.f0, B.f0, tz));
+          gb[sz + sy] = add_rn(coef_of<T>(a, sv[b][5], byte_off((uint16_t *)ob, oZ + oY)),
+                               mgx_lerp(A.gE, B.gE, tz));
+          gb[sz + sy + 1] =
+              add_rn(coef_of<T>(a, sv[b][6], byte_off((uint16_t *)ob, oZ + oX + oY)),
+                     mgx_lerp(A.gO, B.gO, tz));
+          A = B;
+        }
+      } else {
+        // 1-D / 2-D tiles: stride-1 nodes of the interior, then copy out
+        for (int id = tid; id < TS::TZ * TS::TY * TS::TX; id += HIER_THREADS) {
+          const int i = id % TS::TX, j = (id / TS::TX) % TS::TY,
+                    kk = id / (TS::TX * TS::TY);
+          if (((i | j | kk) & 1) == 0)
+            continue;
+          inv_node<T, HALF, TS>(tile, tables, a, x0 + i, y0 + j, z0 + kk, x0, y0, z0,
+                                a.L);
+        }
+        __syncthreads();
+        for (int id = tid; id < TS::TZ * TS::TY * TS::TX; id += HIER_THREADS) {
+          const int i = id % TS::TX, j = (id / TS::TX) % TS::TY,
+                    kk = id / (TS::TX * TS::TY);
+          out[(uint64_t)(z0 + kk) * sz + (uint64_t)(y0 + j) * sy + x0 + i] =
+              tile[(kk * TS::HY + j) * TS::PX + i];
+        }
+      }
+    } else {
+      // tile touching the last node of an axis: every level by the generic
+      // per-node rule on the clipped extended box
+      const uint32_t ez = min((uint32_t)TS::HZ, nz - z0),
+                     ey = min((uint32_t)TS::HY, ny - y0),
+                     ex = min((uint32_t)TS::TX + 1, nx - x0);
+      const uint32_t cnt = ez * ey * ex;
+      const uint32_t *nl = &a.nl[0][0];
+      for (uint32_t id = tid; id < cnt; id += HIER_THREADS) {
+        const uint32_t i = id % ex, j = (id / ex) % ey, kk = id / (ex * ey);
+        const uint32_t gx = x0 + i, gy = y0 + j, gz = z0 + kk;
+        const int l = max(axis_info(gx, nx, a.L, nl, 2).lvl,
+                          max(axis_info(gy, ny, a.L, nl, 1).lvl,
+                              axis_info(gz, nz, a.L, nl, 0).lvl));
+        if (l <= a.L - P) {
+          const uint32_t ci = coarse_index(gx, nx, P, a.cdim[2]),
+                         cj = coarse_index(gy, ny, P, a.cdim[1]),
+                         ck = coarse_index(gz, nz, P, a.cdim[0]);
+          tile[(kk * TS::HY + j) * TS::PX + i] =
+              a.coarse[((uint64_t)ck * a.cdim[1] + cj) * a.cdim[2] + ci];
+        }
+      }
+      for (int pp = P - 1; pp >= 0; pp--) {
+        __syncthreads();
+        for (uint32_t id = tid; id < cnt; id += HIER_THREADS) {
+          const uint32_t i = id % ex, j = (id / ex) % ey, kk = id / (ex * ey);
+          inv_node<T, HALF, TS>(tile, tables, a, x0 + i, y0 + j, z0 + kk, x0, y0, z0,
+                                a.L - pp);
+        }
+      }
+      __syncthreads();
+      const uint32_t vz = min((uint32_t)TS::TZ, nz - z0),
+                     vy = min((uint32_t)TS::TY, ny - y0),
+                     vx = min((uint32_t)TS::TX, nx - x0);
+      for (uint32_t id = tid; id < vz * vy * vx; id += HIER_THREADS) {
+        const uint32_t i = id % vx, j = (id / vx) % vy, kk = id / (vx * vy);
+        out[(uint64_t)(z0 + kk) * sz + (uint64_t)(y0 + j) * sy + x0 + i] =
+            tile[(kk * TS::HY + j) * TS::PX + i];
+      }
+    }
+    cx += dx;
+    cy += dy;
+    cz += dz;
+    if (cx >= T2) {
+      cx -= T2;
+      ++cy;
+    }
+    if (cy >= T1) {
+      cy -= T1;
+      ++cz;
+    }
+  }
+}
+
+// symbols of the coarse box [0, n_{L-P})^3 -> compact array of coefficients
+template <typename T>
+__global__ void __launch_bounds__(256)
+    k_coarse_gather(T *__restrict__ dst, const __grid_constant__ HierArgs<T> a) {
+  const uint64_t total = (uint64_t)a.cdim[0] * a.cdim[1] * a.cdim[2];
+  const uint64_t sy = a.n[2], sz = (uint64_t)a.n[2] * a.n[1];
+  for (uint64_t i = blockIdx.x * 256ull + threadIdx.x; i < total;
+       i += (uint64_t)gridDim.x * 256) {
+    const uint32_t x = (uint32_t)(i % a.cdim[2]);
+    const uint32_t y = (uint32_t)((i / a.cdim[2]) % a.cdim[1]);
+    const uint32_t z = (uint32_t)(i / ((uint64_t)a.cdim[2] * a.cdim[1]));
+    const uint16_t *at = a.sym + (z * sz + y * sy + x);
+    dst[i] = coef_of<T>(a, (uint32_t)__ldg(at), at);
+  }
+}
+
 typedef TileShape<3, 3, 6> Tile3D;  // 8 x 8 x 64
 typedef TileShape<0, 5, 7> Tile2D;  // 32 x 128
 typedef TileShape<0, 0, 10> Tile1D; // 1024
@@ -753,12 +1068,11 @@ int launch_forward_shape(mgx_ctx *ctx, const void *d_in, HierArgs<T> &a) {
 }
 
 template <typename T>
-int hier_forward_t(mgx_ctx *ctx, const void *d_in, int rel, double tol_d,
-                   double norm_d) {
+void fill_hier_args(mgx_ctx *ctx, HierArgs<T> &a, int rel, double tol_d,
+                    double norm_d) {
   const MgxLevels &lv = ctx->lv;
   const MgxHostTables<T> &tb = *reinterpret_cast<const MgxHostTables<T> *>(
       mgx_is_f32(ctx) ? (const void *)&ctx->tbf : (const void *)&ctx->tbd);
-  HierArgs<T> a;
   for (int d = 0; d < 3; d++)
     a.n[d] = (uint32_t)lv.shape[2 + d];
   for (int l = 0; l <= lv.L; l++)
@@ -774,11 +1088,108 @@ int hier_forward_t(mgx_ctx *ctx, const void *d_in, int rel, double tol_d,
     abs_tol *= norm;
   abs_tol *= 2;
   T qv = (T)((abs_tol) / (uint64_t)(lv.L + 1));
+  a.dq = qv;
   a.qv = 1.0f / qv;
   a.shift = (int)(ctx->dict / 2);
   a.dict = ctx->dict;
+  a.coarse = nullptr;
+  a.n_out = 0;
+  a.cdim[0] = a.cdim[1] = a.cdim[2] = 1;
+}
+
+template <typename T>
+int hier_forward_t(mgx_ctx *ctx, const void *d_in, int rel, double tol_d,
+                   double norm_d) {
+  const MgxHostTables<T> &tb = *reinterpret_cast<const MgxHostTables<T> *>(
+      mgx_is_f32(ctx) ? (const void *)&ctx->tbf : (const void *)&ctx->tbd);
+  HierArgs<T> a;
+  fill_hier_args<T>(ctx, a, rel, tol_d, norm_d);
   return tb.ratios_half ? launch_forward_shape<T, true>(ctx, d_in, a)
                         : launch_forward_shape<T, false>(ctx, d_in, a);
+}
+
+template <typename T, bool HALF, class TS>
+int launch_inverse(mgx_ctx *ctx, void *d_out, HierArgs<T> &a) {
+  constexpr int P = TS::PASSES;
+  if (a.L < P)
+    return MGX_FAILURE + 101;
+  const int tdim[3] = {TS::TZ, TS::TY, TS::TX};
+  for (int d = 0; d < 3; d++)
+    a.tiles[d] = (a.n[d] + tdim[d] - 1) / tdim[d];
+  a.ntiles = (uint64_t)a.tiles[0] * a.tiles[1] * a.tiles[2];
+  for (int p = 0; p < 8; p++) {
+    const int l = a.L - p;
+    const uint64_t sy = a.n[2], sz = (uint64_t)a.n[2] * a.n[1];
+    for (int d = 0; d < 3; d++)
+      a.oct[p][d] = 0;
+    if (l >= 1) {
+      a.oct[p][0] = 2ull * a.nl[l - 1][2];
+      a.oct[p][1] = 2ull * a.nl[l - 1][1] * sy;
+      a.oct[p][2] = 2ull * a.nl[l - 1][0] * sz;
+    }
+  }
+  // coarse lattice = level-(L-P) grid: gather + dequantise its box, recompose
+  // it with the level kernels on a compact array
+  const int lc = a.L - P;
+  uint64_t celems = 1;
+  for (int d = 0; d < 3; d++) {
+    a.cdim[d] = a.nl[lc][d];
+    celems *= a.cdim[d];
+  }
+  const size_t need = celems * sizeof(T);
+  if (ctx->coarse_bytes < need) {
+    if (ctx->d_coarse0)
+      cudaFree(ctx->d_coarse0);
+    if (ctx->d_coarse1)
+      cudaFree(ctx->d_coarse1);
+    MGX_CUDA(cudaMalloc(&ctx->d_coarse0, need));
+    MGX_CUDA(cudaMalloc(&ctx->d_coarse1, need));
+    ctx->coarse_bytes = need;
+  }
+  k_coarse_gather<T><<<mgx_grid_for(celems, 256, ctx->num_sms * 8), 256, 0,
+                       ctx->stream>>>((T *)ctx->d_coarse0, a);
+  ctx->launches++;
+  int rc = mgxk_recompose_compact(ctx, ctx->d_coarse0, ctx->d_coarse1, lc);
+  if (rc)
+    return rc;
+  a.coarse = (const T *)ctx->d_coarse0;
+  const size_t smem = sizeof(T) * TS::tile_elems;
+  auto kern = k_hier_inverse<T, HALF, TS>;
+  MGX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)smem));
+  int occ = 1;
+  MGX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, HIER_THREADS,
+                                                         smem));
+  unsigned grid = (unsigned)std::min<uint64_t>(
+      a.ntiles, (uint64_t)std::max(occ, 1) * ctx->num_sms);
+  kern<<<grid, HIER_THREADS, smem, ctx->stream>>>((T *)d_out,
+                                                  (const T *)ctx->d_tables, a);
+  ctx->launches++;
+  MGX_CUDA(cudaGetLastError());
+  return MGX_SUCCESS;
+}
+
+template <typename T>
+int hier_inverse_t(mgx_ctx *ctx, int rel, double tol_d, double norm_d, void *d_out,
+                   const uint64_t *d_oidx, const int64_t *d_oval, uint64_t n_out) {
+  const MgxHostTables<T> &tb = *reinterpret_cast<const MgxHostTables<T> *>(
+      mgx_is_f32(ctx) ? (const void *)&ctx->tbf : (const void *)&ctx->tbd);
+  HierArgs<T> a;
+  fill_hier_args<T>(ctx, a, rel, tol_d, norm_d);
+  a.sym = ctx->d_sym;
+  a.out_idx = (unsigned long long *)d_oidx;
+  a.out_val = (long long *)d_oval;
+  a.n_out = n_out;
+  a.out_count = nullptr;
+  a.out_cap = 0;
+  if (a.n[0] > 1)
+    return tb.ratios_half ? launch_inverse<T, true, Tile3D>(ctx, d_out, a)
+                          : launch_inverse<T, false, Tile3D>(ctx, d_out, a);
+  if (a.n[1] > 1)
+    return tb.ratios_half ? launch_inverse<T, true, Tile2D>(ctx, d_out, a)
+                          : launch_inverse<T, false, Tile2D>(ctx, d_out, a);
+  return tb.ratios_half ? launch_inverse<T, true, Tile1D>(ctx, d_out, a)
+                        : launch_inverse<T, false, Tile1D>(ctx, d_out, a);
 }
 
 } // namespace
@@ -791,4 +1202,17 @@ int mgxk_hier_forward(mgx_ctx *ctx, const void *d_in, int rel, double tol, bool,
   }
   return mgx_is_f32(ctx) ? hier_forward_t<float>(ctx, d_in, rel, tol, norm)
                          : hier_forward_t<double>(ctx, d_in, rel, tol, norm);
+}
+
+int mgxk_hier_inverse(mgx_ctx *ctx, int rel, double tol, double norm, void *d_out,
+                      const uint64_t *d_oidx, const int64_t *d_oval,
+                      uint64_t n_out) {
+  if (ctx->lv.D > 3) {
+    ctx->err = "hierarchical fast path needs D <= 3";
+    return MGX_FAILURE;
+  }
+  return mgx_is_f32(ctx)
+             ? hier_inverse_t<float>(ctx, rel, tol, norm, d_out, d_oidx, d_oval, n_out)
+             : hier_inverse_t<double>(ctx, rel, tol, norm, d_out, d_oidx, d_oval,
+                                      n_out);
 }

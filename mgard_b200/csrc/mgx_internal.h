@@ -77,6 +77,8 @@ struct mgx_ctx {
   uint64_t *d_scalars = nullptr;    // small device scalars (see MGX_SC_*)
   uint64_t *h_scalars = nullptr;    // pinned mirror
   void *d_lut = nullptr;            // decode look-up table
+  void *d_coarse0 = nullptr, *d_coarse1 = nullptr; // fused inverse: coarse lattice
+  size_t coarse_bytes = 0;
   void *d_sort_tmp = nullptr;
   size_t sort_tmp_bytes = 0;
   uint64_t *d_out_idx2 = nullptr;
@@ -143,8 +145,13 @@ int mgxk_dequantize_sym_out(mgx_ctx *ctx, int rel, double tol, double s,
 // histogram + outliers, quantiser derived on the device from the norm scalar
 int mgxk_hier_forward(mgx_ctx *ctx, const void *d_in, int rel, double tol,
                       bool norm_on_device, double norm);
-int mgxk_hier_inverse(mgx_ctx *ctx, int rel, double tol, double norm,
-                      void *d_out);
+// fused inverse: symbols (ctx->d_sym) + sorted outlier list -> field.  Returns
+// MGX_FAILURE + 101 when the shape has too few levels for it (caller falls
+// back to dequantise + level-by-level recompose).
+int mgxk_hier_inverse(mgx_ctx *ctx, int rel, double tol, double norm, void *d_out,
+                      const uint64_t *d_oidx, const int64_t *d_oval,
+                      uint64_t n_out);
+int mgxk_recompose_compact(mgx_ctx *ctx, void *d_v, void *d_w, int levels);
 
 int mgxk_codes_to_symbols(mgx_ctx *ctx, const int64_t *d_codes, uint64_t n);
 int mgxk_histogram_reset(mgx_ctx *ctx);

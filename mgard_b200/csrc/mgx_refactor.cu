@@ -482,6 +482,39 @@ int mgxk_decompose(mgx_ctx *ctx, void *d_data, int orthogonal) {
   return rc;
 }
 
+// Hierarchical (no correction) recompose of levels 1..levels on a COMPACT array
+// holding the level-`levels` box; used by the fused inverse for the coarse
+// lattice.  d_v: in/out, d_w: scratch of the same size.
+template <typename T>
+static int recompose_compact_t(mgx_ctx *ctx, T *v, T *w, int levels) {
+  const T *tables = (const T *)ctx->d_tables;
+  const unsigned maxb = ctx->num_sms * 16;
+  uint64_t st[MGX_MAX_D];
+  uint64_t acc = 1;
+  for (int d = MGX_MAX_D - 1; d >= 0; d--) {
+    st[d] = acc;
+    acc *= ctx->lv.n[levels][d];
+  }
+  for (int l = 1; l <= levels; l++) {
+    LevelArgs a = make_level_args(ctx, l);
+    for (int d = 0; d < MGX_MAX_D; d++)
+      a.st[d] = st[d];
+    unsigned g = mgx_grid_for(a.total, 256, maxb);
+    k_level_restore<T><<<g, 256, 0, ctx->stream>>>(v, w, tables, a);
+    k_copy_box<T><<<g, 256, 0, ctx->stream>>>(w, v, a);
+    ctx->launches += 2;
+  }
+  return MGX_SUCCESS;
+}
+
+int mgxk_recompose_compact(mgx_ctx *ctx, void *d_v, void *d_w, int levels) {
+  int rc = mgx_is_f32(ctx)
+               ? recompose_compact_t<float>(ctx, (float *)d_v, (float *)d_w, levels)
+               : recompose_compact_t<double>(ctx, (double *)d_v, (double *)d_w, levels);
+  MGX_CUDA(cudaGetLastError());
+  return rc;
+}
+
 int mgxk_recompose(mgx_ctx *ctx, void *d_data, int orthogonal) {
   int rc = mgx_ensure_workspaces(ctx, true, false);
   if (rc)
