@@ -52,7 +52,7 @@ template <typename T> struct HierArgs {
   uint32_t dict;
   uint32_t tiles[3];
   uint64_t ntiles;
-  uint64_t oct[8][3];            // pass p: byte offsets of the odd x / y / z blocks
+  uint64_t oct[12][3];            // pass p: byte offsets of the odd x / y / z blocks
   T dq;                          // dequantisation step (inverse)
   const T *coarse;               // inverse: nodal values of the level-(L-PASSES) grid
   uint32_t cdim[3];              // its shape
@@ -784,23 +784,104 @@ inv_node(T *tile, const T *__restrict__ tables, const HierArgs<T> &a, uint32_t g
   tile[((gz - z0) * TS::HY + (gy - y0)) * TS::PX + (gx - x0)] = add_rn(c, h0);
 }
 
-// passes PASSES-1 .. 1 of an interior tile over its extended lattice
+// One 2 x 2 x 2 block of the stride-2^P lattice of an interior tile: anchor node
+// (2bi, 2bj, 2bk) * 2^P is known, its up to 7 companions are reconstructed with
+// the march's operation order (x, then y, then z lerps).  The last block of an
+// axis is the +1 halo plane: it has no odd half along that axis (hx / hy / hz).
 template <typename T, bool HALF, class TS, int P>
+__device__ __forceinline__ void
+inv_block(T *tile, const T *__restrict__ tables, const HierArgs<T> &a, uint32_t x0,
+          uint32_t y0, uint32_t z0, int bi, int bj, int bk, bool hx, bool hy,
+          bool hz) {
+  constexpr int H = 1 << P;
+  constexpr int SX = H, SY = H * TS::PX, SZ = H * TS::HY * TS::PX;
+  const int l = a.L - P;
+  const uint64_t sy = a.n[2], sz = (uint64_t)a.n[2] * a.n[1];
+  const uint64_t oX = a.oct[P][0], oY = a.oct[P][1], oZ = a.oct[P][2];
+  const uint16_t *ob = a.sym + ((uint64_t)((z0 >> (P + 1)) + bk) * sz +
+                                (uint64_t)((y0 >> (P + 1)) + bj) * sy +
+                                (x0 >> (P + 1)) + bi);
+  // all symbol loads first (one exposed latency per pass)
+  const bool e0_ = !hx, e1_ = !hy, e2_ = !hx && !hy, e3_ = !hz, e4_ = !hx && !hz,
+             e5_ = !hy && !hz, e6_ = !hx && !hy && !hz;
+  const uint16_t *at[7] = {
+      byte_off((uint16_t *)ob, oX),      byte_off((uint16_t *)ob, oY),
+      byte_off((uint16_t *)ob, oX + oY), byte_off((uint16_t *)ob, oZ),
+      byte_off((uint16_t *)ob, oZ + oX), byte_off((uint16_t *)ob, oZ + oY),
+      byte_off((uint16_t *)ob, oZ + oX + oY)};
+  const bool ex_[7] = {e0_, e1_, e2_, e3_, e4_, e5_, e6_};
+  uint32_t sv[7];
+#pragma unroll
+  for (int i = 0; i < 7; i++)
+    sv[i] = ex_[i] ? (uint32_t)__ldg(at[i]) : 0u;
+  T tx = (T)0.5, ty = (T)0.5, tz = (T)0.5;
+  if (!HALF) {
+    if (!hx) tx = tables[a.roff[l][2] + (x0 >> P) + 2 * bi];
+    if (!hy) ty = tables[a.roff[l][1] + (y0 >> P) + 2 * bj];
+    if (!hz) tz = tables[a.roff[l][0] + (z0 >> P) + 2 * bk];
+  }
+  T *q = tile + (2 * bk) * SZ + (2 * bj) * SY + (2 * bi) * SX;
+  auto plane = [&](const T *r, PlaneP<T> &Q) {
+    const T e0 = r[0];
+    const T r0 = hx ? e0 : r[2 * SX];
+    const T e2 = hy ? e0 : r[2 * SY];
+    const T r2 = (hx || hy) ? e0 : r[2 * SY + 2 * SX];
+    Q.e0 = e0;
+    Q.f0 = mgx_lerp(e0, r0, tx);
+    const T f2 = mgx_lerp(e2, r2, tx);
+    Q.gE = mgx_lerp(e0, e2, ty);
+    Q.gO = mgx_lerp(Q.f0, f2, ty);
+  };
+  PlaneP<T> A, B;
+  plane(q, A);
+  if (e0_) q[SX] = add_rn(coef_of<T>(a, sv[0], at[0]), A.f0);
+  if (e1_) q[SY] = add_rn(coef_of<T>(a, sv[1], at[1]), A.gE);
+  if (e2_) q[SY + SX] = add_rn(coef_of<T>(a, sv[2], at[2]), A.gO);
+  if (!hz) {
+    plane(q + 2 * SZ, B);
+    q[SZ] = add_rn(coef_of<T>(a, sv[3], at[3]), mgx_lerp(A.e0, B.e0, tz));
+    if (e4_)
+      q[SZ + SX] = add_rn(coef_of<T>(a, sv[4], at[4]), mgx_lerp(A.f0, B.f0, tz));
+    if (e5_)
+      q[SZ + SY] = add_rn(coef_of<T>(a, sv[5], at[5]), mgx_lerp(A.gE, B.gE, tz));
+    if (e6_)
+      q[SZ + SY + SX] =
+          add_rn(coef_of<T>(a, sv[6], at[6]), mgx_lerp(A.gO, B.gO, tz));
+  }
+}
+
+// pass P over the extended lattice (interior_only: stride-1 pass of tiles whose
+// results are copied out of shared memory afterwards)
+template <typename T, bool HALF, class TS, int P>
+__device__ __forceinline__ void
+inv_pass(T *tile, const T *__restrict__ tables, const HierArgs<T> &a, uint32_t x0,
+         uint32_t y0, uint32_t z0, bool interior_only) {
+  constexpr int NBX = (TS::TX >> (P + 1)) + 1;
+  constexpr int NBY = TS::RY ? (TS::TY >> (P + 1)) + 1 : 1;
+  constexpr int NBZ = TS::RZ ? (TS::TZ >> (P + 1)) + 1 : 1;
+  // spread the coarse passes over different warps
+  constexpr int FIRST = (P == 1 || NBX * NBY * NBZ >= HIER_THREADS) ? 0
+                        : (P == 2 ? 160 : 224);
+  for (int id = (int)threadIdx.x - FIRST; id >= 0 && id < NBX * NBY * NBZ;
+       id += HIER_THREADS - FIRST) {
+    const int bi = id % NBX, bj = (id / NBX) % NBY, bk = id / (NBX * NBY);
+    const bool hx = bi == NBX - 1, hy = !TS::RY || bj == NBY - 1,
+               hz = !TS::RZ || bk == NBZ - 1;
+    if (interior_only && (hx || (TS::RY && hy) || (TS::RZ && hz)))
+      continue;
+    inv_block<T, HALF, TS, P>(tile, tables, a, x0, y0, z0, bi, bj, bk, hx, hy, hz);
+  }
+}
+
+// passes PASSES-1 .. LAST of an interior tile, a barrier before each
+template <typename T, bool HALF, class TS, int P, int LAST>
 __device__ __forceinline__ void
 inv_coarse_passes(T *tile, const T *__restrict__ tables, const HierArgs<T> &a,
                   uint32_t x0, uint32_t y0, uint32_t z0) {
-  if constexpr (P >= 1) {
-    constexpr int NX = (TS::TX >> P) + 1, NY = TS::RY ? (TS::TY >> P) + 1 : 1,
-                  NZ = TS::RZ ? (TS::TZ >> P) + 1 : 1;
+  if constexpr (P >= LAST) {
     __syncthreads();
-    for (int id = threadIdx.x; id < NX * NY * NZ; id += HIER_THREADS) {
-      const int i = id % NX, j = (id / NX) % NY, k = id / (NX * NY);
-      if (((i | j | k) & 1) == 0)
-        continue; // node of a coarser lattice
-      inv_node<T, HALF, TS>(tile, tables, a, x0 + (i << P), y0 + (j << P),
-                            z0 + (k << P), x0, y0, z0, a.L - P);
-    }
-    inv_coarse_passes<T, HALF, TS, P - 1>(tile, tables, a, x0, y0, z0);
+    inv_pass<T, HALF, TS, P>(tile, tables, a, x0, y0, z0, P == 0);
+    inv_coarse_passes<T, HALF, TS, P - 1, LAST>(tile, tables, a, x0, y0, z0);
   }
 }
 
@@ -864,7 +945,8 @@ __global__ void __launch_bounds__(HIER_THREADS, 3)
         tile[(((kk << P) * TS::HY) + (j << P)) * TS::PX + (i << P)] =
             a.coarse[((uint64_t)ck * a.cdim[1] + cj) * a.cdim[2] + ci];
       }
-      inv_coarse_passes<T, HALF, TS, P - 1>(tile, tables, a, x0, y0, z0);
+      inv_coarse_passes<T, HALF, TS, P - 1, (TS::RZ ? 1 : 0)>(tile, tables, a, x0, y0,
+                                                               z0);
       __syncthreads();
       if constexpr (TS::RZ) {
         // stride 1: the forward march run backwards (x, then y, then z lerps of
@@ -915,16 +997,7 @@ __global__ void __launch_bounds__(HIER_THREADS, 3)
           A = B;
         }
       } else {
-        // 1-D / 2-D tiles: stride-1 nodes of the interior, then copy out
-        for (int id = tid; id < TS::TZ * TS::TY * TS::TX; id += HIER_THREADS) {
-          const int i = id % TS::TX, j = (id / TS::TX) % TS::TY,
-                    kk = id / (TS::TX * TS::TY);
-          if (((i | j | kk) & 1) == 0)
-            continue;
-          inv_node<T, HALF, TS>(tile, tables, a, x0 + i, y0 + j, z0 + kk, x0, y0, z0,
-                                a.L);
-        }
-        __syncthreads();
+        // 1-D / 2-D tiles: the stride-1 pass ran in shared memory; copy out
         for (int id = tid; id < TS::TZ * TS::TY * TS::TX; id += HIER_THREADS) {
           const int i = id % TS::TX, j = (id / TS::TX) % TS::TY,
                     kk = id / (TS::TX * TS::TY);
@@ -1021,7 +1094,7 @@ int launch_forward(mgx_ctx *ctx, const void *d_in, HierArgs<T> &a) {
                                                          smem));
   unsigned grid = (unsigned)std::min<uint64_t>(
       a.ntiles, (uint64_t)std::max(occ, 1) * ctx->num_sms);
-  for (int p = 0; p < 8; p++) {
+  for (int p = 0; p < 12; p++) {
     const int l = a.L - p;
     const uint64_t sy = a.n[2], sz = (uint64_t)a.n[2] * a.n[1];
     for (int d = 0; d < 3; d++)
@@ -1117,7 +1190,7 @@ int launch_inverse(mgx_ctx *ctx, void *d_out, HierArgs<T> &a) {
   for (int d = 0; d < 3; d++)
     a.tiles[d] = (a.n[d] + tdim[d] - 1) / tdim[d];
   a.ntiles = (uint64_t)a.tiles[0] * a.tiles[1] * a.tiles[2];
-  for (int p = 0; p < 8; p++) {
+  for (int p = 0; p < 12; p++) {
     const int l = a.L - p;
     const uint64_t sy = a.n[2], sz = (uint64_t)a.n[2] * a.n[1];
     for (int d = 0; d < 3; d++)
