@@ -784,36 +784,47 @@ inv_node(T *tile, const T *__restrict__ tables, const HierArgs<T> &a, uint32_t g
   tile[((gz - z0) * TS::HY + (gy - y0)) * TS::PX + (gx - x0)] = add_rn(c, h0);
 }
 
-// One 2 x 2 x 2 block of the stride-2^P lattice of an interior tile: anchor node
-// (2bi, 2bj, 2bk) * 2^P is known, its up to 7 companions are reconstructed with
-// the march's operation order (x, then y, then z lerps).  The last block of an
-// axis is the +1 halo plane: it has no odd half along that axis (hx / hy / hz).
+// addresses of the 7 companion symbols of block (bi, bj, bk) of pass P
+template <typename T, int P>
+__device__ __forceinline__ void
+block_sym_ptrs(const HierArgs<T> &a, uint32_t x0, uint32_t y0, uint32_t z0, int bi,
+               int bj, int bk, const uint16_t *(&at)[7]) {
+  const uint64_t sy = a.n[2], sz = (uint64_t)a.n[2] * a.n[1];
+  const uint64_t oX = a.oct[P][0], oY = a.oct[P][1], oZ = a.oct[P][2];
+  uint16_t *ob = a.sym + ((uint64_t)((z0 >> (P + 1)) + bk) * sz +
+                          (uint64_t)((y0 >> (P + 1)) + bj) * sy +
+                          (x0 >> (P + 1)) + bi);
+  at[0] = byte_off(ob, oX);
+  at[1] = byte_off(ob, oY);
+  at[2] = byte_off(ob, oX + oY);
+  at[3] = byte_off(ob, oZ);
+  at[4] = byte_off(ob, oZ + oX);
+  at[5] = byte_off(ob, oZ + oY);
+  at[6] = byte_off(ob, oZ + oX + oY);
+}
+
+// which of the 7 companions exist in a block with missing odd halves
+__device__ __forceinline__ void block_exists(bool hx, bool hy, bool hz, bool (&e)[7]) {
+  e[0] = !hx;
+  e[1] = !hy;
+  e[2] = !hx && !hy;
+  e[3] = !hz;
+  e[4] = !hx && !hz;
+  e[5] = !hy && !hz;
+  e[6] = !hx && !hy && !hz;
+}
+
 template <typename T, bool HALF, class TS, int P>
 __device__ __forceinline__ void
-inv_block(T *tile, const T *__restrict__ tables, const HierArgs<T> &a, uint32_t x0,
-          uint32_t y0, uint32_t z0, int bi, int bj, int bk, bool hx, bool hy,
-          bool hz) {
+inv_block_core(T *tile, const T *__restrict__ tables, const HierArgs<T> &a,
+               uint32_t x0, uint32_t y0, uint32_t z0, int bi, int bj, int bk, bool hx,
+               bool hy, bool hz, const uint32_t (&sv)[7],
+               const uint16_t *const (&at)[7]) {
   constexpr int H = 1 << P;
   constexpr int SX = H, SY = H * TS::PX, SZ = H * TS::HY * TS::PX;
   const int l = a.L - P;
-  const uint64_t sy = a.n[2], sz = (uint64_t)a.n[2] * a.n[1];
-  const uint64_t oX = a.oct[P][0], oY = a.oct[P][1], oZ = a.oct[P][2];
-  const uint16_t *ob = a.sym + ((uint64_t)((z0 >> (P + 1)) + bk) * sz +
-                                (uint64_t)((y0 >> (P + 1)) + bj) * sy +
-                                (x0 >> (P + 1)) + bi);
-  // all symbol loads first (one exposed latency per pass)
-  const bool e0_ = !hx, e1_ = !hy, e2_ = !hx && !hy, e3_ = !hz, e4_ = !hx && !hz,
-             e5_ = !hy && !hz, e6_ = !hx && !hy && !hz;
-  const uint16_t *at[7] = {
-      byte_off((uint16_t *)ob, oX),      byte_off((uint16_t *)ob, oY),
-      byte_off((uint16_t *)ob, oX + oY), byte_off((uint16_t *)ob, oZ),
-      byte_off((uint16_t *)ob, oZ + oX), byte_off((uint16_t *)ob, oZ + oY),
-      byte_off((uint16_t *)ob, oZ + oX + oY)};
-  const bool ex_[7] = {e0_, e1_, e2_, e3_, e4_, e5_, e6_};
-  uint32_t sv[7];
-#pragma unroll
-  for (int i = 0; i < 7; i++)
-    sv[i] = ex_[i] ? (uint32_t)__ldg(at[i]) : 0u;
+  bool e[7];
+  block_exists(hx, hy, hz, e);
   T tx = (T)0.5, ty = (T)0.5, tz = (T)0.5;
   if (!HALF) {
     if (!hx) tx = tables[a.roff[l][2] + (x0 >> P) + 2 * bi];
@@ -834,20 +845,41 @@ inv_block(T *tile, const T *__restrict__ tables, const HierArgs<T> &a, uint32_t 
   };
   PlaneP<T> A, B;
   plane(q, A);
-  if (e0_) q[SX] = add_rn(coef_of<T>(a, sv[0], at[0]), A.f0);
-  if (e1_) q[SY] = add_rn(coef_of<T>(a, sv[1], at[1]), A.gE);
-  if (e2_) q[SY + SX] = add_rn(coef_of<T>(a, sv[2], at[2]), A.gO);
+  if (e[0]) q[SX] = add_rn(coef_of<T>(a, sv[0], at[0]), A.f0);
+  if (e[1]) q[SY] = add_rn(coef_of<T>(a, sv[1], at[1]), A.gE);
+  if (e[2]) q[SY + SX] = add_rn(coef_of<T>(a, sv[2], at[2]), A.gO);
   if (!hz) {
     plane(q + 2 * SZ, B);
     q[SZ] = add_rn(coef_of<T>(a, sv[3], at[3]), mgx_lerp(A.e0, B.e0, tz));
-    if (e4_)
+    if (e[4])
       q[SZ + SX] = add_rn(coef_of<T>(a, sv[4], at[4]), mgx_lerp(A.f0, B.f0, tz));
-    if (e5_)
+    if (e[5])
       q[SZ + SY] = add_rn(coef_of<T>(a, sv[5], at[5]), mgx_lerp(A.gE, B.gE, tz));
-    if (e6_)
+    if (e[6])
       q[SZ + SY + SX] =
           add_rn(coef_of<T>(a, sv[6], at[6]), mgx_lerp(A.gO, B.gO, tz));
   }
+}
+
+// One 2 x 2 x 2 block of the stride-2^P lattice of an interior tile: anchor node
+// (2bi, 2bj, 2bk) * 2^P is known, its up to 7 companions are reconstructed with
+// the march's operation order (x, then y, then z lerps).  The last block of an
+// axis is the +1 halo plane: it has no odd half along that axis (hx / hy / hz).
+template <typename T, bool HALF, class TS, int P>
+__device__ __forceinline__ void
+inv_block(T *tile, const T *__restrict__ tables, const HierArgs<T> &a, uint32_t x0,
+          uint32_t y0, uint32_t z0, int bi, int bj, int bk, bool hx, bool hy,
+          bool hz) {
+  const uint16_t *at[7];
+  block_sym_ptrs<T, P>(a, x0, y0, z0, bi, bj, bk, at);
+  bool e[7];
+  block_exists(hx, hy, hz, e);
+  uint32_t sv[7];
+#pragma unroll
+  for (int i = 0; i < 7; i++)
+    sv[i] = e[i] ? (uint32_t)__ldg(at[i]) : 0u; // all loads first
+  inv_block_core<T, HALF, TS, P>(tile, tables, a, x0, y0, z0, bi, bj, bk, hx, hy, hz,
+                                 sv, at);
 }
 
 // pass P over the extended lattice (interior_only: stride-1 pass of tiles whose
@@ -886,7 +918,7 @@ inv_coarse_passes(T *tile, const T *__restrict__ tables, const HierArgs<T> &a,
 }
 
 template <typename T, bool HALF, class TS>
-__global__ void __launch_bounds__(HIER_THREADS, 3)
+__global__ void __launch_bounds__(HIER_THREADS, 5)
     k_hier_inverse(T *__restrict__ out, const T *__restrict__ tables,
                    const __grid_constant__ HierArgs<T> a) {
   extern __shared__ __align__(16) unsigned char smem[];
@@ -1059,6 +1091,218 @@ __global__ void __launch_bounds__(HIER_THREADS, 3)
   }
 }
 
+// 3-D specialisation with everything a tile needs from global memory (its
+// stride-1 symbols, the symbols of its two coarse passes, its coarse-lattice
+// values) fetched into registers ONE TILE AHEAD: the loads of tile i+1 are in
+// flight while tile i runs its four barrier-separated phases out of registers and
+// shared memory, so no global latency sits on a tile's critical path.
+// Static roles: threads 0..152 own the 17x3x3 blocks of pass 1, threads 160..195
+// the 9x2x2 blocks of pass 2, threads 224..255 the 9x2x2 coarse-lattice nodes;
+// every thread owns two stride-1 blocks (x pair, y pair, z half) of the interior.
+template <typename T> struct InvPref {
+  uint32_t p0[7]; // stride-1 symbols: low half = first z block, high = second
+  uint32_t pc[7]; // symbols of this thread's coarse-pass block
+  T deep[2];
+};
+
+template <typename T, bool HALF>
+__global__ void __launch_bounds__(HIER_THREADS, 3)
+    k_hier_inverse3d(T *__restrict__ out, const T *__restrict__ tables,
+                     const __grid_constant__ HierArgs<T> a) {
+  typedef TileShape<3, 3, 6> TS;
+  constexpr int P = TS::PASSES;
+  extern __shared__ __align__(16) unsigned char smem[];
+  T *tile = (T *)smem;
+  const int tid = threadIdx.x;
+  const uint32_t nz = a.n[0], ny = a.n[1], nx = a.n[2];
+  const uint64_t sy = nx, sz = (uint64_t)nx * ny;
+  // static roles
+  const int k = tid & 31, ya = (tid >> 5) & 3, zb = (tid >> 7) * 2;
+  const bool r1 = tid < 153, r2 = tid >= 160 && tid < 196, rd = tid >= 224;
+  const int id1 = tid, id2 = tid - 160, idd = tid - 224;
+  const int b1i = id1 % 17, b1j = (id1 / 17) % 3, b1k = id1 / 51;
+  const int b2i = id2 % 9, b2j = (id2 / 9) % 2, b2k = id2 / 18;
+  const bool h1x = b1i == 16, h1y = b1j == 2, h1z = b1k == 2;
+  const bool h2x = b2i == 8, h2y = b2j == 1, h2z = b2k == 1;
+
+  auto is_regular = [&](uint32_t x0, uint32_t y0, uint32_t z0) {
+    return x0 + TS::TX <= nx - 1 && y0 + TS::TY <= ny - 1 && z0 + TS::TZ <= nz - 1;
+  };
+  auto deep_value = [&](int id, uint32_t x0, uint32_t y0, uint32_t z0) {
+    const int i = id % 9, j = (id / 9) % 2, kk = id / 18;
+    const uint32_t ci = coarse_index(x0 + (i << P), nx, P, a.cdim[2]),
+                   cj = coarse_index(y0 + (j << P), ny, P, a.cdim[1]),
+                   ck = coarse_index(z0 + (kk << P), nz, P, a.cdim[0]);
+    return __ldg(a.coarse + ((uint64_t)ck * a.cdim[1] + cj) * a.cdim[2] + ci);
+  };
+  auto prefetch = [&](uint32_t x0, uint32_t y0, uint32_t z0, InvPref<T> &pf) {
+    if (!is_regular(x0, y0, z0))
+      return;
+    const uint16_t *at[7];
+    block_sym_ptrs<T, 0>(a, x0, y0, z0, k, ya, zb, at);
+#pragma unroll
+    for (int i = 0; i < 7; i++)
+      pf.p0[i] = (uint32_t)__ldg(at[i]) | ((uint32_t)__ldg(at[i] + sz) << 16);
+    bool e[7];
+    if (r1) {
+      block_sym_ptrs<T, 1>(a, x0, y0, z0, b1i, b1j, b1k, at);
+      block_exists(h1x, h1y, h1z, e);
+#pragma unroll
+      for (int i = 0; i < 7; i++)
+        pf.pc[i] = e[i] ? (uint32_t)__ldg(at[i]) : 0u;
+    } else if (r2) {
+      block_sym_ptrs<T, 2>(a, x0, y0, z0, b2i, b2j, b2k, at);
+      block_exists(h2x, h2y, h2z, e);
+#pragma unroll
+      for (int i = 0; i < 7; i++)
+        pf.pc[i] = e[i] ? (uint32_t)__ldg(at[i]) : 0u;
+    } else if (rd) {
+      pf.deep[0] = deep_value(idd, x0, y0, z0);
+      if (idd + 32 < 36)
+        pf.deep[1] = deep_value(idd + 32, x0, y0, z0);
+    }
+  };
+
+  const uint32_t T2 = a.tiles[2], T1 = a.tiles[1], T0 = a.tiles[0];
+  uint32_t cx = blockIdx.x % T2, cy = (blockIdx.x / T2) % T1,
+           cz = blockIdx.x / (T2 * T1);
+  const uint32_t dx = gridDim.x % T2, dy = (gridDim.x / T2) % T1,
+                 dz = gridDim.x / (T2 * T1);
+  InvPref<T> cur = {}, nxt = {};
+  if (cz < T0)
+    prefetch(cx * TS::TX, cy * TS::TY, cz * TS::TZ, cur);
+  while (cz < T0) {
+    const uint32_t z0 = cz * TS::TZ, y0 = cy * TS::TY, x0 = cx * TS::TX;
+    uint32_t ncx = cx + dx, ncy = cy + dy, ncz = cz + dz;
+    if (ncx >= T2) {
+      ncx -= T2;
+      ++ncy;
+    }
+    if (ncy >= T1) {
+      ncy -= T1;
+      ++ncz;
+    }
+    if (ncz < T0)
+      prefetch(ncx * TS::TX, ncy * TS::TY, ncz * TS::TZ, nxt);
+    __syncthreads(); // previous tile no longer read
+    if (is_regular(x0, y0, z0)) {
+      if (rd) {
+        {
+          const int i = idd % 9, j = (idd / 9) % 2, kk = idd / 18;
+          tile[(((kk << P) * TS::HY) + (j << P)) * TS::PX + (i << P)] = cur.deep[0];
+        }
+        if (idd + 32 < 36) {
+          const int id = idd + 32, i = id % 9, j = (id / 9) % 2, kk = id / 18;
+          tile[(((kk << P) * TS::HY) + (j << P)) * TS::PX + (i << P)] = cur.deep[1];
+        }
+      }
+      __syncthreads();
+      const uint16_t *at[7];
+      if (r2) {
+        block_sym_ptrs<T, 2>(a, x0, y0, z0, b2i, b2j, b2k, at);
+        inv_block_core<T, HALF, TS, 2>(tile, tables, a, x0, y0, z0, b2i, b2j, b2k, h2x,
+                                       h2y, h2z, cur.pc, at);
+      }
+      __syncthreads();
+      if (r1) {
+        block_sym_ptrs<T, 1>(a, x0, y0, z0, b1i, b1j, b1k, at);
+        inv_block_core<T, HALF, TS, 1>(tile, tables, a, x0, y0, z0, b1i, b1j, b1k, h1x,
+                                       h1y, h1z, cur.pc, at);
+      }
+      __syncthreads();
+      // stride 1: the forward march run backwards, results straight to global
+      constexpr int SY = TS::PX, SZ = TS::HY * TS::PX;
+      const int l = a.L;
+      T tx = (T)0.5, ty = (T)0.5;
+      if (!HALF) {
+        tx = tables[a.roff[l][2] + x0 + 2 * k];
+        ty = tables[a.roff[l][1] + y0 + 2 * ya];
+      }
+      block_sym_ptrs<T, 0>(a, x0, y0, z0, k, ya, zb, at);
+      const T *p = tile + (2 * zb) * SZ + (2 * ya) * SY + 2 * k;
+      T *g = out + ((uint64_t)(z0 + 2 * zb) * sz + (uint64_t)(y0 + 2 * ya) * sy + x0 +
+                    2 * k);
+      auto plane = [&](const T *q, PlaneP<T> &Q) {
+        const T e0 = q[0], r0 = q[2], e2 = q[2 * SY], r2_ = q[2 * SY + 2];
+        Q.e0 = e0;
+        Q.f0 = mgx_lerp(e0, r0, tx);
+        const T f2 = mgx_lerp(e2, r2_, tx);
+        Q.gE = mgx_lerp(e0, e2, ty);
+        Q.gO = mgx_lerp(Q.f0, f2, ty);
+      };
+      PlaneP<T> A, B;
+      plane(p, A);
+#pragma unroll
+      for (int b = 0; b < 2; b++) {
+        const T *q = p + (2 * b) * SZ;
+        T *gb = g + (uint64_t)(2 * b) * sz;
+        plane(q + 2 * SZ, B);
+        T tz = (T)0.5;
+        if (!HALF)
+          tz = tables[a.roff[l][0] + z0 + 2 * (zb + b)];
+        uint32_t sv[7];
+#pragma unroll
+        for (int i = 0; i < 7; i++)
+          sv[i] = (cur.p0[i] >> (16 * b)) & 0xffffu;
+        const uint64_t bo = (uint64_t)b * sz;
+        gb[0] = A.e0;
+        gb[1] = add_rn(coef_of<T>(a, sv[0], at[0] + bo), A.f0);
+        gb[sy] = add_rn(coef_of<T>(a, sv[1], at[1] + bo), A.gE);
+        gb[sy + 1] = add_rn(coef_of<T>(a, sv[2], at[2] + bo), A.gO);
+        gb[sz] = add_rn(coef_of<T>(a, sv[3], at[3] + bo), mgx_lerp(A.e0, B.e0, tz));
+        gb[sz + 1] = add_rn(coef_of<T>(a, sv[4], at[4] + bo), mgx_lerp(A.f0, B.f0, tz));
+        gb[sz + sy] = add_rn(coef_of<T>(a, sv[5], at[5] + bo), mgx_lerp(A.gE, B.gE, tz));
+        gb[sz + sy + 1] =
+            add_rn(coef_of<T>(a, sv[6], at[6] + bo), mgx_lerp(A.gO, B.gO, tz));
+        A = B;
+      }
+    } else {
+      // tile touching the last node of an axis: every level by the generic
+      // per-node rule on the clipped extended box
+      const uint32_t ez = min((uint32_t)TS::HZ, nz - z0),
+                     ey = min((uint32_t)TS::HY, ny - y0),
+                     ex = min((uint32_t)TS::TX + 1, nx - x0);
+      const uint32_t cnt = ez * ey * ex;
+      const uint32_t *nl = &a.nl[0][0];
+      for (uint32_t id = tid; id < cnt; id += HIER_THREADS) {
+        const uint32_t i = id % ex, j = (id / ex) % ey, kk = id / (ex * ey);
+        const uint32_t gx = x0 + i, gy = y0 + j, gz = z0 + kk;
+        const int l = max(axis_info(gx, nx, a.L, nl, 2).lvl,
+                          max(axis_info(gy, ny, a.L, nl, 1).lvl,
+                              axis_info(gz, nz, a.L, nl, 0).lvl));
+        if (l <= a.L - P) {
+          const uint32_t ci = coarse_index(gx, nx, P, a.cdim[2]),
+                         cj = coarse_index(gy, ny, P, a.cdim[1]),
+                         ck = coarse_index(gz, nz, P, a.cdim[0]);
+          tile[(kk * TS::HY + j) * TS::PX + i] =
+              a.coarse[((uint64_t)ck * a.cdim[1] + cj) * a.cdim[2] + ci];
+        }
+      }
+      for (int pp = P - 1; pp >= 0; pp--) {
+        __syncthreads();
+        for (uint32_t id = tid; id < cnt; id += HIER_THREADS) {
+          const uint32_t i = id % ex, j = (id / ex) % ey, kk = id / (ex * ey);
+          inv_node<T, HALF, TS>(tile, tables, a, x0 + i, y0 + j, z0 + kk, x0, y0, z0,
+                                a.L - pp);
+        }
+      }
+      __syncthreads();
+      const uint32_t vz = min((uint32_t)TS::TZ, nz - z0),
+                     vy = min((uint32_t)TS::TY, ny - y0),
+                     vx = min((uint32_t)TS::TX, nx - x0);
+      for (uint32_t id = tid; id < vz * vy * vx; id += HIER_THREADS) {
+        const uint32_t i = id % vx, j = (id / vx) % vy, kk = id / (vx * vy);
+        out[(uint64_t)(z0 + kk) * sz + (uint64_t)(y0 + j) * sy + x0 + i] =
+            tile[(kk * TS::HY + j) * TS::PX + i];
+      }
+    }
+    cur = nxt;
+    cx = ncx;
+    cy = ncy;
+    cz = ncz;
+  }
+}
+
 // symbols of the coarse box [0, n_{L-P})^3 -> compact array of coefficients
 template <typename T>
 __global__ void __launch_bounds__(256)
@@ -1227,7 +1471,9 @@ int launch_inverse(mgx_ctx *ctx, void *d_out, HierArgs<T> &a) {
     return rc;
   a.coarse = (const T *)ctx->d_coarse0;
   const size_t smem = sizeof(T) * TS::tile_elems;
-  auto kern = k_hier_inverse<T, HALF, TS>;
+  void (*kern)(T *, const T *, const HierArgs<T>) = k_hier_inverse<T, HALF, TS>;
+  if (TS::RZ)
+    kern = k_hier_inverse3d<T, HALF>;
   MGX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)smem));
   int occ = 1;
