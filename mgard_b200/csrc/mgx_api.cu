@@ -217,7 +217,7 @@ int mgx_plan(mgx_ctx *ctx, int D, const uint64_t *shape, int dtype,
   MGX_CUDA(cudaMalloc(&ctx->d_chunk_bits, nchunk * 8));
   MGX_CUDA(cudaMalloc(&ctx->d_chunk_off, (nchunk + 1) * 8));
   MGX_CUDA(cudaMalloc(&ctx->d_scan_state, (nchunk + 2) * 8));
-  MGX_CUDA(cudaMalloc(&ctx->d_lut, 4096 * 4));
+  MGX_CUDA(cudaMalloc(&ctx->d_lut, 4096 * 4 + 4096 * 8)); // single + multi-symbol
   rc = grow_outliers(ctx, std::max<uint64_t>(1u << 16, N / 64));
   if (rc)
     return rc;

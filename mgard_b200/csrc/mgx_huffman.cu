@@ -906,6 +906,171 @@ __global__ void __launch_bounds__(128)
   }
 }
 
+// Multi-symbol prefix table: entry for a 12-bit window = up to four complete
+// codes found in it (smooth fields spend 1-2 bits on most symbols, so one
+// look-up usually yields 3-4 symbols).
+//   bits 0..3 total length, bits 4..6 count (0 = first code longer than the
+//   window), then four 13-bit symbols from bit 8 (dictionaries up to 8192).
+__global__ void __launch_bounds__(256)
+    k_build_mlut(const uint32_t *__restrict__ lut1, u64 *__restrict__ mlut) {
+  for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < (1u << LUT_BITS);
+       idx += gridDim.x * blockDim.x) {
+    uint32_t pos = 0, cnt = 0;
+    u64 e = 0;
+    while (cnt < 4) {
+      const uint32_t sub = (idx << pos) & ((1u << LUT_BITS) - 1);
+      const uint32_t t = lut1[sub];
+      const uint32_t len = t >> 16;
+      if (len == 0 || len > LUT_BITS - pos)
+        break; // not fully inside the window
+      e |= (u64)(t & 0x1fffu) << (8 + 13 * cnt);
+      pos += len;
+      ++cnt;
+    }
+    mlut[idx] = e | pos | ((u64)cnt << 4);
+  }
+}
+
+constexpr int DEC_THREADS = 128;
+constexpr int DEC_RING = 20; // symbols per thread (40 B: 2-way bank conflicts)
+
+// DecodeFunctor, Decode.hpp:14-130: one thread per chunk; the stream is read in
+// 32-bit units into a 64-bit bit buffer, up to four symbols come out of one
+// shared-memory look-up, and symbols leave through a small per-thread ring in
+// shared memory as 16-byte stores.
+__global__ void __launch_bounds__(DEC_THREADS)
+    k_decode_multi(const u64 *__restrict__ packed, const u64 *__restrict__ meta,
+                   uint64_t nchunk, uint32_t chunk, uint64_t n,
+                   const u64 *__restrict__ db, const u64 *__restrict__ g_mlut,
+                   uint16_t *__restrict__ sym) {
+  __shared__ u64 mlut[1 << LUT_BITS];
+  __shared__ u64 s_first[64], s_entry[64];
+  __shared__ __align__(8) uint16_t s_ring[DEC_THREADS * DEC_RING];
+  for (uint32_t i = threadIdx.x; i < (1u << LUT_BITS); i += blockDim.x)
+    mlut[i] = g_mlut[i];
+  if (threadIdx.x < 64) {
+    s_first[threadIdx.x] = db[threadIdx.x];
+    s_entry[threadIdx.x] = db[64 + threadIdx.x];
+  }
+  __syncthreads();
+  const u64 *keys = db + 128;
+  uint16_t *ring = s_ring + threadIdx.x * DEC_RING;
+  for (uint64_t c = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; c < nchunk;
+       c += (uint64_t)gridDim.x * blockDim.x) {
+    const u64 *w = packed + meta[nchunk + c];
+    const uint32_t *w32 = (const uint32_t *)w; // unit u = w32[u ^ 1]
+    const uint64_t total = meta[c];
+    const uint32_t nunits = (uint32_t)(((total + 63) >> 6) << 1);
+    const uint64_t base = c * chunk;
+    const uint32_t count = (uint32_t)min((uint64_t)chunk, n - base);
+    uint16_t *dst = sym + base;
+    auto unit = [&](uint32_t u) -> uint32_t { return u < nunits ? w32[u ^ 1] : 0u; };
+    u64 buf = ((u64)unit(0) << 32) | unit(1);
+    uint32_t nbits = 64, next_unit = 2;
+    uint64_t pos = 0;
+    uint32_t k = 0, produced = 0, written = 0;
+    while (produced < count) {
+      const u64 e = mlut[(uint32_t)(buf >> (64 - LUT_BITS))];
+      uint32_t cnt = (uint32_t)(e >> 4) & 7u;
+      uint32_t len = (uint32_t)e & 15u;
+      if (cnt == 0) {
+        // first code is longer than the window: canonical search on the raw
+        // words (Decode.hpp:60-66), then re-prime the bit buffer
+        const uint32_t wi = (uint32_t)(pos >> 6), used = (uint32_t)(pos & 63);
+        const u64 cur = w[wi];
+        const u64 nxt = ((uint64_t)(wi + 1) * 64 < total) ? w[wi + 1] : 0;
+        const u64 window = used ? ((cur << used) | (nxt >> (64 - used))) : cur;
+        uint32_t l = LUT_BITS;
+        u64 v;
+        do {
+          ++l;
+          v = window >> (64 - l);
+        } while (v < s_first[l] && l < 63);
+        ring[k] = (uint16_t)keys[s_entry[l] + v - s_first[l]];
+        ++k;
+        ++produced;
+        pos += l;
+        const uint32_t u0 = (uint32_t)(pos >> 5), r = (uint32_t)(pos & 31);
+        buf = (((u64)unit(u0) << 32) | unit(u0 + 1)) << r;
+        nbits = 64 - r;
+        next_unit = u0 + 2;
+      } else {
+        cnt = min(cnt, count - produced);
+        ring[k + 0] = (uint16_t)((e >> 8) & 0x1fff);
+        ring[k + 1] = (uint16_t)((e >> 21) & 0x1fff);
+        ring[k + 2] = (uint16_t)((e >> 34) & 0x1fff);
+        ring[k + 3] = (uint16_t)((e >> 47) & 0x1fff);
+        k += cnt;
+        produced += cnt;
+        pos += len;
+        buf <<= len;
+        nbits -= len;
+      }
+      if (nbits <= 32) {
+        buf |= (u64)unit(next_unit) << (32 - nbits);
+        nbits += 32;
+        ++next_unit;
+      }
+      if (k >= 8) {
+        const uint2 a0 = *reinterpret_cast<const uint2 *>(ring);
+        const uint2 a1 = *reinterpret_cast<const uint2 *>(ring + 4);
+        *reinterpret_cast<uint4 *>(dst + written) = make_uint4(a0.x, a0.y, a1.x, a1.y);
+        *reinterpret_cast<uint2 *>(ring) = *reinterpret_cast<const uint2 *>(ring + 8);
+        written += 8;
+        k -= 8;
+      }
+    }
+    for (uint32_t j = 0; j < k; j++)
+      dst[written + j] = ring[j];
+  }
+}
+
+// out[0] = status (0 ok, 1 bad signature, 2 truncated), then n, dict, chunk,
+// huffmeta, decodebook bytes, packed words, outlier count
+__global__ void k_parse_header(const uint8_t *in, uint64_t bytes, u64 *out) {
+  const char sig[7] = {'M', 'G', 'X', 'H', 'U', 'F', 'F'};
+  for (int i = 0; i < 8; i++)
+    out[i] = 0;
+  for (int i = 0; i < 7; i++)
+    if (in[i] != (uint8_t)sig[i]) {
+      out[0] = 1;
+      return;
+    }
+  const u64 n = *(const u64 *)(in + 8);
+  const int32_t dict = *(const int32_t *)(in + 16);
+  const int32_t chunk = *(const int32_t *)(in + 20);
+  const u64 huffmeta = *(const u64 *)(in + 24);
+  out[1] = n;
+  out[2] = (u64)(int64_t)dict;
+  out[3] = (u64)(int64_t)chunk;
+  out[4] = huffmeta;
+  if (chunk <= 0 || n == 0) {
+    out[0] = 2;
+    return;
+  }
+  const u64 nchunk = (n - 1) / (u64)chunk + 1;
+  const u64 off_dbs = 32 + 16 * nchunk;
+  if (off_dbs + 8 > bytes) {
+    out[0] = 2;
+    return;
+  }
+  const u64 dbs = *(const u64 *)(in + off_dbs);
+  out[5] = dbs;
+  const u64 off_ddata = off_dbs + 8 + dbs;
+  if (dbs > bytes || off_ddata + 8 > bytes) {
+    out[0] = 2;
+    return;
+  }
+  const u64 ddata = *(const u64 *)(in + off_ddata);
+  out[6] = ddata;
+  const u64 off_outc = off_ddata + 8 + 8 * ddata;
+  if (ddata > bytes / 8 || off_outc + 8 > bytes) {
+    out[0] = 2;
+    return;
+  }
+  out[7] = *(const u64 *)(in + off_outc);
+}
+
 struct ParsedHeader {
   uint64_t n, nchunk, dbs, ddata, n_out;
   int32_t dict, chunk;
@@ -923,50 +1088,41 @@ int mgxk_decode_container(mgx_ctx *ctx, const uint8_t *d_in, uint64_t bytes,
     ctx->err = "bad Huffman container (size/alignment)";
     return MGX_FAILURE;
   }
-  // fixed part of the header
-  uint8_t *hs = (uint8_t *)ctx->h_scalars;
-  MGX_CUDA(cudaMemcpyAsync(hs, d_in, 32, cudaMemcpyDeviceToHost, ctx->stream));
+  // the section sizes chain through the container (Huffman.hpp:453-518): one
+  // single-thread kernel follows the chain, one read-back brings it to the host
+  k_parse_header<<<1, 1, 0, ctx->stream>>>(d_in, bytes, (u64 *)ctx->d_scalars);
+  ctx->launches++;
+  MGX_CUDA(cudaMemcpyAsync(ctx->h_scalars, ctx->d_scalars, MGX_SC_COUNT * 8,
+                           cudaMemcpyDeviceToHost, ctx->stream));
   MGX_CUDA(cudaStreamSynchronize(ctx->stream));
-  if (memcmp(hs, "MGXHUFF", 7) != 0) {
+  const uint64_t *hs = ctx->h_scalars;
+  if (hs[0] == 1) {
     ctx->err = "Huffman signature mismatch."; // Huffman.hpp:459-461
     return MGX_FAILURE;
   }
+  if (hs[0] != 0) {
+    ctx->err = "truncated or inconsistent Huffman container";
+    return MGX_FAILURE;
+  }
   ParsedHeader p;
-  memcpy(&p.n, hs + 8, 8);
-  memcpy(&p.dict, hs + 16, 4);
-  memcpy(&p.chunk, hs + 20, 4);
-  uint64_t huffmeta;
-  memcpy(&huffmeta, hs + 24, 8);
+  p.n = hs[1];
+  p.dict = (int32_t)hs[2];
+  p.chunk = (int32_t)hs[3];
+  const uint64_t huffmeta = hs[4];
+  p.dbs = hs[5];
+  p.ddata = hs[6];
+  p.n_out = hs[7];
   if (p.n != n || p.chunk <= 0 || p.dict <= 0 || p.dict > 65536) {
     ctx->err = "Huffman container does not match the plan";
     return MGX_FAILURE;
   }
   p.nchunk = (p.n - 1) / (uint64_t)p.chunk + 1;
-  if (huffmeta != 2 * p.nchunk)
+  if (huffmeta != 2 * p.nchunk || p.dbs != 8ull * (128 + (uint64_t)p.dict))
     return MGX_FAILURE;
   p.off_meta = 32;
-  uint64_t off_dbs = 32 + 16 * p.nchunk;
-  if (off_dbs + 8 > bytes)
-    return MGX_FAILURE;
-  MGX_CUDA(cudaMemcpyAsync(hs, d_in + off_dbs, 8, cudaMemcpyDeviceToHost,
-                           ctx->stream));
-  MGX_CUDA(cudaStreamSynchronize(ctx->stream));
-  memcpy(&p.dbs, hs, 8);
-  p.off_db = off_dbs + 8;
-  if (p.dbs != 8ull * (128 + (uint64_t)p.dict) || p.off_db + p.dbs + 8 > bytes)
-    return MGX_FAILURE;
-  MGX_CUDA(cudaMemcpyAsync(hs, d_in + p.off_db + p.dbs, 8,
-                           cudaMemcpyDeviceToHost, ctx->stream));
-  MGX_CUDA(cudaStreamSynchronize(ctx->stream));
-  memcpy(&p.ddata, hs, 8);
+  p.off_db = 32 + 16 * p.nchunk + 8;
   p.off_packed = p.off_db + p.dbs + 8;
-  uint64_t off_outc = p.off_packed + 8 * p.ddata;
-  if (off_outc + 8 > bytes)
-    return MGX_FAILURE;
-  MGX_CUDA(cudaMemcpyAsync(hs, d_in + off_outc, 8, cudaMemcpyDeviceToHost,
-                           ctx->stream));
-  MGX_CUDA(cudaStreamSynchronize(ctx->stream));
-  memcpy(&p.n_out, hs, 8);
+  const uint64_t off_outc = p.off_packed + 8 * p.ddata;
   p.off_oidx = off_outc + 8;
   p.off_oval = p.off_oidx + 8 * p.n_out;
   if (p.off_oval + 8 * p.n_out > bytes)
@@ -978,12 +1134,23 @@ int mgxk_decode_container(mgx_ctx *ctx, const uint8_t *d_in, uint64_t bytes,
   const u64 *db = (const u64 *)(d_in + p.off_db);
   k_build_lut<<<1, 256, 0, ctx->stream>>>(db, (uint32_t)p.dict,
                                           (uint32_t *)ctx->d_lut);
-  k_decode<<<mgx_grid_for(p.nchunk, 128, ctx->num_sms * 16), 128, 0,
-             ctx->stream>>>((const u64 *)(d_in + p.off_packed),
-                            (const u64 *)(d_in + p.off_meta), p.nchunk,
-                            (uint32_t)p.chunk, p.n, db,
-                            (const uint32_t *)ctx->d_lut, ctx->d_sym);
-  ctx->launches += 2;
+  // 16-byte symbol stores need chunks that start on 16-byte boundaries
+  if (p.dict <= 8192 && p.chunk % 8 == 0) {
+    u64 *mlut = (u64 *)((uint8_t *)ctx->d_lut + 4096 * 4);
+    k_build_mlut<<<16, 256, 0, ctx->stream>>>((const uint32_t *)ctx->d_lut, mlut);
+    k_decode_multi<<<mgx_grid_for(p.nchunk, DEC_THREADS, ctx->num_sms * 16),
+                     DEC_THREADS, 0, ctx->stream>>>(
+        (const u64 *)(d_in + p.off_packed), (const u64 *)(d_in + p.off_meta),
+        p.nchunk, (uint32_t)p.chunk, p.n, db, mlut, ctx->d_sym);
+    ctx->launches += 3;
+  } else {
+    k_decode<<<mgx_grid_for(p.nchunk, 128, ctx->num_sms * 16), 128, 0,
+               ctx->stream>>>((const u64 *)(d_in + p.off_packed),
+                              (const u64 *)(d_in + p.off_meta), p.nchunk,
+                              (uint32_t)p.chunk, p.n, db,
+                              (const uint32_t *)ctx->d_lut, ctx->d_sym);
+    ctx->launches += 2;
+  }
   MGX_CUDA(cudaGetLastError());
   return MGX_SUCCESS;
 }
