@@ -931,27 +931,21 @@ __global__ void __launch_bounds__(256)
   }
 }
 
-constexpr int DEC_THREADS = 256;
-constexpr int DEC_WARPS = DEC_THREADS / 32;
-constexpr int DEC_RING = 20;    // symbols per thread (40 B: 2-way bank conflicts)
-constexpr int DEC_STAGE = 1024; // u64 words staged per warp (32 chunks, <= 2 bit/symbol)
+constexpr int DEC_THREADS = 128;
+constexpr int DEC_RING = 20; // symbols per thread (40 B: 2-way bank conflicts)
 
-// DecodeFunctor, Decode.hpp:14-130: one thread per chunk.  The 32 chunks of a
-// warp are contiguous in the packed stream, so the warp first copies that range
-// into shared memory with coalesced loads (when it fits) and every lane then
-// decodes out of shared memory: the stream is read in 32-bit units into a 64-bit
-// bit buffer, up to four symbols come out of one table look-up, and symbols
-// leave through a small per-thread ring as 16-byte stores.
+// DecodeFunctor, Decode.hpp:14-130: one thread per chunk; the stream is read in
+// 32-bit units into a 64-bit bit buffer, up to four symbols come out of one
+// shared-memory look-up, and symbols leave through a small per-thread ring in
+// shared memory as 16-byte stores.
 __global__ void __launch_bounds__(DEC_THREADS)
     k_decode_multi(const u64 *__restrict__ packed, const u64 *__restrict__ meta,
                    uint64_t nchunk, uint32_t chunk, uint64_t n,
                    const u64 *__restrict__ db, const u64 *__restrict__ g_mlut,
                    uint16_t *__restrict__ sym) {
-  extern __shared__ __align__(16) unsigned char dec_smem[];
-  u64 *mlut = (u64 *)dec_smem;                 // 1 << LUT_BITS entries
-  u64 *s_first = mlut + (1 << LUT_BITS), *s_entry = s_first + 64;
-  u64 *s_stage = s_entry + 64;                 // DEC_WARPS * DEC_STAGE
-  uint16_t *s_ring = (uint16_t *)(s_stage + DEC_WARPS * DEC_STAGE);
+  __shared__ u64 mlut[1 << LUT_BITS];
+  __shared__ u64 s_first[64], s_entry[64];
+  __shared__ __align__(8) uint16_t s_ring[DEC_THREADS * DEC_RING];
   for (uint32_t i = threadIdx.x; i < (1u << LUT_BITS); i += blockDim.x)
     mlut[i] = g_mlut[i];
   if (threadIdx.x < 64) {
@@ -960,121 +954,71 @@ __global__ void __launch_bounds__(DEC_THREADS)
   }
   __syncthreads();
   const u64 *keys = db + 128;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   uint16_t *ring = s_ring + threadIdx.x * DEC_RING;
-  u64 *stage = s_stage + warp * DEC_STAGE;
-  const uint64_t cstride = (uint64_t)gridDim.x * DEC_THREADS;
-  for (uint64_t cb = ((uint64_t)blockIdx.x * DEC_WARPS + warp) * 32; cb < nchunk;
-       cb += cstride) {
-    const uint64_t c = cb + lane;
-    const bool have = c < nchunk;
-    const u64 off = have ? meta[nchunk + c] : 0;
-    const uint64_t total = have ? meta[c] : 0;
-    const uint32_t nwords = (uint32_t)((total + 63) >> 6);
-    // range of the warp's chunks in the packed stream
-    const u64 w_begin = __shfl_sync(0xffffffffu, off, 0);
-    u64 w_end = have ? off + nwords : 0;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1)
-      w_end = max(w_end, __shfl_xor_sync(0xffffffffu, w_end, o));
-    const bool staged = w_end - w_begin <= DEC_STAGE;
-    __syncwarp();
-    if (staged) {
-      const uint32_t nw = (uint32_t)(w_end - w_begin);
-      for (uint32_t i = lane; i < nw; i += 32)
-        stage[i] = packed[w_begin + i];
-      __syncwarp();
-    }
-    if (!have)
-      continue;
-    const uint32_t nunits = nwords << 1;
+  for (uint64_t c = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; c < nchunk;
+       c += (uint64_t)gridDim.x * blockDim.x) {
+    const u64 *w = packed + meta[nchunk + c];
+    const uint32_t *w32 = (const uint32_t *)w; // unit u = w32[u ^ 1]
+    const uint64_t total = meta[c];
+    const uint32_t nunits = (uint32_t)(((total + 63) >> 6) << 1);
     const uint64_t base = c * chunk;
     const uint32_t count = (uint32_t)min((uint64_t)chunk, n - base);
     uint16_t *dst = sym + base;
-    uint32_t k = 0, written = 0;
-    // the body is instantiated twice so that the staged case compiles to plain
-    // shared-memory loads instead of generic ones
-    auto decode_chunk = [&](auto wptr) {
-      const auto w = wptr;
-      auto unit = [&](uint32_t u) -> uint32_t {
-        if (u >= nunits)
-          return 0u;
-        const u64 x = w[u >> 1];
-        return (u & 1) ? (uint32_t)x : (uint32_t)(x >> 32);
-      };
-      u64 buf = ((u64)unit(0) << 32) | unit(1);
-      uint32_t nbits = 64, next_unit = 2;
-      uint32_t ahead = unit(2); // the next refill, loaded before it is needed
-      uint64_t pos = 0;
-      uint32_t produced = 0;
-      while (produced < count) {
-        const u64 e = mlut[(uint32_t)(buf >> (64 - LUT_BITS))];
-        uint32_t cnt = (uint32_t)(e >> 4) & 7u;
-        uint32_t len = (uint32_t)e & 15u;
-        if (cnt == 0) {
-          // first code is longer than the window: canonical search on the raw
-          // words (Decode.hpp:60-66), then re-prime the bit buffer
-          const uint32_t wi = (uint32_t)(pos >> 6), used = (uint32_t)(pos & 63);
-          const u64 cur = w[wi];
-          const u64 nxt = ((uint64_t)(wi + 1) * 64 < total) ? w[wi + 1] : 0;
-          const u64 window = used ? ((cur << used) | (nxt >> (64 - used))) : cur;
-          uint32_t l = LUT_BITS;
-          u64 v;
-          do {
-            ++l;
-            v = window >> (64 - l);
-          } while (v < s_first[l] && l < 63);
-          ring[k] = (uint16_t)keys[s_entry[l] + v - s_first[l]];
-          ++k;
-          ++produced;
-          pos += l;
-          const uint32_t u0 = (uint32_t)(pos >> 5), r = (uint32_t)(pos & 31);
-          buf = (((u64)unit(u0) << 32) | unit(u0 + 1)) << r;
-          nbits = 64 - r;
-          next_unit = u0 + 2;
-          ahead = unit(next_unit);
-        } else {
-          cnt = min(cnt, count - produced);
-          ring[k + 0] = (uint16_t)((e >> 8) & 0x1fff);
-          ring[k + 1] = (uint16_t)((e >> 21) & 0x1fff);
-          ring[k + 2] = (uint16_t)((e >> 34) & 0x1fff);
-          ring[k + 3] = (uint16_t)((e >> 47) & 0x1fff);
-          k += cnt;
-          produced += cnt;
-          pos += len;
-          buf <<= len;
-          nbits -= len;
-        }
-        if (nbits <= 32) {
-          buf |= (u64)ahead << (32 - nbits);
-          nbits += 32;
-          ++next_unit;
-          ahead = unit(next_unit);
-        }
-        if (k >= 8) {
-          const uint2 a0 = *reinterpret_cast<const uint2 *>(ring);
-          const uint2 a1 = *reinterpret_cast<const uint2 *>(ring + 4);
-          *reinterpret_cast<uint4 *>(dst + written) =
-              make_uint4(a0.x, a0.y, a1.x, a1.y);
-          *reinterpret_cast<uint2 *>(ring) = *reinterpret_cast<const uint2 *>(ring + 8);
-          written += 8;
-          k -= 8;
-        }
+    auto unit = [&](uint32_t u) -> uint32_t { return u < nunits ? w32[u ^ 1] : 0u; };
+    u64 buf = ((u64)unit(0) << 32) | unit(1);
+    uint32_t nbits = 64, next_unit = 2;
+    uint64_t pos = 0;
+    uint32_t k = 0, produced = 0, written = 0;
+    while (produced < count) {
+      const u64 e = mlut[(uint32_t)(buf >> (64 - LUT_BITS))];
+      uint32_t cnt = (uint32_t)(e >> 4) & 7u;
+      uint32_t len = (uint32_t)e & 15u;
+      if (cnt == 0) {
+        // first code is longer than the window: canonical search on the raw
+        // words (Decode.hpp:60-66), then re-prime the bit buffer
+        const uint32_t wi = (uint32_t)(pos >> 6), used = (uint32_t)(pos & 63);
+        const u64 cur = w[wi];
+        const u64 nxt = ((uint64_t)(wi + 1) * 64 < total) ? w[wi + 1] : 0;
+        const u64 window = used ? ((cur << used) | (nxt >> (64 - used))) : cur;
+        uint32_t l = LUT_BITS;
+        u64 v;
+        do {
+          ++l;
+          v = window >> (64 - l);
+        } while (v < s_first[l] && l < 63);
+        ring[k] = (uint16_t)keys[s_entry[l] + v - s_first[l]];
+        ++k;
+        ++produced;
+        pos += l;
+        const uint32_t u0 = (uint32_t)(pos >> 5), r = (uint32_t)(pos & 31);
+        buf = (((u64)unit(u0) << 32) | unit(u0 + 1)) << r;
+        nbits = 64 - r;
+        next_unit = u0 + 2;
+      } else {
+        cnt = min(cnt, count - produced);
+        ring[k + 0] = (uint16_t)((e >> 8) & 0x1fff);
+        ring[k + 1] = (uint16_t)((e >> 21) & 0x1fff);
+        ring[k + 2] = (uint16_t)((e >> 34) & 0x1fff);
+        ring[k + 3] = (uint16_t)((e >> 47) & 0x1fff);
+        k += cnt;
+        produced += cnt;
+        pos += len;
+        buf <<= len;
+        nbits -= len;
       }
-    };
-    if (staged) {
-      // index into the dynamic shared array directly: address space stays known
-      const uint32_t so = (uint32_t)(warp * DEC_STAGE + (off - w_begin));
-      struct SharedWords {
-        const u64 *base;
-        uint32_t o;
-        __device__ __forceinline__ u64 operator[](uint32_t i) const {
-          return base[o + i];
-        }
-      };
-      decode_chunk(SharedWords{s_stage, so});
-    } else {
-      decode_chunk(packed + off);
+      if (nbits <= 32) {
+        buf |= (u64)unit(next_unit) << (32 - nbits);
+        nbits += 32;
+        ++next_unit;
+      }
+      if (k >= 8) {
+        const uint2 a0 = *reinterpret_cast<const uint2 *>(ring);
+        const uint2 a1 = *reinterpret_cast<const uint2 *>(ring + 4);
+        *reinterpret_cast<uint4 *>(dst + written) = make_uint4(a0.x, a0.y, a1.x, a1.y);
+        *reinterpret_cast<uint2 *>(ring) = *reinterpret_cast<const uint2 *>(ring + 8);
+        written += 8;
+        k -= 8;
+      }
     }
     for (uint32_t j = 0; j < k; j++)
       dst[written + j] = ring[j];
@@ -1194,14 +1138,8 @@ int mgxk_decode_container(mgx_ctx *ctx, const uint8_t *d_in, uint64_t bytes,
   if (p.dict <= 8192 && p.chunk % 8 == 0) {
     u64 *mlut = (u64 *)((uint8_t *)ctx->d_lut + 4096 * 4);
     k_build_mlut<<<16, 256, 0, ctx->stream>>>((const uint32_t *)ctx->d_lut, mlut);
-    const size_t dsmem = (size_t)(1 << LUT_BITS) * 8 + 128 * 8 +
-                         (size_t)DEC_WARPS * DEC_STAGE * 8 +
-                         (size_t)DEC_THREADS * DEC_RING * 2;
-    MGX_CUDA(cudaFuncSetAttribute(k_decode_multi,
-                                  cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)dsmem));
-    k_decode_multi<<<mgx_grid_for(p.nchunk, DEC_THREADS, ctx->num_sms * 2),
-                     DEC_THREADS, dsmem, ctx->stream>>>(
+    k_decode_multi<<<mgx_grid_for(p.nchunk, DEC_THREADS, ctx->num_sms * 16),
+                     DEC_THREADS, 0, ctx->stream>>>(
         (const u64 *)(d_in + p.off_packed), (const u64 *)(d_in + p.off_meta),
         p.nchunk, (uint32_t)p.chunk, p.n, db, mlut, ctx->d_sym);
     ctx->launches += 3;
