@@ -16,8 +16,66 @@ c_dbl = ctypes.c_double
 c_int = ctypes.c_int
 c_vp = ctypes.c_void_p
 
+
+
+class MgxConfig(ctypes.Structure):
+    """mgx_config of include/mgard_b200_x.h"""
+    _fields_ = [("dev_type", c_int), ("dev_id", c_int),
+                ("domain_decomposition", c_int), ("decomposition", c_int),
+                ("lossless", c_int), ("huff_dict_size", c_u32),
+                ("huff_block_size", c_u32), ("reorder", c_u32),
+                ("normalize_coordinates", c_int),
+                ("auto_pin_host_buffers", c_int),
+                ("compress_with_dryrun", c_int), ("auto_cache_release", c_int),
+                ("log_level", c_int), ("max_larget_level", c_u64),
+                ("max_memory_footprint", c_u64)]
+
+
+class MgxMetadata(ctypes.Structure):
+    """mgx_metadata of include/mgard_b200_x.h"""
+    _fields_ = [("version", c_u32 * 3), ("file_version", c_u32 * 3),
+                ("D", c_u32), ("shape", c_u64 * 5), ("nonuniform", c_int),
+                ("dtype", c_int), ("mode", c_int), ("linf", c_int),
+                ("s", c_dbl), ("norm", c_dbl), ("tol", c_dbl),
+                ("decomposed", c_int), ("dd_type", c_int), ("dd_dim", c_u32),
+                ("dd_size", c_u64), ("decomposition", c_int),
+                ("l_target", c_u32), ("lossless", c_int),
+                ("huff_dict_size", c_u32), ("huff_block_size", c_u32),
+                ("reorder", c_u32), ("backend", c_int)]
+
+
+_cfgp = ctypes.POINTER(MgxConfig)
+_szp = ctypes.POINTER(ctypes.c_size_t)
+
 # name -> (restype, argtypes); must list every symbol of include/mgard_b200.h
+# and include/mgard_b200_x.h
 SIGNATURES = {
+    "mgx_config_default": (None, [_cfgp]),
+    "mgx_x_compress": (c_int, [c_int, c_int, ctypes.POINTER(c_u64), c_dbl, c_dbl,
+                               c_int, c_vp, ctypes.POINTER(c_vp), _szp, _cfgp,
+                               c_int]),
+    "mgx_x_decompress": (c_int, [c_vp, ctypes.c_size_t, ctypes.POINTER(c_vp),
+                                 ctypes.POINTER(c_u64), ctypes.POINTER(c_int),
+                                 ctypes.POINTER(c_int), _cfgp, c_int]),
+    "mgx_x_release_cache": (c_int, [_cfgp]),
+    "mgx_x_pin_memory": (c_int, [c_vp, c_u64, _cfgp]),
+    "mgx_x_check_memory_pinned": (c_int, [c_vp, _cfgp]),
+    "mgx_x_unpin_memory": (c_int, [c_vp, _cfgp]),
+    "mgx_x_last_error": (ctypes.c_char_p, []),
+    "mgx_x_launch_count": (c_u64, []),
+    "mgx_metadata_serialize": (c_int, [ctypes.POINTER(MgxMetadata), c_vp, c_u64,
+                                       ctypes.POINTER(c_u64)]),
+    "mgx_metadata_parse": (c_int, [c_vp, c_u64, ctypes.POINTER(MgxMetadata),
+                                   ctypes.POINTER(c_u64)]),
+    "mgx_metadata_size": (c_int, [c_vp, c_u64, ctypes.POINTER(c_u64)]),
+    "mgx_crc32": (c_u32, [c_vp, c_u64]),
+    "mgx_estimate_footprint": (c_u64, [c_int, ctypes.POINTER(c_u64), c_int,
+                                       c_dbl, c_int]),
+    "mgx_max_dim_by_memory": (c_int, [c_int, ctypes.POINTER(c_u64), c_int, c_dbl,
+                                      c_u64, ctypes.POINTER(c_int),
+                                      ctypes.POINTER(c_int),
+                                      ctypes.POINTER(c_u64),
+                                      ctypes.POINTER(c_u64)]),
     "mgx_create": (c_int, [ctypes.POINTER(c_vp), c_int, c_vp]),
     "mgx_destroy": (None, [c_vp]),
     "mgx_last_error": (ctypes.c_char_p, [c_vp]),

@@ -1,0 +1,1506 @@
+// mgard_b200 -- the high-level path around the low-level compressor: what the
+// reference's general_compress / general_decompress do with a whole dataset
+// (CompressionHighLevel.hpp:47-309, 373-579; GPUPipelines.hpp:3-567;
+// DomainDecomposer.hpp:118-330; Metadata.cpp:259-762).  Host code only: every
+// array operation goes through the low-level C ABI (include/mgard_b200.h).
+//
+// Design notes (B200):
+//   * one compute stream + one copy-in + one copy-out stream per device; the
+//     next subdomain's H2D and the previous payload's D2H run under the current
+//     subdomain's kernels (two input and two payload buffers);
+//   * a device-resident input is never copied when its slab is contiguous
+//     (MaxDim along dim 0, or no decomposition): the kernels read it in place;
+//   * at most two planned contexts are kept (full slab + leftover), the same
+//     working set the reference's hierarchy cache holds for MaxDim.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <limits>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/mgard_b200_x.h"
+
+namespace {
+
+std::string g_err;
+std::mutex g_mu; // the reference's cache is process-global and not
+                 // thread-safe; calls are serialised here instead
+
+int fail(int rc, const std::string &msg) {
+  g_err = msg;
+  return rc;
+}
+
+// ---- CRC-32 (IEEE 802.3, reflected 0xEDB88320) == zlib crc32_z --------------
+uint32_t g_crc_table[256];
+bool g_crc_ready = false;
+void crc_init() {
+  for (uint32_t i = 0; i < 256; i++) {
+    uint32_t c = i;
+    for (int k = 0; k < 8; k++)
+      c = (c & 1) ? 0xEDB88320u ^ (c >> 1) : c >> 1;
+    g_crc_table[i] = c;
+  }
+  g_crc_ready = true;
+}
+
+// ---- proto3 wire format -------------------------------------------------------
+// Emission rules of the protobuf C++ serializer the reference links: fields in
+// field-number order, scalar fields equal to their default are skipped (doubles
+// compared by bit pattern), repeated scalars packed, sub-messages that were
+// touched with mutable_*() are always present even when empty.
+struct PbWriter {
+  std::vector<uint8_t> b;
+  void varint(uint64_t v) {
+    while (v >= 0x80) {
+      b.push_back((uint8_t)(v | 0x80));
+      v >>= 7;
+    }
+    b.push_back((uint8_t)v);
+  }
+  void key(uint32_t field, uint32_t wire) { varint(((uint64_t)field << 3) | wire); }
+  void put_uint(uint32_t field, uint64_t v) {
+    if (v) {
+      key(field, 0);
+      varint(v);
+    }
+  }
+  void put_double(uint32_t field, double d) {
+    uint64_t bits;
+    memcpy(&bits, &d, 8);
+    if (bits) {
+      key(field, 1);
+      for (int i = 0; i < 8; i++)
+        b.push_back((uint8_t)(bits >> (8 * i)));
+    }
+  }
+  void put_message(uint32_t field, const PbWriter &m) {
+    key(field, 2);
+    varint(m.b.size());
+    b.insert(b.end(), m.b.begin(), m.b.end());
+  }
+  void put_packed_uint(uint32_t field, const uint64_t *v, size_t n) {
+    if (!n)
+      return;
+    PbWriter t;
+    for (size_t i = 0; i < n; i++)
+      t.varint(v[i]);
+    put_message(field, t);
+  }
+};
+
+struct PbReader {
+  const uint8_t *p, *e;
+  bool varint(uint64_t &v) {
+    v = 0;
+    for (int shift = 0; shift < 64 && p < e; shift += 7) {
+      uint8_t c = *p++;
+      v |= (uint64_t)(c & 0x7F) << shift;
+      if (!(c & 0x80))
+        return true;
+    }
+    return false;
+  }
+  bool next(uint32_t &field, uint32_t &wire) {
+    uint64_t k;
+    if (!varint(k))
+      return false;
+    field = (uint32_t)(k >> 3);
+    wire = (uint32_t)(k & 7);
+    return field != 0;
+  }
+  bool fixed64(uint64_t &v) {
+    if (e - p < 8)
+      return false;
+    v = 0;
+    for (int i = 0; i < 8; i++)
+      v |= (uint64_t)p[i] << (8 * i);
+    p += 8;
+    return true;
+  }
+  bool sub(PbReader &r) {
+    uint64_t n;
+    if (!varint(n) || (uint64_t)(e - p) < n)
+      return false;
+    r.p = p;
+    r.e = p + n;
+    p += n;
+    return true;
+  }
+  bool skip(uint32_t wire) {
+    uint64_t v;
+    PbReader r;
+    switch (wire) {
+    case 0:
+      return varint(v);
+    case 1:
+      return fixed64(v);
+    case 2:
+      return sub(r);
+    case 5:
+      if (e - p < 4)
+        return false;
+      p += 4;
+      return true;
+    default:
+      return false;
+    }
+  }
+  bool done() const { return p >= e; }
+};
+
+const char SIGNATURE[5] = {'M', 'G', 'A', 'R', 'D'};
+const uint64_t PREAMBLE = 5 + 8 + 4;
+const uint32_t SW_VERSION_MAJOR = 1;   // MGARD 1.6.0 (reference CMakeLists.txt:13-15)
+const uint32_t FILE_VERSION_MAJOR = 1; // file format 1.0.0 (:17-19)
+
+// mgard.pb enum numbers (src/mgard.proto)
+enum { PB_ABSOLUTE = 0, PB_RELATIVE = 1 };
+enum { PB_L_INFINITY = 0, PB_S_NORM = 1 };
+enum { PB_NOOP_METHOD = 0, PB_MAX_DIMENSION = 1, PB_BLOCK = 2, PB_VARIABLE = 3 };
+enum { PB_MULTIDIM = 1, PB_ONE_DIM = 2, PB_HYBRID = 3 };
+enum { PB_COEFFICIENTWISE_LINEAR = 1, PB_INT64_T = 3 };
+enum { PB_CPU_HUFFMAN_ZSTD = 2, PB_X_HUFFMAN = 3, PB_X_HUFFMAN_LZ4 = 4, PB_X_HUFFMAN_ZSTD = 5 };
+
+void put_version(PbWriter &h, uint32_t field, const uint32_t v[3]) {
+  PbWriter m;
+  m.put_uint(1, v[0]);
+  m.put_uint(2, v[1]);
+  m.put_uint(3, v[2]);
+  h.put_message(field, m);
+}
+
+std::vector<uint8_t> header_bytes(const mgx_metadata &md) {
+  PbWriter h;
+  put_version(h, 2, md.version);
+  put_version(h, 3, md.file_version);
+  { // Domain
+    PbWriter grid, dom;
+    grid.put_uint(1, md.D);
+    grid.put_packed_uint(2, md.shape, md.D);
+    dom.put_message(2, grid); // topology CARTESIAN_GRID = 0, geometry UNIT_CUBE = 0
+    h.put_message(4, dom);
+  }
+  { // Dataset
+    PbWriter m;
+    m.put_uint(1, md.dtype == MGX_F64 ? 1 : 0);
+    m.put_uint(2, 1);
+    h.put_message(5, m);
+  }
+  { // ErrorControl
+    PbWriter m;
+    m.put_uint(1, md.mode == MGX_EB_REL ? PB_RELATIVE : PB_ABSOLUTE);
+    m.put_uint(2, md.linf ? PB_L_INFINITY : PB_S_NORM);
+    m.put_double(3, md.s);
+    if (md.mode == MGX_EB_REL)
+      m.put_double(4, md.norm);
+    m.put_double(5, md.tol);
+    h.put_message(6, m);
+  }
+  { // DomainDecomposition
+    PbWriter m;
+    uint32_t method = PB_NOOP_METHOD;
+    if (md.decomposed)
+      method = md.dd_type == MGX_DD_MAXDIM  ? PB_MAX_DIMENSION
+               : md.dd_type == MGX_DD_BLOCK ? PB_BLOCK
+                                            : PB_VARIABLE;
+    m.put_uint(1, method);
+    m.put_uint(2, md.dd_dim);
+    m.put_uint(3, md.dd_size);
+    h.put_message(7, m);
+  }
+  { // FunctionDecomposition
+    PbWriter m;
+    m.put_uint(2, md.decomposition == MGX_DC_MULTIDIM    ? PB_MULTIDIM
+                  : md.decomposition == MGX_DC_SINGLEDIM ? PB_ONE_DIM
+                                                         : PB_HYBRID);
+    m.put_uint(3, md.l_target);
+    h.put_message(8, m);
+  }
+  { // Quantization
+    PbWriter m;
+    m.put_uint(1, PB_COEFFICIENTWISE_LINEAR);
+    m.put_uint(3, PB_INT64_T); // bin_widths PER_COEFFICIENT = 0, little endian
+    h.put_message(9, m);
+  }
+  h.put_message(10, PbWriter()); // BitplaneEncoding: NOOP
+  { // Encoding
+    PbWriter m;
+    m.put_uint(1, md.reorder ? 1 : 0);
+    uint32_t comp = PB_X_HUFFMAN;
+    if (md.lossless == MGX_LL_HUFFMAN_LZ4)
+      comp = PB_X_HUFFMAN_LZ4;
+    else if (md.lossless == MGX_LL_HUFFMAN_ZSTD)
+      comp = PB_X_HUFFMAN_ZSTD;
+    else if (md.lossless == MGX_LL_CPU)
+      comp = PB_CPU_HUFFMAN_ZSTD;
+    m.put_uint(2, comp);
+    if (md.lossless != MGX_LL_CPU) {
+      m.put_uint(3, md.huff_dict_size);
+      m.put_uint(4, md.huff_block_size);
+    }
+    h.put_message(11, m);
+  }
+  { // Device
+    PbWriter m;
+    m.put_uint(1, (uint32_t)md.backend);
+    h.put_message(12, m);
+  }
+  return h.b;
+}
+
+bool parse_version(PbReader r, uint32_t v[3]) {
+  uint32_t f, w;
+  while (!r.done()) {
+    if (!r.next(f, w))
+      return false;
+    uint64_t x;
+    if (w == 0 && f >= 1 && f <= 3) {
+      if (!r.varint(x))
+        return false;
+      v[f - 1] = (uint32_t)x;
+    } else if (!r.skip(w))
+      return false;
+  }
+  return true;
+}
+
+// repeated uint64, packed or not
+bool parse_grid(PbReader r, mgx_metadata &md, uint64_t &count) {
+  uint32_t f, w;
+  count = 0;
+  while (!r.done()) {
+    if (!r.next(f, w))
+      return false;
+    uint64_t x;
+    if (f == 1 && w == 0) {
+      if (!r.varint(x))
+        return false;
+      md.D = (uint32_t)x;
+    } else if (f == 2 && w == 2) {
+      PbReader s;
+      if (!r.sub(s))
+        return false;
+      while (!s.done()) {
+        if (!s.varint(x))
+          return false;
+        if (count < 5)
+          md.shape[count] = x;
+        count++;
+      }
+    } else if (f == 2 && w == 0) {
+      if (!r.varint(x))
+        return false;
+      if (count < 5)
+        md.shape[count] = x;
+      count++;
+    } else if (!r.skip(w))
+      return false;
+  }
+  return true;
+}
+
+// generic scalar message: varint fields into u[field], fixed64 into d[field]
+bool parse_scalars(PbReader r, uint64_t *u, double *d, uint32_t nf) {
+  uint32_t f, w;
+  while (!r.done()) {
+    if (!r.next(f, w))
+      return false;
+    uint64_t x;
+    if (w == 0) {
+      if (!r.varint(x))
+        return false;
+      if (f < nf && u)
+        u[f] = x;
+    } else if (w == 1) {
+      if (!r.fixed64(x))
+        return false;
+      if (f < nf && d)
+        memcpy(&d[f], &x, 8);
+    } else if (!r.skip(w))
+      return false;
+  }
+  return true;
+}
+
+int parse_header(const uint8_t *p, uint64_t n, mgx_metadata &md) {
+  memset(&md, 0, sizeof(md));
+  md.linf = 1; // proto3 default ErrorControl.norm == L_INFINITY
+  md.mode = MGX_EB_ABS;
+  PbReader r{p, p + n};
+  uint32_t f, w;
+  uint64_t shape_count = 0;
+  uint32_t quant_method = 0, bitplane_method = 0, hierarchy = 0, compressor = 0;
+  bool have_norm_kind = false;
+  uint64_t norm_kind = 0;
+  while (!r.done()) {
+    if (!r.next(f, w))
+      return fail(MGX_FAILURE, "header parsing encountered read or format error");
+    if (w != 2) {
+      if (!r.skip(w))
+        return fail(MGX_FAILURE, "header parsing encountered read or format error");
+      continue;
+    }
+    PbReader m;
+    if (!r.sub(m))
+      return fail(MGX_FAILURE, "header parsing encountered read or format error");
+    bool ok = true;
+    uint64_t u[8] = {};
+    double d[8] = {};
+    switch (f) {
+    case 2:
+      ok = parse_version(m, md.version);
+      break;
+    case 3:
+      ok = parse_version(m, md.file_version);
+      break;
+    case 4: { // Domain
+      uint32_t f2, w2;
+      while (ok && !m.done()) {
+        if (!m.next(f2, w2)) {
+          ok = false;
+          break;
+        }
+        if (f2 == 2 && w2 == 2) {
+          PbReader g;
+          ok = m.sub(g) && parse_grid(g, md, shape_count);
+        } else if (f2 == 3 && w2 == 0) {
+          uint64_t x;
+          ok = m.varint(x);
+          md.nonuniform = x == 1;
+        } else
+          ok = m.skip(w2);
+      }
+      break;
+    }
+    case 5:
+      ok = parse_scalars(m, u, nullptr, 8);
+      md.dtype = u[1] == 1 ? MGX_F64 : MGX_F32;
+      break;
+    case 6:
+      ok = parse_scalars(m, u, d, 8);
+      md.mode = u[1] == PB_RELATIVE ? MGX_EB_REL : MGX_EB_ABS;
+      norm_kind = u[2];
+      have_norm_kind = true;
+      md.s = d[3];
+      md.norm = d[4];
+      md.tol = d[5];
+      break;
+    case 7:
+      ok = parse_scalars(m, u, nullptr, 8);
+      md.decomposed = u[1] != PB_NOOP_METHOD;
+      md.dd_type = u[1] == PB_BLOCK ? MGX_DD_BLOCK
+                   : u[1] == PB_VARIABLE ? MGX_DD_VARIABLE
+                                         : MGX_DD_MAXDIM;
+      md.dd_dim = (uint32_t)u[2];
+      md.dd_size = u[3];
+      break;
+    case 8:
+      ok = parse_scalars(m, u, nullptr, 8);
+      hierarchy = (uint32_t)u[2];
+      md.l_target = (uint32_t)u[3];
+      break;
+    case 9:
+      ok = parse_scalars(m, u, nullptr, 8);
+      quant_method = (uint32_t)u[1];
+      break;
+    case 10:
+      ok = parse_scalars(m, u, nullptr, 8);
+      bitplane_method = (uint32_t)u[1];
+      break;
+    case 11:
+      ok = parse_scalars(m, u, nullptr, 8);
+      md.reorder = u[1] == 1;
+      compressor = (uint32_t)u[2];
+      md.huff_dict_size = (uint32_t)u[3];
+      md.huff_block_size = (uint32_t)u[4];
+      break;
+    case 12:
+      ok = parse_scalars(m, u, nullptr, 8);
+      md.backend = (int)u[1];
+      break;
+    default:
+      break;
+    }
+    if (!ok)
+      return fail(MGX_FAILURE, "header parsing encountered read or format error");
+  }
+  (void)have_norm_kind;
+  // the checks of MetadataBase::Deserialize (Metadata.cpp:519-760)
+  if (md.version[0] > SW_VERSION_MAJOR)
+    return fail(MGX_FAILURE, "MGARD version mismatch.");
+  if (md.file_version[0] > FILE_VERSION_MAJOR)
+    return fail(MGX_FAILURE, "MGARD file format version mismatch.");
+  if (md.D != shape_count)
+    return fail(MGX_FAILURE, "grid shape does not match given dimension.");
+  if (norm_kind == PB_L_INFINITY) {
+    md.linf = 1;
+    md.s = std::numeric_limits<double>::infinity();
+  } else {
+    md.linf = 0;
+  }
+  if (hierarchy == PB_MULTIDIM)
+    md.decomposition = MGX_DC_MULTIDIM;
+  else if (hierarchy == PB_ONE_DIM)
+    md.decomposition = MGX_DC_SINGLEDIM;
+  else if (hierarchy == PB_HYBRID)
+    md.decomposition = MGX_DC_HYBRID;
+  else
+    return fail(MGX_FAILURE, "this decomposition hierarchy mismatch the hierarchy "
+                             "used in MGARD-X.");
+  if ((quant_method != 0) == (bitplane_method != 0))
+    return fail(MGX_FAILURE, "cannot determine whether this is compressed or "
+                             "refactored data.");
+  if (compressor == PB_X_HUFFMAN)
+    md.lossless = MGX_LL_HUFFMAN;
+  else if (compressor == PB_X_HUFFMAN_LZ4)
+    md.lossless = MGX_LL_HUFFMAN_LZ4;
+  else if (compressor == PB_X_HUFFMAN_ZSTD)
+    md.lossless = MGX_LL_HUFFMAN_ZSTD;
+  else if (compressor == PB_CPU_HUFFMAN_ZSTD)
+    md.lossless = MGX_LL_CPU;
+  else
+    return fail(MGX_FAILURE, "unknown lossless compressor type.");
+  if (md.backend == 0)
+    return fail(MGX_FAILURE, "this data was not compressed with MGARD-X.");
+  return MGX_SUCCESS;
+}
+
+// ---- where does a pointer live -----------------------------------------------
+struct PtrLoc {
+  bool device = false;
+  int dev = 0;
+};
+PtrLoc locate(const void *p) {
+  PtrLoc loc;
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) == cudaSuccess) {
+    if (at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged) {
+      loc.device = true;
+      loc.dev = at.device;
+    }
+  } else {
+    cudaGetLastError(); // plain host memory on old drivers: clear the error
+  }
+  return loc;
+}
+
+bool host_registered(const void *p) {
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return at.type == cudaMemoryTypeHost;
+}
+
+// pin for the duration of a call (CompressionHighLevel.hpp:157-183)
+struct ScopedPin {
+  void *p = nullptr;
+  void pin(const void *ptr, size_t bytes, bool enabled) {
+    if (!enabled || !ptr || !bytes || host_registered(ptr))
+      return;
+    if (cudaHostRegister((void *)ptr, bytes, cudaHostRegisterDefault) == cudaSuccess)
+      p = (void *)ptr;
+    else
+      cudaGetLastError(); // pageable copies still work, only slower
+  }
+  ~ScopedPin() {
+    if (p)
+      cudaHostUnregister(p);
+  }
+};
+
+// ---- per-device cache (role of CompressorCache.hpp:25-147) --------------------
+struct PlanEntry {
+  std::vector<uint64_t> shape;
+  int dtype;
+  uint32_t dict, chunk;
+  uint64_t max_level;
+  mgx_ctx *ctx;
+  uint64_t stamp;
+};
+
+struct DeviceCache {
+  int dev = 0;
+  cudaStream_t compute = nullptr, copy_in = nullptr, copy_out = nullptr;
+  cudaEvent_t ev_in[2] = {}, ev_out[2] = {}, ev_free[2] = {};
+  std::vector<PlanEntry> plans;
+  void *sub[2] = {nullptr, nullptr};
+  size_t sub_bytes[2] = {0, 0};
+  void *cbuf[2] = {nullptr, nullptr};
+  size_t cbuf_bytes[2] = {0, 0};
+  uint64_t stamp = 0;
+  uint64_t retired_launches = 0;
+  bool ready = false;
+
+  size_t held() const {
+    return sub_bytes[0] + sub_bytes[1] + cbuf_bytes[0] + cbuf_bytes[1];
+  }
+};
+
+std::map<int, DeviceCache> g_cache;
+
+#define X_CUDA(call)                                                           \
+  do {                                                                         \
+    cudaError_t e_ = (call);                                                   \
+    if (e_ != cudaSuccess)                                                     \
+      return fail(MGX_FAILURE, std::string(#call) + ": " + cudaGetErrorString(e_)); \
+  } while (0)
+
+int cache_get(int dev, DeviceCache **out) {
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || dev < 0 || dev >= count) {
+    cudaGetLastError();
+    return fail(MGX_BACKEND_UNAVAILABLE, "no CUDA device " + std::to_string(dev));
+  }
+  X_CUDA(cudaSetDevice(dev));
+  DeviceCache &c = g_cache[dev];
+  if (!c.ready) {
+    c.dev = dev;
+    X_CUDA(cudaStreamCreateWithFlags(&c.compute, cudaStreamNonBlocking));
+    X_CUDA(cudaStreamCreateWithFlags(&c.copy_in, cudaStreamNonBlocking));
+    X_CUDA(cudaStreamCreateWithFlags(&c.copy_out, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; i++) {
+      X_CUDA(cudaEventCreateWithFlags(&c.ev_in[i], cudaEventDisableTiming));
+      X_CUDA(cudaEventCreateWithFlags(&c.ev_out[i], cudaEventDisableTiming));
+      X_CUDA(cudaEventCreateWithFlags(&c.ev_free[i], cudaEventDisableTiming));
+    }
+    c.ready = true;
+  }
+  *out = &c;
+  return MGX_SUCCESS;
+}
+
+void cache_release(DeviceCache &c) {
+  if (!c.ready)
+    return;
+  cudaSetDevice(c.dev);
+  cudaDeviceSynchronize();
+  for (auto &p : c.plans) {
+    c.retired_launches += mgx_launch_count(p.ctx);
+    mgx_destroy(p.ctx);
+  }
+  c.plans.clear();
+  for (int i = 0; i < 2; i++) {
+    if (c.sub[i])
+      cudaFree(c.sub[i]);
+    if (c.cbuf[i])
+      cudaFree(c.cbuf[i]);
+    c.sub[i] = c.cbuf[i] = nullptr;
+    c.sub_bytes[i] = c.cbuf_bytes[i] = 0;
+    cudaEventDestroy(c.ev_in[i]);
+    cudaEventDestroy(c.ev_out[i]);
+    cudaEventDestroy(c.ev_free[i]);
+  }
+  cudaStreamDestroy(c.compute);
+  cudaStreamDestroy(c.copy_in);
+  cudaStreamDestroy(c.copy_out);
+  c.ready = false;
+}
+
+int cache_ctx(DeviceCache &c, int D, const uint64_t *shape, int dtype,
+              const mgx_config &cfg, mgx_ctx **out) {
+  for (auto &p : c.plans)
+    if (p.dtype == dtype && p.dict == cfg.huff_dict_size &&
+        p.chunk == cfg.huff_block_size && p.max_level == cfg.max_larget_level &&
+        p.shape.size() == (size_t)D && std::equal(p.shape.begin(), p.shape.end(), shape)) {
+      p.stamp = ++c.stamp;
+      *out = p.ctx;
+      return MGX_SUCCESS;
+    }
+  if (c.plans.size() >= 2) { // evict the least recently used plan
+    size_t victim = c.plans[0].stamp < c.plans[1].stamp ? 0 : 1;
+    c.retired_launches += mgx_launch_count(c.plans[victim].ctx);
+    mgx_destroy(c.plans[victim].ctx);
+    c.plans.erase(c.plans.begin() + victim);
+  }
+  mgx_ctx *ctx = nullptr;
+  int rc = mgx_create(&ctx, c.dev, c.compute);
+  if (rc)
+    return fail(rc, "mgx_create failed");
+  rc = mgx_plan(ctx, D, shape, dtype, cfg.huff_dict_size, cfg.huff_block_size,
+                cfg.max_larget_level);
+  if (rc) {
+    std::string msg = mgx_last_error(ctx);
+    mgx_destroy(ctx);
+    return fail(rc, "mgx_plan: " + msg);
+  }
+  c.plans.push_back({std::vector<uint64_t>(shape, shape + D), dtype,
+                     cfg.huff_dict_size, cfg.huff_block_size, cfg.max_larget_level,
+                     ctx, ++c.stamp});
+  *out = ctx;
+  return MGX_SUCCESS;
+}
+
+int ensure_buffer(void *&p, size_t &have, size_t want) {
+  if (have >= want)
+    return MGX_SUCCESS;
+  if (p)
+    cudaFree(p);
+  p = nullptr;
+  have = 0;
+  X_CUDA(cudaMalloc(&p, want));
+  have = want;
+  return MGX_SUCCESS;
+}
+
+// ---- the decomposition of one call ----------------------------------------------
+struct Slabs {
+  int D = 0;
+  uint64_t shape[5] = {};
+  size_t es = 4;
+  bool decomposed = false;
+  int dim = 0;
+  uint64_t size = 0, num = 1;
+  uint64_t outer = 1, inner = 1; // products of the dims before / after `dim`
+
+  void finish() {
+    outer = inner = 1;
+    for (int d = 0; d < dim; d++)
+      outer *= shape[d];
+    for (int d = dim + 1; d < D; d++)
+      inner *= shape[d];
+  }
+  void sub_shape(uint64_t id, uint64_t *out, uint64_t *off) const {
+    if (!decomposed) {
+      for (int d = 0; d < D; d++)
+        out[d] = shape[d];
+      *off = 0;
+      return;
+    }
+    mgx_subdomain_shape(D, shape, dim, size, id, out, off);
+  }
+  uint64_t elems(uint64_t id) const {
+    uint64_t s[5], off, n = 1;
+    sub_shape(id, s, &off);
+    for (int d = 0; d < D; d++)
+      n *= s[d];
+    return n;
+  }
+  // a slab is one contiguous range of the dense array
+  bool contiguous() const { return !decomposed || outer == 1; }
+};
+
+// DomainDecomposer::copy_subdomain (DomainDecomposer.hpp:628-820) for MaxDim:
+// `whole` is the dense array, `slab` a dense sub-array; either side may be host
+// or device memory.
+int copy_slab(const Slabs &sl, uint64_t id, void *slab, void *whole, bool to_slab,
+              cudaStream_t stream) {
+  uint64_t s[5], off;
+  sl.sub_shape(id, s, &off);
+  const size_t width = (size_t)s[sl.dim] * sl.inner * sl.es;
+  const size_t pitch = (size_t)sl.shape[sl.dim] * sl.inner * sl.es;
+  char *w = (char *)whole + (size_t)off * sl.inner * sl.es;
+  if (sl.outer == 1 || !sl.decomposed) {
+    if (to_slab)
+      X_CUDA(cudaMemcpyAsync(slab, w, width, cudaMemcpyDefault, stream));
+    else
+      X_CUDA(cudaMemcpyAsync(w, slab, width, cudaMemcpyDefault, stream));
+    return MGX_SUCCESS;
+  }
+  if (pitch < ((size_t)1 << 31)) {
+    if (to_slab)
+      X_CUDA(cudaMemcpy2DAsync(slab, width, w, pitch, width, sl.outer,
+                               cudaMemcpyDefault, stream));
+    else
+      X_CUDA(cudaMemcpy2DAsync(w, pitch, slab, width, width, sl.outer,
+                               cudaMemcpyDefault, stream));
+    return MGX_SUCCESS;
+  }
+  for (uint64_t o = 0; o < sl.outer; o++) { // rows too long for a pitched copy
+    char *a = (char *)slab + o * width, *b = w + o * pitch;
+    if (to_slab)
+      X_CUDA(cudaMemcpyAsync(a, b, width, cudaMemcpyDefault, stream));
+    else
+      X_CUDA(cudaMemcpyAsync(b, a, width, cudaMemcpyDefault, stream));
+  }
+  return MGX_SUCCESS;
+}
+
+bool uses_correction(int D, double s) { return !(std::isinf(s) && D <= 3); }
+
+uint64_t footprint(int D, const uint64_t *shape, int dtype, double s, int prefetch) {
+  const uint64_t es = dtype == MGX_F64 ? 8 : 4;
+  uint64_t n = 1;
+  for (int d = 0; d < D; d++)
+    n *= shape[d];
+  // subdomain buffer + payload staging buffer (a payload larger than the raw
+  // data is replaced by the raw data, so N*es + container overhead bounds it)
+  uint64_t io = n * es + (n * es + (n / 1024 + 1) * 16 + (1u << 20));
+  if (prefetch)
+    io *= 2;
+  // context: 16-bit symbols, chunk tables, outlier list, and for the
+  // orthogonal-projection path the level workspace + value scratch +
+  // correction ping/pong buffers
+  uint64_t ws = n * 2 + (n / 256 + 1) * 24 + n / 8 + (1u << 20);
+  if (uses_correction(D, s))
+    ws += n * es * 2 + (n * es * 3) / 4;
+  else
+    ws += (n * es) / 256 + (1u << 16); // coarse lattice of the fused inverse
+  return io + ws;
+}
+
+int decide_slabs(int D, const uint64_t *shape, int dtype, double s,
+                 uint64_t available, Slabs *sl) {
+  sl->D = D;
+  sl->es = dtype == MGX_F64 ? 8 : 4;
+  for (int d = 0; d < D; d++)
+    sl->shape[d] = shape[d];
+  int dec = 0, dim = 0;
+  uint64_t size = 0, num = 1;
+  int rc = mgx_max_dim_by_memory(D, shape, dtype, s, available, &dec, &dim, &size, &num);
+  if (rc)
+    return fail(rc, "dataset cannot be decomposed to fit the device");
+  sl->decomposed = dec != 0;
+  sl->dim = dim;
+  sl->size = size;
+  sl->num = num;
+  sl->finish();
+  return MGX_SUCCESS;
+}
+
+int check_config(const mgx_config &cfg) {
+  if (cfg.dev_type != MGX_DEV_AUTO && cfg.dev_type != MGX_DEV_CUDA)
+    return fail(MGX_BACKEND_UNAVAILABLE,
+                "only the CUDA backend is built (no CPU fallback by design)");
+  if (cfg.lossless != MGX_LL_HUFFMAN)
+    return fail(MGX_FAILURE, "lossless type not supported: Huffman only");
+  if (cfg.decomposition != MGX_DC_MULTIDIM)
+    return fail(MGX_FAILURE, "decomposition type not supported: MultiDim only");
+  if (cfg.domain_decomposition != MGX_DD_MAXDIM)
+    return fail(MGX_FAILURE, "domain decomposition not supported: MaxDim only");
+  if (!cfg.normalize_coordinates)
+    return fail(MGX_FAILURE, "normalize_coordinates = false is not supported");
+  if (cfg.huff_dict_size == 0 || cfg.huff_block_size == 0)
+    return fail(MGX_FAILURE, "huff_dict_size / huff_block_size must be non-zero");
+  return MGX_SUCCESS;
+}
+
+uint64_t available_bytes(const DeviceCache &c, const mgx_config &cfg) {
+  size_t free_b = 0, total_b = 0;
+  if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) {
+    cudaGetLastError();
+    free_b = 0;
+  }
+  uint64_t avail = (uint64_t)free_b + c.held();
+  return avail < cfg.max_memory_footprint ? avail : cfg.max_memory_footprint;
+}
+
+void put_u64_le(uint8_t *p, uint64_t v) {
+  for (int i = 0; i < 8; i++)
+    p[i] = (uint8_t)(v >> (8 * i));
+}
+
+// ---- compress ------------------------------------------------------------------
+int x_compress(int D, int dtype, const uint64_t *shape, double tol, double s,
+               int mode, const void *in, void **out, size_t *out_size,
+               const mgx_config &cfg, int prealloc) {
+  if (D > 5)
+    return fail(MGX_TOO_MANY_DIMENSIONS, "more than 5 dimensions");
+  if (dtype != MGX_F32 && dtype != MGX_F64)
+    return fail(MGX_BAD_DATA_TYPE, "data type not supported");
+  if (D < 1 || !shape || !in || !out || !out_size)
+    return fail(MGX_FAILURE, "bad argument");
+  int rc = check_config(cfg);
+  if (rc)
+    return rc;
+  const size_t es = dtype == MGX_F64 ? 8 : 4;
+  // the templated reference entry takes tol and s as T (CompressionHighLevel.hpp:311)
+  const double tolT = dtype == MGX_F32 ? (double)(float)tol : tol;
+  const double sT = dtype == MGX_F32 ? (double)(float)s : s;
+  const int rel = mode == MGX_EB_REL;
+  const int linf = std::isinf(sT) ? 1 : 0;
+  uint64_t N = 1;
+  for (int d = 0; d < D; d++) {
+    if (shape[d] == 0)
+      return fail(MGX_FAILURE, "empty dimension");
+    N *= shape[d];
+  }
+
+  const PtrLoc in_loc = locate(in);
+  const int dev = in_loc.device ? in_loc.dev : cfg.dev_id;
+  DeviceCache *cp = nullptr;
+  rc = cache_get(dev, &cp);
+  if (rc)
+    return rc;
+  DeviceCache &c = *cp;
+
+  Slabs sl;
+  rc = decide_slabs(D, shape, dtype, sT, available_bytes(c, cfg), &sl);
+  if (rc)
+    return rc;
+
+  // output buffer in the same memory space as the input (:141-154)
+  size_t cap;
+  bool allocated_here = false;
+  if (!prealloc) {
+    cap = N * es + 1000000;
+    if (in_loc.device) {
+      X_CUDA(cudaMalloc(out, cap));
+    } else {
+      *out = malloc(cap);
+      if (!*out)
+        return fail(MGX_FAILURE, "out of host memory");
+    }
+    allocated_here = true;
+  } else {
+    cap = *out_size;
+    if (!*out)
+      return fail(MGX_FAILURE, "output_pre_allocated without a buffer");
+  }
+  struct FreeOnError {
+    void **out;
+    bool dev, armed;
+    ~FreeOnError() {
+      if (armed) {
+        if (dev)
+          cudaFree(*out);
+        else
+          free(*out);
+        *out = nullptr;
+      }
+    }
+  } guard{out, in_loc.device, allocated_here};
+
+  const PtrLoc out_loc = locate(*out);
+  ScopedPin pin_in, pin_out;
+  if (!in_loc.device)
+    pin_in.pin(in, N * es, cfg.auto_pin_host_buffers);
+  if (!out_loc.device)
+    pin_out.pin(*out, cap, cfg.auto_pin_host_buffers);
+
+  mgx_metadata md;
+  memset(&md, 0, sizeof(md));
+  md.version[0] = FILE_VERSION_MAJOR; // see mgard_b200_x.h: the reference stores
+                                      // its file version in mgard_version
+  md.D = D;
+  for (int d = 0; d < D; d++)
+    md.shape[d] = shape[d];
+  md.dtype = dtype;
+  md.mode = mode == MGX_EB_REL ? MGX_EB_REL : MGX_EB_ABS;
+  md.linf = linf;
+  md.s = sT;
+  md.tol = tolT;
+  md.norm = 1;
+  md.decomposed = sl.decomposed;
+  md.dd_type = MGX_DD_MAXDIM;
+  md.dd_dim = sl.dim;
+  md.dd_size = sl.decomposed ? sl.size : shape[0];
+  md.decomposition = MGX_DC_MULTIDIM;
+  md.lossless = MGX_LL_HUFFMAN;
+  md.huff_dict_size = cfg.huff_dict_size;
+  md.huff_block_size = cfg.huff_block_size;
+  md.reorder = cfg.reorder;
+  md.backend = 3; // X_CUDA
+  std::vector<uint8_t> head = header_bytes(md);
+  const uint64_t M = PREAMBLE + head.size();
+  if (cap < M)
+    return fail(MGX_OUTPUT_TOO_LARGE, "output buffer smaller than the header");
+
+  // input of subdomain i as a dense device array
+  const bool in_place = in_loc.device && sl.contiguous();
+  uint64_t max_elems = 0;
+  for (uint64_t i = 0; i < sl.num; i++)
+    max_elems = std::max(max_elems, sl.elems(i));
+  const size_t pay_cap = max_elems * es + (max_elems / cfg.huff_block_size + 2) * 16 +
+                         (size_t)(128 + cfg.huff_dict_size) * 8 + 4096;
+  if (!in_place) {
+    const int nb = sl.num > 1 ? 2 : 1;
+    for (int b = 0; b < nb; b++)
+      if ((rc = ensure_buffer(c.sub[b], c.sub_bytes[b], max_elems * es)))
+        return rc;
+  }
+  for (int b = 0; b < (sl.num > 1 ? 2 : 1); b++)
+    if ((rc = ensure_buffer(c.cbuf[b], c.cbuf_bytes[b], pay_cap)))
+      return rc;
+
+  auto slab_ptr = [&](uint64_t i, int b) -> const void * {
+    if (!in_place)
+      return c.sub[b];
+    uint64_t sh[5], off;
+    sl.sub_shape(i, sh, &off);
+    return (const char *)in + (size_t)off * sl.inner * es;
+  };
+  auto fetch = [&](uint64_t i, int b) -> int { // OriginalToSubdomain
+    if (in_place)
+      return MGX_SUCCESS;
+    // the buffer is free once the kernels that read it are done
+    X_CUDA(cudaStreamWaitEvent(c.copy_in, c.ev_free[b], 0));
+    int r = copy_slab(sl, i, c.sub[b], (void *)in, true, c.copy_in);
+    if (r)
+      return r;
+    X_CUDA(cudaEventRecord(c.ev_in[b], c.copy_in));
+    return MGX_SUCCESS;
+  };
+
+  // global norm + per-subdomain absolute tolerance (:100-131,
+  // ErrorToleranceCalculator.hpp:61-147)
+  double norm = 1, local_tol = tolT;
+  int local_rel = rel;
+  if (sl.decomposed) {
+    if (rel) {
+      double acc = 0;
+      if ((rc = fetch(0, 0)))
+        return rc;
+      for (uint64_t i = 0; i < sl.num; i++) {
+        const int b = (int)(i & 1);
+        if (i + 1 < sl.num && (rc = fetch(i + 1, b ^ 1)))
+          return rc;
+        uint64_t sh[5], off;
+        sl.sub_shape(i, sh, &off);
+        mgx_ctx *ctx;
+        if ((rc = cache_ctx(c, D, sh, dtype, cfg, &ctx)))
+          return rc;
+        if (!in_place)
+          X_CUDA(cudaStreamWaitEvent(c.compute, c.ev_in[b], 0));
+        double part = 0;
+        rc = mgx_norm_partial(ctx, slab_ptr(i, b), linf, &part);
+        if (rc)
+          return fail(rc, std::string("norm: ") + mgx_last_error(ctx));
+        X_CUDA(cudaEventRecord(c.ev_free[b], c.compute));
+        acc = linf ? std::max(acc, part) : acc + part;
+      }
+      norm = mgx_finish_norm(dtype, linf, acc, N, 1);
+    }
+    local_tol = mgx_local_abs_tol(dtype, rel, norm, tolT, sT, sl.num);
+    local_rel = 0; // ABS inside every subdomain (:126-129)
+  }
+
+  uint8_t *obase = (uint8_t *)*out;
+  uint64_t offset = M; // bytes written so far
+  uint8_t size_le[8];
+  if ((rc = fetch(0, 0)))
+    return rc;
+  for (uint64_t i = 0; i < sl.num; i++) {
+    const int b = (int)(i & 1);
+    if (i + 1 < sl.num && (rc = fetch(i + 1, b ^ 1)))
+      return rc;
+    uint64_t sh[5], off;
+    sl.sub_shape(i, sh, &off);
+    const uint64_t n_sub = sl.elems(i);
+    mgx_ctx *ctx;
+    if ((rc = cache_ctx(c, D, sh, dtype, cfg, &ctx)))
+      return rc;
+    if (!in_place)
+      X_CUDA(cudaStreamWaitEvent(c.compute, c.ev_in[b], 0));
+    // the payload buffer is free once its previous D2H has finished
+    X_CUDA(cudaStreamWaitEvent(c.compute, c.ev_out[b], 0));
+    const void *d_in = slab_ptr(i, b);
+    uint64_t bytes = 0;
+    double nrm = local_rel ? 0.0 : norm;
+    rc = mgx_compress(ctx, d_in, local_rel, local_tol, sT, &nrm,
+                      (uint8_t *)c.cbuf[b], pay_cap, &bytes);
+    if (rc != MGX_SUCCESS && rc != MGX_OUTPUT_TOO_LARGE)
+      return fail(rc, std::string("compress: ") + mgx_last_error(ctx));
+    if (!sl.decomposed && rel)
+      norm = nrm;
+    const void *payload = c.cbuf[b];
+    // CR < 1: store the subdomain itself (GPUPipelines.hpp:139-156)
+    if (rc == MGX_OUTPUT_TOO_LARGE || bytes > n_sub * es) {
+      payload = d_in;
+      bytes = n_sub * es;
+    }
+    if (offset + 8 > cap || bytes > cap - offset - 8)
+      return fail(MGX_OUTPUT_TOO_LARGE, "output too large");
+    put_u64_le(size_le, bytes);
+    if (out_loc.device)
+      X_CUDA(cudaMemcpy(obase + offset, size_le, 8, cudaMemcpyHostToDevice));
+    else
+      memcpy(obase + offset, size_le, 8);
+    offset += 8;
+    // mgx_compress has synchronised the compute stream: the payload is final
+    X_CUDA(cudaMemcpyAsync(obase + offset, payload, bytes, cudaMemcpyDefault,
+                           c.copy_out));
+    X_CUDA(cudaEventRecord(c.ev_out[b], c.copy_out));
+    if (payload == d_in && !in_place) { // raw copy still reads the slab buffer
+      X_CUDA(cudaStreamWaitEvent(c.compute, c.ev_out[b], 0));
+    }
+    X_CUDA(cudaEventRecord(c.ev_free[b], c.compute));
+    offset += bytes;
+  }
+  X_CUDA(cudaStreamSynchronize(c.copy_out));
+  X_CUDA(cudaStreamSynchronize(c.compute));
+
+  // header with the final norm (:230-262)
+  md.norm = dtype == MGX_F32 ? (double)(float)norm : norm;
+  head = header_bytes(md);
+  std::vector<uint8_t> pre(PREAMBLE + head.size());
+  memcpy(pre.data(), SIGNATURE, 5);
+  put_u64_le(pre.data() + 5, head.size());
+  const uint32_t crc = mgx_crc32(head.data(), head.size());
+  for (int i = 0; i < 4; i++)
+    pre[13 + i] = (uint8_t)(crc >> (8 * i));
+  memcpy(pre.data() + PREAMBLE, head.data(), head.size());
+  if (pre.size() != M)
+    return fail(MGX_FAILURE, "header size changed");
+  if (out_loc.device)
+    X_CUDA(cudaMemcpy(obase, pre.data(), M, cudaMemcpyHostToDevice));
+  else
+    memcpy(obase, pre.data(), M);
+  *out_size = offset;
+  guard.armed = false;
+  if (cfg.auto_cache_release)
+    cache_release(c);
+  return MGX_SUCCESS;
+}
+
+// ---- decompress ------------------------------------------------------------------
+int fetch_header(const void *in, size_t in_size, const PtrLoc &loc,
+                 std::vector<uint8_t> *buf) {
+  if (in_size < PREAMBLE)
+    return fail(MGX_FAILURE, "stream shorter than the MGARD preamble");
+  uint8_t pre[PREAMBLE];
+  if (loc.device)
+    X_CUDA(cudaMemcpy(pre, in, PREAMBLE, cudaMemcpyDeviceToHost));
+  else
+    memcpy(pre, in, PREAMBLE);
+  uint64_t total = 0;
+  int rc = mgx_metadata_size(pre, PREAMBLE, &total);
+  if (rc)
+    return rc;
+  if (total > in_size)
+    return fail(MGX_FAILURE, "stream shorter than its header");
+  buf->resize(total);
+  if (loc.device)
+    X_CUDA(cudaMemcpy(buf->data(), in, total, cudaMemcpyDeviceToHost));
+  else
+    memcpy(buf->data(), in, total);
+  return MGX_SUCCESS;
+}
+
+int x_decompress(const void *in, size_t in_size, void **out, uint64_t *shape_out,
+                 int *D_out, int *dtype_out, const mgx_config &cfg_in, int prealloc) {
+  if (!in || !out)
+    return fail(MGX_FAILURE, "bad argument");
+  if (cfg_in.dev_type != MGX_DEV_AUTO && cfg_in.dev_type != MGX_DEV_CUDA)
+    return fail(MGX_BACKEND_UNAVAILABLE,
+                "only the CUDA backend is built (no CPU fallback by design)");
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0) {
+    cudaGetLastError();
+    return fail(MGX_BACKEND_UNAVAILABLE, "no CUDA device");
+  }
+  const PtrLoc in_loc = locate(in);
+  std::vector<uint8_t> hb;
+  int rc = fetch_header(in, in_size, in_loc, &hb);
+  if (rc)
+    return rc;
+  mgx_metadata md;
+  uint64_t M = 0;
+  rc = mgx_metadata_parse(hb.data(), hb.size(), &md, &M);
+  if (rc)
+    return rc;
+  if (md.D > 5)
+    return fail(MGX_TOO_MANY_DIMENSIONS, "more than 5 dimensions");
+  if (md.D < 1)
+    return fail(MGX_FAILURE, "header without a shape");
+  if (md.nonuniform)
+    return fail(MGX_FAILURE, "non-uniform grids are not supported");
+  // MetadataBase::InitializeConfig (Metadata.cpp:129-149)
+  mgx_config cfg = cfg_in;
+  cfg.domain_decomposition = md.dd_type;
+  cfg.decomposition = md.decomposition;
+  cfg.lossless = md.lossless;
+  if (md.huff_dict_size)
+    cfg.huff_dict_size = md.huff_dict_size;
+  if (md.huff_block_size)
+    cfg.huff_block_size = md.huff_block_size;
+  cfg.reorder = md.reorder;
+  if ((rc = check_config(cfg)))
+    return rc;
+
+  const int D = (int)md.D, dtype = md.dtype;
+  const size_t es = dtype == MGX_F64 ? 8 : 4;
+  uint64_t N = 1;
+  for (int d = 0; d < D; d++)
+    N *= md.shape[d];
+  if (shape_out)
+    for (int d = 0; d < D; d++)
+      shape_out[d] = md.shape[d];
+  if (D_out)
+    *D_out = D;
+  if (dtype_out)
+    *dtype_out = dtype;
+
+  const int dev = in_loc.device ? in_loc.dev : cfg.dev_id;
+  DeviceCache *cp = nullptr;
+  if ((rc = cache_get(dev, &cp)))
+    return rc;
+  DeviceCache &c = *cp;
+
+  bool allocated_here = false;
+  if (!prealloc) {
+    if (in_loc.device) {
+      X_CUDA(cudaMalloc(out, N * es));
+    } else {
+      *out = malloc(N * es);
+      if (!*out)
+        return fail(MGX_FAILURE, "out of host memory");
+    }
+    allocated_here = true;
+  } else if (!*out) {
+    return fail(MGX_FAILURE, "output_pre_allocated without a buffer");
+  }
+  struct FreeOnError {
+    void **out;
+    bool dev, armed;
+    ~FreeOnError() {
+      if (armed) {
+        if (dev)
+          cudaFree(*out);
+        else
+          free(*out);
+        *out = nullptr;
+      }
+    }
+  } guard{out, in_loc.device, allocated_here};
+  const PtrLoc out_loc = locate(*out);
+  ScopedPin pin_in, pin_out;
+  if (!in_loc.device)
+    pin_in.pin(in, in_size, cfg.auto_pin_host_buffers);
+  if (!out_loc.device)
+    pin_out.pin(*out, N * es, cfg.auto_pin_host_buffers);
+
+  Slabs sl;
+  sl.D = D;
+  sl.es = es;
+  for (int d = 0; d < D; d++)
+    sl.shape[d] = md.shape[d];
+  sl.decomposed = md.decomposed != 0;
+  if (sl.decomposed) {
+    if (md.dd_type != MGX_DD_MAXDIM || md.dd_dim >= (uint32_t)D || md.dd_size == 0)
+      return fail(MGX_FAILURE, "bad domain decomposition in the header");
+    sl.dim = (int)md.dd_dim;
+    sl.size = md.dd_size;
+    sl.num = (md.shape[sl.dim] - 1) / sl.size + 1;
+  }
+  sl.finish();
+
+  const int rel = md.mode == MGX_EB_REL;
+  const double sT = dtype == MGX_F32 ? (double)(float)md.s : md.s;
+  const double normT = dtype == MGX_F32 ? (double)(float)md.norm : md.norm;
+  double local_tol = dtype == MGX_F32 ? (double)(float)md.tol : md.tol;
+  int local_rel = rel;
+  if (sl.decomposed) {
+    local_tol = mgx_local_abs_tol(dtype, rel, md.norm, md.tol, md.s, sl.num);
+    local_rel = 0;
+  }
+
+  const bool in_place = out_loc.device && sl.contiguous();
+  uint64_t max_elems = 0;
+  for (uint64_t i = 0; i < sl.num; i++)
+    max_elems = std::max(max_elems, sl.elems(i));
+  if (!in_place)
+    for (int b = 0; b < (sl.num > 1 ? 2 : 1); b++)
+      if ((rc = ensure_buffer(c.sub[b], c.sub_bytes[b], max_elems * es)))
+        return rc;
+
+  // walk the records once on the host side to know sizes and offsets
+  // (a device-resident stream costs one 8-byte D2H per subdomain, like the
+  // reference's Deserialize<SIZE>, GPUPipelines.hpp:338-340)
+  std::vector<uint64_t> rec_off(sl.num), rec_bytes(sl.num);
+  uint64_t pos = M, max_rec = 0;
+  for (uint64_t i = 0; i < sl.num; i++) {
+    if (pos + 8 > in_size)
+      return fail(MGX_FAILURE, "stream ends inside a subdomain record");
+    uint8_t le[8];
+    if (in_loc.device)
+      X_CUDA(cudaMemcpy(le, (const uint8_t *)in + pos, 8, cudaMemcpyDeviceToHost));
+    else
+      memcpy(le, (const uint8_t *)in + pos, 8);
+    uint64_t n = 0;
+    for (int k = 0; k < 8; k++)
+      n |= (uint64_t)le[k] << (8 * k);
+    pos += 8;
+    if (n > in_size - pos)
+      return fail(MGX_FAILURE, "stream ends inside a subdomain record");
+    rec_off[i] = pos;
+    rec_bytes[i] = n;
+    max_rec = std::max(max_rec, n);
+    pos += n;
+  }
+  for (int b = 0; b < (sl.num > 1 ? 2 : 1); b++)
+    if ((rc = ensure_buffer(c.cbuf[b], c.cbuf_bytes[b], max_rec + 64)))
+      return rc;
+
+  auto fetch = [&](uint64_t i, int b) -> int {
+    X_CUDA(cudaStreamWaitEvent(c.copy_in, c.ev_free[b], 0));
+    X_CUDA(cudaMemcpyAsync(c.cbuf[b], (const uint8_t *)in + rec_off[i], rec_bytes[i],
+                           cudaMemcpyDefault, c.copy_in));
+    X_CUDA(cudaEventRecord(c.ev_in[b], c.copy_in));
+    return MGX_SUCCESS;
+  };
+
+  if ((rc = fetch(0, 0)))
+    return rc;
+  for (uint64_t i = 0; i < sl.num; i++) {
+    const int b = (int)(i & 1);
+    if (i + 1 < sl.num && (rc = fetch(i + 1, b ^ 1)))
+      return rc;
+    uint64_t sh[5], off;
+    sl.sub_shape(i, sh, &off);
+    const uint64_t n_sub = sl.elems(i);
+    void *d_out = in_place ? (void *)((char *)*out + (size_t)off * sl.inner * es)
+                           : c.sub[b];
+    X_CUDA(cudaStreamWaitEvent(c.compute, c.ev_in[b], 0));
+    if (!in_place) // previous copy-out of this buffer
+      X_CUDA(cudaStreamWaitEvent(c.compute, c.ev_out[b], 0));
+    // CR > 1 -> compressed; otherwise the record is the raw subdomain
+    // (GPUPipelines.hpp:407-421)
+    const double CR = (double)n_sub * es / (double)rec_bytes[i];
+    if (CR > 1.0) {
+      mgx_ctx *ctx;
+      if ((rc = cache_ctx(c, D, sh, dtype, cfg, &ctx)))
+        return rc;
+      rc = mgx_decompress(ctx, (const uint8_t *)c.cbuf[b], rec_bytes[i], local_rel,
+                          local_tol, sT, normT, d_out);
+      if (rc)
+        return fail(rc, std::string("decompress: ") + mgx_last_error(ctx));
+    } else {
+      if (rec_bytes[i] != n_sub * es)
+        return fail(MGX_FAILURE, "raw subdomain record of the wrong size");
+      X_CUDA(cudaMemcpyAsync(d_out, c.cbuf[b], rec_bytes[i], cudaMemcpyDeviceToDevice,
+                             c.compute));
+      X_CUDA(cudaStreamSynchronize(c.compute));
+    }
+    X_CUDA(cudaEventRecord(c.ev_free[b], c.compute));
+    if (!in_place) { // SubdomainToOriginal, after the kernels that fill the slab
+      X_CUDA(cudaStreamWaitEvent(c.copy_out, c.ev_free[b], 0));
+      if ((rc = copy_slab(sl, i, c.sub[b], *out, false, c.copy_out)))
+        return rc;
+      X_CUDA(cudaEventRecord(c.ev_out[b], c.copy_out));
+    }
+  }
+  X_CUDA(cudaStreamSynchronize(c.copy_out));
+  X_CUDA(cudaStreamSynchronize(c.compute));
+  guard.armed = false;
+  if (cfg.auto_cache_release)
+    cache_release(c);
+  return MGX_SUCCESS;
+}
+
+} // namespace
+
+extern "C" {
+
+void mgx_config_default(mgx_config *cfg) {
+  if (!cfg)
+    return;
+  cfg->dev_type = MGX_DEV_AUTO;
+  cfg->dev_id = 0;
+  cfg->domain_decomposition = MGX_DD_MAXDIM;
+  cfg->decomposition = MGX_DC_MULTIDIM;
+  cfg->lossless = MGX_LL_HUFFMAN;
+  cfg->huff_dict_size = 8192;
+  cfg->huff_block_size = 1024;
+  cfg->reorder = 0;
+  cfg->normalize_coordinates = 1;
+  cfg->auto_pin_host_buffers = 1;
+  cfg->compress_with_dryrun = 0;
+  cfg->auto_cache_release = 0;
+  cfg->log_level = 1;
+  cfg->max_larget_level = std::numeric_limits<uint64_t>::max();
+  cfg->max_memory_footprint = std::numeric_limits<uint64_t>::max();
+}
+
+uint32_t mgx_crc32(const void *data, uint64_t bytes) {
+  if (!g_crc_ready)
+    crc_init();
+  const uint8_t *p = (const uint8_t *)data;
+  uint32_t c = 0xFFFFFFFFu;
+  for (uint64_t i = 0; i < bytes; i++)
+    c = g_crc_table[(c ^ p[i]) & 0xFF] ^ (c >> 8);
+  return c ^ 0xFFFFFFFFu;
+}
+
+int mgx_metadata_serialize(const mgx_metadata *m, uint8_t *out, uint64_t cap,
+                           uint64_t *bytes) {
+  if (!m || !bytes || m->D < 1 || m->D > 5)
+    return MGX_FAILURE;
+  std::vector<uint8_t> head = header_bytes(*m);
+  *bytes = PREAMBLE + head.size();
+  if (!out || cap < *bytes)
+    return MGX_OUTPUT_TOO_LARGE;
+  memcpy(out, SIGNATURE, 5);
+  put_u64_le(out + 5, head.size());
+  const uint32_t crc = mgx_crc32(head.data(), head.size());
+  for (int i = 0; i < 4; i++)
+    out[13 + i] = (uint8_t)(crc >> (8 * i));
+  memcpy(out + PREAMBLE, head.data(), head.size());
+  return MGX_SUCCESS;
+}
+
+int mgx_metadata_size(const uint8_t *in, uint64_t bytes, uint64_t *header_bytes_out) {
+  if (!in || bytes < 13 || !header_bytes_out)
+    return fail(MGX_FAILURE, "stream shorter than the MGARD preamble");
+  if (memcmp(in, SIGNATURE, 5) != 0)
+    return fail(MGX_FAILURE, "signature mismatch.");
+  uint64_t n = 0;
+  for (int k = 0; k < 8; k++)
+    n |= (uint64_t)in[5 + k] << (8 * k);
+  if (n > ((uint64_t)1 << 31))
+    return fail(MGX_FAILURE, "header is too large (size would overflow).");
+  *header_bytes_out = n + PREAMBLE;
+  return MGX_SUCCESS;
+}
+
+int mgx_metadata_parse(const uint8_t *in, uint64_t bytes, mgx_metadata *m,
+                       uint64_t *header_bytes_out) {
+  if (!m)
+    return MGX_FAILURE;
+  uint64_t total = 0;
+  int rc = mgx_metadata_size(in, bytes, &total);
+  if (rc)
+    return rc;
+  if (bytes < total)
+    return fail(MGX_FAILURE, "stream shorter than its header");
+  uint32_t crc = 0;
+  for (int i = 0; i < 4; i++)
+    crc |= (uint32_t)in[13 + i] << (8 * i);
+  if (crc != mgx_crc32(in + PREAMBLE, total - PREAMBLE))
+    return fail(MGX_FAILURE, "header CRC32 mismatch.");
+  rc = parse_header(in + PREAMBLE, total - PREAMBLE, *m);
+  if (rc)
+    return rc;
+  if (header_bytes_out)
+    *header_bytes_out = total;
+  return MGX_SUCCESS;
+}
+
+uint64_t mgx_estimate_footprint(int D, const uint64_t *shape, int dtype, double s,
+                                int prefetch) {
+  if (D < 1 || D > 5 || !shape)
+    return 0;
+  return footprint(D, shape, dtype, s, prefetch);
+}
+
+int mgx_max_dim_by_memory(int D, const uint64_t *shape, int dtype, double s,
+                          uint64_t available, int *decomposed, int *dim,
+                          uint64_t *size, uint64_t *num) {
+  if (D > 5)
+    return MGX_TOO_MANY_DIMENSIONS;
+  if (D < 1 || !shape || !decomposed || !dim || !size || !num)
+    return MGX_FAILURE;
+  // DomainDecomposer(shape, config), DomainDecomposer.hpp:293-330
+  if (footprint(D, shape, dtype, s, 0) < available) {
+    *decomposed = 0;
+    *dim = 0;
+    *size = shape[0];
+    *num = 1;
+    return MGX_SUCCESS;
+  }
+  uint64_t chunk[5];
+  uint64_t best = 0;
+  int bd = 0;
+  for (int d = 0; d < D; d++) {
+    chunk[d] = shape[d];
+    if (shape[d] > best) {
+      best = shape[d];
+      bd = d;
+    }
+  }
+  int prefetch = 0;
+  uint64_t n = 1;
+  while (footprint(D, chunk, dtype, s, prefetch) >= available) {
+    if (chunk[bd] <= 1)
+      return MGX_FAILURE; // not even one row fits
+    chunk[bd] = (chunk[bd] - 1) / 2 + 1; // divide by 2 and round up
+    n = (best - 1) / chunk[bd] + 1;
+    prefetch = n > 1;
+  }
+  *decomposed = 1;
+  *dim = bd;
+  *size = chunk[bd];
+  *num = (best - 1) / chunk[bd] + 1;
+  return MGX_SUCCESS;
+}
+
+int mgx_x_compress(int D, int dtype, const uint64_t *shape, double tol, double s,
+                   int mode, const void *in, void **out, size_t *out_size,
+                   const mgx_config *cfg, int output_pre_allocated) {
+  std::lock_guard<std::mutex> lock(g_mu);
+  mgx_config c;
+  if (cfg)
+    c = *cfg;
+  else
+    mgx_config_default(&c);
+  g_err.clear();
+  return x_compress(D, dtype, shape, tol, s, mode, in, out, out_size, c,
+                    output_pre_allocated);
+}
+
+int mgx_x_decompress(const void *in, size_t in_size, void **out,
+                     uint64_t *shape_out, int *D_out, int *dtype_out,
+                     const mgx_config *cfg, int output_pre_allocated) {
+  std::lock_guard<std::mutex> lock(g_mu);
+  mgx_config c;
+  if (cfg)
+    c = *cfg;
+  else
+    mgx_config_default(&c);
+  g_err.clear();
+  return x_decompress(in, in_size, out, shape_out, D_out, dtype_out, c,
+                      output_pre_allocated);
+}
+
+static int backend_ok(const mgx_config *cfg) {
+  int t = cfg ? cfg->dev_type : MGX_DEV_AUTO;
+  return t == MGX_DEV_AUTO || t == MGX_DEV_CUDA;
+}
+
+int mgx_x_release_cache(const mgx_config *cfg) {
+  std::lock_guard<std::mutex> lock(g_mu);
+  if (!backend_ok(cfg))
+    return MGX_BACKEND_UNAVAILABLE;
+  for (auto &kv : g_cache)
+    cache_release(kv.second);
+  return MGX_SUCCESS;
+}
+
+int mgx_x_pin_memory(void *ptr, uint64_t bytes, const mgx_config *cfg) {
+  if (!backend_ok(cfg))
+    return MGX_BACKEND_UNAVAILABLE;
+  if (cudaHostRegister(ptr, bytes, cudaHostRegisterDefault) != cudaSuccess) {
+    cudaGetLastError();
+    return MGX_FAILURE;
+  }
+  return MGX_SUCCESS;
+}
+
+int mgx_x_check_memory_pinned(void *ptr, const mgx_config *cfg) {
+  if (!backend_ok(cfg))
+    return 0;
+  return host_registered(ptr) ? 1 : 0;
+}
+
+int mgx_x_unpin_memory(void *ptr, const mgx_config *cfg) {
+  if (!backend_ok(cfg))
+    return MGX_BACKEND_UNAVAILABLE;
+  if (cudaHostUnregister(ptr) != cudaSuccess) {
+    cudaGetLastError();
+    return MGX_FAILURE;
+  }
+  return MGX_SUCCESS;
+}
+
+const char *mgx_x_last_error(void) { return g_err.c_str(); }
+
+uint64_t mgx_x_launch_count(void) {
+  std::lock_guard<std::mutex> lock(g_mu);
+  uint64_t n = 0;
+  for (auto &kv : g_cache) {
+    n += kv.second.retired_launches;
+    for (auto &p : kv.second.plans)
+      n += mgx_launch_count(p.ctx);
+  }
+  return n;
+}
+
+} // extern "C"

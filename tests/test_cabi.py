@@ -12,13 +12,16 @@ import pytest
 import oracle_lib
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-HEADER = os.path.join(ROOT, "include", "mgard_b200.h")
+HEADERS = [os.path.join(ROOT, "include", "mgard_b200.h"),
+           os.path.join(ROOT, "include", "mgard_b200_x.h")]
 
 
 def declared_functions():
-    src = open(HEADER).read()
-    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-    names = re.findall(r"\b(mgx_[a-z0-9_]+)\s*\(", src)
+    names = []
+    for h in HEADERS:
+        src = open(h).read()
+        src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+        names += re.findall(r"\b(mgx_[a-z0-9_]+)\s*\(", src)
     return sorted(set(names))
 
 
@@ -27,7 +30,9 @@ def test_header_declares_the_boundary():
     for must in ("mgx_create", "mgx_destroy", "mgx_plan", "mgx_compress",
                  "mgx_decompress", "mgx_decompose", "mgx_recompose", "mgx_quantize",
                  "mgx_dequantize", "mgx_huff_encode", "mgx_huff_decode",
-                 "mgx_compress_host", "mgx_decompress_host"):
+                 "mgx_compress_host", "mgx_decompress_host", "mgx_x_compress",
+                 "mgx_x_decompress", "mgx_metadata_serialize",
+                 "mgx_metadata_parse"):
         assert must in names
 
 

@@ -1,0 +1,275 @@
+"""GPU tests of the high-level path (mgard_x::compress / decompress, reference
+include/compress_x.hpp:31-178) through the C ABI of include/mgard_b200_x.h.
+
+The stream is header + [u64 size][payload] per subdomain.  Every payload must be
+the byte-exact container the CPU oracle writes for that subdomain with the
+tolerance the reference derives for it (calc_local_abs_tol, global norm), the
+header must parse, and decompress must honour the bound on every element."""
+import ctypes
+import math
+import os
+import struct
+import subprocess
+
+import numpy as np
+import pytest
+import torch
+
+import oracle_lib
+from oracle_lib import Oracle, smooth_field, same_container
+
+import mgard_b200 as mg
+from mgard_b200 import _lib, highlevel as hl
+
+pytestmark = pytest.mark.gpu
+INF = float("inf")
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def records(stream):
+    """-> (metadata, [payload bytes per subdomain])"""
+    stream = np.asarray(stream.cpu() if hasattr(stream, "cpu") else stream)
+    md, pos = hl.read_metadata(bytes(stream[:4096]))
+    out = []
+    while pos < stream.size:
+        (n,) = struct.unpack_from("<Q", stream, pos)
+        pos += 8
+        out.append(stream[pos:pos + n].copy())
+        pos += n
+    assert pos == stream.size
+    return md, out
+
+
+def footprint(shape, dtype, s, prefetch=0):
+    shp = (ctypes.c_uint64 * len(shape))(*shape)
+    return _lib.load().mgx_estimate_footprint(len(shape), shp,
+                                              1 if dtype == np.float64 else 0,
+                                              s, prefetch)
+
+
+def slabs_of(md):
+    shape = [md.shape[d] for d in range(md.D)]
+    if not md.decomposed:
+        return [tuple(slice(None) for _ in shape)]
+    out = []
+    n, size, dim = shape[md.dd_dim], md.dd_size, md.dd_dim
+    for i in range((n - 1) // size + 1):
+        sl = [slice(None)] * md.D
+        sl[dim] = slice(i * size, min((i + 1) * size, n))
+        out.append(tuple(sl))
+    return out
+
+
+def check_bound(u, back, rel, tol, s):
+    u64, b64 = u.astype(np.float64), np.asarray(back).astype(np.float64)
+    if math.isinf(s):
+        scale = np.abs(u64).max() if rel else 1.0
+        assert np.abs(u64 - b64).max() <= tol * scale
+    else:
+        # Utilities/ErrorCalculator.h:56-97 with normalised coordinates
+        err = math.sqrt(((u64 - b64) ** 2).sum() / u64.size)
+        scale = math.sqrt((u64 ** 2).sum() / u64.size) if rel else 1.0
+        assert err <= tol * scale
+
+
+@pytest.mark.parametrize("shape,dtype,s,mode", [
+    ((33, 40, 65), np.float32, INF, hl.REL),
+    ((129, 70), np.float64, 0.0, hl.ABS),
+    ((5000,), np.float32, INF, hl.ABS),
+    ((5, 6, 7, 30), np.float64, 1.0, hl.REL),
+])
+@pytest.mark.parametrize("where", ["device", "host"])
+def test_single_domain_stream(shape, dtype, s, mode, where):
+    u = smooth_field(shape, dtype)
+    tol = 1e-3
+    x = torch.from_numpy(u).cuda() if where == "device" else u
+    stream = hl.compress(x, tol, s, mode)
+    assert (where == "device") == hasattr(stream, "is_cuda")
+    md, recs = records(stream)
+    assert not md.decomposed and md.dd_size == shape[0] and len(recs) == 1
+    assert md.backend == 3 and md.dtype == (1 if dtype == np.float64 else 0)
+    tolT = float(np.float32(tol)) if dtype == np.float32 else tol
+    assert md.tol == tolT and md.mode == mode
+    want, norm = Oracle("port").compress(u, int(mode == hl.REL), tolT, s)
+    assert same_container(recs[0], want)
+    if mode == hl.REL:
+        assert md.norm == norm
+    back = hl.decompress(stream)
+    assert tuple(back.shape) == shape
+    check_bound(u, back.cpu().numpy() if where == "device" else back,
+                mode == hl.REL, tol, s)
+
+
+def test_host_and_device_streams_are_identical():
+    u = smooth_field((40, 33, 50), np.float32)
+    a = hl.compress(u, 1e-3, INF, hl.REL)
+    b = hl.compress(torch.from_numpy(u).cuda(), 1e-3, INF, hl.REL).cpu().numpy()
+    assert np.array_equal(a, b)
+    # a host stream decodes on the device path and vice versa
+    x = hl.decompress(torch.from_numpy(a).cuda()).cpu().numpy()
+    y = hl.decompress(b)
+    assert np.array_equal(x, y)
+
+
+@pytest.mark.parametrize("shape,dtype,s,mode", [
+    ((70, 40, 33), np.float32, INF, hl.REL),     # dim 0: contiguous slabs
+    ((20, 90, 33), np.float32, INF, hl.ABS),     # dim 1: pitched copies
+    ((12, 30, 95), np.float64, INF, hl.REL),     # dim 2
+    ((300, 129), np.float64, 0.0, hl.REL),       # L2: tolerance split over slabs
+    ((6, 5, 7, 60), np.float64, 1.0, hl.ABS),    # 4-D, s-norm
+])
+@pytest.mark.parametrize("where", ["device", "host"])
+def test_max_dim_decomposition(shape, dtype, s, mode, where):
+    """max_memory_footprint forces MaxDim slabs (DomainDecomposer.hpp:192-223);
+    every record is the oracle's container for that slab compressed with an ABS
+    bound of calc_local_abs_tol (ErrorToleranceCalculator.hpp:126-147)."""
+    u = smooth_field(shape, dtype)
+    tol = 1e-3
+    cfg = hl.Config(max_memory_footprint=footprint(shape, dtype, s) - 1)
+    # stop after about three halvings: find the budget that does that
+    big = max(shape)
+    size = big
+    for _ in range(3):
+        size = (size - 1) // 2 + 1
+    sub = list(shape)
+    sub[shape.index(big)] = size
+    cfg.max_memory_footprint = footprint(sub, dtype, s, 1) + 1
+    x = torch.from_numpy(u).cuda() if where == "device" else u
+    stream = hl.compress(x, tol, s, mode, config=cfg)
+    md, recs = records(stream)
+    assert md.decomposed and md.dd_type == 0
+    assert md.dd_dim == shape.index(big) and md.dd_size <= size
+    sls = slabs_of(md)
+    assert len(recs) == len(sls) and len(recs) >= 2
+    # global norm, local tolerance
+    lib = _lib.load()
+    code = 1 if dtype == np.float64 else 0
+    tolT = float(np.float32(tol)) if dtype == np.float32 else tol
+    rel = int(mode == hl.REL)
+    norm = 1.0
+    if rel:
+        u64 = u.astype(np.float64)
+        part = np.abs(u64).max() if math.isinf(s) else (u64 ** 2).sum()
+        norm = lib.mgx_finish_norm(code, int(math.isinf(s)), part, u.size, 1)
+        assert md.norm == pytest.approx(norm, rel=1e-6)
+        norm = md.norm
+    ltol = lib.mgx_local_abs_tol(code, rel, norm, tolT, s, len(sls))
+    port = Oracle("port")
+    for rec, sl in zip(recs, sls):
+        piece = np.ascontiguousarray(u[sl])
+        want, _ = port.compress(piece, 0, ltol, s)
+        assert same_container(rec, want)
+    back = hl.decompress(stream)
+    check_bound(u, back.cpu().numpy() if where == "device" else back, rel, tol, s)
+
+
+def test_raw_fallback_when_a_subdomain_does_not_compress():
+    """CR < 1 -> the record is the raw subdomain (GPUPipelines.hpp:139-156) and
+    decompress copies it back (:407-421)."""
+    rng = np.random.default_rng(3)
+    u = rng.standard_normal((40, 30, 20)).astype(np.float32)
+    for x in (u, torch.from_numpy(u).cuda()):
+        stream = hl.compress(x, 1e-9, INF, hl.REL)
+        md, recs = records(stream)
+        assert len(recs) == 1 and recs[0].size == u.nbytes
+        assert np.array_equal(recs[0].view(np.float32).reshape(u.shape), u)
+        back = hl.decompress(stream)
+        back = back.cpu().numpy() if hasattr(back, "cpu") else back
+        assert np.array_equal(back, u)
+
+
+def test_status_codes():
+    lib = _lib.load()
+    cfg = hl.Config()
+    u = smooth_field((17, 17, 17), np.float32)
+    shp = (ctypes.c_uint64 * 6)(17, 17, 17, 1, 1, 1)
+    out = np.empty(1 << 20, np.uint8)
+    p, size = ctypes.c_void_p(out.ctypes.data), ctypes.c_size_t(out.size)
+
+    def call(D=3, dtype=0, cfg=cfg, cap=out.size):
+        size.value = cap
+        return lib.mgx_x_compress(D, dtype, shp, 1e-3, INF, 0, u.ctypes.data,
+                                  ctypes.byref(p), ctypes.byref(size),
+                                  ctypes.byref(cfg), 1)
+    assert call() == 0
+    good = out[:size.value].copy()
+    assert call(D=6) == 3           # NotSupportHigherNumberOfDimensionsFailure
+    assert call(dtype=7) == 4       # NotSupportDataTypeFailure
+    assert call(cfg=hl.Config(dev_type=hl.OPENMP)) == 5   # BackendNotAvailable
+    assert call(cfg=hl.Config(lossless=2)) == 1           # Huffman_Zstd: Failure
+    assert call(cap=64) == 2        # OutputTooLargeFailure
+    assert call(cap=300) == 2
+    assert b"too large" in lib.mgx_x_last_error()
+    # decompress: truncated / corrupted streams fail, never crash
+    for bad in (good[:40], good[:good.size // 2]):
+        with pytest.raises(mg.MgardError):
+            hl.decompress(bad)
+    # library-allocated output (output_pre_allocated = false), host input
+    q, n = ctypes.c_void_p(), ctypes.c_size_t()
+    assert lib.mgx_x_compress(3, 0, shp, 1e-3, INF, 0, u.ctypes.data,
+                              ctypes.byref(q), ctypes.byref(n),
+                              ctypes.byref(cfg), 0) == 0
+    got = np.ctypeslib.as_array(ctypes.cast(q, ctypes.POINTER(ctypes.c_uint8)),
+                                (n.value,)).copy()
+    assert np.array_equal(got, good)
+    r = ctypes.c_void_p()
+    shape_out = (ctypes.c_uint64 * 5)()
+    D, dt = ctypes.c_int(), ctypes.c_int()
+    assert lib.mgx_x_decompress(q, n.value, ctypes.byref(r), shape_out,
+                                ctypes.byref(D), ctypes.byref(dt),
+                                ctypes.byref(cfg), 0) == 0
+    assert D.value == 3 and dt.value == 0 and list(shape_out[:3]) == [17, 17, 17]
+    back = np.ctypeslib.as_array(ctypes.cast(r, ctypes.POINTER(ctypes.c_float)),
+                                 (u.size,)).reshape(u.shape)
+    assert np.abs(back - u).max() <= 1e-3 * np.abs(u).max()
+    libc = ctypes.CDLL(None)
+    libc.free.argtypes = [ctypes.c_void_p]
+    libc.free(q)
+    libc.free(r)
+    assert lib.mgx_x_release_cache(ctypes.byref(cfg)) == 0
+    # the cache is rebuilt on demand
+    assert call() == 0 and np.array_equal(out[:size.value], good)
+
+
+def test_pin_memory_api():
+    lib = _lib.load()
+    cfg = hl.Config()
+    buf = np.zeros(1 << 20, np.uint8)
+    assert lib.mgx_x_check_memory_pinned(buf.ctypes.data, ctypes.byref(cfg)) == 0
+    assert lib.mgx_x_pin_memory(buf.ctypes.data, buf.size, ctypes.byref(cfg)) == 0
+    assert lib.mgx_x_check_memory_pinned(buf.ctypes.data, ctypes.byref(cfg)) == 1
+    assert lib.mgx_x_unpin_memory(buf.ctypes.data, ctypes.byref(cfg)) == 0
+    assert lib.mgx_x_check_memory_pinned(buf.ctypes.data, ctypes.byref(cfg)) == 0
+
+
+def test_reference_decoder_reads_a_decomposed_record():
+    """interoperability: the reference's own low-level Decompress (oracle/_ref)
+    decodes a record taken out of our decomposed stream."""
+    if not oracle_lib.have_ref():
+        pytest.skip("oracle/_ref was not built")
+    shape = (70, 40, 33)
+    u = smooth_field(shape, np.float32)
+    cfg = hl.Config(max_memory_footprint=footprint((35, 40, 33), np.float32, INF, 1) + 1)
+    stream = hl.compress(u, 1e-3, INF, hl.REL, config=cfg)
+    md, recs = records(stream)
+    sls = slabs_of(md)
+    assert md.decomposed and len(recs) == len(sls) >= 2
+    ltol = _lib.load().mgx_local_abs_tol(0, 1, md.norm, md.tol, INF, len(sls))
+    for rec, sl in zip(recs, sls):
+        piece = u[sl]
+        back = oracle_lib.fresh("ref", "decompress", rec, piece.shape, np.float32,
+                                0, ltol, INF, 1.0)
+        assert np.abs(back - piece).max() <= 1e-3 * np.abs(u).max()
+
+
+def test_cpp_api_example_program():
+    """a program written against the reference's C++ API (namespace mgard_x,
+    examples/mgard-x/HighLevelAPIs/Example.cpp:18-36) built with
+    include/mgard_b200/compress_x.hpp"""
+    exe = os.path.join(ROOT, "tests", "cpp", "_build", "highlevel_example")
+    if not os.path.exists(exe):
+        pytest.fail("tests/cpp/_build/highlevel_example missing: run "
+                    "__graft_entry__.build()")
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "ALL OK" in r.stdout
