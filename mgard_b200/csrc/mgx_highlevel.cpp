@@ -733,13 +733,13 @@ uint64_t footprint(int D, const uint64_t *shape, int dtype, double s, int prefet
     n *= shape[d];
   // subdomain buffer + payload staging buffer (a payload larger than the raw
   // data is replaced by the raw data, so N*es + container overhead bounds it)
-  uint64_t io = n * es + (n * es + (n / 1024 + 1) * 16 + (1u << 20));
+  uint64_t io = n * es + (n * es + (n / 1024 + 1) * 16 + (1u << 17));
   if (prefetch)
     io *= 2;
   // context: 16-bit symbols, chunk tables, outlier list, and for the
   // orthogonal-projection path the level workspace + value scratch +
   // correction ping/pong buffers
-  uint64_t ws = n * 2 + (n / 256 + 1) * 24 + n / 8 + (1u << 20);
+  uint64_t ws = n * 2 + (n / 256 + 1) * 24 + n / 8 + (1u << 18);
   if (uses_correction(D, s))
     ws += n * es * 2 + (n * es * 3) / 4;
   else

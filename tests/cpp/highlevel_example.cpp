@@ -97,7 +97,7 @@ int main() {
                     mgard_x::error_bound_type::REL, config);
   roundtrip<float>({100000}, mgard_x::data_type::Float, 1e-2, inf,
                    mgard_x::error_bound_type::ABS, config);
-  roundtrip<double>({5, 6, 7, 40}, mgard_x::data_type::Double, 1e-3, 1.0,
+  roundtrip<double>({9, 10, 12, 60}, mgard_x::data_type::Double, 1e-3, 1.0,
                     mgard_x::error_bound_type::ABS, config);
 
   // a memory budget that forces domain decomposition
