@@ -89,9 +89,9 @@ def read_metadata(stream_head):
     return md, nb.value
 
 
-def decompress(stream, config=None):
+def decompress(stream, config=None, out=None):
     """-> array of the shape / dtype recorded in the stream, in the memory space
-    of ``stream``."""
+    of ``stream`` (``out``: optional pre-allocated array of that kind)."""
     lib = _lib.load()
     cfg = config if config is not None else Config()
     on_dev = _is_tensor(stream)
@@ -110,11 +110,13 @@ def decompress(stream, config=None):
     md, _ = read_metadata(full)
     shape = tuple(md.shape[d] for d in range(md.D))
     if on_dev:
-        out = torch.empty(shape, dtype=torch.float64 if md.dtype == 1
-                          else torch.float32, device=stream.device)
+        if out is None:
+            out = torch.empty(shape, dtype=torch.float64 if md.dtype == 1
+                              else torch.float32, device=stream.device)
         in_ptr, out_ptr, nbytes = stream.data_ptr(), out.data_ptr(), stream.numel()
     else:
-        out = np.empty(shape, dtype=np.float64 if md.dtype == 1 else np.float32)
+        if out is None:
+            out = np.empty(shape, dtype=np.float64 if md.dtype == 1 else np.float32)
         in_ptr, out_ptr, nbytes = stream.ctypes.data, out.ctypes.data, stream.size
     p = ctypes.c_void_p(out_ptr)
     _check(lib.mgx_x_decompress(ctypes.c_void_p(in_ptr), nbytes, ctypes.byref(p),
