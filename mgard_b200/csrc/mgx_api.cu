@@ -1,6 +1,7 @@
 // C ABI of mgard_b200 (see include/mgard_b200.h for the reference interface
 // each entry point replaces).
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <new>
@@ -57,11 +58,12 @@ bool need_orthogonal(const mgx_ctx *ctx, double s) {
 
 } // namespace
 
-int mgx_ensure_workspaces(mgx_ctx *ctx, bool need_w, bool need_v) {
+int mgx_ensure_workspaces(mgx_ctx *ctx, bool need_w, bool need_v, bool need_c) {
   const size_t es = mgx_elem(ctx);
   const MgxLevels &lv = ctx->lv;
-  if (need_w && !ctx->d_w) {
+  if (need_w && !ctx->d_w)
     MGX_CUDA(cudaMalloc(&ctx->d_w, lv.N * es));
+  if ((need_w || need_c) && !ctx->d_c0) {
     // correction ping/pong buffers: outputs of the first and second
     // restriction sweeps at the finest level are the largest ones
     uint64_t c0 = 1, c1 = 1;
@@ -99,6 +101,11 @@ int mgx_create(mgx_ctx **out, int device, void *cuda_stream) {
   if (!ctx)
     return MGX_FAILURE;
   ctx->device = device;
+  {
+    // A/B switch for measurements and tests: the superseded gather kernels
+    const char *e = getenv("MGX_LEGACY_LEVELS");
+    ctx->legacy_levels = e && e[0] == '1';
+  }
   cudaDeviceProp prop;
   if (cudaGetDeviceProperties(&prop, device) == cudaSuccess)
     ctx->num_sms = prop.multiProcessorCount;
@@ -292,7 +299,19 @@ double mgx_finish_norm(int dtype, int linf, double partial, uint64_t total_elems
 
 int mgx_decompose(mgx_ctx *ctx, void *d_data, int orthogonal) {
   MGX_CHECK_PLAN();
-  int rc = mgxk_decompose(ctx, d_data, orthogonal);
+  int rc;
+  if (orthogonal && !ctx->legacy_levels) {
+    // the row-streaming level kernels are out of place: nodes are read from a
+    // copy, coefficients land in the caller's array
+    rc = mgx_ensure_workspaces(ctx, true, false);
+    if (rc)
+      return rc;
+    MGX_CUDA(cudaMemcpyAsync(ctx->d_w, d_data, ctx->lv.N * mgx_elem(ctx),
+                             cudaMemcpyDeviceToDevice, ctx->stream));
+    rc = mgxk_decompose_rows(ctx, ctx->d_w, d_data);
+  } else {
+    rc = mgxk_decompose(ctx, d_data, orthogonal);
+  }
   if (rc)
     return rc;
   MGX_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -301,7 +320,18 @@ int mgx_decompose(mgx_ctx *ctx, void *d_data, int orthogonal) {
 
 int mgx_recompose(mgx_ctx *ctx, void *d_data, int orthogonal) {
   MGX_CHECK_PLAN();
-  int rc = mgxk_recompose(ctx, d_data, orthogonal);
+  int rc;
+  if (orthogonal && !ctx->legacy_levels) {
+    rc = mgx_ensure_workspaces(ctx, true, false);
+    if (rc)
+      return rc;
+    rc = mgxk_recompose_rows(ctx, d_data, ctx->d_w);
+    if (!rc)
+      MGX_CUDA(cudaMemcpyAsync(d_data, ctx->d_w, ctx->lv.N * mgx_elem(ctx),
+                               cudaMemcpyDeviceToDevice, ctx->stream));
+  } else {
+    rc = mgxk_recompose(ctx, d_data, orthogonal);
+  }
   if (rc)
     return rc;
   MGX_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -451,6 +481,9 @@ int mgx_compress(mgx_ctx *ctx, const void *d_in, int rel, double tol, double s,
     if (!orth) {
       // fused: coefficients of every level + quantise + histogram in one pass
       rc = mgxk_hier_forward(ctx, d_in, rel, tol, false, norm);
+    } else if (!ctx->legacy_levels) {
+      // level kernels with the quantiser fused into the coefficient pass
+      rc = mgxk_decompose_quantize_rows(ctx, d_in, rel, tol, s, norm);
     } else {
       rc = mgx_ensure_workspaces(ctx, true, true);
       if (rc)
@@ -496,7 +529,15 @@ int mgx_decompress(mgx_ctx *ctx, const uint8_t *d_in, uint64_t bytes, int rel,
   rc = MGX_FAILURE + 101;
   if (!orth) // fused dequantise + recompose (hierarchical basis)
     rc = mgxk_hier_inverse(ctx, rel, tol, norm, d_out, oidx, oval, n_out);
-  if (rc == MGX_FAILURE + 101) {
+  if (rc == MGX_FAILURE + 101 && orth && !ctx->legacy_levels) {
+    rc = mgx_ensure_workspaces(ctx, false, true);
+    if (!rc)
+      rc = mgxk_dequantize_sym_out(ctx, rel, tol, s, norm, ctx->d_v, oidx, oval,
+                                   n_out);
+    mgx_tick(ctx, MGX_TICK_D_DEQUANT);
+    if (!rc)
+      rc = mgxk_recompose_rows(ctx, ctx->d_v, d_out);
+  } else if (rc == MGX_FAILURE + 101) {
     rc = mgxk_dequantize_sym_out(ctx, rel, tol, s, norm, d_out, oidx, oval, n_out);
     mgx_tick(ctx, MGX_TICK_D_DEQUANT);
     if (!rc)

@@ -132,6 +132,11 @@ void mgx_build_tables(const MgxLevels &lv, MgxHostTables<T> *tb) {
       tb->buf.insert(tb->buf.end(), am.begin(), am.end());
       tb->off.bm[l][d] = (uint32_t)tb->buf.size();
       tb->buf.insert(tb->buf.end(), bm.begin(), bm.end());
+      // am[i] / bm[i], the forward-elimination factor of tridiag_forward2
+      // (IPKFunctor.h:13-30); data independent, so rounded once here
+      tb->off.abr[l][d] = (uint32_t)tb->buf.size();
+      for (uint64_t i = 0; i <= dof; i++)
+        tb->buf.push_back(am[i] / bm[i]);
     }
   // lwqzk volume factor, Quantization/LinearQuantization.hpp:74-90: product
   // over d = D-1 .. 0 starting from 1, then sqrt in T

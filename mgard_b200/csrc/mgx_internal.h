@@ -27,6 +27,7 @@ struct MgxTableOffsets {
   uint32_t ratio[MGX_MAX_L][MGX_MAX_D];
   uint32_t am[MGX_MAX_L][MGX_MAX_D];
   uint32_t bm[MGX_MAX_L][MGX_MAX_D];
+  uint32_t abr[MGX_MAX_L][MGX_MAX_D]; // am[i] / bm[i]
 };
 
 template <typename T> struct MgxHostTables {
@@ -50,6 +51,7 @@ struct mgx_ctx {
   int num_sms = 148;
   std::string err;
   uint64_t launches = 0;
+  bool legacy_levels = false; // MGX_LEGACY_LEVELS=1: gather kernels of mgx_refactor.cu
 
   bool planned = false;
   int dtype = MGX_F32;
@@ -168,4 +170,16 @@ int mgxk_symbols_to_codes(mgx_ctx *ctx, uint64_t n, int64_t *d_codes,
                           const uint64_t *d_oidx, const int64_t *d_oval,
                           uint64_t n_out);
 
-int mgx_ensure_workspaces(mgx_ctx *ctx, bool need_w, bool need_v);
+int mgx_ensure_workspaces(mgx_ctx *ctx, bool need_w, bool need_v,
+                          bool need_c = false);
+
+// row-streaming level kernels for the orthogonal-projection path (mgx_level.cu);
+// all out of place: source and destination must differ
+int mgxk_decompose_rows(mgx_ctx *ctx, const void *d_src, void *d_coeff);
+int mgxk_decompose_quantize_rows(mgx_ctx *ctx, const void *d_src, int rel,
+                                 double tol, double s, double norm);
+int mgxk_recompose_rows(mgx_ctx *ctx, const void *d_coeff, void *d_dst);
+// per-level quantiser (reciprocal for quantise) and volume factor, as doubles
+// holding the T-precision values (CalcQuantizers, LinearQuantization.hpp:234-297)
+void mgx_level_quantizers(const mgx_ctx *ctx, int rel, double tol, double s,
+                          double norm, bool reciprocal, double *q, double *vol);

@@ -260,6 +260,25 @@ __global__ void __launch_bounds__(256)
 
 } // namespace
 
+void mgx_level_quantizers(const mgx_ctx *ctx, int rel, double tol, double s,
+                          double norm, bool reciprocal, double *q, double *vol) {
+  if (mgx_is_f32(ctx)) {
+    QuantArgs<float> a;
+    fill_quant_args<float>(ctx, &a, rel, tol, s, norm, reciprocal);
+    for (int l = 0; l <= ctx->lv.L; l++) {
+      q[l] = a.q[l];
+      vol[l] = a.vol[l];
+    }
+  } else {
+    QuantArgs<double> a;
+    fill_quant_args<double>(ctx, &a, rel, tol, s, norm, reciprocal);
+    for (int l = 0; l <= ctx->lv.L; l++) {
+      q[l] = a.q[l];
+      vol[l] = a.vol[l];
+    }
+  }
+}
+
 int mgxk_norm_partial(mgx_ctx *ctx, const void *d_in, int linf) {
   unsigned long long *out =
       (unsigned long long *)(ctx->d_scalars + MGX_SC_NORM);
