@@ -5,6 +5,7 @@
 #include <cstring>
 #include <limits>
 #include <new>
+#include <vector>
 
 #include "mgx_internal.h"
 
@@ -21,6 +22,7 @@ template <typename P> void free_dev(P *&p) {
 
 void release_plan(mgx_ctx *ctx) {
   free_dev(ctx->d_tables);
+  free_dev(ctx->d_rcp);
   free_dev(ctx->d_w);
   free_dev(ctx->d_c0);
   free_dev(ctx->d_c1);
@@ -215,6 +217,27 @@ int mgx_plan(mgx_ctx *ctx, int D, const uint64_t *shape, int dtype,
   MGX_CUDA(cudaMalloc(&ctx->d_tables, bytes));
   MGX_CUDA(cudaMemcpyAsync(ctx->d_tables, src, bytes, cudaMemcpyHostToDevice,
                            ctx->stream));
+  {
+    // double-precision reciprocals of every table entry (used at the bm
+    // offsets by the Thomas solves' exactly rounded fast division); the fast
+    // path is switched off if a divisor has an all-ones significand, the one
+    // case the correction-step theorem excludes
+    const size_t cnt = bytes / mgx_elem(ctx);
+    std::vector<double> rcp(cnt);
+    ctx->fast_div = true;
+    for (size_t k = 0; k < cnt; k++) {
+      double b = dtype == MGX_F32 ? (double)ctx->tbf.buf[k] : ctx->tbd.buf[k];
+      rcp[k] = 1.0 / b;
+      if (dtype == MGX_F64) {
+        uint64_t bits;
+        std::memcpy(&bits, &b, 8);
+        if ((bits & 0xFFFFFFFFFFFFFull) == 0xFFFFFFFFFFFFFull)
+          ctx->fast_div = false;
+      }
+    }
+    MGX_CUDA(cudaMalloc(&ctx->d_rcp, cnt * 8));
+    MGX_CUDA(cudaMemcpy(ctx->d_rcp, rcp.data(), cnt * 8, cudaMemcpyHostToDevice));
+  }
   const uint64_t N = ctx->lv.N;
   const uint64_t nchunk = (N - 1) / chunk_size + 1;
   MGX_CUDA(cudaMalloc(&ctx->d_sym, N * 2 + 64));

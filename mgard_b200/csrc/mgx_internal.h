@@ -60,6 +60,8 @@ struct mgx_ctx {
   MgxHostTables<float> tbf;
   MgxHostTables<double> tbd;
   void *d_tables = nullptr; // T[] copy of tb.buf
+  double *d_rcp = nullptr;  // 1.0 / tb.buf[k] in double, same offsets
+  bool fast_div = true;
 
   // workspaces (allocated on first use, sized for the plan)
   void *d_w = nullptr;      // N elements of T (level workspace)

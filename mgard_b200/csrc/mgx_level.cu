@@ -42,7 +42,9 @@ struct LvGeom {
   uint32_t roff[MGX_MAX_D]; // ratio tables of level l
   uint32_t dist_f;          // dist table of the contiguous dim, level l
   uint64_t rows;            // prod nf[0..3]
-  uint32_t rows_per_block;
+  uint32_t rows_per_task;   // a warp task = one column chunk x this many rows
+  uint32_t col_chunks;      // column chunks per row
+  uint64_t tasks;           // col_chunks * ceil(rows / rows_per_task)
   int half;                 // every ratio is exactly 0.5
 };
 
@@ -98,17 +100,21 @@ __device__ __forceinline__ T mass_apply(const MassK<T> &m, T a, T b, T c, T d,
 }
 
 // ---- row walker ----------------------------------------------------------------
-// A block owns a contiguous range of rows of the level box in REORDERED row
-// order (p[d] < nc[d]: coarse node, else coefficient).  For the current row:
-//   q[d]    interleaved index of the row along d, odd[d] = it is a coefficient row
-//   nodd    number of odd outer dimensions; lo[j]/hi[j] element offsets of the
-//           two neighbour rows along the j-th odd dimension (innermost first),
-//           tt[j] its interpolation ratio
+// A warp owns a contiguous range of rows of the level box in REORDERED row
+// order (p[d] < nc[d]: coarse node, else coefficient) and one chunk of columns.
+// For the current row:
+//   so/vo/ao  offsets of the row in the node array / full array / coarse box A
+//   nodd      number of odd (coefficient) outer dimensions; hi[j] element offset
+//             to the upper neighbour row along the j-th odd dimension (innermost
+//             first), tt[j] its interpolation ratio.  FORWARD: neighbours are
+//             rows q -/+ 1 of the interleaved node array (lower = -hi);
+//             otherwise rows (q-1)/2 and (q-1)/2 + 1 of A (lower = +0).
+// Everything is indexed with compile-time constants so the state stays in
+// registers.
 template <typename T> struct Row {
-  uint32_t p[OUTER];
-  uint64_t so, vo, ao; // offsets of the row in the node array / full array / A
+  uint64_t so, vo, ao;
   int nodd;
-  int64_t lo[OUTER], hi[OUTER];
+  int64_t hi[OUTER];
   T tt[OUTER];
 };
 
@@ -123,34 +129,31 @@ __device__ __forceinline__ void pos_to_node(uint32_t p, uint32_t nf, uint32_t nc
   }
 }
 
-template <typename T>
-__device__ __forceinline__ void row_first(Row<T> &r, const LvGeom &g,
+__device__ __forceinline__ void row_first(uint32_t (&p)[OUTER], const LvGeom &g,
                                           uint64_t row) {
 #pragma unroll
   for (int d = OUTER - 1; d >= 0; d--) {
-    r.p[d] = (uint32_t)(row % g.nf[d]);
+    p[d] = (uint32_t)(row % g.nf[d]);
     row /= g.nf[d];
   }
 }
 
-template <typename T>
-__device__ __forceinline__ void row_next(Row<T> &r, const LvGeom &g) {
+__device__ __forceinline__ void row_next(uint32_t (&p)[OUTER], const LvGeom &g) {
   bool carry = true;
 #pragma unroll
   for (int d = OUTER - 1; d >= 0; d--) {
     if (carry) {
-      r.p[d]++;
-      carry = r.p[d] == g.nf[d];
+      p[d]++;
+      carry = p[d] == g.nf[d];
       if (carry)
-        r.p[d] = 0;
+        p[d] = 0;
     }
   }
 }
 
-// FORWARD: neighbours are rows of the interleaved node array (q -/+ 1);
-// otherwise rows of the compact coarse box A (positions (q-1)/2 and (q-1)/2+1).
 template <typename T, bool FORWARD>
-__device__ __forceinline__ void row_setup(Row<T> &r, const LvGeom &g,
+__device__ __forceinline__ void row_setup(Row<T> &r, const uint32_t (&p)[OUTER],
+                                          const LvGeom &g,
                                           const T *__restrict__ tables) {
   r.so = 0;
   r.vo = 0;
@@ -158,38 +161,31 @@ __device__ __forceinline__ void row_setup(Row<T> &r, const LvGeom &g,
   r.nodd = 0;
 #pragma unroll
   for (int j = 0; j < OUTER; j++) {
-    r.lo[j] = 0;
     r.hi[j] = 0;
     r.tt[j] = (T)0.5;
   }
+  // outermost dimension first, each odd one pushed to the front: the
+  // innermost odd dimension ends at index 0
 #pragma unroll
-  for (int d = OUTER - 1; d >= 0; d--) {
+  for (int d = 0; d < OUTER; d++) {
     uint32_t q;
     bool odd;
-    pos_to_node(r.p[d], g.nf[d], g.nc[d], q, odd);
+    pos_to_node(p[d], g.nf[d], g.nc[d], q, odd);
     r.so += (uint64_t)q * g.sst[d];
-    r.vo += (uint64_t)r.p[d] * g.vst[d];
+    r.vo += (uint64_t)p[d] * g.vst[d];
     if (odd) {
-      T t = g.half ? (T)0.5 : tables[g.roff[d] + q - 1];
-      int64_t l, h;
-      if (FORWARD) {
-        l = -(int64_t)g.sst[d];
-        h = (int64_t)g.sst[d];
-      } else {
-        r.ao += (uint64_t)((q - 1) / 2) * g.ast[d];
-        l = 0;
-        h = (int64_t)g.ast[d];
-      }
 #pragma unroll
-      for (int j = 0; j < OUTER; j++)
-        if (j == r.nodd) {
-          r.lo[j] = l;
-          r.hi[j] = h;
-          r.tt[j] = t;
-        }
+      for (int j = OUTER - 1; j > 0; j--) {
+        r.hi[j] = r.hi[j - 1];
+        r.tt[j] = r.tt[j - 1];
+      }
+      r.hi[0] = (int64_t)(FORWARD ? g.sst[d] : g.ast[d]);
+      r.tt[0] = g.half ? (T)0.5 : tables[g.roff[d] + q - 1];
       r.nodd++;
+      if (!FORWARD)
+        r.ao += (uint64_t)((q - 1) / 2) * g.ast[d];
     } else {
-      r.ao += (uint64_t)r.p[d] * g.ast[d];
+      r.ao += (uint64_t)p[d] * g.ast[d];
     }
   }
 }
@@ -198,7 +194,7 @@ __device__ __forceinline__ void row_setup(Row<T> &r, const LvGeom &g,
 // column to its right (b, interpolated along the contiguous dim FIRST, then
 // along the odd outer dims innermost to outermost -- the reference's f, c, r
 // order, GridProcessingKernel3D.hpp).
-template <typename T, int K>
+template <typename T, int K, bool FORWARD>
 __device__ __forceinline__ void corners(const T *__restrict__ base, int64_t off,
                                         const Row<T> &r, uint32_t e0, uint32_t e1,
                                         bool has_odd, T tf, T &a, T &b) {
@@ -208,10 +204,49 @@ __device__ __forceinline__ void corners(const T *__restrict__ base, int64_t off,
     b = has_odd ? mgx_lerp(x0, base[off + e1], tf) : (T)0;
   } else {
     T a0, b0, a1, b1;
-    corners<T, K - 1>(base, off + r.lo[K - 1], r, e0, e1, has_odd, tf, a0, b0);
-    corners<T, K - 1>(base, off + r.hi[K - 1], r, e0, e1, has_odd, tf, a1, b1);
+    corners<T, K - 1, FORWARD>(base, FORWARD ? off - r.hi[K - 1] : off, r, e0, e1,
+                               has_odd, tf, a0, b0);
+    corners<T, K - 1, FORWARD>(base, off + r.hi[K - 1], r, e0, e1, has_odd, tf, a1,
+                               b1);
     a = mgx_lerp(a0, a1, r.tt[K - 1]);
     b = mgx_lerp(b0, b1, r.tt[K - 1]);
+  }
+}
+
+// L2 -> L1 prefetch of what the NEXT row will load (the row loop is one
+// dependent load -> compute -> store chain per warp; without this every row
+// pays a full memory latency)
+__device__ __forceinline__ void prefetch_l1(const void *p) {
+  asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+}
+template <typename T, int K, bool FORWARD>
+__device__ __forceinline__ void prefetch_corners(const T *__restrict__ base,
+                                                 int64_t off, const Row<T> &r) {
+  if constexpr (K == 0) {
+    prefetch_l1(base + off);
+  } else {
+    prefetch_corners<T, K - 1, FORWARD>(base, FORWARD ? off - r.hi[K - 1] : off, r);
+    prefetch_corners<T, K - 1, FORWARD>(base, off + r.hi[K - 1], r);
+  }
+}
+template <typename T, bool FORWARD>
+__device__ __forceinline__ void prefetch_row(const T *__restrict__ base, int64_t off,
+                                             const Row<T> &r) {
+  switch (r.nodd) {
+  case 0:
+    break;
+  case 1:
+    prefetch_corners<T, 1, FORWARD>(base, off, r);
+    break;
+  case 2:
+    prefetch_corners<T, 2, FORWARD>(base, off, r);
+    break;
+  case 3:
+    prefetch_corners<T, 3, FORWARD>(base, off, r);
+    break;
+  default:
+    prefetch_corners<T, 4, FORWARD>(base, off, r);
+    break;
   }
 }
 
@@ -271,8 +306,8 @@ __device__ __forceinline__ void forward_row(
         co = sub_rn(vo, mgx_lerp(ve, srow[2 * i + 2], tf));
     } else {
       T a, b;
-      corners<T, K>(src, (int64_t)r.so, r, qe, (uint32_t)(2 * i + 2), has_odd, tf,
-                    a, b);
+      corners<T, K, true>(src, (int64_t)r.so, r, qe, (uint32_t)(2 * i + 2), has_odd,
+                          tf, a, b);
       ce = sub_rn(ve, a);
       if (has_odd)
         co = sub_rn(vo, b);
@@ -305,23 +340,35 @@ __global__ void __launch_bounds__(FW_WARPS * 32)
   }
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint32_t ncf = g.nc[FD], nff = g.nf[FD], ncoef = nff - ncf;
-  const int64_t i = (int64_t)(blockIdx.x * FW_WARPS + warp) * FW_OWN - 1 + lane;
-  const bool pair_ok = i >= 0 && i < (int64_t)ncf;
-  const bool has_odd = i >= 0 && i < (int64_t)ncoef;
-  const bool owned = lane >= 1 && lane <= FW_OWN;
-  const uint32_t qe = pair_ok ? ((i == (int64_t)ncf - 1) ? nff - 1 : (uint32_t)(2 * i)) : 0;
-  const T tf = (g.half || !has_odd) ? (T)0.5 : tables[g.roff[FD] + 2 * i];
-  MassK<T> mk = mass_consts<T>(tables + g.dist_f, pair_ok ? 2 * i : 0, nff);
-  const uint64_t row0 = (uint64_t)blockIdx.y * g.rows_per_block;
-  const uint64_t row1 = min(g.rows, row0 + g.rows_per_block);
-  // whole warp-columns past the end have nothing to do (but must still take
-  // part in the histogram flush below)
-  const bool warp_live = (int64_t)(blockIdx.x * FW_WARPS + warp) * FW_OWN < (int64_t)ncf;
-  if (warp_live && row0 < row1) {
+  const uint64_t task = (uint64_t)blockIdx.x * FW_WARPS + warp;
+  if (task < g.tasks) {
+    const uint32_t cw = (uint32_t)(task % g.col_chunks);
+    const uint64_t rg = task / g.col_chunks;
+    const int64_t i = (int64_t)cw * FW_OWN - 1 + lane;
+    const bool pair_ok = i >= 0 && i < (int64_t)ncf;
+    const bool has_odd = i >= 0 && i < (int64_t)ncoef;
+    const bool owned = lane >= 1 && lane <= FW_OWN;
+    const uint32_t qe =
+        pair_ok ? ((i == (int64_t)ncf - 1) ? nff - 1 : (uint32_t)(2 * i)) : 0;
+    const T tf = (g.half || !has_odd) ? (T)0.5 : tables[g.roff[FD] + 2 * i];
+    const MassK<T> mk = mass_consts<T>(tables + g.dist_f, pair_ok ? 2 * i : 0, nff);
+    const uint64_t row0 = rg * g.rows_per_task;
+    const uint64_t row1 = min(g.rows, row0 + g.rows_per_task);
+    uint32_t p[OUTER];
+    row_first(p, g, row0);
     Row<T> r;
-    row_first(r, g, row0);
+    row_setup<T, true>(r, p, g, tables);
     for (uint64_t row = row0; row < row1; row++) {
-      row_setup<T, true>(r, g, tables);
+      const bool more = row + 1 < row1;
+      if (more) {
+        row_next(p, g);
+        Row<T> nx;
+        row_setup<T, true>(nx, p, g, tables);
+        if (pair_ok) {
+          prefetch_l1(src + nx.so + qe);
+          prefetch_row<T, true>(src, (int64_t)nx.so + qe, nx);
+        }
+      }
       switch (r.nodd) {
       case 0:
         forward_row<T, QUANT, 0>(src, v, A, R, r, g, qo, s_hist, mk, i, pair_ok,
@@ -344,7 +391,8 @@ __global__ void __launch_bounds__(FW_WARPS * 32)
                                  has_odd, owned, qe, tf, row);
         break;
       }
-      row_next(r, g);
+      if (more)
+        row_setup<T, true>(r, p, g, tables);
     }
   }
   if (QUANT) {
@@ -363,25 +411,39 @@ __global__ void __launch_bounds__(256)
     k_lpk_first(const T *__restrict__ v, T *__restrict__ R,
                 const T *__restrict__ tables, const __grid_constant__ LvGeom g) {
   const uint32_t ncf = g.nc[FD], nff = g.nf[FD], ncoef = nff - ncf;
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  const uint64_t task = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (task >= g.tasks)
+    return;
+  const uint32_t cw = (uint32_t)(task % g.col_chunks);
+  const uint64_t rg = task / g.col_chunks;
+  const int64_t i = (int64_t)cw * 32 + lane;
   if (i >= (int64_t)ncf)
     return;
   MassK<T> mk = mass_consts<T>(tables + g.dist_f, 2 * i, nff);
-  const uint64_t row0 = (uint64_t)blockIdx.y * g.rows_per_block;
-  const uint64_t row1 = min(g.rows, row0 + g.rows_per_block);
-  if (row0 >= row1)
-    return;
-  Row<T> r;
-  row_first(r, g, row0);
+  const uint64_t row0 = rg * g.rows_per_task;
+  const uint64_t row1 = min(g.rows, row0 + g.rows_per_task);
+  uint32_t p[OUTER];
+  row_first(p, g, row0);
   for (uint64_t row = row0; row < row1; row++) {
     bool coarse_row = true;
     uint64_t vo = 0;
 #pragma unroll
     for (int d = 0; d < OUTER; d++) {
-      coarse_row = coarse_row && r.p[d] < g.nc[d];
-      vo += (uint64_t)r.p[d] * g.vst[d];
+      coarse_row = coarse_row && p[d] < g.nc[d];
+      vo += (uint64_t)p[d] * g.vst[d];
     }
     const T *vr = v + vo;
+    row_next(p, g);
+    if (row + 1 < row1) {
+      uint64_t vn = 0;
+#pragma unroll
+      for (int d = 0; d < OUTER; d++)
+        vn += (uint64_t)p[d] * g.vst[d];
+      prefetch_l1(v + vn + i);
+      if (i < (int64_t)ncoef)
+        prefetch_l1(v + vn + ncf + i);
+    }
     T a = 0, b = 0, c = 0, d = 0, e = 0;
     if (!coarse_row) {
       a = i >= 1 ? vr[i - 1] : (T)0;
@@ -391,7 +453,6 @@ __global__ void __launch_bounds__(256)
     b = (i >= 1 && i - 1 < (int64_t)ncoef) ? vr[ncf + i - 1] : (T)0;
     d = i < (int64_t)ncoef ? vr[ncf + i] : (T)0;
     R[row * ncf + (uint64_t)i] = mass_apply(mk, a, b, c, d, e);
-    row_next(r, g);
   }
 }
 
@@ -430,168 +491,350 @@ __global__ void __launch_bounds__(256)
 // tridiag_forward2 / tridiag_backward2 (IPKFunctor.h:13-50):
 //   forward : x[i] = x[i] - x[i-1] * (am[i] / bm[i])        (abr = am/bm table)
 //   backward: x[i] = (x[i] - am[i+1] * x[i+1]) / bm[i+1]
-// ACC != 0: the backward sweep does not store x but adds (ACC > 0) or subtracts
-// (ACC < 0) it into acc at the same compact index -- the reference's separate
-// Lwpk ADD / SUBTRACT pass (LevelwiseProcessingKernel.hpp:21-127).
+// ACC != 0: the backward sweep does not store x but adds (sign > 0) or
+// subtracts (sign < 0) it into acc at the same compact index -- the reference's
+// separate Lwpk ADD / SUBTRACT pass (LevelwiseProcessingKernel.hpp:21-127).
 //
+// The recurrences are sequential per line, and bit-exactness rules out cyclic
+// reduction, so a 2-D 8193^2 level has only ~4k independent chains: the kernels
+// are bound by the latency of one chain step.  Two things keep that step short:
+//   * data moves through a per-thread cp.async ring (dozens of rows in flight
+//     per thread, none of it on the dependent chain);
+//   * the division is replaced by an exactly rounded equivalent that uses the
+//     precomputed reciprocal y = RN(1/b):
+//       fp64: q0 = a*y; two residual corrections q <- fma(fma(-b,q,a), y, q).
+//             After the first q is faithful, and then the second is the
+//             correctly rounded a/b (Markstein's theorem; y correctly rounded,
+//             b's significand not all ones -- checked at plan time; operands
+//             outside 1e-270..1e270 take the true division);
+//       fp32: RN32((double)a * RN64(1/b)): the product is within 2^-52 of a/b
+//             and no quotient of two 24-bit significands lies within 2^-49 of a
+//             25-bit midpoint, so the rounding equals that of the true quotient.
+//     172 -> ~75 cycles per fp64 step on B200.
+// fast quotient (valid when range_bad() is 0 for the dividend) ...
+__device__ __forceinline__ double div_fast(double a, double b, double y) {
+  double q = __dmul_rn(a, y);
+  q = __fma_rn(__fma_rn(-b, q, a), y, q);
+  return __fma_rn(__fma_rn(-b, q, a), y, q);
+}
+__device__ __forceinline__ float div_fast(float a, float, double y) {
+  return __double2float_rn(__dmul_rn((double)a, y));
+}
+// ... and its validity test, integer only so that it stays off the dependent
+// fp64 chain: exponent outside [2^-897, 2^897] and not an exact zero
+__device__ __forceinline__ unsigned range_bad(double a) {
+  const unsigned hi = (unsigned)__double2hiint(a), lo = (unsigned)__double2loint(a);
+  const unsigned e = (hi >> 20) & 0x7ffu;
+  return ((e - 126u) > 1794u) && (((hi & 0x7fffffffu) | lo) != 0u);
+}
+__device__ __forceinline__ unsigned range_bad(float) { return 0u; }
+
+// NB steps of the backward recurrence x[i] = (c - am*x[i+1]) / bm, last step
+// first in c[]; results in res[].  The fast quotients are verified per batch
+// (off the chain) and the batch is redone with true divisions if need be.
+template <typename T, int NB>
+__device__ __forceinline__ T backward_batch(const T (&c)[NB], const T (&a1)[NB],
+                                            const T (&b1)[NB],
+                                            const double (&y1)[NB], int cnt,
+                                            T prev, bool fast, T (&res)[NB]) {
+  const T prev0 = prev;
+  unsigned bad = fast ? 0u : 1u;
+#pragma unroll
+  for (int k = 0; k < NB; k++)
+    if (k < cnt) {
+      T t = sub_rn(c[k], mul_rn(a1[k], prev));
+      bad |= range_bad(t);
+      prev = div_fast(t, b1[k], y1[k]);
+      res[k] = prev;
+    }
+  if (bad) {
+    prev = prev0;
+#pragma unroll
+    for (int k = 0; k < NB; k++)
+      if (k < cnt) {
+        prev = div_rn(sub_rn(c[k], mul_rn(a1[k], prev)), b1[k]);
+        res[k] = prev;
+      }
+  }
+  return prev;
+}
+
+template <int BYTES>
+__device__ __forceinline__ void cp_async(void *smem, const void *gmem) {
+  unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], %2;\n" ::"r"(sa), "l"(gmem),
+               "n"(BYTES)
+               : "memory");
+}
+__device__ __forceinline__ void cp_commit() {
+  asm volatile("cp.async.commit_group;\n" ::: "memory");
+}
+template <int N> __device__ __forceinline__ void cp_wait() {
+  asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory");
+}
+
 // Strided variant (solve dimension not contiguous): a thread owns one line,
-// consecutive threads consecutive `inner` indices; loads are issued a batch
-// ahead of the dependent chain.
-template <typename T, int B>
+// consecutive threads consecutive `inner` indices.  Ring: S stages of B rows.
+constexpr int IPK_B = 8;
+
+template <typename T, bool ACC, int IPK_S>
 __global__ void __launch_bounds__(128)
     k_ipk_strided(T *__restrict__ x, const T *__restrict__ am,
-                  const T *__restrict__ bm, const T *__restrict__ abr, uint32_t n,
-                  uint64_t inner, uint64_t lines, T *__restrict__ acc, int sign) {
-  const uint64_t ln = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
-  if (ln >= lines)
-    return;
+                  const T *__restrict__ bm, const T *__restrict__ abr,
+                  const double *__restrict__ rbm, uint32_t n, uint64_t inner,
+                  uint64_t lines, T *__restrict__ acc, int sign, int fast) {
+  extern __shared__ __align__(16) unsigned char ipk_smem[];
+  const uint32_t tpb = blockDim.x, tid = threadIdx.x;
+  const uint32_t lane = tid & 31, warp = tid >> 5, nwarp = tpb >> 5;
+  uint64_t ln = blockIdx.x * (uint64_t)blockDim.x + tid;
+  // lanes past the last line shadow it (no stores) so that warps stay whole
+  const bool active = ln < lines;
+  if (!active)
+    ln = lines - 1;
+  // ring of S stages: B rows of x (and of acc), plus the table entries of
+  // those B rows per warp -- a table entry is used once per SM, so without
+  // the ring every batch would wait on an L1-missing table load
+  double *ty = reinterpret_cast<double *>(ipk_smem) + (size_t)warp * IPK_S * IPK_B;
+  T *tt = reinterpret_cast<T *>(reinterpret_cast<double *>(ipk_smem) +
+                                (size_t)nwarp * IPK_S * IPK_B) +
+          (size_t)warp * IPK_S * 2 * IPK_B;
+  T *rx = reinterpret_cast<T *>(reinterpret_cast<double *>(ipk_smem) +
+                                (size_t)nwarp * IPK_S * IPK_B) +
+          (size_t)nwarp * IPK_S * 2 * IPK_B;
+  T *ra = rx + (size_t)IPK_S * IPK_B * tpb;
   const uint64_t o = ln / inner, in = ln % inner;
   T *p = x + o * n * inner + in;
-  T *pa = acc ? acc + o * n * inner + in : nullptr;
-  T cur[B], nxt[B];
-  T prev = 0;
+  T *pa = ACC ? acc + o * n * inner + in : nullptr;
+  const uint32_t nb = (n + IPK_B - 1) / IPK_B;
+  // ---- forward ----
+  auto issue_f = [&](uint32_t j) {
+    if (j < nb) {
+      const uint32_t slot = j % IPK_S;
 #pragma unroll
-  for (int k = 0; k < B; k++)
-    cur[k] = (uint32_t)k < n ? p[(uint64_t)k * inner] : (T)0;
-  for (uint32_t i0 = 0; i0 < n; i0 += B) {
-#pragma unroll
-    for (int k = 0; k < B; k++) {
-      uint32_t i = i0 + B + k;
-      nxt[k] = i < n ? p[(uint64_t)i * inner] : (T)0;
-    }
-#pragma unroll
-    for (int k = 0; k < B; k++) {
-      uint32_t i = i0 + k;
-      if (i < n) {
-        prev = sub_rn(cur[k], mul_rn(prev, abr[i]));
-        p[(uint64_t)i * inner] = prev;
+      for (int k = 0; k < IPK_B; k++) {
+        uint32_t i = j * IPK_B + k;
+        if (i < n)
+          cp_async<sizeof(T)>(&rx[(slot * IPK_B + k) * tpb + tid],
+                              p + (uint64_t)i * inner);
       }
+      if (lane < IPK_B && j * IPK_B + lane < n)
+        cp_async<sizeof(T)>(&tt[slot * 2 * IPK_B + lane], abr + j * IPK_B + lane);
+    }
+    cp_commit();
+  };
+  for (uint32_t j = 0; j < IPK_S - 1; j++)
+    issue_f(j);
+  T prev = 0;
+  for (uint32_t j = 0; j < nb; j++) {
+    __syncwarp(); // everyone is done with the slot about to be refilled
+    issue_f(j + IPK_S - 1);
+    cp_wait<IPK_S - 1>();
+    __syncwarp();
+    const uint32_t slot = j % IPK_S;
+    T c[IPK_B], f[IPK_B];
+#pragma unroll
+    for (int k = 0; k < IPK_B; k++) {
+      c[k] = rx[(slot * IPK_B + k) * tpb + tid];
+      f[k] = tt[slot * 2 * IPK_B + k];
     }
 #pragma unroll
-    for (int k = 0; k < B; k++)
-      cur[k] = nxt[k];
-  }
-  // backward, from the last element; batch j covers i = n-1-j*B-k
-  prev = 0;
-  T ca[B], na[B];
-#pragma unroll
-  for (int k = 0; k < B; k++) {
-    bool ok = (uint32_t)k < n;
-    uint64_t off = (uint64_t)(n - 1 - (ok ? k : 0)) * inner;
-    cur[k] = ok ? p[off] : (T)0;
-    ca[k] = (ok && pa) ? pa[off] : (T)0;
-  }
-  for (uint32_t j0 = 0; j0 < n; j0 += B) {
-#pragma unroll
-    for (int k = 0; k < B; k++) {
-      uint32_t j = j0 + B + k;
-      bool ok = j < n;
-      uint64_t off = (uint64_t)(n - 1 - (ok ? j : 0)) * inner;
-      nxt[k] = ok ? p[off] : (T)0;
-      na[k] = (ok && pa) ? pa[off] : (T)0;
-    }
-#pragma unroll
-    for (int k = 0; k < B; k++) {
-      uint32_t j = j0 + k;
-      if (j < n) {
-        uint32_t i = n - 1 - j;
-        prev = div_rn(sub_rn(cur[k], mul_rn(am[i + 1], prev)), bm[i + 1]);
-        if (pa)
-          pa[(uint64_t)i * inner] =
-              sign > 0 ? add_rn(ca[k], prev) : sub_rn(ca[k], prev);
-        else
+    for (int k = 0; k < IPK_B; k++) {
+      uint32_t i = j * IPK_B + k;
+      if (i < n) {
+        prev = sub_rn(c[k], mul_rn(prev, f[k]));
+        if (active)
           p[(uint64_t)i * inner] = prev;
       }
     }
+  }
+  cp_wait<0>();
+  __threadfence_block(); // the backward sweep re-reads what was just stored
+  __syncwarp();
+  // ---- backward: batch j covers i = n-1-(j*B+k) ----
+  auto issue_b = [&](uint32_t j) {
+    if (j < nb) {
+      const uint32_t slot = j % IPK_S;
 #pragma unroll
-    for (int k = 0; k < B; k++) {
-      cur[k] = nxt[k];
-      ca[k] = na[k];
+      for (int k = 0; k < IPK_B; k++) {
+        uint32_t jj = j * IPK_B + k;
+        if (jj < n) {
+          uint64_t off = (uint64_t)(n - 1 - jj) * inner;
+          cp_async<sizeof(T)>(&rx[(slot * IPK_B + k) * tpb + tid], p + off);
+          if (ACC)
+            cp_async<sizeof(T)>(&ra[(slot * IPK_B + k) * tpb + tid], pa + off);
+        }
+      }
+      const uint32_t jj = j * IPK_B + lane;
+      if (lane < IPK_B && jj < n) {
+        const uint32_t i1 = n - jj; // i + 1
+        cp_async<sizeof(T)>(&tt[slot * 2 * IPK_B + lane], am + i1);
+        cp_async<sizeof(T)>(&tt[slot * 2 * IPK_B + IPK_B + lane], bm + i1);
+        cp_async<8>(&ty[slot * IPK_B + lane], rbm + i1);
+      }
+    }
+    cp_commit();
+  };
+  for (uint32_t j = 0; j < IPK_S - 1; j++)
+    issue_b(j);
+  prev = 0;
+  for (uint32_t j = 0; j < nb; j++) {
+    __syncwarp();
+    issue_b(j + IPK_S - 1);
+    cp_wait<IPK_S - 1>();
+    __syncwarp();
+    const uint32_t slot = j % IPK_S;
+    T c[IPK_B], a1[IPK_B], b1[IPK_B], av[IPK_B], res[IPK_B];
+    double y1[IPK_B];
+    const int cnt = (int)min((uint32_t)IPK_B, n - j * IPK_B);
+#pragma unroll
+    for (int k = 0; k < IPK_B; k++) {
+      c[k] = rx[(slot * IPK_B + k) * tpb + tid];
+      av[k] = ACC ? ra[(slot * IPK_B + k) * tpb + tid] : (T)0;
+      a1[k] = tt[slot * 2 * IPK_B + k];
+      b1[k] = tt[slot * 2 * IPK_B + IPK_B + k];
+      y1[k] = ty[slot * IPK_B + k];
+    }
+    prev = backward_batch<T, IPK_B>(c, a1, b1, y1, cnt, prev, fast != 0, res);
+    if (active) {
+#pragma unroll
+      for (int k = 0; k < IPK_B; k++)
+        if (k < cnt) {
+          uint32_t i = n - 1 - (j * IPK_B + k);
+          if (ACC)
+            pa[(uint64_t)i * inner] =
+                sign > 0 ? add_rn(av[k], res[k]) : sub_rn(av[k], res[k]);
+          else
+            p[(uint64_t)i * inner] = res[k];
+        }
     }
   }
+  cp_wait<0>();
 }
 
-// Contiguous variant: one warp owns 32 lines; 32x32 tiles are moved with
-// coalesced row accesses and transposed through shared memory so that lane r
-// walks line r.  The next tile is loaded into registers while the current one
-// is being eliminated.
+// Contiguous variant: one warp owns 32 lines; 32x32 tiles are fetched row-wise
+// (coalesced) by cp.async into a ring of shared-memory tiles and walked
+// transposed, lane r on line r; results go back row-wise.
+constexpr int IPC_S = 4;
+
 template <typename T>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(32)
     k_ipk_contig(T *__restrict__ x, const T *__restrict__ am,
-                 const T *__restrict__ bm, const T *__restrict__ abr, uint32_t n,
-                 uint64_t lines, T *__restrict__ acc, int sign) {
-  __shared__ T tile[4][32][33];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  T(*t)[33] = tile[warp];
-  const uint64_t l0 = (blockIdx.x * 4ull + warp) * 32;
+                 const T *__restrict__ bm, const T *__restrict__ abr,
+                 const double *__restrict__ rbm, uint32_t n, uint64_t lines,
+                 T *__restrict__ acc, int sign, int fast) {
+  __shared__ T tile[IPC_S][32][33];
+  __shared__ T tabs[IPC_S][2][32];  // abr | am, bm of the tile's 32 columns
+  __shared__ double taby[IPC_S][32]; // 1 / bm
+  const int lane = threadIdx.x;
+  const uint64_t l0 = (uint64_t)blockIdx.x * 32;
   if (l0 >= lines)
     return;
   const uint32_t nl = (uint32_t)min((uint64_t)32, lines - l0);
   const uint32_t nch = (n + 31) / 32;
   T *xb = x + l0 * n;
   T *ab = acc ? acc + l0 * n : nullptr;
-  T reg[32];
-  auto load_tile = [&](uint32_t c0) {
-#pragma unroll
-    for (uint32_t r = 0; r < 32; r++)
-      reg[r] = (r < nl && c0 + lane < n) ? xb[(uint64_t)r * n + c0 + lane] : (T)0;
+  auto issue = [&](uint32_t ch, bool backward) {
+    if (ch < nch) {
+      const uint32_t c0 = (backward ? nch - 1 - ch : ch) * 32;
+      const uint32_t slot = ch % IPC_S;
+      T(*t)[33] = tile[slot];
+      if (c0 + lane < n) {
+        for (uint32_t r = 0; r < nl; r++)
+          cp_async<sizeof(T)>(&t[r][lane], xb + (uint64_t)r * n + c0 + lane);
+        if (!backward) {
+          cp_async<sizeof(T)>(&tabs[slot][0][lane], abr + c0 + lane);
+        } else {
+          cp_async<sizeof(T)>(&tabs[slot][0][lane], am + c0 + lane + 1);
+          cp_async<sizeof(T)>(&tabs[slot][1][lane], bm + c0 + lane + 1);
+          cp_async<8>(&taby[slot][lane], rbm + c0 + lane + 1);
+        }
+      }
+    }
+    cp_commit();
   };
-  // forward
+  // ---- forward ----
+  for (uint32_t ch = 0; ch < IPC_S - 1; ch++)
+    issue(ch, false);
   T prev = 0;
-  load_tile(0);
   for (uint32_t ch = 0; ch < nch; ch++) {
+    issue(ch + IPC_S - 1, false);
+    cp_wait<IPC_S - 1>();
+    __syncwarp();
     const uint32_t c0 = ch * 32;
     const uint32_t ncol = min(32u, n - c0);
-#pragma unroll
-    for (uint32_t r = 0; r < 32; r++)
-      t[r][lane] = reg[r];
-    __syncwarp();
-    if (ch + 1 < nch)
-      load_tile(c0 + 32);
-    if ((uint32_t)lane < nl)
-      for (uint32_t j = 0; j < ncol; j++) {
-        prev = sub_rn(t[lane][j], mul_rn(prev, abr[c0 + j]));
-        t[lane][j] = prev;
+    T(*t)[33] = tile[ch % IPC_S];
+    const T *fa = tabs[ch % IPC_S][0];
+    if ((uint32_t)lane < nl) {
+      if (ncol == 32) {
+#pragma unroll 8
+        for (uint32_t j = 0; j < 32; j++) {
+          prev = sub_rn(t[lane][j], mul_rn(prev, fa[j]));
+          t[lane][j] = prev;
+        }
+      } else {
+        for (uint32_t j = 0; j < ncol; j++) {
+          prev = sub_rn(t[lane][j], mul_rn(prev, fa[j]));
+          t[lane][j] = prev;
+        }
       }
+    }
     __syncwarp();
-    for (uint32_t r = 0; r < nl; r++)
-      if ((uint32_t)lane < ncol)
+    if ((uint32_t)lane < ncol)
+      for (uint32_t r = 0; r < nl; r++)
         xb[(uint64_t)r * n + c0 + lane] = t[r][lane];
     __syncwarp();
   }
-  // backward
+  cp_wait<0>();
+  __threadfence_block();
+  __syncwarp();
+  // ---- backward ----
+  for (uint32_t ch = 0; ch < IPC_S - 1; ch++)
+    issue(ch, true);
   prev = 0;
-  load_tile((nch - 1) * 32);
-  for (uint32_t cc = 0; cc < nch; cc++) {
-    const uint32_t c0 = (nch - 1 - cc) * 32;
+  for (uint32_t ch = 0; ch < nch; ch++) {
+    issue(ch + IPC_S - 1, true);
+    cp_wait<IPC_S - 1>();
+    __syncwarp();
+    const uint32_t c0 = (nch - 1 - ch) * 32;
     const uint32_t ncol = min(32u, n - c0);
+    const uint32_t slot = ch % IPC_S;
+    T(*t)[33] = tile[slot];
+    if ((uint32_t)lane < nl) {
+      for (uint32_t j0 = 0; j0 < ncol; j0 += 8) {
+        // sub-batch covers columns ncol-1-j0 ... down, 8 at a time
+        T c[8], a1[8], b1[8], res[8];
+        double y1[8];
+        const int cnt = (int)min(8u, ncol - j0);
 #pragma unroll
-    for (uint32_t r = 0; r < 32; r++)
-      t[r][lane] = reg[r];
-    __syncwarp();
-    if (cc + 1 < nch)
-      load_tile(c0 - 32);
-    if ((uint32_t)lane < nl)
-      for (uint32_t jj = 0; jj < ncol; jj++) {
-        uint32_t j = ncol - 1 - jj;
-        uint32_t i = c0 + j;
-        prev = div_rn(sub_rn(t[lane][j], mul_rn(am[i + 1], prev)), bm[i + 1]);
-        t[lane][j] = prev;
+        for (int k = 0; k < 8; k++) {
+          uint32_t j = k < cnt ? ncol - 1 - j0 - k : 0;
+          c[k] = t[lane][j];
+          a1[k] = tabs[slot][0][j];
+          b1[k] = tabs[slot][1][j];
+          y1[k] = taby[slot][j];
+        }
+        prev = backward_batch<T, 8>(c, a1, b1, y1, cnt, prev, fast != 0, res);
+#pragma unroll
+        for (int k = 0; k < 8; k++)
+          if (k < cnt)
+            t[lane][ncol - 1 - j0 - k] = res[k];
       }
+    }
     __syncwarp();
-    if (ab) {
-      for (uint32_t r = 0; r < nl; r++)
-        if ((uint32_t)lane < ncol) {
+    if ((uint32_t)lane < ncol) {
+      if (ab) {
+        for (uint32_t r = 0; r < nl; r++) {
           uint64_t off = (uint64_t)r * n + c0 + lane;
           ab[off] = sign > 0 ? add_rn(ab[off], t[r][lane]) : sub_rn(ab[off], t[r][lane]);
         }
-    } else {
-      for (uint32_t r = 0; r < nl; r++)
-        if ((uint32_t)lane < ncol)
+      } else {
+        for (uint32_t r = 0; r < nl; r++)
           xb[(uint64_t)r * n + c0 + lane] = t[r][lane];
+      }
     }
     __syncwarp();
   }
+  cp_wait<0>();
 }
 
 // ---- inverse level kernel ------------------------------------------------------------
@@ -614,7 +857,7 @@ __device__ __forceinline__ void restore_row(const T *__restrict__ v,
       drow[2 * i + 1] = add_rn(vr[ncf + i], mgx_lerp(a0, arow[i + 1], tf));
   } else {
     T a, b;
-    corners<T, K>(A, (int64_t)r.ao, r, i, i + 1, has_odd, tf, a, b);
+    corners<T, K, false>(A, (int64_t)r.ao, r, i, i + 1, has_odd, tf, a, b);
     drow[qe] = add_rn(vr[i], a);
     if (has_odd)
       drow[2 * i + 1] = add_rn(vr[ncf + i], b);
@@ -627,21 +870,37 @@ __global__ void __launch_bounds__(256)
                          T *__restrict__ dst, const T *__restrict__ tables,
                          const __grid_constant__ LvGeom g) {
   const uint32_t ncf = g.nc[FD], nff = g.nf[FD], ncoef = nff - ncf;
-  const uint64_t ii = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  const uint64_t task = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (task >= g.tasks)
+    return;
+  const uint32_t cw = (uint32_t)(task % g.col_chunks);
+  const uint64_t rg = task / g.col_chunks;
+  const uint64_t ii = (uint64_t)cw * 32 + lane;
   if (ii >= ncf)
     return;
   const uint32_t i = (uint32_t)ii;
   const bool has_odd = i < ncoef;
   const uint32_t qe = (i == ncf - 1) ? nff - 1 : 2 * i;
   const T tf = (g.half || !has_odd) ? (T)0.5 : tables[g.roff[FD] + 2 * i];
-  const uint64_t row0 = (uint64_t)blockIdx.y * g.rows_per_block;
-  const uint64_t row1 = min(g.rows, row0 + g.rows_per_block);
-  if (row0 >= row1)
-    return;
+  const uint64_t row0 = rg * g.rows_per_task;
+  const uint64_t row1 = min(g.rows, row0 + g.rows_per_task);
+  uint32_t p[OUTER];
+  row_first(p, g, row0);
   Row<T> r;
-  row_first(r, g, row0);
+  row_setup<T, false>(r, p, g, tables);
   for (uint64_t row = row0; row < row1; row++) {
-    row_setup<T, false>(r, g, tables);
+    const bool more = row + 1 < row1;
+    if (more) {
+      row_next(p, g);
+      Row<T> nx;
+      row_setup<T, false>(nx, p, g, tables);
+      prefetch_l1(v + nx.vo + i);
+      if (has_odd)
+        prefetch_l1(v + nx.vo + ncf + i);
+      prefetch_l1(A + nx.ao + i);
+      prefetch_row<T, false>(A, (int64_t)nx.ao + i, nx);
+    }
     switch (r.nodd) {
     case 0:
       restore_row<T, 0>(v, A, dst, r, g, i, has_odd, qe, tf);
@@ -659,7 +918,8 @@ __global__ void __launch_bounds__(256)
       restore_row<T, 4>(v, A, dst, r, g, i, has_odd, qe, tf);
       break;
     }
-    row_next(r, g);
+    if (more)
+      row_setup<T, false>(r, p, g, tables);
   }
 }
 
@@ -720,9 +980,9 @@ void compact_strides(const uint64_t *n, uint64_t *st) {
 
 // geometry of level l; `node_full`: the interleaved level-l node array is the
 // full array (l == L), else the compact level-l box
+// `cols_per_chunk`: columns (pairs) one warp covers per row
 template <typename T>
-LvGeom level_geom(const mgx_ctx *ctx, int l, unsigned target_blocks,
-                  unsigned col_blocks) {
+LvGeom level_geom(const mgx_ctx *ctx, int l, uint32_t cols_per_chunk) {
   const MgxLevels &lv = ctx->lv;
   const MgxTableOffsets &off = host_tables<T>(ctx).off;
   LvGeom g;
@@ -742,16 +1002,20 @@ LvGeom level_geom(const mgx_ctx *ctx, int l, unsigned target_blocks,
   }
   g.dist_f = off.dist[l][FD];
   g.half = host_tables<T>(ctx).ratios_half ? 1 : 0;
-  // rows per block: enough blocks to fill the machine, contiguous row ranges
-  uint64_t want_y = std::max<uint64_t>(1, target_blocks / std::max(1u, col_blocks));
-  want_y = std::min<uint64_t>(want_y, 65535);
-  uint64_t rpb = (g.rows + want_y - 1) / want_y;
-  g.rows_per_block = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(rpb, 1u << 30));
+  // warp tasks: enough of them to fill the machine a few times over, each a
+  // contiguous run of rows (neighbour rows are then shared through L1)
+  g.col_chunks = (g.nc[FD] + cols_per_chunk - 1) / cols_per_chunk;
+  const uint64_t want_tasks = (uint64_t)ctx->num_sms * 64 * 3;
+  uint64_t groups = std::max<uint64_t>(1, want_tasks / g.col_chunks);
+  uint64_t rpt = (g.rows + groups - 1) / groups;
+  rpt = std::max<uint64_t>(rpt, std::min<uint64_t>(g.rows, 4));
+  g.rows_per_task = (uint32_t)std::min<uint64_t>(rpt, 1u << 30);
+  g.tasks = (uint64_t)g.col_chunks * ((g.rows + g.rows_per_task - 1) / g.rows_per_task);
   return g;
 }
 
-unsigned grid_y(const LvGeom &g) {
-  return (unsigned)((g.rows + g.rows_per_block - 1) / g.rows_per_block);
+unsigned task_grid(const LvGeom &g, unsigned warps_per_block) {
+  return (unsigned)((g.tasks + warps_per_block - 1) / warps_per_block);
 }
 
 struct Scratch {
@@ -825,16 +1089,45 @@ int correction_tail(mgx_ctx *ctx, int l, T *R0, T *R1, T *A, int sign) {
       outer *= lv.n[l - 1][e];
     const T *am = tables + off.am[l - 1][d], *bm = tables + off.bm[l - 1][d],
             *abr = tables + off.abr[l - 1][d];
+    const double *rbm = ctx->d_rcp + off.bm[l - 1][d];
     const uint64_t lines = outer * inner;
+    const int fast = ctx->fast_div ? 1 : 0;
     T *acc = (d == pad) ? A : nullptr;
     if (inner == 1) {
-      uint64_t groups = (lines + 127) / 128;
-      k_ipk_contig<T><<<(unsigned)groups, 128, 0, ctx->stream>>>(
-          corr, am, bm, abr, n, lines, acc, sign);
+      k_ipk_contig<T><<<(unsigned)((lines + 31) / 32), 32, 0, ctx->stream>>>(
+          corr, am, bm, abr, rbm, n, lines, acc, sign, fast);
     } else {
-      constexpr int B = sizeof(T) == 4 ? 16 : 8;
-      k_ipk_strided<T, B><<<(unsigned)((lines + 127) / 128), 128, 0, ctx->stream>>>(
-          corr, am, bm, abr, n, inner, lines, acc, sign);
+      // few lines: small blocks, so that every SM gets a chain to work on
+      unsigned tpb = 128;
+      while (tpb > 32 && lines / tpb < (uint64_t)ctx->num_sms * 2)
+        tpb >>= 1;
+      const unsigned grid = (unsigned)((lines + tpb - 1) / tpb);
+      // deep ring when chains are scarce (latency bound), shallow otherwise
+      const bool deep = lines < (uint64_t)ctx->num_sms * 512;
+      const size_t stages = deep ? 8 : 2;
+      const size_t smem = stages * IPK_B * tpb * sizeof(T) * (acc ? 2 : 1) +
+                          (size_t)(tpb / 32) * stages * IPK_B * (8 + 2 * sizeof(T));
+#define MGX_IPK_LAUNCH(ACCF, S)                                                  \
+  do {                                                                           \
+    static bool attr_set = false;                                                \
+    if (!attr_set) {                                                             \
+      MGX_CUDA(cudaFuncSetAttribute(k_ipk_strided<T, ACCF, S>,                   \
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                    8 * IPK_B * 128 * 8 * 2 + 4 * 8 * IPK_B * 24));                   \
+      attr_set = true;                                                           \
+    }                                                                            \
+    k_ipk_strided<T, ACCF, S><<<grid, tpb, smem, ctx->stream>>>(                 \
+        corr, am, bm, abr, rbm, n, inner, lines, acc, sign, fast);               \
+  } while (0)
+      if (acc && deep)
+        MGX_IPK_LAUNCH(true, 8);
+      else if (acc)
+        MGX_IPK_LAUNCH(true, 2);
+      else if (deep)
+        MGX_IPK_LAUNCH(false, 8);
+      else
+        MGX_IPK_LAUNCH(false, 2);
+#undef MGX_IPK_LAUNCH
     }
     ctx->launches++;
   }
@@ -877,12 +1170,10 @@ int decompose_rows(mgx_ctx *ctx, const T *src, T *v, const double *q,
   const T *cur = src;
   int which = 0;
   for (int l = lv.L; l >= 1; l--) {
-    const uint32_t ncf = (uint32_t)lv.n[l - 1][FD];
-    unsigned gx = (ncf + FW_WARPS * FW_OWN - 1) / (FW_WARPS * FW_OWN);
-    LvGeom g = level_geom<T>(ctx, l, ctx->num_sms * 6, gx);
+    LvGeom g = level_geom<T>(ctx, l, FW_OWN);
     fill_quant<T>(ctx, &qo, q, vol, l);
     T *A = (T *)s.A[which];
-    k_level_forward<T, QUANT><<<dim3(gx, grid_y(g)), FW_WARPS * 32, smem,
+    k_level_forward<T, QUANT><<<task_grid(g, FW_WARPS), FW_WARPS * 32, smem,
                                 ctx->stream>>>(cur, v, A, (T *)s.R[0], tables, g, qo);
     ctx->launches++;
     rc = correction_tail<T>(ctx, l, (T *)s.R[0], (T *)s.R[1], A, +1);
@@ -949,18 +1240,16 @@ template <typename T> int recompose_rows(mgx_ctx *ctx, const T *v, T *dst) {
       A, const_cast<T *>(v), g0, qo);
   ctx->launches++;
   for (int l = 1; l <= lv.L; l++) {
-    const uint32_t ncf = (uint32_t)lv.n[l - 1][FD];
-    unsigned gx = (ncf + 255) / 256;
-    LvGeom g = level_geom<T>(ctx, l, ctx->num_sms * 6, gx);
-    k_lpk_first<T><<<dim3(gx, grid_y(g)), 256, 0, ctx->stream>>>(
-        v, (T *)s.R[0], tables, g);
+    LvGeom g = level_geom<T>(ctx, l, 32);
+    k_lpk_first<T><<<task_grid(g, 8), 256, 0, ctx->stream>>>(v, (T *)s.R[0], tables,
+                                                            g);
     ctx->launches++;
     rc = correction_tail<T>(ctx, l, (T *)s.R[0], (T *)s.R[1], A, -1);
     if (rc)
       return rc;
     T *out = (l == lv.L) ? dst : (T *)s.A[which ^ 1];
-    k_level_restore_rows<T><<<dim3(gx, grid_y(g)), 256, 0, ctx->stream>>>(
-        v, A, out, tables, g);
+    k_level_restore_rows<T><<<task_grid(g, 8), 256, 0, ctx->stream>>>(v, A, out,
+                                                                     tables, g);
     ctx->launches++;
     A = out;
     which ^= 1;
