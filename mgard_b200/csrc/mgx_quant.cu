@@ -242,6 +242,45 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+// Row-wise variant: one block per run of rows of the contiguous dimension; the
+// level of the outer coordinates is found once per row, the level of the
+// column by descending the level shapes (half the columns stop at the first
+// test), so there is no per-element division.
+template <typename T>
+__global__ void __launch_bounds__(256)
+    k_dequantize_sym_rows(const uint16_t *__restrict__ sym, T *__restrict__ c,
+                          const __grid_constant__ QuantArgs<T> a, uint64_t rows) {
+  const uint32_t nf = a.shape[MGX_MAX_D - 1];
+  for (uint64_t row = blockIdx.x; row < rows; row += gridDim.x) {
+    int row_level = 0;
+    if (a.calc_vol) {
+      uint64_t r = row;
+#pragma unroll
+      for (int d = MGX_MAX_D - 2; d >= 0; d--) {
+        uint32_t p = (uint32_t)(r % a.shape[d]);
+        r /= a.shape[d];
+        int m = 0;
+        while (m < a.L && p >= a.n[m][d])
+          m++;
+        row_level = max(row_level, m);
+      }
+    }
+    const uint16_t *srow = sym + row * nf;
+    T *crow = c + row * nf;
+    for (uint32_t x = threadIdx.x; x < nf; x += blockDim.x) {
+      int level = 0;
+      if (a.calc_vol) {
+        int m = a.L;
+        while (m > 0 && x < a.n[m - 1][MGX_MAX_D - 1])
+          m--;
+        level = max(row_level, m);
+      }
+      long long q = (long long)srow[x] - a.shift;
+      crow[x] = mul_rn(mul_rn(a.q[level], a.vol[level]), (T)q);
+    }
+  }
+}
+
 // outliers carry the true code: overwrite the dequantised value
 template <typename T>
 __global__ void __launch_bounds__(256)
@@ -372,8 +411,16 @@ static int dequantize_sym_t(mgx_ctx *ctx, int rel, double tol, double s,
                             uint64_t n_out) {
   QuantArgs<T> a;
   fill_quant_args<T>(ctx, &a, rel, tol, s, norm, false);
-  k_dequantize_sym<T><<<mgx_grid_for(a.total, 256, ctx->num_sms * 16), 256, 0,
-                        ctx->stream>>>(ctx->d_sym, (T *)d_coeff, a);
+  const uint64_t nf = ctx->lv.shape[MGX_MAX_D - 1];
+  if (nf >= 128) {
+    const uint64_t rows = a.total / nf;
+    k_dequantize_sym_rows<T><<<(unsigned)std::min<uint64_t>(rows, ctx->num_sms * 16),
+                               256, 0, ctx->stream>>>(ctx->d_sym, (T *)d_coeff, a,
+                                                      rows);
+  } else {
+    k_dequantize_sym<T><<<mgx_grid_for(a.total, 256, ctx->num_sms * 16), 256, 0,
+                          ctx->stream>>>(ctx->d_sym, (T *)d_coeff, a);
+  }
   ctx->launches++;
   if (n_out) {
     k_dequantize_outliers<T><<<mgx_grid_for(n_out, 256, ctx->num_sms * 4), 256,

@@ -218,3 +218,77 @@ def test_fused_hierarchical_forward(shape, dtype, rel, tol):
     bad = np.argwhere(got != want)
     assert len(bad) == 0, "%d codes differ, first %s: got %s want %s" % (
         len(bad), bad[:5].tolist(), got[tuple(bad[0])], want[tuple(bad[0])])
+
+
+# ---- row-streaming level kernels (mgx_level.cu): orthogonal-projection path ----
+ORTH_SHAPES = [((1025,), np.float64), ((300, 77), np.float64), ((257, 513), np.float32),
+               ((66, 33, 130), np.float64), ((31, 64, 65), np.float32),
+               ((6, 7, 9, 70), np.float32), ((5, 6, 7, 8, 40), np.float64)]
+
+
+@pytest.mark.parametrize("shape,dtype", ORTH_SHAPES)
+def test_level_kernels_vs_oracle_and_gather_kernels(shape, dtype, monkeypatch):
+    """decompose / recompose with the correction: the row-streaming kernels
+    against the oracle AND against the superseded gather kernels
+    (MGX_LEGACY_LEVELS=1), bit for bit; even sizes, ragged rows, 1-5 D."""
+    rng = np.random.default_rng(7)
+    u = (smooth_field(shape, dtype) + 0.01 * rng.standard_normal(shape)).astype(dtype)
+    comp, tdt = make(shape, dtype)
+    d = torch.from_numpy(u).cuda()
+    comp.Decompose(d, 1)
+    got = d.cpu().numpy()
+    want = Oracle("port").decompose(u, 1)
+    assert np.array_equal(got, want)
+    monkeypatch.setenv("MGX_LEGACY_LEVELS", "1")
+    old, _ = make(shape, dtype)
+    monkeypatch.delenv("MGX_LEGACY_LEVELS")
+    d2 = torch.from_numpy(u).cuda()
+    old.Decompose(d2, 1)
+    assert np.array_equal(d2.cpu().numpy(), got)
+    comp.Recompose(d, 1)
+    old.Recompose(d2, 1)
+    assert np.array_equal(d.cpu().numpy(), d2.cpu().numpy())
+    assert np.array_equal(d.cpu().numpy(), Oracle("port").recompose(want, 1))
+
+
+@pytest.mark.parametrize("scale", [1e-300, 1e-280, 1e280, 0.0])
+def test_thomas_fast_division_falls_back_outside_its_range(scale):
+    """The Thomas solves divide through a precomputed reciprocal with two
+    exact-residual corrections; dividends outside 2^-897..2^897 (and the
+    batches they sit in) must take the true division.  Mixed magnitudes and
+    exact zeros against the oracle, bit for bit."""
+    shape, dtype = (129, 65), np.float64
+    u = smooth_field(shape, dtype)
+    u[::3, :] *= scale if scale else 0.0
+    u[5:40, 7:20] = 0.0
+    comp, tdt = make(shape, dtype)
+    d = torch.from_numpy(u).cuda()
+    comp.Decompose(d, 1)
+    want = Oracle("port").decompose(u, 1)
+    assert np.array_equal(d.cpu().numpy(), want)
+    comp.Recompose(d, 1)
+    assert np.array_equal(d.cpu().numpy(), Oracle("port").recompose(want, 1))
+
+
+ORTH_E2E = [((300, 77), np.float64, 0.0, 1, 1e-4), ((257, 513), np.float32, 1.0, 1, 1e-3),
+            ((66, 33, 130), np.float32, 0.0, 0, 1e-3), ((6, 7, 9, 70), np.float64, INF, 1, 1e-3),
+            ((5, 6, 7, 8, 40), np.float32, 0.5, 1, 1e-2), ((1025,), np.float64, 0.0, 1, 1e-5)]
+
+
+@pytest.mark.parametrize("shape,dtype,s,rel,tol", ORTH_E2E)
+def test_fused_level_quantize_containers(shape, dtype, s, rel, tol):
+    """mgx_compress on the orthogonal path quantises inside the level kernel
+    (no coefficient array exists): containers must still be byte-identical to
+    the oracle's, and decode to the oracle's reconstruction."""
+    u = smooth_field(shape, dtype)
+    o = Oracle("port")
+    want, norm = o.compress(u, rel, tol, s)
+    comp, tdt = make(shape, dtype)
+    eb = mg.REL if rel else mg.ABS
+    blob, _ = comp.Compress(torch.from_numpy(u).cuda(), eb, tol, s,
+                            norm=norm if rel else 0.0)
+    got = blob.cpu().numpy()
+    assert got.size == want.size
+    assert np.array_equal(np.delete(got, 7), np.delete(want, 7))
+    dec = comp.Decompress(blob, eb, tol, s, norm).cpu().numpy()
+    assert np.array_equal(dec, o.decompress(want, shape, dtype, rel, tol, s, norm))
