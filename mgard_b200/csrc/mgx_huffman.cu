@@ -403,6 +403,56 @@ pack_runs(uint32_t *dst, const uint4 (&v)[R], const int (&cnt)[R],
   }
 }
 
+// A run whose codes total at most 64 bits (and none longer than 26) is already
+// merged into one MSB-first blob by the length pass; placing it takes at most
+// three unit-wide ORs and no per-symbol work.
+__device__ __forceinline__ void place64(uint32_t *dst, u64 blob, uint32_t bits,
+                                        uint32_t start) {
+  if (!bits)
+    return;
+  const u64 A = blob << (64 - bits);
+  const uint32_t unit = start >> 5, fill = start & 31;
+  const uint32_t u0 = (uint32_t)(A >> (32 + fill));
+  const uint32_t u1 = (uint32_t)(A >> fill);
+  const uint32_t u2 = fill ? (uint32_t)(A << (32 - fill)) : 0u;
+  if (u0)
+    atomicOr(&dst[unit ^ 1], u0);
+  if (u1)
+    atomicOr(&dst[(unit + 1) ^ 1], u1);
+  if (u2)
+    atomicOr(&dst[(unit + 2) ^ 1], u2);
+}
+
+template <int R, bool FULL>
+__device__ __forceinline__ void
+pack_merged(uint32_t *dst, const uint4 (&v)[R], const int (&cnt)[R],
+            const uint32_t (&start)[R], const u64 (&blob)[R],
+            const uint32_t (&rbits)[R], unsigned slow, const uint32_t *s_tab,
+            const u64 *__restrict__ codebook) {
+#pragma unroll
+  for (int j = 0; j < R; j++) {
+    if (__builtin_expect((slow >> j) & 1u, 0)) {
+      BitSink bs;
+      bs.begin(dst, start[j]);
+#pragma unroll 1
+      for (int e = 0; e < 8; e++) {
+        if (FULL || e < cnt[j]) {
+          const uint32_t w = e < 2 ? v[j].x : e < 4 ? v[j].y : e < 6 ? v[j].z : v[j].w;
+          const uint32_t sy = (e & 1) ? (w >> 16) : (w & 0xffffu);
+          const uint32_t t = s_tab[sy];
+          if (t >= (27u << 26))
+            bs.put(__ldg(&codebook[sy]));
+          else
+            bs.put32(t & 0x3ffffffu, t >> 26);
+        }
+      }
+      bs.end();
+    } else {
+      place64(dst, blob[j], rbits[j], start[j]);
+    }
+  }
+}
+
 // Tiles of ENC_WARPS chunks, one per packer warp, plus a ninth "scanner" warp.
 // Nobody meets at a CTA barrier: a packer adds its word count to the tile's
 // slot in shared memory and goes on packing; the scanner waits for the eight
@@ -448,7 +498,7 @@ __global__ void __launch_bounds__((ENC_WARPS + 1) * 32, 3)
     for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++iter) {
       const int slot = iter & (ENC_SLOTS - 1);
       while (v_arrived[slot] != ENC_WARPS)
-        ;
+        __nanosleep(40); // leave the issue slots to the packers
       __threadfence_block();
       u64 agg = lane < ENC_WARPS ? ((volatile uint32_t *)s_words[slot])[lane] : 0;
 #pragma unroll
@@ -468,8 +518,10 @@ __global__ void __launch_bounds__((ENC_WARPS + 1) * 32, 3)
           const int stop = inc ? __ffs(inc) - 1 : 31; // nearest inclusive prefix
           const unsigned need = stop == 31 ? 0xffffffffu : ((2u << stop) - 1u);
           const unsigned ready = __ballot_sync(0xffffffffu, (x >> 62) != 0);
-          if ((ready & need) != need)
+          if ((ready & need) != need) {
+            __nanosleep(20);
             continue;
+          }
           u64 part = lane <= stop ? (x & VAL_MASK) : 0;
 #pragma unroll
           for (int o = 16; o > 0; o >>= 1)
@@ -535,13 +587,26 @@ __global__ void __launch_bounds__((ENC_WARPS + 1) * 32, 3)
       v[j] = cnt[j] > 0 ? *(const uint4 *)(sym + idx) : make_uint4(0, 0, 0, 0);
     }
     uint32_t carry = 0;
+    u64 blob[R];
+    uint32_t rbits[R];
+    unsigned slow = 0;
 #pragma unroll
     for (int j = 0; j < R; j++) {
-      uint32_t rb = 0;
+      uint32_t rb = 0, mx = 0;
+      u64 a = 0;
 #pragma unroll
       for (int e = 0; e < 8; e++)
-        if (full || e < cnt[j])
-          rb += s_tab[sym_of(v[j], e)] >> 26;
+        if (full || e < cnt[j]) {
+          const uint32_t t = s_tab[sym_of(v[j], e)];
+          const uint32_t len = t >> 26;
+          rb += len;
+          mx = max(mx, t);
+          a = (a << len) | (t & 0x3ffffffu);
+        }
+      blob[j] = a;
+      rbits[j] = rb;
+      if (rb > 64 || mx >= (27u << 26))
+        slow |= 1u << j;
       uint32_t incl = rb;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
@@ -567,9 +632,10 @@ __global__ void __launch_bounds__((ENC_WARPS + 1) * 32, 3)
         img[i] = 0;
       __syncwarp();
       if (full)
-        pack_runs<R, true>(img, v, cnt, start, s_tab, codebook);
+        pack_merged<R, true>(img, v, cnt, start, blob, rbits, slow, s_tab, codebook);
       else
-        pack_runs<R, false>(img, v, cnt, start, s_tab, codebook);
+        pack_merged<R, false>(img, v, cnt, start, blob, rbits, slow, s_tab,
+                              codebook);
       __syncwarp();
     }
     if (pend) { // previous tile: its prefix has had a whole tile of time
