@@ -107,6 +107,8 @@ int mgx_create(mgx_ctx **out, int device, void *cuda_stream) {
     // A/B switch for measurements and tests: the superseded gather kernels
     const char *e = getenv("MGX_LEGACY_LEVELS");
     ctx->legacy_levels = e && e[0] == '1';
+    e = getenv("MGX_NO_WS");
+    ctx->no_ws = e && e[0] == '1';
   }
   cudaDeviceProp prop;
   if (cudaGetDeviceProperties(&prop, device) == cudaSuccess)

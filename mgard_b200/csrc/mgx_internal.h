@@ -62,6 +62,7 @@ struct mgx_ctx {
   void *d_tables = nullptr; // T[] copy of tb.buf
   double *d_rcp = nullptr;  // 1.0 / tb.buf[k] in double, same offsets
   bool fast_div = true;
+  bool no_ws = false;       // MGX_NO_WS=1: single-warp Thomas kernels only (A/B)
 
   // workspaces (allocated on first use, sized for the plan)
   void *d_w = nullptr;      // N elements of T (level workspace)

@@ -837,6 +837,267 @@ __global__ void __launch_bounds__(32)
   cp_wait<0>();
 }
 
+// ---- warp-specialised Thomas solves (scarce chains) ---------------------------------
+// When a level has only a few thousand lines (2-D grids), every SM holds a
+// single warp of chains and that warp's instruction stream IS the run time:
+// measured 424 cycles per element with loads, table fetches, address
+// arithmetic and stores issued around a 93-cycle dependent chain.  Here a block
+// is a pair of warps: warp 1 streams batches into a shared-memory ring
+// (cp.async), signals them FULL, and -- once the consumer marks them DONE --
+// drains the results to global memory (adding them into `acc` on the last
+// solve) and refills the slot; warp 0 does nothing but LDS -> chain -> STS.
+// Synchronisation: one named barrier per ring slot and direction
+// (bar.arrive / bar.sync over the 64 threads), no CTA-wide barrier.
+constexpr int WS_B = 16, WS_S = 4;
+constexpr int WS_FULL = 1, WS_DONE = 1 + WS_S; // named-barrier ids
+
+__device__ __forceinline__ void bar_sync(int id) {
+  asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory");
+}
+__device__ __forceinline__ void bar_arrive(int id) {
+  asm volatile("bar.arrive %0, 64;" ::"r"(id) : "memory");
+}
+
+template <typename T, bool ACC>
+__global__ void __launch_bounds__(64)
+    k_ipk_strided_ws(T *__restrict__ x, const T *__restrict__ am,
+                     const T *__restrict__ bm, const T *__restrict__ abr,
+                     const double *__restrict__ rbm, uint32_t n, uint64_t inner,
+                     uint64_t lines, T *__restrict__ acc, int sign, int fast) {
+  __shared__ T sx[WS_S][WS_B][32];
+  __shared__ T sa[ACC ? WS_S : 1][WS_B][32];
+  __shared__ T st[WS_S][2][WS_B];
+  __shared__ double sy[WS_S][WS_B];
+  const uint32_t lane = threadIdx.x & 31;
+  const bool producer = threadIdx.x >= 32;
+  uint64_t ln = (uint64_t)blockIdx.x * 32 + lane;
+  const bool active = ln < lines;
+  if (!active)
+    ln = lines - 1;
+  const uint64_t o = ln / inner, in = ln % inner;
+  T *p = x + o * n * inner + in;
+  T *pa = ACC ? acc + o * n * inner + in : nullptr;
+  const uint32_t nb = (n + WS_B - 1) / WS_B;
+#pragma unroll 1
+  for (int bwd = 0; bwd < 2; bwd++) {
+    if (producer) {
+      auto issue = [&](uint32_t j) {
+        if (j < nb) {
+          const uint32_t slot = j % WS_S;
+#pragma unroll
+          for (int k = 0; k < WS_B; k++) {
+            const uint32_t r = j * WS_B + k;
+            if (r < n) {
+              const uint64_t off = (uint64_t)(bwd ? n - 1 - r : r) * inner;
+              cp_async<sizeof(T)>(&sx[slot][k][lane], p + off);
+              if (ACC && bwd)
+                cp_async<sizeof(T)>(&sa[slot][k][lane], pa + off);
+            }
+          }
+          const uint32_t r = j * WS_B + lane;
+          if (lane < WS_B && r < n) {
+            if (!bwd) {
+              cp_async<sizeof(T)>(&st[slot][0][lane], abr + r);
+            } else {
+              const uint32_t i1 = n - r; // i + 1
+              cp_async<sizeof(T)>(&st[slot][0][lane], am + i1);
+              cp_async<sizeof(T)>(&st[slot][1][lane], bm + i1);
+              cp_async<8>(&sy[slot][lane], rbm + i1);
+            }
+          }
+        }
+        cp_commit();
+      };
+      for (uint32_t j = 0; j < WS_S; j++)
+        issue(j);
+      cp_wait<WS_S - 1>();
+      bar_arrive(WS_FULL + 0);
+      for (uint32_t j = 0; j < nb; j++) {
+        const uint32_t slot = j % WS_S;
+        if (j + 1 < nb) {
+          cp_wait<WS_S - 2>();
+          bar_arrive(WS_FULL + (j + 1) % WS_S);
+        }
+        bar_sync(WS_DONE + slot);
+        if (active) {
+#pragma unroll
+          for (int k = 0; k < WS_B; k++) {
+            const uint32_t r = j * WS_B + k;
+            if (r < n) {
+              const uint64_t off = (uint64_t)(bwd ? n - 1 - r : r) * inner;
+              const T v = sx[slot][k][lane];
+              if (ACC && bwd)
+                pa[off] = sign > 0 ? add_rn(sa[slot][k][lane], v)
+                                   : sub_rn(sa[slot][k][lane], v);
+              else
+                p[off] = v;
+            }
+          }
+        }
+        issue(j + WS_S);
+      }
+      cp_wait<0>();
+      __threadfence_block(); // the backward sweep re-reads what was just stored
+    } else {
+      T prev = 0;
+      for (uint32_t j = 0; j < nb; j++) {
+        const uint32_t slot = j % WS_S;
+        const int cnt = (int)min((uint32_t)WS_B, n - j * WS_B);
+        bar_sync(WS_FULL + slot);
+        if (!bwd) {
+          T c[WS_B], f[WS_B];
+#pragma unroll
+          for (int k = 0; k < WS_B; k++) {
+            c[k] = sx[slot][k][lane];
+            f[k] = st[slot][0][k];
+          }
+#pragma unroll
+          for (int k = 0; k < WS_B; k++)
+            if (k < cnt) {
+              prev = sub_rn(c[k], mul_rn(prev, f[k]));
+              sx[slot][k][lane] = prev;
+            }
+        } else {
+#pragma unroll
+          for (int h = 0; h < WS_B; h += 8) {
+            T c[8], a1[8], b1[8], res[8];
+            double y1[8];
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+              c[k] = sx[slot][h + k][lane];
+              a1[k] = st[slot][0][h + k];
+              b1[k] = st[slot][1][h + k];
+              y1[k] = sy[slot][h + k];
+            }
+            prev = backward_batch<T, 8>(c, a1, b1, y1, cnt - h, prev, fast != 0, res);
+#pragma unroll
+            for (int k = 0; k < 8; k++)
+              if (h + k < cnt)
+                sx[slot][h + k][lane] = res[k];
+          }
+        }
+        bar_arrive(WS_DONE + slot);
+      }
+    }
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(64)
+    k_ipk_contig_ws(T *__restrict__ x, const T *__restrict__ am,
+                    const T *__restrict__ bm, const T *__restrict__ abr,
+                    const double *__restrict__ rbm, uint32_t n, uint64_t lines,
+                    T *__restrict__ acc, int sign, int fast) {
+  __shared__ T tile[WS_S][32][33];
+  __shared__ T tabs[WS_S][2][32];
+  __shared__ double taby[WS_S][32];
+  const uint32_t lane = threadIdx.x & 31;
+  const bool producer = threadIdx.x >= 32;
+  const uint64_t l0 = (uint64_t)blockIdx.x * 32;
+  const uint32_t nl = (uint32_t)min((uint64_t)32, lines - l0);
+  const uint32_t nch = (n + 31) / 32;
+  T *xb = x + l0 * n;
+  T *ab = acc ? acc + l0 * n : nullptr;
+#pragma unroll 1
+  for (int bwd = 0; bwd < 2; bwd++) {
+    if (producer) {
+      auto issue = [&](uint32_t ch) {
+        if (ch < nch) {
+          const uint32_t c0 = (bwd ? nch - 1 - ch : ch) * 32;
+          const uint32_t slot = ch % WS_S;
+          if (c0 + lane < n) {
+            for (uint32_t r = 0; r < nl; r++)
+              cp_async<sizeof(T)>(&tile[slot][r][lane], xb + (uint64_t)r * n + c0 + lane);
+            if (!bwd) {
+              cp_async<sizeof(T)>(&tabs[slot][0][lane], abr + c0 + lane);
+            } else {
+              cp_async<sizeof(T)>(&tabs[slot][0][lane], am + c0 + lane + 1);
+              cp_async<sizeof(T)>(&tabs[slot][1][lane], bm + c0 + lane + 1);
+              cp_async<8>(&taby[slot][lane], rbm + c0 + lane + 1);
+            }
+          }
+        }
+        cp_commit();
+      };
+      for (uint32_t ch = 0; ch < WS_S; ch++)
+        issue(ch);
+      cp_wait<WS_S - 1>();
+      bar_arrive(WS_FULL + 0);
+      for (uint32_t ch = 0; ch < nch; ch++) {
+        const uint32_t slot = ch % WS_S;
+        if (ch + 1 < nch) {
+          cp_wait<WS_S - 2>();
+          bar_arrive(WS_FULL + (ch + 1) % WS_S);
+        }
+        bar_sync(WS_DONE + slot);
+        const uint32_t c0 = (bwd ? nch - 1 - ch : ch) * 32;
+        if (c0 + lane < n) {
+          if (ab && bwd) {
+            for (uint32_t r = 0; r < nl; r++) {
+              const uint64_t off = (uint64_t)r * n + c0 + lane;
+              ab[off] = sign > 0 ? add_rn(ab[off], tile[slot][r][lane])
+                                 : sub_rn(ab[off], tile[slot][r][lane]);
+            }
+          } else {
+            for (uint32_t r = 0; r < nl; r++)
+              xb[(uint64_t)r * n + c0 + lane] = tile[slot][r][lane];
+          }
+        }
+        issue(ch + WS_S);
+      }
+      cp_wait<0>();
+      __threadfence_block();
+    } else {
+      T prev = 0;
+      for (uint32_t ch = 0; ch < nch; ch++) {
+        const uint32_t slot = ch % WS_S;
+        const uint32_t c0 = (bwd ? nch - 1 - ch : ch) * 32;
+        const uint32_t ncol = min(32u, n - c0);
+        bar_sync(WS_FULL + slot);
+        T(*t)[33] = tile[slot];
+        if (lane < nl) {
+          if (!bwd) {
+            const T *fa = tabs[slot][0];
+            if (ncol == 32) {
+#pragma unroll 8
+              for (uint32_t j = 0; j < 32; j++) {
+                prev = sub_rn(t[lane][j], mul_rn(prev, fa[j]));
+                t[lane][j] = prev;
+              }
+            } else {
+              for (uint32_t j = 0; j < ncol; j++) {
+                prev = sub_rn(t[lane][j], mul_rn(prev, fa[j]));
+                t[lane][j] = prev;
+              }
+            }
+          } else {
+            for (uint32_t j0 = 0; j0 < ncol; j0 += 8) {
+              T c[8], a1[8], b1[8], res[8];
+              double y1[8];
+              const int cnt = (int)min(8u, ncol - j0);
+#pragma unroll
+              for (int k = 0; k < 8; k++) {
+                uint32_t j = k < cnt ? ncol - 1 - j0 - k : 0;
+                c[k] = t[lane][j];
+                a1[k] = tabs[slot][0][j];
+                b1[k] = tabs[slot][1][j];
+                y1[k] = taby[slot][j];
+              }
+              prev = backward_batch<T, 8>(c, a1, b1, y1, cnt, prev, fast != 0, res);
+#pragma unroll
+              for (int k = 0; k < 8; k++)
+                if (k < cnt)
+                  t[lane][ncol - 1 - j0 - k] = res[k];
+            }
+          }
+        }
+        __syncwarp();
+        bar_arrive(WS_DONE + slot);
+      }
+    }
+  }
+}
+
 // ---- inverse level kernel ------------------------------------------------------------
 // coefficients (v, reordered) + corrected coarse box A -> interleaved level-l
 // nodes (GpkRev3D, GridProcessingKernel3D.hpp:1230-2412)
@@ -1093,9 +1354,22 @@ int correction_tail(mgx_ctx *ctx, int l, T *R0, T *R1, T *A, int sign) {
     const uint64_t lines = outer * inner;
     const int fast = ctx->fast_div ? 1 : 0;
     T *acc = (d == pad) ? A : nullptr;
-    if (inner == 1) {
+    // scarce chains: the producer/consumer pair kernels (one pair per 32 lines)
+    const bool scarce = lines < (uint64_t)ctx->num_sms * 128 && !ctx->no_ws;
+    if (inner == 1 && scarce) {
+      k_ipk_contig_ws<T><<<(unsigned)((lines + 31) / 32), 64, 0, ctx->stream>>>(
+          corr, am, bm, abr, rbm, n, lines, acc, sign, fast);
+    } else if (inner == 1) {
       k_ipk_contig<T><<<(unsigned)((lines + 31) / 32), 32, 0, ctx->stream>>>(
           corr, am, bm, abr, rbm, n, lines, acc, sign, fast);
+    } else if (scarce) {
+      const unsigned grid = (unsigned)((lines + 31) / 32);
+      if (acc)
+        k_ipk_strided_ws<T, true><<<grid, 64, 0, ctx->stream>>>(
+            corr, am, bm, abr, rbm, n, inner, lines, acc, sign, fast);
+      else
+        k_ipk_strided_ws<T, false><<<grid, 64, 0, ctx->stream>>>(
+            corr, am, bm, abr, rbm, n, inner, lines, nullptr, sign, fast);
     } else {
       // few lines: small blocks, so that every SM gets a chain to work on
       unsigned tpb = 128;

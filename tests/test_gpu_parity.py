@@ -292,3 +292,20 @@ def test_fused_level_quantize_containers(shape, dtype, s, rel, tol):
     assert np.array_equal(np.delete(got, 7), np.delete(want, 7))
     dec = comp.Decompress(blob, eb, tol, s, norm).cpu().numpy()
     assert np.array_equal(dec, o.decompress(want, shape, dtype, rel, tol, s, norm))
+
+
+@pytest.mark.parametrize("shape,dtype", [((300, 77), np.float64), ((66, 33, 130), np.float32),
+                                         ((5, 6, 7, 8, 40), np.float64)])
+def test_single_warp_thomas_kernels(shape, dtype, monkeypatch):
+    """Levels with many lines use the single-warp ring kernels instead of the
+    producer/consumer pairs; MGX_NO_WS=1 forces them at test sizes."""
+    u = smooth_field(shape, dtype)
+    monkeypatch.setenv("MGX_NO_WS", "1")
+    comp, tdt = make(shape, dtype)
+    monkeypatch.delenv("MGX_NO_WS")
+    d = torch.from_numpy(u).cuda()
+    comp.Decompose(d, 1)
+    want = Oracle("port").decompose(u, 1)
+    assert np.array_equal(d.cpu().numpy(), want)
+    comp.Recompose(d, 1)
+    assert np.array_equal(d.cpu().numpy(), Oracle("port").recompose(want, 1))
