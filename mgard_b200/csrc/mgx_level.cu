@@ -842,14 +842,16 @@ __global__ void __launch_bounds__(32)
 // single warp of chains and that warp's instruction stream IS the run time:
 // measured 424 cycles per element with loads, table fetches, address
 // arithmetic and stores issued around a 93-cycle dependent chain.  Here a block
-// is a pair of warps: warp 1 streams batches into a shared-memory ring
-// (cp.async), signals them FULL, and -- once the consumer marks them DONE --
-// drains the results to global memory (adding them into `acc` on the last
-// solve) and refills the slot; warp 0 does nothing but LDS -> chain -> STS.
-// Synchronisation: one named barrier per ring slot and direction
-// (bar.arrive / bar.sync over the 64 threads), no CTA-wide barrier.
+// is three warps around a shared-memory ring of WS_S batches:
+//   warp 2 (loader)  : cp.async of the batch's rows (+ acc rows + table
+//                      entries) -> FULL[slot] once they have landed;
+//   warp 0 (consumer): nothing but LDS -> chain -> STS -> DONE[slot];
+//   warp 1 (drainer) : results -> global (added into `acc` on the last solve)
+//                      -> FREE[slot], which lets the loader refill it.
+// Synchronisation: one named barrier per slot and edge (bar.arrive / bar.sync
+// over the two warps involved), no CTA-wide barrier.
 constexpr int WS_B = 16, WS_S = 4;
-constexpr int WS_FULL = 1, WS_DONE = 1 + WS_S; // named-barrier ids
+constexpr int WS_FULL = 1, WS_DONE = 1 + WS_S, WS_FREE = 1 + 2 * WS_S; // barrier ids
 
 __device__ __forceinline__ void bar_sync(int id) {
   asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory");
@@ -859,7 +861,7 @@ __device__ __forceinline__ void bar_arrive(int id) {
 }
 
 template <typename T, bool ACC>
-__global__ void __launch_bounds__(64)
+__global__ void __launch_bounds__(96)
     k_ipk_strided_ws(T *__restrict__ x, const T *__restrict__ am,
                      const T *__restrict__ bm, const T *__restrict__ abr,
                      const double *__restrict__ rbm, uint32_t n, uint64_t inner,
@@ -869,7 +871,7 @@ __global__ void __launch_bounds__(64)
   __shared__ T st[WS_S][2][WS_B];
   __shared__ double sy[WS_S][WS_B];
   const uint32_t lane = threadIdx.x & 31;
-  const bool producer = threadIdx.x >= 32;
+  const int role = threadIdx.x >> 5; // 0 consumer, 1 drainer, 2 loader
   uint64_t ln = (uint64_t)blockIdx.x * 32 + lane;
   const bool active = ln < lines;
   if (!active)
@@ -878,21 +880,28 @@ __global__ void __launch_bounds__(64)
   T *p = x + o * n * inner + in;
   T *pa = ACC ? acc + o * n * inner + in : nullptr;
   const uint32_t nb = (n + WS_B - 1) / WS_B;
+  const int64_t step = (int64_t)inner; // elements between consecutive rows
 #pragma unroll 1
   for (int bwd = 0; bwd < 2; bwd++) {
-    if (producer) {
+    // row r of the sweep is element (bwd ? n-1-r : r) of the line
+    const int64_t dstep = bwd ? -step : step;
+    if (role == 2) { // ---- loader ----
+      const T *src = bwd ? p + (uint64_t)(n - 1) * inner : p;
+      const T *srca = ACC ? (bwd ? pa + (uint64_t)(n - 1) * inner : pa) : nullptr;
       auto issue = [&](uint32_t j) {
         if (j < nb) {
           const uint32_t slot = j % WS_S;
+          const bool whole = (j + 1) * WS_B <= n;
 #pragma unroll
           for (int k = 0; k < WS_B; k++) {
-            const uint32_t r = j * WS_B + k;
-            if (r < n) {
-              const uint64_t off = (uint64_t)(bwd ? n - 1 - r : r) * inner;
-              cp_async<sizeof(T)>(&sx[slot][k][lane], p + off);
+            if (whole || j * WS_B + k < n) {
+              cp_async<sizeof(T)>(&sx[slot][k][lane], src);
               if (ACC && bwd)
-                cp_async<sizeof(T)>(&sa[slot][k][lane], pa + off);
+                cp_async<sizeof(T)>(&sa[slot][k][lane], srca);
             }
+            src += dstep;
+            if (ACC)
+              srca += dstep;
           }
           const uint32_t r = j * WS_B + lane;
           if (lane < WS_B && r < n) {
@@ -913,32 +922,40 @@ __global__ void __launch_bounds__(64)
       cp_wait<WS_S - 1>();
       bar_arrive(WS_FULL + 0);
       for (uint32_t j = 0; j < nb; j++) {
-        const uint32_t slot = j % WS_S;
         if (j + 1 < nb) {
           cp_wait<WS_S - 2>();
           bar_arrive(WS_FULL + (j + 1) % WS_S);
         }
-        bar_sync(WS_DONE + slot);
-        if (active) {
-#pragma unroll
-          for (int k = 0; k < WS_B; k++) {
-            const uint32_t r = j * WS_B + k;
-            if (r < n) {
-              const uint64_t off = (uint64_t)(bwd ? n - 1 - r : r) * inner;
-              const T v = sx[slot][k][lane];
-              if (ACC && bwd)
-                pa[off] = sign > 0 ? add_rn(sa[slot][k][lane], v)
-                                   : sub_rn(sa[slot][k][lane], v);
-              else
-                p[off] = v;
-            }
-          }
-        }
+        bar_sync(WS_FREE + j % WS_S); // batch j drained: its slot is free
         issue(j + WS_S);
       }
       cp_wait<0>();
-      __threadfence_block(); // the backward sweep re-reads what was just stored
-    } else {
+    } else if (role == 1) { // ---- drainer ----
+      T *dst = bwd ? p + (uint64_t)(n - 1) * inner : p;
+      T *dsta = ACC ? (bwd ? pa + (uint64_t)(n - 1) * inner : pa) : nullptr;
+      for (uint32_t j = 0; j < nb; j++) {
+        const uint32_t slot = j % WS_S;
+        const bool whole = (j + 1) * WS_B <= n;
+        bar_sync(WS_DONE + slot);
+#pragma unroll
+        for (int k = 0; k < WS_B; k++) {
+          if (active && (whole || j * WS_B + k < n)) {
+            const T v = sx[slot][k][lane];
+            if (ACC && bwd)
+              *dsta = sign > 0 ? add_rn(sa[slot][k][lane], v)
+                               : sub_rn(sa[slot][k][lane], v);
+            else
+              *dst = v;
+          }
+          dst += dstep;
+          if (ACC)
+            dsta += dstep;
+        }
+        if (!bwd)
+          __threadfence_block(); // the backward sweep's loader re-reads these
+        bar_arrive(WS_FREE + slot);
+      }
+    } else { // ---- consumer ----
       T prev = 0;
       for (uint32_t j = 0; j < nb; j++) {
         const uint32_t slot = j % WS_S;
@@ -983,7 +1000,7 @@ __global__ void __launch_bounds__(64)
 }
 
 template <typename T>
-__global__ void __launch_bounds__(64)
+__global__ void __launch_bounds__(96)
     k_ipk_contig_ws(T *__restrict__ x, const T *__restrict__ am,
                     const T *__restrict__ bm, const T *__restrict__ abr,
                     const double *__restrict__ rbm, uint32_t n, uint64_t lines,
@@ -992,7 +1009,7 @@ __global__ void __launch_bounds__(64)
   __shared__ T tabs[WS_S][2][32];
   __shared__ double taby[WS_S][32];
   const uint32_t lane = threadIdx.x & 31;
-  const bool producer = threadIdx.x >= 32;
+  const int role = threadIdx.x >> 5; // 0 consumer, 1 drainer, 2 loader
   const uint64_t l0 = (uint64_t)blockIdx.x * 32;
   const uint32_t nl = (uint32_t)min((uint64_t)32, lines - l0);
   const uint32_t nch = (n + 31) / 32;
@@ -1000,14 +1017,21 @@ __global__ void __launch_bounds__(64)
   T *ab = acc ? acc + l0 * n : nullptr;
 #pragma unroll 1
   for (int bwd = 0; bwd < 2; bwd++) {
-    if (producer) {
+    if (role == 2) { // ---- loader ----
       auto issue = [&](uint32_t ch) {
         if (ch < nch) {
           const uint32_t c0 = (bwd ? nch - 1 - ch : ch) * 32;
           const uint32_t slot = ch % WS_S;
           if (c0 + lane < n) {
-            for (uint32_t r = 0; r < nl; r++)
-              cp_async<sizeof(T)>(&tile[slot][r][lane], xb + (uint64_t)r * n + c0 + lane);
+            const T *src = xb + c0 + lane;
+            if (nl == 32) {
+#pragma unroll 8
+              for (uint32_t r = 0; r < 32; r++, src += n)
+                cp_async<sizeof(T)>(&tile[slot][r][lane], src);
+            } else {
+              for (uint32_t r = 0; r < nl; r++, src += n)
+                cp_async<sizeof(T)>(&tile[slot][r][lane], src);
+            }
             if (!bwd) {
               cp_async<sizeof(T)>(&tabs[slot][0][lane], abr + c0 + lane);
             } else {
@@ -1024,30 +1048,42 @@ __global__ void __launch_bounds__(64)
       cp_wait<WS_S - 1>();
       bar_arrive(WS_FULL + 0);
       for (uint32_t ch = 0; ch < nch; ch++) {
-        const uint32_t slot = ch % WS_S;
         if (ch + 1 < nch) {
           cp_wait<WS_S - 2>();
           bar_arrive(WS_FULL + (ch + 1) % WS_S);
         }
-        bar_sync(WS_DONE + slot);
-        const uint32_t c0 = (bwd ? nch - 1 - ch : ch) * 32;
-        if (c0 + lane < n) {
-          if (ab && bwd) {
-            for (uint32_t r = 0; r < nl; r++) {
-              const uint64_t off = (uint64_t)r * n + c0 + lane;
-              ab[off] = sign > 0 ? add_rn(ab[off], tile[slot][r][lane])
-                                 : sub_rn(ab[off], tile[slot][r][lane]);
-            }
-          } else {
-            for (uint32_t r = 0; r < nl; r++)
-              xb[(uint64_t)r * n + c0 + lane] = tile[slot][r][lane];
-          }
-        }
+        bar_sync(WS_FREE + ch % WS_S);
         issue(ch + WS_S);
       }
       cp_wait<0>();
-      __threadfence_block();
-    } else {
+    } else if (role == 1) { // ---- drainer ----
+      for (uint32_t ch = 0; ch < nch; ch++) {
+        const uint32_t slot = ch % WS_S;
+        const uint32_t c0 = (bwd ? nch - 1 - ch : ch) * 32;
+        bar_sync(WS_DONE + slot);
+        if (c0 + lane < n) {
+          if (ab && bwd) {
+            T *d = ab + c0 + lane;
+            for (uint32_t r = 0; r < nl; r++, d += n)
+              *d = sign > 0 ? add_rn(*d, tile[slot][r][lane])
+                            : sub_rn(*d, tile[slot][r][lane]);
+          } else {
+            T *d = xb + c0 + lane;
+            if (nl == 32) {
+#pragma unroll 8
+              for (uint32_t r = 0; r < 32; r++, d += n)
+                *d = tile[slot][r][lane];
+            } else {
+              for (uint32_t r = 0; r < nl; r++, d += n)
+                *d = tile[slot][r][lane];
+            }
+          }
+        }
+        if (!bwd)
+          __threadfence_block();
+        bar_arrive(WS_FREE + slot);
+      }
+    } else { // ---- consumer ----
       T prev = 0;
       for (uint32_t ch = 0; ch < nch; ch++) {
         const uint32_t slot = ch % WS_S;
@@ -1357,7 +1393,7 @@ int correction_tail(mgx_ctx *ctx, int l, T *R0, T *R1, T *A, int sign) {
     // scarce chains: the producer/consumer pair kernels (one pair per 32 lines)
     const bool scarce = lines < (uint64_t)ctx->num_sms * 128 && !ctx->no_ws;
     if (inner == 1 && scarce) {
-      k_ipk_contig_ws<T><<<(unsigned)((lines + 31) / 32), 64, 0, ctx->stream>>>(
+      k_ipk_contig_ws<T><<<(unsigned)((lines + 31) / 32), 96, 0, ctx->stream>>>(
           corr, am, bm, abr, rbm, n, lines, acc, sign, fast);
     } else if (inner == 1) {
       k_ipk_contig<T><<<(unsigned)((lines + 31) / 32), 32, 0, ctx->stream>>>(
@@ -1365,10 +1401,10 @@ int correction_tail(mgx_ctx *ctx, int l, T *R0, T *R1, T *A, int sign) {
     } else if (scarce) {
       const unsigned grid = (unsigned)((lines + 31) / 32);
       if (acc)
-        k_ipk_strided_ws<T, true><<<grid, 64, 0, ctx->stream>>>(
+        k_ipk_strided_ws<T, true><<<grid, 96, 0, ctx->stream>>>(
             corr, am, bm, abr, rbm, n, inner, lines, acc, sign, fast);
       else
-        k_ipk_strided_ws<T, false><<<grid, 64, 0, ctx->stream>>>(
+        k_ipk_strided_ws<T, false><<<grid, 96, 0, ctx->stream>>>(
             corr, am, bm, abr, rbm, n, inner, lines, nullptr, sign, fast);
     } else {
       // few lines: small blocks, so that every SM gets a chain to work on
