@@ -800,8 +800,10 @@ int mgxk_encode_container(mgx_ctx *ctx, uint64_t n, uint8_t *d_out, uint64_t cap
   const uint64_t off_outc = h.off_packed + 8 * ddata;
   const uint64_t total = off_outc + 8 + 16 * n_out;
   *out_bytes = total;
-  if (total > cap || (ctx->h_scalars[MGX_SC_ERR] & 8))
+  if (total > cap || (ctx->h_scalars[MGX_SC_ERR] & 8)) {
+    ctx->err = "compressed stream does not fit the output buffer";
     return MGX_OUTPUT_TOO_LARGE;
+  }
   // metadata sections
   k_write_header<<<1, 32, 0, ctx->stream>>>(d_out, h, (const u64 *)ctx->d_scalars);
   ctx->launches++;

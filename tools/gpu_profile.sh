@@ -10,7 +10,7 @@ for k in k_norm k_hier_forward k_codebook k_encode k_decode_multi k_hier_inverse
   ncu --set full --import-source on --clock-control none -k regex:$k -c 1 -f -o gpurun_out/full_$k \
       python bench.py --steps 1 --warmup 0 --no-cpu --no-e2e >> gpurun_out/ncu.log 2>&1
 done
-for k in k_level_forward k_lpk_mid k_ipk_contig k_ipk_strided k_level_restore_rows; do
+for k in k_level_forward k_lpk_mid k_ipk_contig_ws k_ipk_strided_ws k_level_restore_rows; do
   ncu --set full --import-source on --clock-control none -k regex:$k -c 1 -f -o gpurun_out/full_cfg2_$k \
       python tools/stage_times.py --shape 8193 8193 --dtype f64 --s 0 --tol 1e-4 --steps 1 --warmup 0 >> gpurun_out/ncu.log 2>&1
 done
