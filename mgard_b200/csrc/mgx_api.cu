@@ -107,6 +107,11 @@ int mgx_create(mgx_ctx **out, int device, void *cuda_stream) {
     // A/B switch for measurements and tests: the superseded gather kernels
     const char *e = getenv("MGX_LEGACY_LEVELS");
     ctx->legacy_levels = e && e[0] == '1';
+    e = getenv("MGX_FW_MINB");
+    if (e && (e[0] == '2' || e[0] == '3'))
+      ctx->fw_minb = e[0] - '0';
+    e = getenv("MGX_NO_SYM_RECOMPOSE");
+    ctx->no_sym_recompose = e && e[0] == '1';
     e = getenv("MGX_NO_WS");
     ctx->no_ws = e && e[0] == '1';
   }
@@ -554,7 +559,12 @@ int mgx_decompress(mgx_ctx *ctx, const uint8_t *d_in, uint64_t bytes, int rel,
   rc = MGX_FAILURE + 101;
   if (!orth) // fused dequantise + recompose (hierarchical basis)
     rc = mgxk_hier_inverse(ctx, rel, tol, norm, d_out, oidx, oval, n_out);
-  if (rc == MGX_FAILURE + 101 && orth && !ctx->legacy_levels) {
+  if (rc == MGX_FAILURE + 101 && orth && !ctx->legacy_levels && n_out == 0 &&
+      !ctx->no_sym_recompose) {
+    // no outliers: the level kernels dequantise the symbols on the fly
+    mgx_tick(ctx, MGX_TICK_D_DEQUANT);
+    rc = mgxk_recompose_sym_rows(ctx, rel, tol, s, norm, d_out);
+  } else if (rc == MGX_FAILURE + 101 && orth && !ctx->legacy_levels) {
     rc = mgx_ensure_workspaces(ctx, false, true);
     if (!rc)
       rc = mgxk_dequantize_sym_out(ctx, rel, tol, s, norm, ctx->d_v, oidx, oval,

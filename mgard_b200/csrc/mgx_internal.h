@@ -62,6 +62,8 @@ struct mgx_ctx {
   void *d_tables = nullptr; // T[] copy of tb.buf
   double *d_rcp = nullptr;  // 1.0 / tb.buf[k] in double, same offsets
   bool fast_div = true;
+  int fw_minb = 0;          // MGX_FW_MINB=2|3: force the k_level_forward variant (0 = by dtype)
+  bool no_sym_recompose = false; // MGX_NO_SYM_RECOMPOSE=1: dequantise to floats first
   bool no_ws = false;       // MGX_NO_WS=1: single-warp Thomas kernels only (A/B)
 
   // workspaces (allocated on first use, sized for the plan)
@@ -182,6 +184,8 @@ int mgxk_decompose_rows(mgx_ctx *ctx, const void *d_src, void *d_coeff);
 int mgxk_decompose_quantize_rows(mgx_ctx *ctx, const void *d_src, int rel,
                                  double tol, double s, double norm);
 int mgxk_recompose_rows(mgx_ctx *ctx, const void *d_coeff, void *d_dst);
+int mgxk_recompose_sym_rows(mgx_ctx *ctx, int rel, double tol, double s,
+                            double norm, void *d_dst);
 // per-level quantiser (reciprocal for quantise) and volume factor, as doubles
 // holding the T-precision values (CalcQuantizers, LinearQuantization.hpp:234-297)
 void mgx_level_quantizers(const mgx_ctx *ctx, int rel, double tol, double s,

@@ -253,6 +253,9 @@ __device__ __forceinline__ void prefetch_row(const T *__restrict__ base, int64_t
 // coefficient -> float store, or -> symbol + histogram + outlier list
 // (lwqzk LinearQuantization.hpp:96-111, OutlierSeparator.hpp:17-120,
 // Histogram.hpp).  Called by all lanes of a warp.
+__device__ __forceinline__ int to_int_sat(float r) { return __float2int_rz(r); }
+__device__ __forceinline__ int to_int_sat(double r) { return __double2int_rz(r); }
+
 template <typename T, bool QUANT>
 __device__ __forceinline__ void emit(T c, bool valid, uint64_t idx,
                                      T *__restrict__ v, const QuantOut<T> &qo,
@@ -261,21 +264,25 @@ __device__ __forceinline__ void emit(T c, bool valid, uint64_t idx,
     if (valid)
       v[idx] = c;
   } else {
-    uint32_t sv = 0;
     if (valid) {
-      long long q = mgx_quantize(c, qo.qv, qo.vol, qo.shift);
-      if (q < 0 || q >= (long long)qo.dict) {
+      // 32-bit fast path: the saturating conversion sends every magnitude that
+      // does not fit an int out of the dictionary range, where the exact
+      // 64-bit code is formed for the outlier list
+      const T r = add_rn((T)0.5, fabs(mul_rn(mul_rn(c, qo.qv), qo.vol)));
+      const int qi = to_int_sat(r);
+      int sv = (c < (T)0 ? -qi : qi) + (int)qo.shift;
+      if (__builtin_expect((unsigned)sv >= qo.dict, 0)) {
+        const long long q = mgx_quantize(c, qo.qv, qo.vol, qo.shift);
         unsigned long long slot = atomicAdd(qo.out_count, 1ull);
         if (slot < qo.out_cap) {
           qo.out_idx[slot] = idx;
           qo.out_val[slot] = q;
         }
-        q = 0;
+        sv = 0;
       }
-      sv = (uint32_t)q;
       qo.sym[idx] = (uint16_t)sv;
+      atomicAdd(&s_hist[sv], 1u); // ATOMS.POPC.INC merges lanes on one bin
     }
-    mgx_hist_add(s_hist, sv, valid);
   }
 }
 
@@ -325,8 +332,8 @@ __device__ __forceinline__ void forward_row(
     R[row * ncf + (uint64_t)i] = mass_apply(mk, cem1, com1, ce, co, cep1);
 }
 
-template <typename T, bool QUANT>
-__global__ void __launch_bounds__(FW_WARPS * 32)
+template <typename T, bool QUANT, int MINB>
+__global__ void __launch_bounds__(FW_WARPS * 32, MINB)
     k_level_forward(const T *__restrict__ src, T *__restrict__ v,
                     T *__restrict__ A, T *__restrict__ R,
                     const T *__restrict__ tables,
@@ -405,10 +412,33 @@ __global__ void __launch_bounds__(FW_WARPS * 32)
   }
 }
 
+// Where recompose reads a level's coefficients from: the float array of the
+// staged API, or -- on the fused decompress path -- the 16-bit symbols, which are
+// dequantised on the fly (lwqzk inverse, LinearQuantization.hpp:113-128:
+// (quantizer * volume) * (T)(code - dict/2), a per-level scalar times the code).
+template <typename T, bool SYM> struct Coef {
+  const T *v;
+  const uint16_t *sym;
+  T dq;      // quantizer * volume of this level
+  int shift; // dict / 2
+  __device__ __forceinline__ T at(uint64_t idx) const {
+    if constexpr (SYM)
+      return mul_rn(dq, (T)((int)sym[idx] - shift));
+    else
+      return v[idx];
+  }
+  __device__ __forceinline__ void prefetch(uint64_t idx) const {
+    if constexpr (SYM)
+      prefetch_l1(sym + idx);
+    else
+      prefetch_l1(v + idx);
+  }
+};
+
 // ---- first restriction sweep from stored coefficients (recompose) ------------------
-template <typename T>
+template <typename T, bool SYM>
 __global__ void __launch_bounds__(256)
-    k_lpk_first(const T *__restrict__ v, T *__restrict__ R,
+    k_lpk_first(const Coef<T, SYM> cf, T *__restrict__ R,
                 const T *__restrict__ tables, const __grid_constant__ LvGeom g) {
   const uint32_t ncf = g.nc[FD], nff = g.nf[FD], ncoef = nff - ncf;
   const int lane = threadIdx.x & 31;
@@ -433,25 +463,24 @@ __global__ void __launch_bounds__(256)
       coarse_row = coarse_row && p[d] < g.nc[d];
       vo += (uint64_t)p[d] * g.vst[d];
     }
-    const T *vr = v + vo;
     row_next(p, g);
     if (row + 1 < row1) {
       uint64_t vn = 0;
 #pragma unroll
       for (int d = 0; d < OUTER; d++)
         vn += (uint64_t)p[d] * g.vst[d];
-      prefetch_l1(v + vn + i);
+      cf.prefetch(vn + i);
       if (i < (int64_t)ncoef)
-        prefetch_l1(v + vn + ncf + i);
+        cf.prefetch(vn + ncf + i);
     }
     T a = 0, b = 0, c = 0, d = 0, e = 0;
     if (!coarse_row) {
-      a = i >= 1 ? vr[i - 1] : (T)0;
-      c = vr[i];
-      e = i + 1 < (int64_t)ncf ? vr[i + 1] : (T)0;
+      a = i >= 1 ? cf.at(vo + i - 1) : (T)0;
+      c = cf.at(vo + i);
+      e = i + 1 < (int64_t)ncf ? cf.at(vo + i + 1) : (T)0;
     }
-    b = (i >= 1 && i - 1 < (int64_t)ncoef) ? vr[ncf + i - 1] : (T)0;
-    d = i < (int64_t)ncoef ? vr[ncf + i] : (T)0;
+    b = (i >= 1 && i - 1 < (int64_t)ncoef) ? cf.at(vo + ncf + i - 1) : (T)0;
+    d = i < (int64_t)ncoef ? cf.at(vo + ncf + i) : (T)0;
     R[row * ncf + (uint64_t)i] = mass_apply(mk, a, b, c, d, e);
   }
 }
@@ -1137,33 +1166,32 @@ __global__ void __launch_bounds__(96)
 // ---- inverse level kernel ------------------------------------------------------------
 // coefficients (v, reordered) + corrected coarse box A -> interleaved level-l
 // nodes (GpkRev3D, GridProcessingKernel3D.hpp:1230-2412)
-template <typename T, int K>
-__device__ __forceinline__ void restore_row(const T *__restrict__ v,
+template <typename T, int K, bool SYM>
+__device__ __forceinline__ void restore_row(const Coef<T, SYM> &cf,
                                             const T *__restrict__ A,
                                             T *__restrict__ dst, const Row<T> &r,
                                             const LvGeom &g, uint32_t i,
                                             bool has_odd, uint32_t qe, T tf) {
   const uint32_t ncf = g.nc[FD];
   T *drow = dst + r.so;
-  const T *vr = v + r.vo;
   if constexpr (K == 0) {
     const T *arow = A + r.ao;
     T a0 = arow[i];
     drow[qe] = a0;
     if (has_odd)
-      drow[2 * i + 1] = add_rn(vr[ncf + i], mgx_lerp(a0, arow[i + 1], tf));
+      drow[2 * i + 1] = add_rn(cf.at(r.vo + ncf + i), mgx_lerp(a0, arow[i + 1], tf));
   } else {
     T a, b;
     corners<T, K, false>(A, (int64_t)r.ao, r, i, i + 1, has_odd, tf, a, b);
-    drow[qe] = add_rn(vr[i], a);
+    drow[qe] = add_rn(cf.at(r.vo + i), a);
     if (has_odd)
-      drow[2 * i + 1] = add_rn(vr[ncf + i], b);
+      drow[2 * i + 1] = add_rn(cf.at(r.vo + ncf + i), b);
   }
 }
 
-template <typename T>
+template <typename T, bool SYM>
 __global__ void __launch_bounds__(256)
-    k_level_restore_rows(const T *__restrict__ v, const T *__restrict__ A,
+    k_level_restore_rows(const Coef<T, SYM> cf, const T *__restrict__ A,
                          T *__restrict__ dst, const T *__restrict__ tables,
                          const __grid_constant__ LvGeom g) {
   const uint32_t ncf = g.nc[FD], nff = g.nf[FD], ncoef = nff - ncf;
@@ -1192,27 +1220,27 @@ __global__ void __launch_bounds__(256)
       row_next(p, g);
       Row<T> nx;
       row_setup<T, false>(nx, p, g, tables);
-      prefetch_l1(v + nx.vo + i);
+      cf.prefetch(nx.vo + i);
       if (has_odd)
-        prefetch_l1(v + nx.vo + ncf + i);
+        cf.prefetch(nx.vo + ncf + i);
       prefetch_l1(A + nx.ao + i);
       prefetch_row<T, false>(A, (int64_t)nx.ao + i, nx);
     }
     switch (r.nodd) {
     case 0:
-      restore_row<T, 0>(v, A, dst, r, g, i, has_odd, qe, tf);
+      restore_row<T, 0, SYM>(cf, A, dst, r, g, i, has_odd, qe, tf);
       break;
     case 1:
-      restore_row<T, 1>(v, A, dst, r, g, i, has_odd, qe, tf);
+      restore_row<T, 1, SYM>(cf, A, dst, r, g, i, has_odd, qe, tf);
       break;
     case 2:
-      restore_row<T, 2>(v, A, dst, r, g, i, has_odd, qe, tf);
+      restore_row<T, 2, SYM>(cf, A, dst, r, g, i, has_odd, qe, tf);
       break;
     case 3:
-      restore_row<T, 3>(v, A, dst, r, g, i, has_odd, qe, tf);
+      restore_row<T, 3, SYM>(cf, A, dst, r, g, i, has_odd, qe, tf);
       break;
     default:
-      restore_row<T, 4>(v, A, dst, r, g, i, has_odd, qe, tf);
+      restore_row<T, 4, SYM>(cf, A, dst, r, g, i, has_odd, qe, tf);
       break;
     }
     if (more)
@@ -1239,7 +1267,8 @@ __global__ void __launch_bounds__(256)
       r /= g.nc[d];
     }
     if constexpr (GATHER) {
-      A[it] = v[o];
+      // v == nullptr: dequantise the level-0 symbols (qo.qv = quantizer * volume)
+      A[it] = v ? v[o] : mul_rn(qo.qv, (T)((int)qo.sym[o] - (int)qo.shift));
     } else if constexpr (!QUANT) {
       v[o] = A[it];
     } else {
@@ -1472,10 +1501,14 @@ int decompose_rows(mgx_ctx *ctx, const T *src, T *v, const double *q,
   const MgxLevels &lv = ctx->lv;
   const T *tables = (const T *)ctx->d_tables;
   const size_t smem = QUANT ? (size_t)ctx->dict * 4 : 0;
-  if (QUANT)
-    MGX_CUDA(cudaFuncSetAttribute(k_level_forward<T, QUANT>,
+  if (QUANT) {
+    MGX_CUDA(cudaFuncSetAttribute(k_level_forward<T, QUANT, 2>,
                                   cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)smem));
+    MGX_CUDA(cudaFuncSetAttribute(k_level_forward<T, QUANT, 3>,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)smem));
+  }
   QuantOut<T> qo;
   const T *cur = src;
   int which = 0;
@@ -1483,8 +1516,15 @@ int decompose_rows(mgx_ctx *ctx, const T *src, T *v, const double *q,
     LvGeom g = level_geom<T>(ctx, l, FW_OWN);
     fill_quant<T>(ctx, &qo, q, vol, l);
     T *A = (T *)s.A[which];
-    k_level_forward<T, QUANT><<<task_grid(g, FW_WARPS), FW_WARPS * 32, smem,
-                                ctx->stream>>>(cur, v, A, (T *)s.R[0], tables, g, qo);
+    // 3 CTAs/SM pays for fp32 (80 regs without spills); fp64 spills at 80
+    if (ctx->fw_minb == 3 || (ctx->fw_minb == 0 && sizeof(T) == 4))
+      k_level_forward<T, QUANT, 3><<<task_grid(g, FW_WARPS), FW_WARPS * 32, smem,
+                                     ctx->stream>>>(cur, v, A, (T *)s.R[0], tables,
+                                                    g, qo);
+    else
+      k_level_forward<T, QUANT, 2><<<task_grid(g, FW_WARPS), FW_WARPS * 32, smem,
+                                     ctx->stream>>>(cur, v, A, (T *)s.R[0], tables,
+                                                    g, qo);
     ctx->launches++;
     rc = correction_tail<T>(ctx, l, (T *)s.R[0], (T *)s.R[1], A, +1);
     if (rc)
@@ -1521,7 +1561,10 @@ int decompose_rows(mgx_ctx *ctx, const T *src, T *v, const double *q,
 }
 
 // recompose: coefficients v (reordered, read only) -> dst (full array), dst != v
-template <typename T> int recompose_rows(mgx_ctx *ctx, const T *v, T *dst) {
+// recompose: coefficients (v, reordered, read only -- or, SYM, the symbols in
+// ctx->d_sym with per-level dequantisers dq[]) -> dst (full array), dst != v
+template <typename T, bool SYM>
+int recompose_rows(mgx_ctx *ctx, const T *v, T *dst, const double *dq) {
   Scratch s;
   int rc = get_scratch(ctx, &s);
   if (rc)
@@ -1530,11 +1573,11 @@ template <typename T> int recompose_rows(mgx_ctx *ctx, const T *v, T *dst) {
   const T *tables = (const T *)ctx->d_tables;
   QuantOut<T> qo;
   fill_quant<T>(ctx, &qo, nullptr, nullptr, 0);
-  if (lv.L == 0) {
-    MGX_CUDA(cudaMemcpyAsync(dst, v, lv.N * sizeof(T), cudaMemcpyDeviceToDevice,
-                             ctx->stream));
-    return MGX_SUCCESS;
-  }
+  Coef<T, SYM> cf;
+  cf.v = v;
+  cf.sym = ctx->d_sym;
+  cf.shift = (int)(ctx->dict / 2);
+  cf.dq = SYM ? (T)dq[0] : (T)0;
   LvGeom g0;
   for (int d = 0; d < MGX_MAX_D; d++) {
     g0.nc[d] = (uint32_t)lv.n[0][d];
@@ -1544,22 +1587,36 @@ template <typename T> int recompose_rows(mgx_ctx *ctx, const T *v, T *dst) {
   for (int d = 0; d < MGX_MAX_D; d++)
     n0 *= lv.n[0][d];
   const unsigned cb_grid = mgx_grid_for(n0, 256, ctx->num_sms * 4);
+  qo.qv = cf.dq;
+  if (lv.L == 0) {
+    if (SYM) {
+      k_coarse_box<T, false, true><<<cb_grid, 256, 0, ctx->stream>>>(dst, nullptr, g0,
+                                                                    qo);
+      ctx->launches++;
+    } else {
+      MGX_CUDA(cudaMemcpyAsync(dst, v, lv.N * sizeof(T), cudaMemcpyDeviceToDevice,
+                               ctx->stream));
+    }
+    return MGX_SUCCESS;
+  }
   int which = 0;
   T *A = (T *)s.A[which];
   k_coarse_box<T, false, true><<<cb_grid, 256, 0, ctx->stream>>>(
-      A, const_cast<T *>(v), g0, qo);
+      A, SYM ? nullptr : const_cast<T *>(v), g0, qo);
   ctx->launches++;
   for (int l = 1; l <= lv.L; l++) {
     LvGeom g = level_geom<T>(ctx, l, 32);
-    k_lpk_first<T><<<task_grid(g, 8), 256, 0, ctx->stream>>>(v, (T *)s.R[0], tables,
-                                                            g);
+    if (SYM)
+      cf.dq = (T)dq[l];
+    k_lpk_first<T, SYM><<<task_grid(g, 8), 256, 0, ctx->stream>>>(cf, (T *)s.R[0],
+                                                                 tables, g);
     ctx->launches++;
     rc = correction_tail<T>(ctx, l, (T *)s.R[0], (T *)s.R[1], A, -1);
     if (rc)
       return rc;
     T *out = (l == lv.L) ? dst : (T *)s.A[which ^ 1];
-    k_level_restore_rows<T><<<task_grid(g, 8), 256, 0, ctx->stream>>>(v, A, out,
-                                                                     tables, g);
+    k_level_restore_rows<T, SYM><<<task_grid(g, 8), 256, 0, ctx->stream>>>(
+        cf, A, out, tables, g);
     ctx->launches++;
     A = out;
     which ^= 1;
@@ -1592,6 +1649,25 @@ int mgxk_decompose_quantize_rows(mgx_ctx *ctx, const void *d_src, int rel,
 
 int mgxk_recompose_rows(mgx_ctx *ctx, const void *d_coeff, void *d_dst) {
   return mgx_is_f32(ctx)
-             ? recompose_rows<float>(ctx, (const float *)d_coeff, (float *)d_dst)
-             : recompose_rows<double>(ctx, (const double *)d_coeff, (double *)d_dst);
+             ? recompose_rows<float, false>(ctx, (const float *)d_coeff,
+                                            (float *)d_dst, nullptr)
+             : recompose_rows<double, false>(ctx, (const double *)d_coeff,
+                                             (double *)d_dst, nullptr);
+}
+
+// dequantise (no outliers) + recompose straight from the symbols in ctx->d_sym
+int mgxk_recompose_sym_rows(mgx_ctx *ctx, int rel, double tol, double s,
+                            double norm, void *d_dst) {
+  double q[MGX_MAX_L], vol[MGX_MAX_L], dq[MGX_MAX_L];
+  mgx_level_quantizers(ctx, rel, tol, s, norm, false, q, vol);
+  for (int l = 0; l <= ctx->lv.L; l++) {
+    // (quantizer * volume) rounded in T, as k_dequantize_sym forms it
+    if (mgx_is_f32(ctx))
+      dq[l] = (double)((float)q[l] * (float)vol[l]);
+    else
+      dq[l] = q[l] * vol[l];
+  }
+  return mgx_is_f32(ctx)
+             ? recompose_rows<float, true>(ctx, nullptr, (float *)d_dst, dq)
+             : recompose_rows<double, true>(ctx, nullptr, (double *)d_dst, dq);
 }

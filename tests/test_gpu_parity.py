@@ -276,7 +276,7 @@ ORTH_E2E = [((300, 77), np.float64, 0.0, 1, 1e-4), ((257, 513), np.float32, 1.0,
 
 
 @pytest.mark.parametrize("shape,dtype,s,rel,tol", ORTH_E2E)
-def test_fused_level_quantize_containers(shape, dtype, s, rel, tol):
+def test_fused_level_quantize_containers(shape, dtype, s, rel, tol, monkeypatch):
     """mgx_compress on the orthogonal path quantises inside the level kernel
     (no coefficient array exists): containers must still be byte-identical to
     the oracle's, and decode to the oracle's reconstruction."""
@@ -292,6 +292,13 @@ def test_fused_level_quantize_containers(shape, dtype, s, rel, tol):
     assert np.array_equal(np.delete(got, 7), np.delete(want, 7))
     dec = comp.Decompress(blob, eb, tol, s, norm).cpu().numpy()
     assert np.array_equal(dec, o.decompress(want, shape, dtype, rel, tol, s, norm))
+    # the decompress side reads the symbols directly when there are no outliers;
+    # the dequantise-to-floats route must give the same bits
+    monkeypatch.setenv("MGX_NO_SYM_RECOMPOSE", "1")
+    comp2, _ = make(shape, dtype)
+    monkeypatch.delenv("MGX_NO_SYM_RECOMPOSE")
+    dec2 = comp2.Decompress(blob, eb, tol, s, norm).cpu().numpy()
+    assert np.array_equal(dec2, dec)
 
 
 @pytest.mark.parametrize("shape,dtype", [((300, 77), np.float64), ((66, 33, 130), np.float32),
