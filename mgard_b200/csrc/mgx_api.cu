@@ -559,11 +559,26 @@ int mgx_decompress(mgx_ctx *ctx, const uint8_t *d_in, uint64_t bytes, int rel,
   rc = MGX_FAILURE + 101;
   if (!orth) // fused dequantise + recompose (hierarchical basis)
     rc = mgxk_hier_inverse(ctx, rel, tol, norm, d_out, oidx, oval, n_out);
-  if (rc == MGX_FAILURE + 101 && orth && !ctx->legacy_levels && n_out == 0 &&
+  if (rc == MGX_FAILURE + 101 && orth && !ctx->legacy_levels &&
       !ctx->no_sym_recompose) {
-    // no outliers: the level kernels dequantise the symbols on the fly
+    // the level kernels dequantise the symbols on the fly; only the coarse
+    // levels that hold outliers (their true codes are in the outlier list) are
+    // dequantised to floats first
+    int sym_from = 0;
+    rc = MGX_SUCCESS;
+    if (n_out) {
+      int lo = 0;
+      rc = mgxk_outlier_max_level(ctx, oidx, n_out, &lo);
+      if (!rc)
+        rc = mgx_ensure_workspaces(ctx, false, true);
+      if (!rc)
+        rc = mgxk_dequantize_box(ctx, lo, rel, tol, s, norm, ctx->d_v, oidx, oval,
+                                 n_out);
+      sym_from = lo + 1;
+    }
     mgx_tick(ctx, MGX_TICK_D_DEQUANT);
-    rc = mgxk_recompose_sym_rows(ctx, rel, tol, s, norm, d_out);
+    if (!rc)
+      rc = mgxk_recompose_sym_rows(ctx, rel, tol, s, norm, ctx->d_v, sym_from, d_out);
   } else if (rc == MGX_FAILURE + 101 && orth && !ctx->legacy_levels) {
     rc = mgx_ensure_workspaces(ctx, false, true);
     if (!rc)

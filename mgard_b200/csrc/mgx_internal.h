@@ -185,7 +185,16 @@ int mgxk_decompose_quantize_rows(mgx_ctx *ctx, const void *d_src, int rel,
                                  double tol, double s, double norm);
 int mgxk_recompose_rows(mgx_ctx *ctx, const void *d_coeff, void *d_dst);
 int mgxk_recompose_sym_rows(mgx_ctx *ctx, int rel, double tol, double s,
-                            double norm, void *d_dst);
+                            double norm, const void *d_coeff, int sym_from,
+                            void *d_dst);
+// dequantise only the level-`level` box [0, n_level)^D (+ all outliers, which the
+// caller knows to lie inside it) into d_coeff; *max_level = highest level that
+// holds an outlier (mgxk_outlier_max_level)
+int mgxk_outlier_max_level(mgx_ctx *ctx, const uint64_t *d_oidx, uint64_t n_out,
+                           int *max_level);
+int mgxk_dequantize_box(mgx_ctx *ctx, int level, int rel, double tol, double s,
+                        double norm, void *d_coeff, const uint64_t *d_oidx,
+                        const int64_t *d_oval, uint64_t n_out);
 // per-level quantiser (reciprocal for quantise) and volume factor, as doubles
 // holding the T-precision values (CalcQuantizers, LinearQuantization.hpp:234-297)
 void mgx_level_quantizers(const mgx_ctx *ctx, int rel, double tol, double s,

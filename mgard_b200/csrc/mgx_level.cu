@@ -1561,10 +1561,13 @@ int decompose_rows(mgx_ctx *ctx, const T *src, T *v, const double *q,
 }
 
 // recompose: coefficients v (reordered, read only) -> dst (full array), dst != v
-// recompose: coefficients (v, reordered, read only -- or, SYM, the symbols in
-// ctx->d_sym with per-level dequantisers dq[]) -> dst (full array), dst != v
-template <typename T, bool SYM>
-int recompose_rows(mgx_ctx *ctx, const T *v, T *dst, const double *dq) {
+// recompose: coefficients -> dst (full array), dst != v.  Levels below
+// `sym_from` read the float coefficients in v (reordered, read only); levels
+// from `sym_from` on read the symbols in ctx->d_sym and dequantise them on the
+// fly with dq[l] (sym_from = L + 1: floats only; 0: symbols only).
+template <typename T>
+int recompose_rows(mgx_ctx *ctx, const T *v, T *dst, const double *dq,
+                   int sym_from) {
   Scratch s;
   int rc = get_scratch(ctx, &s);
   if (rc)
@@ -1573,11 +1576,16 @@ int recompose_rows(mgx_ctx *ctx, const T *v, T *dst, const double *dq) {
   const T *tables = (const T *)ctx->d_tables;
   QuantOut<T> qo;
   fill_quant<T>(ctx, &qo, nullptr, nullptr, 0);
-  Coef<T, SYM> cf;
+  Coef<T, true> cs;
+  cs.v = nullptr;
+  cs.sym = ctx->d_sym;
+  cs.shift = (int)(ctx->dict / 2);
+  cs.dq = (T)0;
+  Coef<T, false> cf;
   cf.v = v;
-  cf.sym = ctx->d_sym;
-  cf.shift = (int)(ctx->dict / 2);
-  cf.dq = SYM ? (T)dq[0] : (T)0;
+  cf.sym = nullptr;
+  cf.shift = 0;
+  cf.dq = (T)0;
   LvGeom g0;
   for (int d = 0; d < MGX_MAX_D; d++) {
     g0.nc[d] = (uint32_t)lv.n[0][d];
@@ -1587,9 +1595,11 @@ int recompose_rows(mgx_ctx *ctx, const T *v, T *dst, const double *dq) {
   for (int d = 0; d < MGX_MAX_D; d++)
     n0 *= lv.n[0][d];
   const unsigned cb_grid = mgx_grid_for(n0, 256, ctx->num_sms * 4);
-  qo.qv = cf.dq;
+  const bool sym0 = sym_from <= 0;
+  if (sym0)
+    qo.qv = (T)dq[0];
   if (lv.L == 0) {
-    if (SYM) {
+    if (sym0) {
       k_coarse_box<T, false, true><<<cb_grid, 256, 0, ctx->stream>>>(dst, nullptr, g0,
                                                                     qo);
       ctx->launches++;
@@ -1602,21 +1612,30 @@ int recompose_rows(mgx_ctx *ctx, const T *v, T *dst, const double *dq) {
   int which = 0;
   T *A = (T *)s.A[which];
   k_coarse_box<T, false, true><<<cb_grid, 256, 0, ctx->stream>>>(
-      A, SYM ? nullptr : const_cast<T *>(v), g0, qo);
+      A, sym0 ? nullptr : const_cast<T *>(v), g0, qo);
   ctx->launches++;
   for (int l = 1; l <= lv.L; l++) {
     LvGeom g = level_geom<T>(ctx, l, 32);
-    if (SYM)
-      cf.dq = (T)dq[l];
-    k_lpk_first<T, SYM><<<task_grid(g, 8), 256, 0, ctx->stream>>>(cf, (T *)s.R[0],
-                                                                 tables, g);
+    const bool use_sym = l >= sym_from;
+    if (use_sym) {
+      cs.dq = (T)dq[l];
+      k_lpk_first<T, true><<<task_grid(g, 8), 256, 0, ctx->stream>>>(cs, (T *)s.R[0],
+                                                                    tables, g);
+    } else {
+      k_lpk_first<T, false><<<task_grid(g, 8), 256, 0, ctx->stream>>>(
+          cf, (T *)s.R[0], tables, g);
+    }
     ctx->launches++;
     rc = correction_tail<T>(ctx, l, (T *)s.R[0], (T *)s.R[1], A, -1);
     if (rc)
       return rc;
     T *out = (l == lv.L) ? dst : (T *)s.A[which ^ 1];
-    k_level_restore_rows<T, SYM><<<task_grid(g, 8), 256, 0, ctx->stream>>>(
-        cf, A, out, tables, g);
+    if (use_sym)
+      k_level_restore_rows<T, true><<<task_grid(g, 8), 256, 0, ctx->stream>>>(
+          cs, A, out, tables, g);
+    else
+      k_level_restore_rows<T, false><<<task_grid(g, 8), 256, 0, ctx->stream>>>(
+          cf, A, out, tables, g);
     ctx->launches++;
     A = out;
     which ^= 1;
@@ -1648,16 +1667,20 @@ int mgxk_decompose_quantize_rows(mgx_ctx *ctx, const void *d_src, int rel,
 }
 
 int mgxk_recompose_rows(mgx_ctx *ctx, const void *d_coeff, void *d_dst) {
+  const int never = ctx->lv.L + 1;
   return mgx_is_f32(ctx)
-             ? recompose_rows<float, false>(ctx, (const float *)d_coeff,
-                                            (float *)d_dst, nullptr)
-             : recompose_rows<double, false>(ctx, (const double *)d_coeff,
-                                             (double *)d_dst, nullptr);
+             ? recompose_rows<float>(ctx, (const float *)d_coeff, (float *)d_dst,
+                                     nullptr, never)
+             : recompose_rows<double>(ctx, (const double *)d_coeff, (double *)d_dst,
+                                      nullptr, never);
 }
 
-// dequantise (no outliers) + recompose straight from the symbols in ctx->d_sym
+// dequantise + recompose from the symbols in ctx->d_sym; levels below
+// `sym_from` (the ones holding outliers) are read from the float coefficients
+// the caller dequantised into d_coeff
 int mgxk_recompose_sym_rows(mgx_ctx *ctx, int rel, double tol, double s,
-                            double norm, void *d_dst) {
+                            double norm, const void *d_coeff, int sym_from,
+                            void *d_dst) {
   double q[MGX_MAX_L], vol[MGX_MAX_L], dq[MGX_MAX_L];
   mgx_level_quantizers(ctx, rel, tol, s, norm, false, q, vol);
   for (int l = 0; l <= ctx->lv.L; l++) {
@@ -1668,6 +1691,8 @@ int mgxk_recompose_sym_rows(mgx_ctx *ctx, int rel, double tol, double s,
       dq[l] = q[l] * vol[l];
   }
   return mgx_is_f32(ctx)
-             ? recompose_rows<float, true>(ctx, nullptr, (float *)d_dst, dq)
-             : recompose_rows<double, true>(ctx, nullptr, (double *)d_dst, dq);
+             ? recompose_rows<float>(ctx, (const float *)d_coeff, (float *)d_dst, dq,
+                                     sym_from)
+             : recompose_rows<double>(ctx, (const double *)d_coeff, (double *)d_dst,
+                                      dq, sym_from);
 }

@@ -297,6 +297,66 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+// level marks regardless of the norm type (node_level() skips them for L-inf)
+template <typename T>
+__device__ __forceinline__ int node_level_always(const QuantArgs<T> &a, uint64_t it) {
+  int level = 0;
+  uint64_t r = it;
+#pragma unroll
+  for (int d = MGX_MAX_D - 1; d >= 0; d--) {
+    uint32_t p = (uint32_t)(r % a.shape[d]);
+    r /= a.shape[d];
+    int m = 0;
+    while (m < a.L && p >= a.n[m][d])
+      m++;
+    level = max(level, m);
+  }
+  return level;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+    k_outlier_max_level(const unsigned long long *__restrict__ idx, uint64_t n_out,
+                        const __grid_constant__ QuantArgs<T> a,
+                        unsigned long long *out) {
+  int lv = 0;
+  for (uint64_t j = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; j < n_out;
+       j += (uint64_t)gridDim.x * blockDim.x)
+    lv = max(lv, node_level_always(a, idx[j]));
+  for (int o = 16; o > 0; o >>= 1)
+    lv = max(lv, __shfl_xor_sync(0xffffffffu, lv, o));
+  if ((threadIdx.x & 31) == 0 && lv > 0)
+    atomicMax(out, (unsigned long long)lv);
+}
+
+// dequantise the box [0, n[level][d]) of the reordered array only
+template <typename T>
+__global__ void __launch_bounds__(256)
+    k_dequantize_sym_box(const uint16_t *__restrict__ sym, T *__restrict__ c,
+                         const __grid_constant__ QuantArgs<T> a, int level,
+                         uint64_t total) {
+  for (uint64_t it = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; it < total;
+       it += (uint64_t)gridDim.x * blockDim.x) {
+    uint64_t r = it, o = 0, st = 1;
+    int lvl = 0;
+#pragma unroll
+    for (int d = MGX_MAX_D - 1; d >= 0; d--) {
+      const uint32_t p = (uint32_t)(r % a.n[level][d]);
+      r /= a.n[level][d];
+      o += (uint64_t)p * st;
+      st *= a.shape[d];
+      int m = 0;
+      while (m < a.L && p >= a.n[m][d])
+        m++;
+      lvl = max(lvl, m);
+    }
+    if (!a.calc_vol)
+      lvl = 0;
+    long long q = (long long)sym[o] - a.shift;
+    c[o] = mul_rn(mul_rn(a.q[lvl], a.vol[lvl]), (T)q);
+  }
+}
+
 } // namespace
 
 void mgx_level_quantizers(const mgx_ctx *ctx, int rel, double tol, double s,
@@ -439,5 +499,61 @@ int mgxk_dequantize_sym_out(mgx_ctx *ctx, int rel, double tol, double s,
   return mgx_is_f32(ctx) ? dequantize_sym_t<float>(ctx, rel, tol, s, norm, d_coeff,
                                                    d_oidx, d_oval, n_out)
                          : dequantize_sym_t<double>(ctx, rel, tol, s, norm,
+                                                    d_coeff, d_oidx, d_oval, n_out);
+}
+
+template <typename T>
+static int outlier_max_level_t(mgx_ctx *ctx, const uint64_t *d_oidx, uint64_t n_out,
+                               int *max_level) {
+  QuantArgs<T> a;
+  fill_quant_args<T>(ctx, &a, 0, 1.0, 0.0, 1.0, false);
+  unsigned long long *out = (unsigned long long *)(ctx->d_scalars + MGX_SC_NZ);
+  MGX_CUDA(cudaMemsetAsync(out, 0, 8, ctx->stream));
+  k_outlier_max_level<T><<<mgx_grid_for(n_out, 256, ctx->num_sms * 4), 256, 0,
+                           ctx->stream>>>((const unsigned long long *)d_oidx, n_out,
+                                          a, out);
+  ctx->launches++;
+  MGX_CUDA(cudaMemcpyAsync(&ctx->h_scalars[MGX_SC_NZ], out, 8, cudaMemcpyDeviceToHost,
+                           ctx->stream));
+  MGX_CUDA(cudaStreamSynchronize(ctx->stream));
+  *max_level = (int)ctx->h_scalars[MGX_SC_NZ];
+  return MGX_SUCCESS;
+}
+
+int mgxk_outlier_max_level(mgx_ctx *ctx, const uint64_t *d_oidx, uint64_t n_out,
+                           int *max_level) {
+  return mgx_is_f32(ctx) ? outlier_max_level_t<float>(ctx, d_oidx, n_out, max_level)
+                         : outlier_max_level_t<double>(ctx, d_oidx, n_out, max_level);
+}
+
+template <typename T>
+static int dequantize_box_t(mgx_ctx *ctx, int level, int rel, double tol, double s,
+                            double norm, void *d_coeff, const uint64_t *d_oidx,
+                            const int64_t *d_oval, uint64_t n_out) {
+  QuantArgs<T> a;
+  fill_quant_args<T>(ctx, &a, rel, tol, s, norm, false);
+  uint64_t total = 1;
+  for (int d = 0; d < MGX_MAX_D; d++)
+    total *= ctx->lv.n[level][d];
+  k_dequantize_sym_box<T><<<mgx_grid_for(total, 256, ctx->num_sms * 8), 256, 0,
+                            ctx->stream>>>(ctx->d_sym, (T *)d_coeff, a, level, total);
+  ctx->launches++;
+  if (n_out) {
+    k_dequantize_outliers<T><<<mgx_grid_for(n_out, 256, ctx->num_sms * 4), 256, 0,
+                               ctx->stream>>>((const unsigned long long *)d_oidx,
+                                              (const long long *)d_oval, n_out,
+                                              (T *)d_coeff, a);
+    ctx->launches++;
+  }
+  MGX_CUDA(cudaGetLastError());
+  return MGX_SUCCESS;
+}
+
+int mgxk_dequantize_box(mgx_ctx *ctx, int level, int rel, double tol, double s,
+                        double norm, void *d_coeff, const uint64_t *d_oidx,
+                        const int64_t *d_oval, uint64_t n_out) {
+  return mgx_is_f32(ctx) ? dequantize_box_t<float>(ctx, level, rel, tol, s, norm,
+                                                   d_coeff, d_oidx, d_oval, n_out)
+                         : dequantize_box_t<double>(ctx, level, rel, tol, s, norm,
                                                     d_coeff, d_oidx, d_oval, n_out);
 }
