@@ -479,8 +479,6 @@ __global__ void __launch_bounds__((ENC_WARPS + 1) * 32, 3)
   __shared__ uint32_t s_arrived[ENC_SLOTS];
   __shared__ u64 s_prefix[ENC_SLOTS];
   __shared__ uint32_t s_epoch[ENC_SLOTS];
-  __shared__ uint32_t s_tile[ENC_SLOTS];   // tile taken for iteration it (ticket)
-  __shared__ uint32_t s_tepoch[ENC_SLOTS]; // == it + 1 once s_tile is posted
   for (uint32_t i = threadIdx.x; i < dict; i += blockDim.x) {
     const u64 cw = codebook[i];
     s_tab[i] = (uint32_t)(cw >> 56) << 26 | (uint32_t)(cw & 0x3ffffffu);
@@ -488,40 +486,17 @@ __global__ void __launch_bounds__((ENC_WARPS + 1) * 32, 3)
   if (threadIdx.x < ENC_SLOTS) {
     s_arrived[threadIdx.x] = 0;
     s_epoch[threadIdx.x] = 0;
-    s_tepoch[threadIdx.x] = 0;
   }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   volatile u64 *vs = state;
   volatile uint32_t *v_arrived = s_arrived, *v_epoch = s_epoch;
   volatile u64 *v_prefix = s_prefix;
-  volatile uint32_t *v_tile = s_tile, *v_tepoch = s_tepoch;
-  // Tiles are handed out by a global ticket, in the order CTAs ask for them
-  // (not round-robin): a tile's predecessors were then all claimed earlier by
-  // running CTAs, and a CTA that falls behind does not sit on low-numbered
-  // tiles everybody else's look-back is waiting for.  The scanner warp draws
-  // the tickets two iterations ahead and posts them in shared memory.
-  unsigned long long *ticket = (unsigned long long *)&scalars[MGX_SC_TICKET];
-  auto post = [&](uint32_t it, unsigned long long t) {
-    v_tile[it & (ENC_SLOTS - 1)] = (uint32_t)min(t, (unsigned long long)ntiles);
-    __threadfence_block();
-    v_tepoch[it & (ENC_SLOTS - 1)] = it + 1;
-  };
 
   if (warp == ENC_WARPS) { // ---- scanner ----------------------------------------
-    if (lane == 0) {
-      post(0, atomicAdd(ticket, 1ull));
-      post(1, atomicAdd(ticket, 1ull));
-    }
-    __syncwarp();
-    for (uint32_t iter = 0;; ++iter) {
+    uint32_t iter = 0;
+    for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++iter) {
       const int slot = iter & (ENC_SLOTS - 1);
-      const uint64_t tile = v_tile[slot];
-      if (tile >= ntiles)
-        break;
-      unsigned long long t_next = 0;
-      if (lane == 0)
-        t_next = atomicAdd(ticket, 1ull); // consumed at the end of the iteration
       while (v_arrived[slot] != ENC_WARPS)
         __nanosleep(40); // leave the issue slots to the packers
       __threadfence_block();
@@ -565,7 +540,6 @@ __global__ void __launch_bounds__((ENC_WARPS + 1) * 32, 3)
         v_arrived[slot] = 0;
         __threadfence_block();
         v_epoch[slot] = iter + 1;
-        post(iter + 2, t_next);
       }
       __syncwarp();
     }
@@ -595,14 +569,8 @@ __global__ void __launch_bounds__((ENC_WARPS + 1) * 32, 3)
   bool pend = false; // a packed tile waits in the other image
   uint64_t pend_c = 0;
   uint32_t pend_words = 0;
-  for (;; ++iter) {
+  for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++iter) {
     const int slot = iter & (ENC_SLOTS - 1);
-    while (v_tepoch[slot] != iter + 1)
-      ;
-    __threadfence_block();
-    const uint64_t tile = v_tile[slot];
-    if (tile >= ntiles)
-      break;
     uint32_t *img = s_img + ((iter & 1) * ENC_WARPS + warp) * UNITS;
     const uint64_t c = tile * ENC_WARPS + warp;
     const bool have = c < nchunk;
