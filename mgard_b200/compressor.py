@@ -85,6 +85,10 @@ class Compressor:
         self.config = config or hierarchy.config
         self.device = torch.device("cuda", self.config.dev_id)
         self._ctx = ctypes.c_void_p()
+        # without a caller stream the context runs on its own non-blocking
+        # stream: inputs produced on torch's stream must be complete before a
+        # call (the calls themselves are synchronous at return)
+        self._own_stream = stream is None
         sptr = ctypes.c_void_p(stream.cuda_stream) if stream is not None else None
         self._check(self.lib.mgx_create(ctypes.byref(self._ctx),
                                         self.config.dev_id, sptr), ctx=False)
@@ -120,12 +124,17 @@ class Compressor:
         self.tdtype = (torch.float32 if hierarchy.dtype_code == 0
                        else torch.float64)
 
+    def _sync_inputs(self):
+        if self._own_stream:
+            torch.cuda.current_stream(self.device).synchronize()
+
     def _dev(self, t, dtype=None):
         t = t.to(self.device)
         if dtype is not None and t.dtype != dtype:
             raise MgardError(4, "dtype mismatch")
         if not t.is_contiguous():
             t = t.contiguous()
+        self._sync_inputs()
         return t
 
     def levels(self):
@@ -183,12 +192,14 @@ class Compressor:
     def Decompose(self, data, orthogonal_projection):
         """in place on a device tensor (reordered level-blocked layout)."""
         assert data.is_cuda and data.is_contiguous() and data.dtype == self.tdtype
+        self._sync_inputs()
         self._check(self.lib.mgx_decompose(self._ctx, data.data_ptr(),
                                            int(bool(orthogonal_projection))))
         return data
 
     def Recompose(self, data, orthogonal_projection):
         assert data.is_cuda and data.is_contiguous() and data.dtype == self.tdtype
+        self._sync_inputs()
         self._check(self.lib.mgx_recompose(self._ctx, data.data_ptr(),
                                            int(bool(orthogonal_projection))))
         return data

@@ -128,7 +128,8 @@ int mgx_create(mgx_ctx **out, int device, void *cuda_stream) {
     }
     ctx->own_stream = true;
   }
-  if (cudaMalloc(&ctx->d_scalars, MGX_SC_COUNT * 8) != cudaSuccess ||
+  if (cudaMalloc(&ctx->d_norm_part, 1024 * 8) != cudaSuccess ||
+      cudaMalloc(&ctx->d_scalars, MGX_SC_COUNT * 8) != cudaSuccess ||
       cudaMallocHost(&ctx->h_scalars, MGX_SC_COUNT * 8) != cudaSuccess) {
     delete ctx;
     return MGX_FAILURE;
@@ -147,6 +148,7 @@ void mgx_destroy(mgx_ctx *ctx) {
       cudaEventDestroy(ctx->ev[i]);
   release_plan(ctx);
   free_dev(ctx->d_scalars);
+  free_dev(ctx->d_norm_part);
   free_dev(ctx->d_sort_tmp);
   free_dev(ctx->d_stage_in);
   free_dev(ctx->d_stage_out);

@@ -83,6 +83,7 @@ struct mgx_ctx {
   uint64_t out_cap = 0;
   uint64_t *d_scalars = nullptr;    // small device scalars (see MGX_SC_*)
   uint64_t *h_scalars = nullptr;    // pinned mirror
+  double *d_norm_part = nullptr;    // per-block partial sums of the norm (1024)
   void *d_lut = nullptr;            // decode look-up table
   void *d_coarse0 = nullptr, *d_coarse1 = nullptr; // fused inverse: coarse lattice
   size_t coarse_bytes = 0;

@@ -20,7 +20,8 @@ namespace {
 // the non-negative double ordering equals the uint64 ordering).
 template <typename T, bool LINF>
 __global__ void __launch_bounds__(512)
-    k_norm(const T *__restrict__ v, uint64_t n, unsigned long long *out) {
+    k_norm(const T *__restrict__ v, uint64_t n, unsigned long long *out,
+           double *__restrict__ block_part) {
   // 16-byte loads, four in flight per thread; |max| of floats is exact in T,
   // sums of squares accumulate in double
   constexpr int VEC = 16 / sizeof(T);
@@ -80,9 +81,26 @@ __global__ void __launch_bounds__(512)
       if (LINF)
         atomicMax(out, (unsigned long long)__double_as_longlong(acc));
       else
-        atomicAdd((double *)out, acc);
+        block_part[blockIdx.x] = acc; // summed in a fixed order by k_norm_final
+
     }
   }
+}
+
+// sum of the per-block partial sums in a fixed order: the L2 / s-norm comes out
+// bit-identical from run to run (atomicAdd of doubles would not)
+__global__ void __launch_bounds__(1024)
+    k_norm_final(const double *__restrict__ part, int n, double *out) {
+  __shared__ double s[1024];
+  s[threadIdx.x] = (int)threadIdx.x < n ? part[threadIdx.x] : 0.0;
+  __syncthreads();
+  for (int o = 512; o > 0; o >>= 1) {
+    if ((int)threadIdx.x < o)
+      s[threadIdx.x] += s[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0)
+    *out = s[0];
 }
 
 // ---- quantiser tables ---------------------------------------------------------
@@ -383,19 +401,28 @@ int mgxk_norm_partial(mgx_ctx *ctx, const void *d_in, int linf) {
       (unsigned long long *)(ctx->d_scalars + MGX_SC_NORM);
   MGX_CUDA(cudaMemsetAsync(out, 0, 8, ctx->stream));
   uint64_t n = ctx->lv.N;
-  unsigned grid = mgx_grid_for(n, 512 * 8, ctx->num_sms * 4);
+  unsigned grid = mgx_grid_for(n, 512 * 8, std::min(ctx->num_sms * 4, 1024));
+  double *part = ctx->d_norm_part;
   if (mgx_is_f32(ctx)) {
     if (linf)
-      k_norm<float, true><<<grid, 512, 0, ctx->stream>>>((const float *)d_in, n, out);
+      k_norm<float, true><<<grid, 512, 0, ctx->stream>>>((const float *)d_in, n, out,
+                                                        part);
     else
-      k_norm<float, false><<<grid, 512, 0, ctx->stream>>>((const float *)d_in, n, out);
+      k_norm<float, false><<<grid, 512, 0, ctx->stream>>>((const float *)d_in, n, out,
+                                                         part);
   } else {
     if (linf)
-      k_norm<double, true><<<grid, 512, 0, ctx->stream>>>((const double *)d_in, n, out);
+      k_norm<double, true><<<grid, 512, 0, ctx->stream>>>((const double *)d_in, n, out,
+                                                         part);
     else
-      k_norm<double, false><<<grid, 512, 0, ctx->stream>>>((const double *)d_in, n, out);
+      k_norm<double, false><<<grid, 512, 0, ctx->stream>>>((const double *)d_in, n,
+                                                          out, part);
   }
   ctx->launches++;
+  if (!linf) {
+    k_norm_final<<<1, 1024, 0, ctx->stream>>>(part, (int)grid, (double *)out);
+    ctx->launches++;
+  }
   MGX_CUDA(cudaGetLastError());
   return MGX_SUCCESS;
 }
