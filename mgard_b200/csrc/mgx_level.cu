@@ -490,7 +490,7 @@ __global__ void __launch_bounds__(256)
 // out: (outer, nc, inner) compact.  A block owns one output index i along the
 // dimension (its nine quotients are formed once) and streams (outer, inner).
 // (Lpk2Reo3D / Lpk3Reo3D, LinearProcessingKernel3D.hpp:374-1097)
-template <typename T>
+template <typename T, int U>
 __global__ void __launch_bounds__(256)
     k_lpk_mid(const T *__restrict__ in, T *__restrict__ out,
               const T *__restrict__ dist, uint32_t outer, uint32_t nf, uint32_t nc,
@@ -500,17 +500,26 @@ __global__ void __launch_bounds__(256)
   const MassK<T> mk = mass_consts<T>(dist, 2 * (int64_t)i, nf);
   const bool ha = i >= 1, hb = i >= 1 && i - 1 < ncoef, hd = i < ncoef,
              he = i + 1 < nc;
-  for (uint32_t o = blockIdx.z; o < outer; o += gridDim.z) {
-    const T *ib = in + (uint64_t)o * nf * inner;
-    T *ob = out + ((uint64_t)o * nc + i) * inner;
+  // U `outer` slices per iteration: 5 U independent loads in flight per thread
+  for (uint32_t o0 = blockIdx.z * U; o0 < outer; o0 += gridDim.z * U) {
     for (uint64_t x = (uint64_t)blockIdx.y * blockDim.x + threadIdx.x; x < inner;
          x += (uint64_t)gridDim.y * blockDim.x) {
-      T a = ha ? ib[(uint64_t)(i - 1) * inner + x] : (T)0;
-      T b = hb ? ib[(uint64_t)(nc + i - 1) * inner + x] : (T)0;
-      T c = ib[(uint64_t)i * inner + x];
-      T d = hd ? ib[(uint64_t)(nc + i) * inner + x] : (T)0;
-      T e = he ? ib[(uint64_t)(i + 1) * inner + x] : (T)0;
-      ob[x] = mass_apply(mk, a, b, c, d, e);
+      T a[U], b[U], c[U], d[U], e[U];
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        const uint32_t o = min(o0 + u, outer - 1);
+        const T *ib = in + (uint64_t)o * nf * inner + x;
+        a[u] = ha ? ib[(uint64_t)(i - 1) * inner] : (T)0;
+        b[u] = hb ? ib[(uint64_t)(nc + i - 1) * inner] : (T)0;
+        c[u] = ib[(uint64_t)i * inner];
+        d[u] = hd ? ib[(uint64_t)(nc + i) * inner] : (T)0;
+        e[u] = he ? ib[(uint64_t)(i + 1) * inner] : (T)0;
+      }
+#pragma unroll
+      for (int u = 0; u < U; u++)
+        if (o0 + u < outer)
+          out[((uint64_t)(o0 + u) * nc + i) * inner + x] =
+              mass_apply(mk, a[u], b[u], c[u], d[u], e[u]);
     }
   }
 }
@@ -1398,9 +1407,16 @@ int correction_tail(mgx_ctx *ctx, int l, T *R0, T *R1, T *A, int sign) {
     const uint32_t nf = (uint32_t)lv.n[l][d], nc = (uint32_t)lv.n[l - 1][d];
     unsigned gy = (unsigned)std::min<uint64_t>((inner + 255) / 256, 65535);
     uint64_t want_z = std::max<uint64_t>(1, (uint64_t)ctx->num_sms * 8 / ((uint64_t)nc * gy));
-    unsigned gz = (unsigned)std::min<uint64_t>(std::min<uint64_t>(outer, want_z), 65535);
-    k_lpk_mid<T><<<dim3(nc, gy, gz), 256, 0, ctx->stream>>>(
-        in, out, tables + off.dist[l][d], (uint32_t)outer, nf, nc, inner);
+    if (outer >= 4) {
+      unsigned gz = (unsigned)std::min<uint64_t>(
+          std::min<uint64_t>((outer + 3) / 4, want_z), 65535);
+      k_lpk_mid<T, 4><<<dim3(nc, gy, gz), 256, 0, ctx->stream>>>(
+          in, out, tables + off.dist[l][d], (uint32_t)outer, nf, nc, inner);
+    } else {
+      unsigned gz = (unsigned)std::min<uint64_t>(std::min<uint64_t>(outer, want_z), 65535);
+      k_lpk_mid<T, 1><<<dim3(nc, gy, gz), 256, 0, ctx->stream>>>(
+          in, out, tables + off.dist[l][d], (uint32_t)outer, nf, nc, inner);
+    }
     ctx->launches++;
     cur[d] = nc;
     std::swap(in, out);
