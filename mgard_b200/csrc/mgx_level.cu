@@ -213,6 +213,29 @@ __device__ __forceinline__ void corners(const T *__restrict__ base, int64_t off,
   }
 }
 
+// Forward variant, called by ALL lanes of the warp: a lane loads only its even
+// column; the even column to the right of its odd one is the next lane's even
+// column and arrives by shuffle (lane 31 is a halo pair whose odd column is
+// never used).  Halves the neighbour-row loads.  (The same trick on the
+// inverse kernel, which has no halo lanes, measured slightly slower.)
+template <typename T, int K>
+__device__ __forceinline__ void corners_fw(const T *__restrict__ base, int64_t off,
+                                           const Row<T> &r, uint32_t e0, T tf, T &a,
+                                           T &b) {
+  if constexpr (K == 0) {
+    const T x0 = base[off + e0];
+    const T x1 = __shfl_down_sync(0xffffffffu, x0, 1);
+    a = x0;
+    b = mgx_lerp(x0, x1, tf);
+  } else {
+    T a0, b0, a1, b1;
+    corners_fw<T, K - 1>(base, off - r.hi[K - 1], r, e0, tf, a0, b0);
+    corners_fw<T, K - 1>(base, off + r.hi[K - 1], r, e0, tf, a1, b1);
+    a = mgx_lerp(a0, a1, r.tt[K - 1]);
+    b = mgx_lerp(b0, b1, r.tt[K - 1]);
+  }
+}
+
 // L2 -> L1 prefetch of what the NEXT row will load (the row loop is one
 // dependent load -> compute -> store chain per warp; without this every row
 // pays a full memory latency)
@@ -301,21 +324,24 @@ __device__ __forceinline__ void forward_row(
     uint32_t *s_hist, const MassK<T> &mk, int64_t i, bool pair_ok, bool has_odd,
     bool owned, uint32_t qe, T tf, uint64_t row) {
   const uint32_t ncf = g.nc[FD];
+  // every lane loads (lanes without a pair read column 0 and are ignored), so
+  // that the shuffles below are warp-wide
   T ce = 0, co = 0;
-  if (pair_ok) {
+  {
     const T *srow = src + r.so;
-    T ve = srow[qe];
-    T vo = has_odd ? srow[2 * i + 1] : (T)0;
+    const T ve = srow[qe];
+    const T vo = has_odd ? srow[2 * i + 1] : (T)0;
     if constexpr (K == 0) {
-      if (owned)
+      const T e2 = __shfl_down_sync(0xffffffffu, ve, 1); // node 2i + 2
+      if (owned && pair_ok)
         A[r.ao + i] = ve; // coarse node of the next level
       if (has_odd)
-        co = sub_rn(vo, mgx_lerp(ve, srow[2 * i + 2], tf));
+        co = sub_rn(vo, mgx_lerp(ve, e2, tf));
     } else {
       T a, b;
-      corners<T, K, true>(src, (int64_t)r.so, r, qe, (uint32_t)(2 * i + 2), has_odd,
-                          tf, a, b);
-      ce = sub_rn(ve, a);
+      corners_fw<T, K>(src, (int64_t)r.so, r, qe, tf, a, b);
+      if (pair_ok)
+        ce = sub_rn(ve, a);
       if (has_odd)
         co = sub_rn(vo, b);
     }
