@@ -5,10 +5,10 @@ mkdir -p gpurun_out
 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err || exit 1
 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_reference.json 2>> gpurun_out/bench.err
 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:^k_ -c 400 --csv \
-    --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 1 --no-cpu --no-e2e > gpurun_out/ncu.log 2>&1
+    --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 1 --no-cpu --no-e2e --no-extra > gpurun_out/ncu.log 2>&1
 for k in k_norm k_hier_forward k_codebook k_encode k_decode_multi k_hier_inverse3d; do
   ncu --set full --import-source on --clock-control none -k regex:$k -c 1 -f -o gpurun_out/full_$k \
-      python bench.py --steps 1 --warmup 0 --no-cpu --no-e2e >> gpurun_out/ncu.log 2>&1
+      python bench.py --steps 1 --warmup 0 --no-cpu --no-e2e --no-extra >> gpurun_out/ncu.log 2>&1
 done
 for k in k_level_forward k_lpk_mid k_ipk_contig_ws k_ipk_strided_ws k_level_restore_rows; do
   ncu --set full --import-source on --clock-control none -k regex:$k -c 1 -f -o gpurun_out/full_cfg2_$k \
