@@ -333,7 +333,8 @@ __global__ void __launch_bounds__(ENC_WARPS * 32)
 //    is then streamed to its final place in the container.  A chunk whose image
 //    would not fit (more than ENC_CAP_BITS bits per symbol on average) is
 //    packed straight into global memory instead.
-constexpr int ENC_CAP_BITS = 16;
+constexpr int ENC_CAP_BITS = 10; // image capacity, bits per symbol on average
+constexpr int ENC_IMGS = 3;      // images per packer warp: packers run 2 tiles ahead
 constexpr u64 CODE_MASK = 0x00ffffffffffffffull;
 
 struct BitSink {
@@ -461,7 +462,7 @@ pack_merged(uint32_t *dst, const uint4 (&v)[R], const int (&cnt)[R],
 // they stream tile i-1 out of its shared-memory image after packing tile i, so
 // the latency of the look-back chain (which couples all resident CTAs) is
 // hidden behind a full tile of work.
-constexpr int ENC_SLOTS = 4;
+constexpr int ENC_SLOTS = 8;
 
 template <int R>
 __global__ void __launch_bounds__((ENC_WARPS + 1) * 32, 3)
@@ -473,8 +474,8 @@ __global__ void __launch_bounds__((ENC_WARPS + 1) * 32, 3)
   constexpr int CHUNK = 256 * R;
   constexpr int UNITS = CHUNK * ENC_CAP_BITS / 32; // per-warp image, u32 units
   extern __shared__ __align__(16) unsigned char enc_smem[];
-  uint32_t *s_img = (uint32_t *)enc_smem;           // [2][ENC_WARPS][UNITS]
-  uint32_t *s_tab = s_img + 2 * ENC_WARPS * UNITS;  // dict entries
+  uint32_t *s_img = (uint32_t *)enc_smem;                  // [ENC_IMGS][ENC_WARPS][UNITS]
+  uint32_t *s_tab = s_img + ENC_IMGS * ENC_WARPS * UNITS;  // dict entries
   __shared__ uint32_t s_words[ENC_SLOTS][ENC_WARPS];
   __shared__ uint32_t s_arrived[ENC_SLOTS];
   __shared__ u64 s_prefix[ENC_SLOTS];
@@ -566,12 +567,24 @@ __global__ void __launch_bounds__((ENC_WARPS + 1) * 32, 3)
     return off;
   };
   uint32_t iter = 0;
-  bool pend = false; // a packed tile waits in the other image
-  uint64_t pend_c = 0;
-  uint32_t pend_words = 0;
+  // packed tiles waiting in their images for the scan: A = tile iter - 2,
+  // B = tile iter - 1.  Two tiles of slack absorb the skew between CTAs (the
+  // prefix of a tile exists only when every earlier tile has been counted).
+  bool pendA = false, pendB = false;
+  uint64_t cA = 0, cB = 0;
+  uint32_t wA = 0, wB = 0, itA = 0, itB = 0;
+  auto drain = [&](uint32_t it, uint64_t c, uint32_t words) {
+    const u64 off = finish(it, c, words);
+    if (off != ~0ull) {
+      const u64 *src =
+          (const u64 *)(s_img + ((it % ENC_IMGS) * ENC_WARPS + warp) * UNITS);
+      for (uint32_t i = lane; i < words; i += 32)
+        packed[off + i] = src[i];
+    }
+  };
   for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++iter) {
     const int slot = iter & (ENC_SLOTS - 1);
-    uint32_t *img = s_img + ((iter & 1) * ENC_WARPS + warp) * UNITS;
+    uint32_t *img = s_img + ((iter % ENC_IMGS) * ENC_WARPS + warp) * UNITS;
     const uint64_t c = tile * ENC_WARPS + warp;
     const bool have = c < nchunk;
     const uint64_t base = c * CHUNK;
@@ -638,20 +651,18 @@ __global__ void __launch_bounds__((ENC_WARPS + 1) * 32, 3)
                               codebook);
       __syncwarp();
     }
-    if (pend) { // previous tile: its prefix has had a whole tile of time
-      const u64 off = finish(iter - 1, pend_c, pend_words);
-      if (off != ~0ull) {
-        const u64 *src = (const u64 *)(s_img +
-                                       (((iter - 1) & 1) * ENC_WARPS + warp) * UNITS);
-        for (uint32_t i = lane; i < pend_words; i += 32)
-          packed[off + i] = src[i];
-      }
-      pend = false;
-    }
+    if (pendA)
+      drain(itA, cA, wA);
+    pendA = pendB;
+    cA = cB;
+    wA = wB;
+    itA = itB;
+    pendB = false;
     if (have && fits) {
-      pend = true;
-      pend_c = c;
-      pend_words = words;
+      pendB = true;
+      cB = c;
+      wB = words;
+      itB = iter;
     } else if (have) { // oversized chunk: pack straight into the container
       const u64 off = finish(iter, c, words);
       if (off != ~0ull) {
@@ -664,15 +675,10 @@ __global__ void __launch_bounds__((ENC_WARPS + 1) * 32, 3)
     }
     __syncwarp();
   }
-  if (pend) {
-    const u64 off = finish(iter - 1, pend_c, pend_words);
-    if (off != ~0ull) {
-      const u64 *src =
-          (const u64 *)(s_img + (((iter - 1) & 1) * ENC_WARPS + warp) * UNITS);
-      for (uint32_t i = lane; i < pend_words; i += 32)
-        packed[off + i] = src[i];
-    }
-  }
+  if (pendA)
+    drain(itA, cA, wA);
+  if (pendB)
+    drain(itB, cB, wB);
 }
 
 // scalar header fields of the container (Huffman.hpp:344-395)
@@ -750,7 +756,7 @@ int mgxk_encode_container(mgx_ctx *ctx, uint64_t n, uint8_t *d_out, uint64_t cap
     const int R = (int)(chunk / 256);
     auto kern = R == 1 ? k_encode<1> : R == 2 ? k_encode<2> : R == 4 ? k_encode<4>
                                                                      : k_encode<8>;
-    size_t smem = 2 * (size_t)ENC_WARPS * (chunk * ENC_CAP_BITS / 32) * 4 + dict * 4;
+    size_t smem = (size_t)ENC_IMGS * ENC_WARPS * (chunk * ENC_CAP_BITS / 32) * 4 + dict * 4;
     MGX_CUDA(cudaFuncSetAttribute(
         kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     MGX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(
