@@ -552,7 +552,7 @@ __global__ void __launch_bounds__((ENC_WARPS + 1) * 32, 3)
   auto finish = [&](uint32_t it, uint64_t c, uint32_t words) {
     const int slot = it & (ENC_SLOTS - 1);
     while (v_epoch[slot] != it + 1)
-      ;
+      __nanosleep(100); // an issue-bound kernel: do not burn slots spinning
     __threadfence_block();
     u64 off = v_prefix[slot];
     for (int w = 0; w < warp; w++)
@@ -592,6 +592,15 @@ __global__ void __launch_bounds__((ENC_WARPS + 1) * 32, 3)
     uint4 v[R];
     int cnt[R];
     uint32_t start[R];
+    {
+      // pull the chunk this warp packs NEXT into L2 now: a warp works on one
+      // chunk at a time, so its 2 B/symbol would otherwise arrive at DRAM
+      // latency in front of every tile
+      const uint64_t nb = ((tile + gridDim.x) * ENC_WARPS + warp) * (uint64_t)CHUNK;
+      const uint64_t pa = nb + (uint64_t)lane * 64; // 128-byte lines of uint16
+      if (lane * 64 < CHUNK && pa < n)
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(sym + pa));
+    }
 #pragma unroll
     for (int j = 0; j < R; j++) {
       const uint64_t idx = base + (uint64_t)(j * 32 + lane) * 8;
