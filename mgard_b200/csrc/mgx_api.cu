@@ -150,6 +150,7 @@ void mgx_destroy(mgx_ctx *ctx) {
   free_dev(ctx->d_scalars);
   free_dev(ctx->d_norm_part);
   free_dev(ctx->d_sort_tmp);
+  free_dev(ctx->d_cb_ws);
   free_dev(ctx->d_stage_in);
   free_dev(ctx->d_stage_out);
   if (ctx->h_scalars)

@@ -143,14 +143,16 @@ int mgxk_codebook(mgx_ctx *ctx, const uint32_t *d_freq, uint64_t *d_codebook,
     P <<= 1;
   size_t ws = mgx_codebook_ws_bytes(dict, P);
   int use_smem = ws <= 200 * 1024;
-  static void *gws = nullptr; // L2-resident fallback workspace (large dicts)
-  static size_t gws_bytes = 0;
-  if (!use_smem && gws_bytes < ws) {
-    if (gws)
-      cudaFree(gws);
-    MGX_CUDA(cudaMalloc(&gws, ws));
-    gws_bytes = ws;
+  // L2-resident fallback workspace (large dicts), owned by the context
+  if (!use_smem && ctx->cb_ws_bytes < ws) {
+    if (ctx->d_cb_ws)
+      cudaFree(ctx->d_cb_ws);
+    ctx->d_cb_ws = nullptr;
+    ctx->cb_ws_bytes = 0;
+    MGX_CUDA(cudaMalloc(&ctx->d_cb_ws, ws));
+    ctx->cb_ws_bytes = ws;
   }
+  void *gws = ctx->d_cb_ws;
   size_t smem = use_smem ? ws : 0;
   MGX_CUDA(mgx_launch_codebook(d_freq, dict, P, d_codebook, d_decodebook,
                                (unsigned char *)gws, use_smem, smem,

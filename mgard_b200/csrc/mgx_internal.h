@@ -88,6 +88,8 @@ struct mgx_ctx {
   void *d_coarse0 = nullptr, *d_coarse1 = nullptr; // fused inverse: coarse lattice
   size_t coarse_bytes = 0;
   void *d_sort_tmp = nullptr;
+  void *d_cb_ws = nullptr;          // codebook workspace when it exceeds shared memory
+  size_t cb_ws_bytes = 0;
   size_t sort_tmp_bytes = 0;
   uint64_t *d_out_idx2 = nullptr;
   int64_t *d_out_val2 = nullptr;

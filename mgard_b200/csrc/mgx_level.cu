@@ -1490,13 +1490,10 @@ int correction_tail(mgx_ctx *ctx, int l, T *R0, T *R1, T *A, int sign) {
                           (size_t)(tpb / 32) * stages * IPK_B * (8 + 2 * sizeof(T));
 #define MGX_IPK_LAUNCH(ACCF, S)                                                  \
   do {                                                                           \
-    static bool attr_set = false;                                                \
-    if (!attr_set) {                                                             \
-      MGX_CUDA(cudaFuncSetAttribute(k_ipk_strided<T, ACCF, S>,                   \
-                                    cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                    8 * IPK_B * 128 * 8 * 2 + 4 * 8 * IPK_B * 24));                   \
-      attr_set = true;                                                           \
-    }                                                                            \
+    /* per device: set on every launch (a process may drive several GPUs) */     \
+    MGX_CUDA(cudaFuncSetAttribute(k_ipk_strided<T, ACCF, S>,                     \
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize,   \
+                                  8 * IPK_B * 128 * 8 * 2 + 4 * 8 * IPK_B * 24)); \
     k_ipk_strided<T, ACCF, S><<<grid, tpb, smem, ctx->stream>>>(                 \
         corr, am, bm, abr, rbm, n, inner, lines, acc, sign, fast);               \
   } while (0)
