@@ -151,7 +151,7 @@ __device__ __forceinline__ void row_next(uint32_t (&p)[OUTER], const LvGeom &g) 
   }
 }
 
-template <typename T, bool FORWARD>
+template <typename T, bool FORWARD, bool SKIP>
 __device__ __forceinline__ void row_setup(Row<T> &r, const uint32_t (&p)[OUTER],
                                           const LvGeom &g,
                                           const T *__restrict__ tables) {
@@ -168,6 +168,9 @@ __device__ __forceinline__ void row_setup(Row<T> &r, const uint32_t (&p)[OUTER],
   // innermost odd dimension ends at index 0
 #pragma unroll
   for (int d = 0; d < OUTER; d++) {
+    if (SKIP && g.nf[d] == 1)
+      continue; // padded dimension (D < 5): contributes nothing (the SKIP
+                // variants serve D < 5; with D = 5 the test only costs)
     uint32_t q;
     bool odd;
     pos_to_node(p[d], g.nf[d], g.nc[d], q, odd);
@@ -358,7 +361,7 @@ __device__ __forceinline__ void forward_row(
     R[row * ncf + (uint64_t)i] = mass_apply(mk, cem1, com1, ce, co, cep1);
 }
 
-template <typename T, bool QUANT, int MINB>
+template <typename T, bool QUANT, int MINB, bool SKIP>
 __global__ void __launch_bounds__(FW_WARPS * 32, MINB)
     k_level_forward(const T *__restrict__ src, T *__restrict__ v,
                     T *__restrict__ A, T *__restrict__ R,
@@ -390,13 +393,13 @@ __global__ void __launch_bounds__(FW_WARPS * 32, MINB)
     uint32_t p[OUTER];
     row_first(p, g, row0);
     Row<T> r;
-    row_setup<T, true>(r, p, g, tables);
+    row_setup<T, true, SKIP>(r, p, g, tables);
     for (uint64_t row = row0; row < row1; row++) {
       const bool more = row + 1 < row1;
       if (more) {
         row_next(p, g);
         Row<T> nx;
-        row_setup<T, true>(nx, p, g, tables);
+        row_setup<T, true, SKIP>(nx, p, g, tables);
         if (pair_ok) {
           prefetch_l1(src + nx.so + qe);
           prefetch_row<T, true>(src, (int64_t)nx.so + qe, nx);
@@ -425,7 +428,7 @@ __global__ void __launch_bounds__(FW_WARPS * 32, MINB)
         break;
       }
       if (more)
-        row_setup<T, true>(r, p, g, tables);
+        row_setup<T, true, SKIP>(r, p, g, tables);
     }
   }
   if (QUANT) {
@@ -1224,7 +1227,7 @@ __device__ __forceinline__ void restore_row(const Coef<T, SYM> &cf,
   }
 }
 
-template <typename T, bool SYM>
+template <typename T, bool SYM, bool SKIP>
 __global__ void __launch_bounds__(256)
     k_level_restore_rows(const Coef<T, SYM> cf, const T *__restrict__ A,
                          T *__restrict__ dst, const T *__restrict__ tables,
@@ -1248,13 +1251,13 @@ __global__ void __launch_bounds__(256)
   uint32_t p[OUTER];
   row_first(p, g, row0);
   Row<T> r;
-  row_setup<T, false>(r, p, g, tables);
+  row_setup<T, false, SKIP>(r, p, g, tables);
   for (uint64_t row = row0; row < row1; row++) {
     const bool more = row + 1 < row1;
     if (more) {
       row_next(p, g);
       Row<T> nx;
-      row_setup<T, false>(nx, p, g, tables);
+      row_setup<T, false, SKIP>(nx, p, g, tables);
       cf.prefetch(nx.vo + i);
       if (has_odd)
         cf.prefetch(nx.vo + ncf + i);
@@ -1279,7 +1282,7 @@ __global__ void __launch_bounds__(256)
       break;
     }
     if (more)
-      row_setup<T, false>(r, p, g, tables);
+      row_setup<T, false, SKIP>(r, p, g, tables);
   }
 }
 
@@ -1540,14 +1543,14 @@ int decompose_rows(mgx_ctx *ctx, const T *src, T *v, const double *q,
   const MgxLevels &lv = ctx->lv;
   const T *tables = (const T *)ctx->d_tables;
   const size_t smem = QUANT ? (size_t)ctx->dict * 4 : 0;
-  if (QUANT) {
-    MGX_CUDA(cudaFuncSetAttribute(k_level_forward<T, QUANT, 2>,
-                                  cudaFuncAttributeMaxDynamicSharedMemorySize,
+  const bool skip = lv.D < MGX_MAX_D; // padded dimensions exist
+  const bool three = ctx->fw_minb == 3 || (ctx->fw_minb == 0 && sizeof(T) == 4);
+  void (*fwd)(const T *, T *, T *, T *, const T *, const LvGeom, const QuantOut<T>) =
+      three ? (skip ? k_level_forward<T, QUANT, 3, true> : k_level_forward<T, QUANT, 3, false>)
+            : (skip ? k_level_forward<T, QUANT, 2, true> : k_level_forward<T, QUANT, 2, false>);
+  if (QUANT)
+    MGX_CUDA(cudaFuncSetAttribute(fwd, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)smem));
-    MGX_CUDA(cudaFuncSetAttribute(k_level_forward<T, QUANT, 3>,
-                                  cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)smem));
-  }
   QuantOut<T> qo;
   const T *cur = src;
   int which = 0;
@@ -1555,15 +1558,9 @@ int decompose_rows(mgx_ctx *ctx, const T *src, T *v, const double *q,
     LvGeom g = level_geom<T>(ctx, l, FW_OWN);
     fill_quant<T>(ctx, &qo, q, vol, l);
     T *A = (T *)s.A[which];
-    // 3 CTAs/SM pays for fp32 (80 regs without spills); fp64 spills at 80
-    if (ctx->fw_minb == 3 || (ctx->fw_minb == 0 && sizeof(T) == 4))
-      k_level_forward<T, QUANT, 3><<<task_grid(g, FW_WARPS), FW_WARPS * 32, smem,
-                                     ctx->stream>>>(cur, v, A, (T *)s.R[0], tables,
-                                                    g, qo);
-    else
-      k_level_forward<T, QUANT, 2><<<task_grid(g, FW_WARPS), FW_WARPS * 32, smem,
-                                     ctx->stream>>>(cur, v, A, (T *)s.R[0], tables,
-                                                    g, qo);
+    // (3 CTAs/SM pays for fp32: 80 regs without spills; fp64 spills at 80)
+    fwd<<<task_grid(g, FW_WARPS), FW_WARPS * 32, smem, ctx->stream>>>(
+        cur, v, A, (T *)s.R[0], tables, g, qo);
     ctx->launches++;
     rc = correction_tail<T>(ctx, l, (T *)s.R[0], (T *)s.R[1], A, +1);
     if (rc)
@@ -1648,6 +1645,7 @@ int recompose_rows(mgx_ctx *ctx, const T *v, T *dst, const double *dq,
     }
     return MGX_SUCCESS;
   }
+  const bool skip = lv.D < MGX_MAX_D;
   int which = 0;
   T *A = (T *)s.A[which];
   k_coarse_box<T, false, true><<<cb_grid, 256, 0, ctx->stream>>>(
@@ -1670,11 +1668,15 @@ int recompose_rows(mgx_ctx *ctx, const T *v, T *dst, const double *dq,
       return rc;
     T *out = (l == lv.L) ? dst : (T *)s.A[which ^ 1];
     if (use_sym)
-      k_level_restore_rows<T, true><<<task_grid(g, 8), 256, 0, ctx->stream>>>(
-          cs, A, out, tables, g);
+      (skip ? k_level_restore_rows<T, true, true>
+            : k_level_restore_rows<T, true, false>)<<<task_grid(g, 8), 256, 0,
+                                                      ctx->stream>>>(cs, A, out,
+                                                                     tables, g);
     else
-      k_level_restore_rows<T, false><<<task_grid(g, 8), 256, 0, ctx->stream>>>(
-          cf, A, out, tables, g);
+      (skip ? k_level_restore_rows<T, false, true>
+            : k_level_restore_rows<T, false, false>)<<<task_grid(g, 8), 256, 0,
+                                                       ctx->stream>>>(cf, A, out,
+                                                                      tables, g);
     ctx->launches++;
     A = out;
     which ^= 1;
