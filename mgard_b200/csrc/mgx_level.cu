@@ -396,9 +396,9 @@ __global__ void __launch_bounds__(FW_WARPS * 32, MINB)
     row_setup<T, true, SKIP>(r, p, g, tables);
     for (uint64_t row = row0; row < row1; row++) {
       const bool more = row + 1 < row1;
+      Row<T> nx = r;
       if (more) {
         row_next(p, g);
-        Row<T> nx;
         row_setup<T, true, SKIP>(nx, p, g, tables);
         if (pair_ok) {
           prefetch_l1(src + nx.so + qe);
@@ -427,8 +427,7 @@ __global__ void __launch_bounds__(FW_WARPS * 32, MINB)
                                  has_odd, owned, qe, tf, row);
         break;
       }
-      if (more)
-        row_setup<T, true, SKIP>(r, p, g, tables);
+      r = nx;
     }
   }
   if (QUANT) {
