@@ -1106,7 +1106,7 @@ template <typename T> struct InvPref {
 };
 
 template <typename T, bool HALF>
-__global__ void __launch_bounds__(HIER_THREADS, 3)
+__global__ void __launch_bounds__(HIER_THREADS, 4)
     k_hier_inverse3d(T *__restrict__ out, const T *__restrict__ tables,
                      const __grid_constant__ HierArgs<T> a) {
   typedef TileShape<3, 3, 6> TS;

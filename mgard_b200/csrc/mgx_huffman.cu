@@ -1052,6 +1052,9 @@ __global__ void __launch_bounds__(DEC_THREADS)
     auto unit = [&](uint32_t u) -> uint32_t { return u < nunits ? w32[u ^ 1] : 0u; };
     u64 buf = ((u64)unit(0) << 32) | unit(1);
     uint32_t nbits = 64, next_unit = 2;
+    // the unit the NEXT refill will need is fetched one refill ahead, so its
+    // L2/DRAM latency is not on the decode chain
+    uint32_t ahead = unit(2);
     uint64_t pos = 0;
     uint32_t k = 0, produced = 0, written = 0;
     while (produced < count) {
@@ -1079,6 +1082,7 @@ __global__ void __launch_bounds__(DEC_THREADS)
         buf = (((u64)unit(u0) << 32) | unit(u0 + 1)) << r;
         nbits = 64 - r;
         next_unit = u0 + 2;
+        ahead = unit(next_unit);
       } else {
         cnt = min(cnt, count - produced);
         ring[k + 0] = (uint16_t)((e >> 8) & 0x1fff);
@@ -1092,9 +1096,10 @@ __global__ void __launch_bounds__(DEC_THREADS)
         nbits -= len;
       }
       if (nbits <= 32) {
-        buf |= (u64)unit(next_unit) << (32 - nbits);
+        buf |= (u64)ahead << (32 - nbits);
         nbits += 32;
         ++next_unit;
+        ahead = unit(next_unit);
       }
       if (k >= 8) {
         const uint2 a0 = *reinterpret_cast<const uint2 *>(ring);
