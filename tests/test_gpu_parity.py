@@ -272,7 +272,11 @@ def test_thomas_fast_division_falls_back_outside_its_range(scale):
 
 ORTH_E2E = [((300, 77), np.float64, 0.0, 1, 1e-4), ((257, 513), np.float32, 1.0, 1, 1e-3),
             ((66, 33, 130), np.float32, 0.0, 0, 1e-3), ((6, 7, 9, 70), np.float64, INF, 1, 1e-3),
-            ((5, 6, 7, 8, 40), np.float32, 0.5, 1, 1e-2), ((1025,), np.float64, 0.0, 1, 1e-5)]
+            ((5, 6, 7, 8, 40), np.float32, 0.5, 1, 1e-2), ((1025,), np.float64, 0.0, 1, 1e-5),
+            # no level to decompose (L = 0) and the smallest grids with one
+            ((3, 3), np.float64, 0.0, 1, 1e-3), ((3, 9), np.float32, 0.0, 0, 1e-3),
+            ((4, 5, 3), np.float64, 1.0, 1, 1e-2), ((5, 5), np.float32, 0.0, 1, 1e-7),
+            ((3, 3, 3, 3), np.float32, INF, 1, 1e-3)]
 
 
 @pytest.mark.parametrize("shape,dtype,s,rel,tol", ORTH_E2E)
