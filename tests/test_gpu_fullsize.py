@@ -136,3 +136,21 @@ def test_257cubed_bytes_equal_the_oracle():
     assert gnorm == norm
     assert got.size == want.size
     assert np.array_equal(np.delete(got, 7), np.delete(want, 7))
+
+
+@pytest.mark.parametrize("shape,tdt,s,tol", [((200, 301, 250), torch.float32, 0.0, 1e-3),
+                                             ((1000, 1537), torch.float64, 1.0, 1e-3),
+                                             ((6, 10, 20, 30, 122), torch.float32, INF, 0.2)])
+def test_ragged_mid_size_kernel_families_agree(shape, tdt, s, tol, monkeypatch):
+    """even / non 2^k+1 sizes at sizes with many warp tasks per level: the
+    level kernels, the gather kernels and the float-dequantise decompress route
+    produce the same bytes."""
+    comp, u, blob, norm, dec = roundtrip(shape, tdt, s, tol)
+    _, _, blob_old, _, dec_old = roundtrip(shape, tdt, s, tol,
+                                           env={"MGX_LEGACY_LEVELS": "1"},
+                                           monkeypatch=monkeypatch)
+    assert torch.equal(blob_old, blob)
+    assert torch.equal(dec_old, dec)
+    _, _, _, _, dec_f = roundtrip(shape, tdt, s, tol, env={"MGX_NO_SYM_RECOMPOSE": "1"},
+                                  monkeypatch=monkeypatch)
+    assert torch.equal(dec_f, dec)
