@@ -154,3 +154,25 @@ def test_ragged_mid_size_kernel_families_agree(shape, tdt, s, tol, monkeypatch):
     _, _, _, _, dec_f = roundtrip(shape, tdt, s, tol, env={"MGX_NO_SYM_RECOMPOSE": "1"},
                                   monkeypatch=monkeypatch)
     assert torch.equal(dec_f, dec)
+
+
+@pytest.mark.parametrize("shape,tdt,s,tol", [((8193, 8193), torch.float64, 0.0, 1e-4),
+                                             ((2049, 4097), torch.float32, 1.0, 1e-3),
+                                             ((257, 300, 513), torch.float32, 0.0, 1e-4),
+                                             ((513, 513, 513), torch.float32, INF, 1e-3)])
+def test_repeated_calls_give_identical_bytes(shape, tdt, s, tol):
+    """the warp-specialised solves, the look-back scan of the encoder and the
+    atomics-fed histogram must not leak run-to-run variation into the stream
+    (stand-in for a race detector: compute-sanitizer is not available here)."""
+    u = device_field(shape, tdt)
+    comp = mg.Compressor(mg.Hierarchy(shape, tdt))
+    first = first_dec = None
+    for it in range(10):
+        blob, norm = comp.Compress(u, mg.REL, tol, s)
+        blob = blob.clone()
+        dec = comp.Decompress(blob, mg.REL, tol, s, norm)
+        if first is None:
+            first, first_dec = blob, dec.clone()
+        else:
+            assert torch.equal(blob, first), "iteration %d: different bytes" % it
+            assert torch.equal(dec, first_dec), "iteration %d: different output" % it
