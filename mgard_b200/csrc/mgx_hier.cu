@@ -1118,8 +1118,8 @@ __global__ void __launch_bounds__(HIER_THREADS, 4)
   const uint64_t sy = nx, sz = (uint64_t)nx * ny;
   // static roles
   const int k = tid & 31, ya = (tid >> 5) & 3, zb = (tid >> 7) * 2;
-  const bool r1 = tid < 153, r2 = tid >= 160 && tid < 196, rd = tid >= 224;
-  const int id1 = tid, id2 = tid - 160, idd = tid - 224;
+  const bool r1 = tid < 153, r2 = tid >= 160 && tid < 196;
+  const int id1 = tid, id2 = tid - 160;
   const int b1i = id1 % 17, b1j = (id1 / 17) % 3, b1k = id1 / 51;
   const int b2i = id2 % 9, b2j = (id2 / 9) % 2, b2k = id2 / 18;
   const bool h1x = b1i == 16, h1y = b1j == 2, h1z = b1k == 2;
@@ -1156,10 +1156,10 @@ __global__ void __launch_bounds__(HIER_THREADS, 4)
 #pragma unroll
       for (int i = 0; i < 7; i++)
         pf.pc[i] = e[i] ? (uint32_t)__ldg(at[i]) : 0u;
-    } else if (rd) {
-      pf.deep[0] = deep_value(idd, x0, y0, z0);
-      if (idd + 32 < 36)
-        pf.deep[1] = deep_value(idd + 32, x0, y0, z0);
+      // the 36 deep (coarse-lattice) values of the tile are staged by the same
+      // 36 threads that run the stride-4 pass on them: the hand-over is then a
+      // barrier between their two warps, not a CTA barrier
+      pf.deep[0] = deep_value(id2, x0, y0, z0);
     }
   };
 
@@ -1186,17 +1186,12 @@ __global__ void __launch_bounds__(HIER_THREADS, 4)
       prefetch(ncx * TS::TX, ncy * TS::TY, ncz * TS::TZ, nxt);
     __syncthreads(); // previous tile no longer read
     if (is_regular(x0, y0, z0)) {
-      if (rd) {
-        {
-          const int i = idd % 9, j = (idd / 9) % 2, kk = idd / 18;
-          tile[(((kk << P) * TS::HY) + (j << P)) * TS::PX + (i << P)] = cur.deep[0];
-        }
-        if (idd + 32 < 36) {
-          const int id = idd + 32, i = id % 9, j = (id / 9) % 2, kk = id / 18;
-          tile[(((kk << P) * TS::HY) + (j << P)) * TS::PX + (i << P)] = cur.deep[1];
-        }
+      if (r2) {
+        const int i = id2 % 9, j = (id2 / 9) % 2, kk = id2 / 18;
+        tile[(((kk << P) * TS::HY) + (j << P)) * TS::PX + (i << P)] = cur.deep[0];
       }
-      __syncthreads();
+      if (tid >= 160 && tid < 224) // warps 5 and 6 hold all r2 threads
+        asm volatile("bar.sync 1, 64;" ::: "memory");
       const uint16_t *at[7];
       if (r2) {
         block_sym_ptrs<T, 2>(a, x0, y0, z0, b2i, b2j, b2k, at);
