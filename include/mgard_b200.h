@@ -168,6 +168,22 @@ enum mgx_tick_id {
   MGX_TICK_D_END = 11,     /* after Recompose                               */
   MGX_TICK_COUNT = 16
 };
+/* Norm reduction WITHOUT any allocation (no cudaMalloc / cudaFree, no context):
+ * for callers under CUDA graph capture, tight serving loops, harnesses that
+ * forbid allocation.  No counterpart in the reference.
+ * Computes what mgx_norm_partial computes (linf != 0:
+ * max |u|, else sum u^2 accumulated in fp64) over n elements of `dtype` at
+ * d_in and writes it to the DEVICE double d_partial, asynchronously on
+ * cuda_stream (a cudaStream_t, or NULL for the default stream) of `device`;
+ * the caller synchronises.  Scratch is a 16 KB static __device__ array that
+ * every GPU loading the library holds until exit.  Limit: n <= 2^31 elements
+ * (2048 blocks x 2^20), larger n returns MGX_OUTPUT_TOO_LARGE.  All calls on a
+ * device share the scratch: calls that overlap on the GPU race.  On failure a
+ * message is copied into err (if err != NULL, capacity err_cap). */
+int mgx_norm_partial_noalloc(int device, void *cuda_stream, const void *d_in,
+                             int dtype, uint64_t n, int linf, double *d_partial,
+                             char *err, uint64_t err_cap);
+
 int mgx_set_timing(mgx_ctx *ctx, int on);
 int mgx_elapsed_ms(mgx_ctx *ctx, int from_tick, int to_tick, float *ms);
 

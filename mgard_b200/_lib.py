@@ -85,6 +85,8 @@ SIGNATURES = {
     "mgx_levels": (c_int, [c_vp, ctypes.POINTER(c_int), ctypes.POINTER(c_u64)]),
     "mgx_max_compressed_bytes": (c_u64, [c_vp]),
     "mgx_norm_partial": (c_int, [c_vp, c_vp, c_int, ctypes.POINTER(c_dbl)]),
+    "mgx_norm_partial_noalloc": (c_int, [c_int, c_vp, c_vp, c_int, c_u64, c_int, c_vp,
+                                         ctypes.c_char_p, c_u64]),
     "mgx_finish_norm": (c_dbl, [c_int, c_int, c_dbl, c_u64, c_int]),
     "mgx_decompose": (c_int, [c_vp, c_vp, c_int]),
     "mgx_recompose": (c_int, [c_vp, c_vp, c_int]),
