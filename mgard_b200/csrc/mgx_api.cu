@@ -114,6 +114,8 @@ int mgx_create(mgx_ctx **out, int device, void *cuda_stream) {
     ctx->no_sym_recompose = e && e[0] == '1';
     e = getenv("MGX_NO_WS");
     ctx->no_ws = e && e[0] == '1';
+    e = getenv("MGX_NO_TMA");
+    ctx->no_tma = e && e[0] == '1';
   }
   cudaDeviceProp prop;
   if (cudaGetDeviceProperties(&prop, device) == cudaSuccess)

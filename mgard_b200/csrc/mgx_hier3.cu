@@ -1,0 +1,749 @@
+// 3-D fused hierarchical forward pass, second generation: TMA-staged tiles and
+// warp-specialised roles (replaces, for 3-D fields, the LDGSTS-staged
+// k_hier_forward of mgx_hier.cu; same outputs bit for bit).
+//
+// What it computes is unchanged -- every level's coefficient of the hierarchical
+// basis from the ORIGINAL nodal values (reference: MultiDimension/
+// DataRefactoring.hpp:77-114, Coefficient/GridProcessingKernel3D.hpp:20-1228),
+// lwqzk quantisation (Quantization/LinearQuantization.hpp:19-145), outlier
+// separation (ParallelHuffman/OutlierSeparator.hpp:17-120) and the histogram
+// (ParallelHuffman/Histogram.hpp:15-235) in ONE pass: 4 B read + 2 B written per
+// fp32 node.  How it moves and schedules the data is new:
+//
+// * tiles of 8 x 8 x 64 nodes (+1 halo plane per axis) are fetched by the TMA
+//   unit.  Rows of a 2^k+1 grid are only element-aligned, which rules out a
+//   tensor map of the array itself (strides must be multiples of 16 bytes), so
+//   the array is DESCRIBED as a 2-D tensor of "super rows" of four consecutive
+//   rows (4 * nx elements; 16 * nx bytes is always a multiple of 16): row R of
+//   the flattened (z, y) index lives at x-offset (R mod 4) * nx of super row
+//   R div 4, and the rows R, R + 4, R + 8 of a tile plane are one box.  36
+//   UTMALDG per tile replace 5 300 per-element LDGSTS; rows land densely in
+//   shared memory, 16-byte aligned, whatever the alignment of the row in HBM.
+// * one CTA per SM, no CTA barrier in steady state: a producer warp issues the
+//   boxes into a ring of S tile buffers (mbarrier full/empty pairs); G groups of
+//   8 warps run the stride-1 pass of one tile each; C further warps run the
+//   stride-2 and stride-4 passes of the same tiles.  Tiles are read-only for all
+//   roles, so a tile needs no synchronisation between its passes.
+// * with ratio 0.5 (uniform grids) lerp(a, b) = (a - RN(a/2)) + RN(b/2): the two
+//   halves of every node are formed once and shared by all the interpolations
+//   that use it -- same roundings as the reference's four-operation lerp
+//   (GPKFunctor.h:13-25), 28 instead of 39 flops per 2 x 2 x 2 block.
+// * a block whose seven coefficients all quantise to zero (|c| <= cmax, the
+//   exact threshold found on the host) writes the symbol dict/2 seven times and
+//   skips conversion, range test and histogram; the bin of dict/2 is never
+//   counted in the kernels and is restored afterwards as N - sum(other bins).
+// * tiles are walked in super blocks of (all x) x 8 x 8 tiles so that the halo
+//   planes shared by neighbouring tiles are still in L2 when they are re-read.
+//
+// Nodes outside the structured passes (multiples of 8 on every axis, and the
+// nodes of the clipped tiles that touch the last node of an axis) go through
+// k_fwd3_rest, a per-node gather from global memory / L2.
+#include <cuda.h>
+
+#include <cstring>
+
+#include "mgx_hier_common.cuh"
+
+namespace {
+
+// ------------------------------------------------------------------ geometry
+template <typename T> struct F3 {
+  static constexpr int TZ = 8, TY = 8, TX = 64;
+  static constexpr int BX = TX + 16 / (int)sizeof(T); // 65 needed; box rows are 16-byte multiples
+  static constexpr int RB = BX * (int)sizeof(T);      // bytes per staged row
+  static constexpr int BOX3 = (3 * RB + 127) / 128 * 128; // rows m, m+4, m+8 (m = 0)
+  static constexpr int BOX2 = (2 * RB + 127) / 128 * 128; // rows m, m+4     (m = 1, 2, 3)
+  static constexpr int PLANE = BOX3 + 3 * BOX2;
+  static constexpr int TILE = 9 * PLANE;
+  static constexpr uint32_t TX_BYTES = 81u * RB; // bytes the 36 boxes of a tile deliver
+  // byte offset of row m (0..8) inside a staged plane
+  __host__ __device__ static constexpr int rowoff(int m) {
+    return (m & 3) == 0 ? (m >> 2) * RB : BOX3 + ((m & 3) - 1) * BOX2 + (m >> 2) * RB;
+  }
+};
+
+constexpr int F3_GW = 8; // stride-1 warps per group (one tile per group at a time)
+constexpr int F3_SMEM_MAX = 227 * 1024;
+constexpr int F3_MAX_DICT = 8192;
+
+template <typename T> constexpr int f3_stages() {
+  return (F3_SMEM_MAX - F3_MAX_DICT * 4 - 1024) / F3<T>::TILE > 8
+             ? 8
+             : (F3_SMEM_MAX - F3_MAX_DICT * 4 - 1024) / F3<T>::TILE;
+}
+// roles per CTA: 1 producer warp, G groups of 8 stride-1 warps, C warps for the
+// stride-2 / stride-4 passes (about 1.6 warp-tiles of work per tile against 8 for
+// the stride-1 pass).  fp64 values take two registers: fewer threads, more each.
+template <typename T> struct F3Cfg {
+  static constexpr int S = f3_stages<T>();
+  static constexpr int G = sizeof(T) == 4 ? 3 : 2;
+  static constexpr int C = sizeof(T) == 4 ? 5 : 3;
+  static constexpr int WARPS = 1 + G * F3_GW + C;
+  static constexpr int THREADS = 32 * WARPS;
+  static_assert(G <= S && C <= S, "end markers need a stage each");
+};
+
+// per-stage tile descriptor written by the producer
+struct F3Info {
+  unsigned long long base[3]; // address of the tile's first symbol of pass P (block 0)
+  uint32_t x0, y0, z0, pad;
+};
+
+template <typename T> struct F3Args {
+  T cmax;               // |c| <= cmax  <=>  the coefficient quantises to code 0
+  uint32_t rt[3];       // regular tiles per axis (z, y, x)
+  uint32_t sby, sbz;    // super blocks (8 x 8 tiles in y, z)
+  uint64_t padded;      // rt[2] * 64 * sby * sbz tile slots
+};
+
+// ------------------------------------------------------------- PTX wrappers
+__device__ __forceinline__ uint32_t saddr(const void *p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar),
+               "r"(bytes)
+               : "memory");
+}
+// bounded wait: a protocol error traps instead of hanging the GPU
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  for (uint32_t spin = 0; !done; ++spin) {
+    asm volatile("{\n\t.reg .pred p;\n\t"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                 "selp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done)
+                 : "r"(bar), "r"(parity)
+                 : "memory");
+    if (spin > (1u << 24))
+      __trap();
+  }
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map,
+                                            uint32_t bar, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
+               " [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+               "l"(map), "r"(bar), "r"(c0), "r"(c1)
+               : "memory");
+}
+
+// symbol store: the address is assembled from integers, so say "global" explicitly
+// (a generic ST would do the address-space check on every store)
+__device__ __forceinline__ void stg_u16(uint16_t *p, uint32_t v) {
+  asm volatile("st.global.u16 [%0], %1;" ::"l"(p), "h"((uint16_t)v) : "memory");
+}
+
+// ---------------------------------------------------------------- quantiser
+// Sink of the TMA kernels: like Sink<T> of mgx_hier_common.cuh, but the modal
+// symbol dict/2 is never counted (restored by k_hist_fix) and a group of seven
+// coefficients that all quantise to zero takes a four-instruction test.
+template <typename T> struct Sink3 {
+  const HierArgs<T> &a;
+  T cmax;
+  uint32_t hist_saddr;
+
+  __device__ __forceinline__ uint32_t quant(T c) const {
+    const T r = add_rn((T)0.5, fabs(mul_rn(c, a.qv)));
+    return (uint32_t)((int)copysign(r, c) + a.shift);
+  }
+  __device__ __forceinline__ void slow7(const T (&c)[7], uint16_t *const (&dst)[7]) const {
+    uint32_t sv[7], worst = 0;
+#pragma unroll
+    for (int i = 0; i < 7; i++) {
+      sv[i] = quant(c[i]);
+      worst = max(worst, sv[i]);
+    }
+    if (__builtin_expect(worst >= a.dict, 0)) {
+#pragma unroll
+      for (int i = 0; i < 7; i++)
+        if (sv[i] >= a.dict) {
+          const T r = add_rn((T)0.5, fabs(mul_rn(c[i], a.qv)));
+          sv[i] = hier_slow_symbol<T>(c[i], r, a, (uint64_t)(dst[i] - a.sym));
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 7; i++) {
+      stg_u16(dst[i], sv[i]);
+      if (sv[i] != (uint32_t)a.shift)
+        asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(hist_saddr + sv[i] * 4u));
+    }
+  }
+  __device__ __forceinline__ void put7(const T (&c)[7], uint16_t *const (&dst)[7]) const {
+    const T m = fmax(fmax(fmax(fabs(c[0]), fabs(c[1])), fmax(fabs(c[2]), fabs(c[3]))),
+                     fmax(fmax(fabs(c[4]), fabs(c[5])), fabs(c[6])));
+    if (m <= cmax) { // (false for NaN)
+#pragma unroll
+      for (int i = 0; i < 7; i++)
+        stg_u16(dst[i], (uint32_t)a.shift);
+    } else {
+      slow7(c, dst);
+    }
+  }
+};
+
+// Sink for the per-node gather of k_fwd3_rest (same conventions)
+template <typename T> struct SinkRest {
+  const HierArgs<T> &a;
+  uint32_t hist_saddr;
+  __device__ __forceinline__ void put(T c, uint64_t opos) const {
+    const T r = add_rn((T)0.5, fabs(mul_rn(c, a.qv)));
+    uint32_t sv = (uint32_t)((int)copysign(r, c) + a.shift);
+    if (sv >= a.dict)
+      sv = hier_slow_symbol<T>(c, r, a, opos);
+    a.sym[opos] = (uint16_t)sv;
+    if (sv != (uint32_t)a.shift)
+      asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(hist_saddr + sv * 4u));
+  }
+};
+
+// ------------------------------------------------------------------- passes
+// One even plane of the march at stride H = 2^P: from the nodes (e0, r0) of row
+// m0 and (e2, r2) of row m2 (x and x + 2H), the interpolants f0 (odd x), gE (odd
+// y), gO (odd x and y) -- plus, with ratio 0.5, the two halves of each value
+// that the next interpolation needs: h = RN(v/2), c = v - h.
+template <typename T, bool HALF> struct Plane3 {
+  T f0, gE, gO;       // interpolants of the plane's own three coefficient classes
+  T e0;               // !HALF: the even node itself
+  T h[4], c[4];       // HALF: halves of (e0, f0, gE, gO)
+};
+
+template <typename T, bool HALF, int P>
+__device__ __forceinline__ void
+plane3(const char *r0p, const char *r2p, Plane3<T, HALF> &Q, T &odd0, T tx, T ty) {
+  constexpr int H = 1 << P;
+  typedef typename std::conditional<sizeof(T) == 4, float2, double2>::type V2;
+  T e0, o0;
+  if constexpr (P == 0) {
+    const V2 own = *reinterpret_cast<const V2 *>(r0p);
+    e0 = own.x;
+    o0 = own.y;
+  } else {
+    e0 = *reinterpret_cast<const T *>(r0p);
+    o0 = *reinterpret_cast<const T *>(r0p + H * sizeof(T));
+  }
+  const T r0 = *reinterpret_cast<const T *>(r0p + 2 * H * sizeof(T));
+  const T e2 = *reinterpret_cast<const T *>(r2p);
+  const T r2 = *reinterpret_cast<const T *>(r2p + 2 * H * sizeof(T));
+  odd0 = o0;
+  if constexpr (HALF) {
+    const T he0 = mul_rn(e0, (T)0.5), ce0 = sub_rn(e0, he0);
+    const T he2 = mul_rn(e2, (T)0.5), ce2 = sub_rn(e2, he2);
+    const T f0 = add_rn(ce0, mul_rn((T)0.5, r0));
+    const T f2 = add_rn(ce2, mul_rn((T)0.5, r2));
+    const T gE = add_rn(ce0, he2);
+    const T hf0 = mul_rn(f0, (T)0.5), cf0 = sub_rn(f0, hf0);
+    const T gO = add_rn(cf0, mul_rn((T)0.5, f2));
+    Q.f0 = f0;
+    Q.gE = gE;
+    Q.gO = gO;
+    Q.h[0] = he0;
+    Q.c[0] = ce0;
+    Q.h[1] = hf0;
+    Q.c[1] = cf0;
+    Q.h[2] = mul_rn(gE, (T)0.5);
+    Q.c[2] = sub_rn(gE, Q.h[2]);
+    Q.h[3] = mul_rn(gO, (T)0.5);
+    Q.c[3] = sub_rn(gO, Q.h[3]);
+  } else {
+    Q.e0 = e0;
+    Q.f0 = mgx_lerp(e0, r0, tx);
+    const T f2 = mgx_lerp(e2, r2, tx);
+    Q.gE = mgx_lerp(e0, e2, ty);
+    Q.gO = mgx_lerp(Q.f0, f2, ty);
+  }
+}
+
+template <typename T, bool HALF>
+__device__ __forceinline__ T zlerp(const Plane3<T, HALF> &A, const Plane3<T, HALF> &B,
+                                   int i, T tz) {
+  if constexpr (HALF) {
+    return add_rn(A.c[i], B.h[i]);
+  } else {
+    const T a = i == 0 ? A.e0 : i == 1 ? A.f0 : i == 2 ? A.gE : A.gO;
+    const T b = i == 0 ? B.e0 : i == 1 ? B.f0 : i == 2 ? B.gE : B.gO;
+    return mgx_lerp(a, b, tz);
+  }
+}
+
+// March of one thread along z at stride H = 2^P: NB consecutive 2 x 2 x 2 blocks
+// of the stride-H lattice whose anchor is (2k, 2ya, 2zb0) * H.  `tile` points at
+// the staged tile; ro[j] = F3::rowoff((2ya + j) * H).
+template <typename T, bool HALF, int P, int NB>
+__device__ __forceinline__ void
+march3(const char *tile, const T *__restrict__ tables, const HierArgs<T> &a,
+       const Sink3<T> &sink, int k, int ya, int zb0, const int (&ro)[3],
+       unsigned long long base, const uint32_t (&tc)[7], uint32_t x0, uint32_t y0,
+       uint32_t z0) {
+  typedef F3<T> G;
+  typedef typename std::conditional<sizeof(T) == 4, float2, double2>::type V2;
+  constexpr int H = 1 << P;
+  const int l = a.L - P;
+  const uint64_t sz2 = 2ull * a.n[2] * a.n[1]; // bytes between z rows of symbols
+  T tx = (T)0.5, ty = (T)0.5;
+  if constexpr (!HALF) {
+    tx = tables[a.roff[l][2] + (x0 >> P) + 2 * k];
+    ty = tables[a.roff[l][1] + (y0 >> P) + 2 * ya];
+  }
+  auto pair = [&](const char *q) -> V2 { // nodes x and x + H of a row
+    if constexpr (P == 0) {
+      return *reinterpret_cast<const V2 *>(q);
+    } else {
+      V2 v;
+      v.x = *reinterpret_cast<const T *>(q);
+      v.y = *reinterpret_cast<const T *>(q + H * sizeof(T));
+      return v;
+    }
+  };
+  const char *p = tile + (2 * zb0 * H) * G::PLANE + (2 * k * H) * (int)sizeof(T);
+  Plane3<T, HALF> A, B;
+  T oA, oB;
+  plane3<T, HALF, P>(p + ro[0], p + ro[2], A, oA, tx, ty);
+#pragma unroll
+  for (int b = 0; b < NB; b++) {
+    const char *q = p + (2 * b * H) * G::PLANE;
+    const V2 r1 = pair(q + ro[1]);
+    plane3<T, HALF, P>(q + 2 * H * G::PLANE + ro[0], q + 2 * H * G::PLANE + ro[2], B, oB,
+                       tx, ty);
+    T tz = (T)0.5;
+    if constexpr (!HALF)
+      tz = tables[a.roff[l][0] + (z0 >> P) + 2 * (zb0 + b)];
+    const V2 s0 = pair(q + H * G::PLANE + ro[0]);
+    const V2 s1 = pair(q + H * G::PLANE + ro[1]);
+    const T c[7] = {sub_rn(oA, A.f0),
+                    sub_rn(r1.x, A.gE),
+                    sub_rn(r1.y, A.gO),
+                    sub_rn(s0.x, zlerp<T, HALF>(A, B, 0, tz)),
+                    sub_rn(s0.y, zlerp<T, HALF>(A, B, 1, tz)),
+                    sub_rn(s1.x, zlerp<T, HALF>(A, B, 2, tz)),
+                    sub_rn(s1.y, zlerp<T, HALF>(A, B, 3, tz))};
+    const unsigned long long bb = base + (unsigned long long)b * sz2;
+    uint16_t *dst[7];
+#pragma unroll
+    for (int i = 0; i < 7; i++)
+      dst[i] = reinterpret_cast<uint16_t *>(bb + 2ull * tc[i]);
+    sink.put7(c, dst);
+    A = B;
+    oA = oB;
+  }
+}
+
+// element offsets of the 7 coefficient classes of pass P relative to the block's
+// first symbol, plus `te` (the thread's own element offset inside the tile)
+template <typename T>
+__device__ __forceinline__ void class_offsets(const HierArgs<T> &a, int P, uint32_t te,
+                                              uint32_t (&tc)[7]) {
+  const uint32_t oX = (uint32_t)(a.oct[P][0] >> 1), oY = (uint32_t)(a.oct[P][1] >> 1),
+                 oZ = (uint32_t)(a.oct[P][2] >> 1);
+  tc[0] = te + oX;
+  tc[1] = te + oY;
+  tc[2] = te + oX + oY;
+  tc[3] = te + oZ;
+  tc[4] = te + oZ + oX;
+  tc[5] = te + oZ + oY;
+  tc[6] = te + oZ + oX + oY;
+}
+
+template <typename T, bool HALF>
+__global__ void __launch_bounds__(F3Cfg<T>::THREADS, 1)
+    k_fwd3(uint32_t *__restrict__ g_freq, const T *__restrict__ tables,
+           const __grid_constant__ HierArgs<T> a, const __grid_constant__ F3Args<T> fa,
+           const __grid_constant__ CUtensorMap tm3,
+           const __grid_constant__ CUtensorMap tm2) {
+  typedef F3<T> G;
+  constexpr int S = F3Cfg<T>::S, F3_G = F3Cfg<T>::G, F3_C = F3Cfg<T>::C,
+                F3_THREADS = F3Cfg<T>::THREADS;
+  extern __shared__ __align__(128) unsigned char smem[];
+  unsigned char *tiles = smem;
+  uint32_t *s_hist = (uint32_t *)(smem + (size_t)S * G::TILE);
+  F3Info *info = (F3Info *)(s_hist + a.dict);
+  unsigned long long *bars = (unsigned long long *)(info + S);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t full0 = saddr(bars), empty0 = saddr(bars + S);
+  for (uint32_t i = tid; i < a.dict; i += F3_THREADS)
+    s_hist[i] = 0;
+  if (tid == 0) {
+    for (int s = 0; s < S; s++) {
+      mbar_init(full0 + 8 * s, 1);
+      mbar_init(empty0 + 8 * s, F3_GW + 1);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  const uint32_t ny = a.n[1], nx = a.n[2];
+  const uint64_t sy = nx, sz = (uint64_t)nx * ny;
+
+  if (warp == 0) {
+    // ------------------------------------------------ producer (one lane)
+    if (lane == 0) {
+      const uint32_t T2 = fa.rt[2];
+      const uint32_t SB = T2 * 64;
+      int s = 0;
+      uint32_t ph = 0;
+      auto next_stage = [&]() {
+        if (++s == S) {
+          s = 0;
+          ph ^= 1;
+        }
+      };
+      for (uint64_t q = blockIdx.x; q < fa.padded; q += gridDim.x) {
+        const uint32_t sb = (uint32_t)(q / SB), r = (uint32_t)(q % SB);
+        const uint32_t tx = r % T2, r2 = r / T2;
+        const uint32_t ty = (sb % fa.sby) * 8 + (r2 & 7), tz = (sb / fa.sby) * 8 + (r2 >> 3);
+        if (ty >= fa.rt[1] || tz >= fa.rt[0])
+          continue;
+        const uint32_t x0 = tx * G::TX, y0 = ty * G::TY, z0 = tz * G::TZ;
+        mbar_wait(empty0 + 8 * s, ph ^ 1);
+        F3Info &fi = info[s];
+#pragma unroll
+        for (int P = 0; P < 3; P++)
+          fi.base[P] = (unsigned long long)(a.sym + ((uint64_t)(z0 >> (P + 1)) * sz +
+                                                     (uint64_t)(y0 >> (P + 1)) * sy +
+                                                     (x0 >> (P + 1))));
+        fi.x0 = x0;
+        fi.y0 = y0;
+        fi.z0 = z0;
+        const uint32_t bar = full0 + 8 * s;
+        mbar_expect_tx(bar, G::TX_BYTES);
+        const uint32_t dst0 = saddr(tiles + (size_t)s * G::TILE);
+#pragma unroll 1
+        for (int p = 0; p < 9; p++) {
+          const uint32_t R0 = (z0 + p) * ny + y0;
+#pragma unroll
+          for (int m = 0; m < 4; m++) {
+            const uint32_t R = R0 + m;
+            tma_load_2d(dst0 + p * G::PLANE + G::rowoff(m), m == 0 ? &tm3 : &tm2, bar,
+                        (int)((R & 3) * nx + x0), (int)(R >> 2));
+          }
+        }
+        next_stage();
+      }
+      // end markers: one for every consumer role's next tile slot
+      for (int e = 0; e < (F3_G > F3_C ? F3_G : F3_C); e++) {
+        mbar_wait(empty0 + 8 * s, ph ^ 1);
+        info[s].x0 = 0xffffffffu;
+        mbar_arrive(full0 + 8 * s);
+        next_stage();
+      }
+    }
+  } else {
+    const Sink3<T> sink{a, fa.cmax, saddr(s_hist)};
+    const int cw = warp - 1;
+    if (cw < F3_G * F3_GW) {
+      // ---------------------------------- stride-1 pass: group g, warp iw
+      const int g = cw / F3_GW, iw = cw % F3_GW;
+      const int k = lane, ya = iw & 3, zb0 = (iw >> 2) * 2;
+      const int ro[3] = {G::rowoff(2 * ya), G::rowoff(2 * ya + 1), G::rowoff(2 * ya + 2)};
+      uint32_t tc[7];
+      class_offsets<T>(a, 0, (uint32_t)(zb0 * sz + ya * sy + k), tc);
+      int s = g;
+      uint32_t ph = 0;
+      while (true) {
+        mbar_wait(full0 + 8 * s, ph);
+        const F3Info &fi = info[s];
+        const uint32_t x0 = fi.x0;
+        if (x0 == 0xffffffffu)
+          break;
+        march3<T, HALF, 0, 2>((const char *)tiles + (size_t)s * G::TILE, tables, a, sink, k,
+                              ya, zb0, ro, fi.base[0], tc, x0, fi.y0, fi.z0);
+        __syncwarp();
+        if (lane == 0)
+          mbar_arrive(empty0 + 8 * s);
+        s += F3_G;
+        if (s >= S) {
+          s -= S;
+          ph ^= 1;
+        }
+      }
+    } else {
+      // ------------------- stride-2 and stride-4 passes: warp c of F3_C
+      const int c = cw - F3_G * F3_GW;
+      // stride 2: 16 x 2 x 2 blocks, lane = (k, ya), march over both z blocks
+      const int k1 = lane & 15, ya1 = lane >> 4;
+      const int ro1[3] = {G::rowoff(4 * ya1), G::rowoff(4 * ya1 + 2), G::rowoff(4 * ya1 + 4)};
+      uint32_t tc1[7];
+      class_offsets<T>(a, 1, (uint32_t)(ya1 * sy + k1), tc1);
+      // stride 4: 8 x 1 x 1 blocks, lanes 0..7
+      const int ro2[3] = {G::rowoff(0), G::rowoff(4), G::rowoff(8)};
+      uint32_t tc2[7];
+      class_offsets<T>(a, 2, (uint32_t)(lane & 7), tc2);
+      int s = c % S;
+      uint32_t ph = (c / S) & 1;
+      while (true) {
+        mbar_wait(full0 + 8 * s, ph);
+        const F3Info &fi = info[s];
+        const uint32_t x0 = fi.x0;
+        if (x0 == 0xffffffffu)
+          break;
+        const char *tile = (const char *)tiles + (size_t)s * G::TILE;
+        march3<T, HALF, 1, 2>(tile, tables, a, sink, k1, ya1, 0, ro1, fi.base[1], tc1, x0,
+                              fi.y0, fi.z0);
+        if (lane < 8)
+          march3<T, HALF, 2, 1>(tile, tables, a, sink, lane, 0, 0, ro2, fi.base[2], tc2, x0,
+                                fi.y0, fi.z0);
+        __syncwarp();
+        if (lane == 0)
+          mbar_arrive(empty0 + 8 * s);
+        s += F3_C;
+        while (s >= S) {
+          s -= S;
+          ph ^= 1;
+        }
+      }
+    }
+  }
+  // flush the CTA histogram (the bin of dict/2 is restored by k_hist_fix)
+  __syncthreads();
+  for (uint32_t i = tid; i < a.dict; i += F3_THREADS) {
+    const uint32_t v = s_hist[i];
+    if (v)
+      atomicAdd(&g_freq[i], v);
+  }
+}
+
+// Nodes outside the structured passes: (1) inside the regular region, the
+// multiples of 8 on every axis (coarser than the in-tile strides; neighbours up
+// to half the grid away); (2) every node of the clipped tiles that touch the
+// last node of an axis, i.e. the region outside [0, 8*rt0) x [0, 8*rt1) x
+// [0, 64*rt2).  Per-node gather from global memory / L2.
+template <typename T, bool HALF>
+__global__ void __launch_bounds__(HIER_THREADS)
+    k_fwd3_rest(const T *__restrict__ u, uint32_t *__restrict__ g_freq,
+                const T *__restrict__ tables, const __grid_constant__ HierArgs<T> a,
+                const __grid_constant__ F3Args<T> fa) {
+  typedef TileShape<3, 3, 6> TS;
+  extern __shared__ __align__(16) unsigned char smem[];
+  uint32_t *s_hist = (uint32_t *)smem;
+  for (uint32_t i = threadIdx.x; i < a.dict; i += HIER_THREADS)
+    s_hist[i] = 0;
+  __syncthreads();
+  const SinkRest<T> sink{a, saddr(s_hist)};
+  const uint32_t nz = a.n[0], ny = a.n[1], nx = a.n[2];
+  const uint32_t RZ = fa.rt[0] * 8, RY = fa.rt[1] * 8, RX = fa.rt[2] * 64;
+  // deep nodes of the regular region, then slabs z >= RZ, y >= RY, x >= RX
+  const uint64_t nd = (uint64_t)fa.rt[0] * fa.rt[1] * (RX / 8);
+  const uint64_t nA = (uint64_t)(nz - RZ) * ny * nx;
+  const uint64_t nB = (uint64_t)RZ * (ny - RY) * nx;
+  const uint64_t nC = (uint64_t)RZ * RY * (nx - RX);
+  const uint64_t total = nd + nA + nB + nC;
+  for (uint64_t i = blockIdx.x * (uint64_t)HIER_THREADS + threadIdx.x; i < total;
+       i += (uint64_t)gridDim.x * HIER_THREADS) {
+    uint32_t gx, gy, gz;
+    if (i < nd) {
+      const uint32_t per = RX / 8;
+      gx = (uint32_t)(i % per) * 8;
+      const uint64_t r = i / per;
+      gy = (uint32_t)(r % fa.rt[1]) * 8;
+      gz = (uint32_t)(r / fa.rt[1]) * 8;
+    } else if (i < nd + nA) {
+      const uint64_t j = i - nd;
+      gx = (uint32_t)(j % nx);
+      gy = (uint32_t)((j / nx) % ny);
+      gz = RZ + (uint32_t)(j / ((uint64_t)nx * ny));
+    } else if (i < nd + nA + nB) {
+      const uint64_t j = i - nd - nA;
+      const uint32_t wy = ny - RY;
+      gx = (uint32_t)(j % nx);
+      gy = RY + (uint32_t)((j / nx) % wy);
+      gz = (uint32_t)(j / ((uint64_t)nx * wy));
+    } else {
+      const uint64_t j = i - nd - nA - nB;
+      const uint32_t wx = nx - RX;
+      gx = RX + (uint32_t)(j % wx);
+      gy = (uint32_t)((j / wx) % RY);
+      gz = (uint32_t)(j / ((uint64_t)wx * RY));
+    }
+    element_generic<T, HALF, TS>(u, (const T *)nullptr, tables, a, gx, gy, gz, 0, 0, 0, 0,
+                                 0, 0, sink);
+  }
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < a.dict; i += HIER_THREADS) {
+    const uint32_t v = s_hist[i];
+    if (v)
+      atomicAdd(&g_freq[i], v);
+  }
+}
+
+// freq[dict/2] = N - sum of all other bins (the kernels above never count it)
+__global__ void __launch_bounds__(1024)
+    k_hist_fix(uint32_t *__restrict__ freq, uint32_t dict, uint32_t modal,
+               unsigned long long n) {
+  __shared__ unsigned long long part[32];
+  unsigned long long s = 0;
+  for (uint32_t i = threadIdx.x; i < dict; i += 1024)
+    if (i != modal)
+      s += freq[i];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1)
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+  if ((threadIdx.x & 31) == 0)
+    part[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned long long t = 0;
+    for (int i = 0; i < 32; i++)
+      t += part[i];
+    freq[modal] = (uint32_t)(n - t);
+  }
+}
+
+// --------------------------------------------------------------- host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *,
+                                  const cuuint64_t *, const cuuint64_t *, const cuuint32_t *,
+                                  const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = []() -> EncodeTiledFn {
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) !=
+            cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      return nullptr;
+    return (EncodeTiledFn)p;
+  }();
+  return fn;
+}
+
+// largest |c| that still quantises to code 0 (exact: bisection over the bit
+// pattern with the kernel's own arithmetic; host files build with
+// -ffp-contract=off).  Negative when even c = 0 does not (non-finite quantiser).
+template <typename T> T zero_threshold(T qv) {
+  typedef typename std::conditional<sizeof(T) == 4, uint32_t, uint64_t>::type U;
+  auto is_zero = [&](T c) {
+    volatile T t = c * qv;
+    volatile T r = (T)0.5 + std::fabs(t);
+    return std::isfinite(r) && (long long)r == 0;
+  };
+  if (!std::isfinite(qv) || !is_zero((T)0))
+    return (T)-1;
+  U lo = 0, hi; // lo: is_zero true; hi: false
+  const T inf = std::numeric_limits<T>::infinity();
+  std::memcpy(&hi, &inf, sizeof(T));
+  while (hi - lo > 1) {
+    const U mid = lo + (hi - lo) / 2;
+    T c;
+    std::memcpy(&c, &mid, sizeof(T));
+    if (is_zero(c))
+      lo = mid;
+    else
+      hi = mid;
+  }
+  T c;
+  std::memcpy(&c, &lo, sizeof(T));
+  return c;
+}
+
+template <typename T, bool HALF>
+int launch_fwd3(mgx_ctx *ctx, const void *d_in, HierArgs<T> &a, bool *used) {
+  typedef F3<T> G;
+  *used = false;
+  const uint64_t nz = a.n[0], ny = a.n[1], nx = a.n[2];
+  const uint64_t N = nz * ny * nx;
+  EncodeTiledFn enc = encode_tiled_fn();
+  if (!enc || ctx->no_tma || a.L < 3 || nz < 9 || ny < 9 || nx < 65 ||
+      ((uintptr_t)d_in & 15) != 0 || N >= (1ull << 32) || ctx->dict > F3_MAX_DICT ||
+      4 * nx >= (1ull << 31))
+    return MGX_SUCCESS;
+  F3Args<T> fa;
+  fa.rt[0] = (uint32_t)((nz - 1) / G::TZ);
+  fa.rt[1] = (uint32_t)((ny - 1) / G::TY);
+  fa.rt[2] = (uint32_t)((nx - 1) / G::TX);
+  // The box of the array's very last row is 16-byte granular and may reach up to
+  // 3 elements past the end of the array (only when that row is not the fourth
+  // of its super row, where the tensor bound clips it).  Harmless as long as
+  // those bytes share a page with the last element; else use the LDGSTS kernel.
+  if ((uint64_t)(fa.rt[2] - 1) * G::TX + G::BX > nx && fa.rt[1] * (uint64_t)G::TY == ny - 1 &&
+      fa.rt[0] * (uint64_t)G::TZ == nz - 1 && ((nz * ny) & 3) != 0) {
+    const uintptr_t end = (uintptr_t)d_in + N * sizeof(T);
+    if ((end & 4095) == 0 || (end & 4095) > 4096 - 16)
+      return MGX_SUCCESS;
+  }
+  fa.sby = (fa.rt[1] + 7) / 8;
+  fa.sbz = (fa.rt[0] + 7) / 8;
+  fa.padded = (uint64_t)fa.rt[2] * 64 * fa.sby * fa.sbz;
+  fa.cmax = zero_threshold<T>(a.qv);
+  for (int p = 0; p < 12; p++) {
+    const int l = a.L - p;
+    const uint64_t sy = a.n[2], sz = (uint64_t)a.n[2] * a.n[1];
+    for (int d = 0; d < 3; d++)
+      a.oct[p][d] = 0;
+    if (l >= 1) {
+      a.oct[p][0] = 2ull * a.nl[l - 1][2];
+      a.oct[p][1] = 2ull * a.nl[l - 1][1] * sy;
+      a.oct[p][2] = 2ull * a.nl[l - 1][0] * sz;
+    }
+  }
+  a.tiles[0] = fa.rt[0];
+  a.tiles[1] = fa.rt[1];
+  a.tiles[2] = fa.rt[2];
+  a.ntiles = (uint64_t)fa.rt[0] * fa.rt[1] * fa.rt[2];
+  a.sym = ctx->d_sym;
+  a.out_count = (unsigned long long *)(ctx->d_scalars + MGX_SC_OUTLIERS);
+  a.out_idx = (unsigned long long *)ctx->d_out_idx;
+  a.out_val = (long long *)ctx->d_out_val;
+  a.out_cap = ctx->out_cap;
+
+  CUtensorMap tm3, tm2;
+  const cuuint64_t dims[2] = {4 * nx, (nz * ny + 3) / 4};
+  const cuuint64_t strides[1] = {4 * nx * sizeof(T)};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUtensorMapDataType dt =
+      sizeof(T) == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT64;
+  for (int rows = 2; rows <= 3; rows++) {
+    const cuuint32_t box[2] = {(cuuint32_t)G::BX, (cuuint32_t)rows};
+    CUresult r = enc(rows == 3 ? &tm3 : &tm2, dt, 2, const_cast<void *>(d_in), dims, strides,
+                     box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+      return MGX_SUCCESS; // fall back to the LDGSTS kernel
+  }
+  constexpr int S = F3Cfg<T>::S;
+  const size_t smem = (size_t)S * G::TILE + (size_t)ctx->dict * 4 + S * sizeof(F3Info) +
+                      2 * S * 8;
+  auto kern = k_fwd3<T, HALF>;
+  MGX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)smem));
+  const unsigned grid = (unsigned)std::min<uint64_t>(a.ntiles, (uint64_t)ctx->num_sms);
+  kern<<<grid, F3Cfg<T>::THREADS, smem, ctx->stream>>>(ctx->d_freq, (const T *)ctx->d_tables, a,
+                                                fa, tm3, tm2);
+  ctx->launches++;
+  {
+    auto rest = k_fwd3_rest<T, HALF>;
+    const size_t hsmem = (size_t)ctx->dict * 4;
+    MGX_CUDA(cudaFuncSetAttribute(rest, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)hsmem));
+    const uint64_t RZ = fa.rt[0] * 8ull, RY = fa.rt[1] * 8ull, RX = fa.rt[2] * 64ull;
+    const uint64_t work = N - RZ * RY * RX + a.ntiles * 8;
+    const unsigned rgrid = mgx_grid_for(work, HIER_THREADS * 2, ctx->num_sms * 6);
+    rest<<<rgrid, HIER_THREADS, hsmem, ctx->stream>>>(
+        (const T *)d_in, ctx->d_freq, (const T *)ctx->d_tables, a, fa);
+    ctx->launches++;
+  }
+  k_hist_fix<<<1, 1024, 0, ctx->stream>>>(ctx->d_freq, ctx->dict, ctx->dict / 2, N);
+  ctx->launches++;
+  MGX_CUDA(cudaGetLastError());
+  *used = true;
+  return MGX_SUCCESS;
+}
+
+} // namespace
+
+// Entry used by mgx_hier.cu: runs the TMA path when the shape / pointer allow
+// it (*used = true), else leaves everything to the caller's LDGSTS kernel.
+template <typename T>
+int mgxk_hier_forward3(mgx_ctx *ctx, const void *d_in, const void *args, bool half,
+                       bool *used) {
+  HierArgs<T> a = *reinterpret_cast<const HierArgs<T> *>(args);
+  return half ? launch_fwd3<T, true>(ctx, d_in, a, used)
+              : launch_fwd3<T, false>(ctx, d_in, a, used);
+}
+template int mgxk_hier_forward3<float>(mgx_ctx *, const void *, const void *, bool, bool *);
+template int mgxk_hier_forward3<double>(mgx_ctx *, const void *, const void *, bool, bool *);

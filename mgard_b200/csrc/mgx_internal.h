@@ -65,6 +65,7 @@ struct mgx_ctx {
   int fw_minb = 0;          // MGX_FW_MINB=2|3: force the k_level_forward variant (0 = by dtype)
   bool no_sym_recompose = false; // MGX_NO_SYM_RECOMPOSE=1: dequantise to floats first
   bool no_ws = false;       // MGX_NO_WS=1: single-warp Thomas kernels only (A/B)
+  bool no_tma = false;      // MGX_NO_TMA=1: 3-D hierarchical forward pass on the LDGSTS kernel (A/B)
 
   // workspaces (allocated on first use, sized for the plan)
   void *d_w = nullptr;      // N elements of T (level workspace)
