@@ -471,6 +471,11 @@ int mgx_hier_quantize(mgx_ctx *ctx, const void *d_in, int rel, double tol,
   MGX_CUDA(cudaMemcpyAsync(ctx->h_scalars, ctx->d_scalars, MGX_SC_COUNT * 8,
                            cudaMemcpyDeviceToHost, ctx->stream));
   MGX_CUDA(cudaStreamSynchronize(ctx->stream));
+  if (ctx->h_scalars[MGX_SC_ERR] & 0xf00ull) {
+    ctx->err = "forward pass: tile pipeline timed out (flags " +
+               std::to_string(ctx->h_scalars[MGX_SC_ERR]) + ")";
+    return MGX_FAILURE;
+  }
   uint64_t n_out = ctx->h_scalars[MGX_SC_OUTLIERS];
   if (n_out > ctx->out_cap) {
     rc = grow_outliers(ctx, n_out);

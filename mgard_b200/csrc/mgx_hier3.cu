@@ -16,9 +16,16 @@
 //   the array is DESCRIBED as a 2-D tensor of "super rows" of four consecutive
 //   rows (4 * nx elements; 16 * nx bytes is always a multiple of 16): row R of
 //   the flattened (z, y) index lives at x-offset (R mod 4) * nx of super row
-//   R div 4, and the rows R, R + 4, R + 8 of a tile plane are one box.  36
-//   UTMALDG per tile replace 5 300 per-element LDGSTS; rows land densely in
-//   shared memory, 16-byte aligned, whatever the alignment of the row in HBM.
+//   R div 4, and the rows R, R + 4, R + 8 of a tile plane are one box.  A box
+//   must START on a 16-byte boundary of the tensor's inner dimension (measured
+//   on B200: any other start coordinate raises "illegal instruction"), so each
+//   box fetches the 16-byte-aligned superset of its row segments and the wanted
+//   node x0 lands `shift` elements into the staged row.  The shift of row m of
+//   staged plane p is ((p * ny + m) * nx) mod E (E = elements per 16 bytes; tile
+//   origins are multiples of 8): it does not depend on the tile, and starting the
+//   box A(p) + B(m) elements early (A(p) = p*ny*nx mod E, B(m) = m*nx mod E, no
+//   wrap) makes the staged address of a node the SUM of a plane term and a row
+//   term.  36 UTMALDG per tile replace 5 300 per-element LDGSTS.
 // * one CTA per SM, no CTA barrier in steady state: a producer warp issues the
 //   boxes into a ring of S tile buffers (mbarrier full/empty pairs); G groups of
 //   8 warps run the stride-1 pass of one tile each; C further warps run the
@@ -40,6 +47,7 @@
 // k_fwd3_rest, a per-node gather from global memory / L2.
 #include <cuda.h>
 
+#include <cstdlib>
 #include <cstring>
 
 #include "mgx_hier_common.cuh"
@@ -49,7 +57,9 @@ namespace {
 // ------------------------------------------------------------------ geometry
 template <typename T> struct F3 {
   static constexpr int TZ = 8, TY = 8, TX = 64;
-  static constexpr int BX = TX + 16 / (int)sizeof(T); // 65 needed; box rows are 16-byte multiples
+  static constexpr int E = 16 / (int)sizeof(T);       // elements per 16 bytes
+  // 65 nodes + up to 2 (E - 1) elements of alignment slack, a multiple of E
+  static constexpr int BX = (TX + 1 + 2 * (E - 1) + E - 1) / E * E; // float 72, double 68
   static constexpr int RB = BX * (int)sizeof(T);      // bytes per staged row
   static constexpr int BOX3 = (3 * RB + 127) / 128 * 128; // rows m, m+4, m+8 (m = 0)
   static constexpr int BOX2 = (2 * RB + 127) / 128 * 128; // rows m, m+4     (m = 1, 2, 3)
@@ -63,6 +73,7 @@ template <typename T> struct F3 {
 };
 
 constexpr int F3_GW = 8; // stride-1 warps per group (one tile per group at a time)
+constexpr int F3_NP = 3; // producer warps (12 of a tile's 36 boxes each)
 constexpr int F3_SMEM_MAX = 227 * 1024;
 constexpr int F3_MAX_DICT = 8192;
 
@@ -71,14 +82,14 @@ template <typename T> constexpr int f3_stages() {
              ? 8
              : (F3_SMEM_MAX - F3_MAX_DICT * 4 - 1024) / F3<T>::TILE;
 }
-// roles per CTA: 1 producer warp, G groups of 8 stride-1 warps, C warps for the
+// roles per CTA: F3_NP producer warps, G groups of 8 stride-1 warps, C warps for the
 // stride-2 / stride-4 passes (about 1.6 warp-tiles of work per tile against 8 for
 // the stride-1 pass).  fp64 values take two registers: fewer threads, more each.
 template <typename T> struct F3Cfg {
   static constexpr int S = f3_stages<T>();
   static constexpr int G = sizeof(T) == 4 ? 3 : 2;
   static constexpr int C = sizeof(T) == 4 ? 5 : 3;
-  static constexpr int WARPS = 1 + G * F3_GW + C;
+  static constexpr int WARPS = F3_NP + G * F3_GW + C;
   static constexpr int THREADS = 32 * WARPS;
   static_assert(G <= S && C <= S, "end markers need a stage each");
 };
@@ -91,6 +102,8 @@ struct F3Info {
 
 template <typename T> struct F3Args {
   T cmax;               // |c| <= cmax  <=>  the coefficient quantises to code 0
+  uint32_t sh_b, sh_c;  // staging shifts: B(m) = m * sh_b mod E, A(p) = p * sh_c mod E
+  uint32_t dbg;         // MGX_F3_DBG (measurements only): 1 = no compute, 2 = no loads
   uint32_t rt[3];       // regular tiles per axis (z, y, x)
   uint32_t sby, sbz;    // super blocks (8 x 8 tiles in y, z)
   uint64_t padded;      // rt[2] * 64 * sby * sbz tile slots
@@ -111,8 +124,10 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
                "r"(bytes)
                : "memory");
 }
-// bounded wait: a protocol error traps instead of hanging the GPU
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+// bounded wait: a protocol error (or a lost TMA transaction) must not hang the
+// GPU.  On time-out the caller raises a flag in the context's error word and
+// leaves its loop; the host then reports MGX_FAILURE.
+__device__ __forceinline__ bool mbar_wait(uint32_t bar, uint32_t parity) {
   uint32_t done = 0;
   for (uint32_t spin = 0; !done; ++spin) {
     asm volatile("{\n\t.reg .pred p;\n\t"
@@ -121,9 +136,10 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
                  : "=r"(done)
                  : "r"(bar), "r"(parity)
                  : "memory");
-    if (spin > (1u << 24))
-      __trap();
+    if (spin > (1u << 22))
+      return false;
   }
+  return true;
 }
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map,
                                             uint32_t bar, int c0, int c1) {
@@ -217,16 +233,9 @@ template <typename T, bool HALF, int P>
 __device__ __forceinline__ void
 plane3(const char *r0p, const char *r2p, Plane3<T, HALF> &Q, T &odd0, T tx, T ty) {
   constexpr int H = 1 << P;
-  typedef typename std::conditional<sizeof(T) == 4, float2, double2>::type V2;
-  T e0, o0;
-  if constexpr (P == 0) {
-    const V2 own = *reinterpret_cast<const V2 *>(r0p);
-    e0 = own.x;
-    o0 = own.y;
-  } else {
-    e0 = *reinterpret_cast<const T *>(r0p);
-    o0 = *reinterpret_cast<const T *>(r0p + H * sizeof(T));
-  }
+  // (scalar loads: staged rows carry an element shift, pairs are not 8-byte aligned)
+  const T e0 = *reinterpret_cast<const T *>(r0p);
+  const T o0 = *reinterpret_cast<const T *>(r0p + H * sizeof(T));
   const T r0 = *reinterpret_cast<const T *>(r0p + 2 * H * sizeof(T));
   const T e2 = *reinterpret_cast<const T *>(r2p);
   const T r2 = *reinterpret_cast<const T *>(r2p + 2 * H * sizeof(T));
@@ -273,11 +282,11 @@ __device__ __forceinline__ T zlerp(const Plane3<T, HALF> &A, const Plane3<T, HAL
 
 // March of one thread along z at stride H = 2^P: NB consecutive 2 x 2 x 2 blocks
 // of the stride-H lattice whose anchor is (2k, 2ya, 2zb0) * H.  `tile` points at
-// the staged tile; ro[j] = F3::rowoff((2ya + j) * H).
+// the staged tile; ro[j] = row term of row (2ya + j) * H (row_term below).
 template <typename T, bool HALF, int P, int NB>
 __device__ __forceinline__ void
 march3(const char *tile, const T *__restrict__ tables, const HierArgs<T> &a,
-       const Sink3<T> &sink, int k, int ya, int zb0, const int (&ro)[3],
+       const Sink3<T> &sink, int k, int ya, int zb0, const int (&ro)[3], uint32_t sh_c,
        unsigned long long base, const uint32_t (&tc)[7], uint32_t x0, uint32_t y0,
        uint32_t z0) {
   typedef F3<T> G;
@@ -291,30 +300,30 @@ march3(const char *tile, const T *__restrict__ tables, const HierArgs<T> &a,
     ty = tables[a.roff[l][1] + (y0 >> P) + 2 * ya];
   }
   auto pair = [&](const char *q) -> V2 { // nodes x and x + H of a row
-    if constexpr (P == 0) {
-      return *reinterpret_cast<const V2 *>(q);
-    } else {
-      V2 v;
-      v.x = *reinterpret_cast<const T *>(q);
-      v.y = *reinterpret_cast<const T *>(q + H * sizeof(T));
-      return v;
-    }
+    V2 v;
+    v.x = *reinterpret_cast<const T *>(q);
+    v.y = *reinterpret_cast<const T *>(q + H * sizeof(T));
+    return v;
   };
-  const char *p = tile + (2 * zb0 * H) * G::PLANE + (2 * k * H) * (int)sizeof(T);
+  // staged plane i (relative to the march's first plane): plane term of the address
+  auto pl = [&](int i) -> int {
+    const int pp = (2 * zb0 + i) * H;
+    return pp * G::PLANE + (int)((pp * sh_c) & (G::E - 1)) * (int)sizeof(T);
+  };
+  const char *p = tile + (2 * k * H) * (int)sizeof(T);
   Plane3<T, HALF> A, B;
   T oA, oB;
-  plane3<T, HALF, P>(p + ro[0], p + ro[2], A, oA, tx, ty);
+  plane3<T, HALF, P>(p + pl(0) + ro[0], p + pl(0) + ro[2], A, oA, tx, ty);
 #pragma unroll
   for (int b = 0; b < NB; b++) {
-    const char *q = p + (2 * b * H) * G::PLANE;
-    const V2 r1 = pair(q + ro[1]);
-    plane3<T, HALF, P>(q + 2 * H * G::PLANE + ro[0], q + 2 * H * G::PLANE + ro[2], B, oB,
-                       tx, ty);
+    const char *q0 = p + pl(2 * b), *q1 = p + pl(2 * b + 1), *q2 = p + pl(2 * b + 2);
+    const V2 r1 = pair(q0 + ro[1]);
+    plane3<T, HALF, P>(q2 + ro[0], q2 + ro[2], B, oB, tx, ty);
     T tz = (T)0.5;
     if constexpr (!HALF)
       tz = tables[a.roff[l][0] + (z0 >> P) + 2 * (zb0 + b)];
-    const V2 s0 = pair(q + H * G::PLANE + ro[0]);
-    const V2 s1 = pair(q + H * G::PLANE + ro[1]);
+    const V2 s0 = pair(q1 + ro[0]);
+    const V2 s1 = pair(q1 + ro[1]);
     const T c[7] = {sub_rn(oA, A.f0),
                     sub_rn(r1.x, A.gE),
                     sub_rn(r1.y, A.gO),
@@ -331,6 +340,11 @@ march3(const char *tile, const T *__restrict__ tables, const HierArgs<T> &a,
     A = B;
     oA = oB;
   }
+}
+
+// row term of a staged address: offset of row m inside a plane + its shift B(m)
+template <typename T> __device__ __forceinline__ int row_term(int m, uint32_t sh_b) {
+  return F3<T>::rowoff(m) + (int)((m * sh_b) & (F3<T>::E - 1)) * (int)sizeof(T);
 }
 
 // element offsets of the 7 coefficient classes of pass P relative to the block's
@@ -378,27 +392,46 @@ __global__ void __launch_bounds__(F3Cfg<T>::THREADS, 1)
   const uint32_t ny = a.n[1], nx = a.n[2];
   const uint64_t sy = nx, sz = (uint64_t)nx * ny;
 
-  if (warp == 0) {
-    // ------------------------------------------------ producer (one lane)
-    if (lane == 0) {
-      const uint32_t T2 = fa.rt[2];
-      const uint32_t SB = T2 * 64;
-      int s = 0;
-      uint32_t ph = 0;
-      auto next_stage = [&]() {
-        if (++s == S) {
-          s = 0;
-          ph ^= 1;
-        }
-      };
-      for (uint64_t q = blockIdx.x; q < fa.padded; q += gridDim.x) {
-        const uint32_t sb = (uint32_t)(q / SB), r = (uint32_t)(q % SB);
-        const uint32_t tx = r % T2, r2 = r / T2;
-        const uint32_t ty = (sb % fa.sby) * 8 + (r2 & 7), tz = (sb / fa.sby) * 8 + (r2 >> 3);
-        if (ty >= fa.rt[1] || tz >= fa.rt[0])
-          continue;
-        const uint32_t x0 = tx * G::TX, y0 = ty * G::TY, z0 = tz * G::TZ;
-        mbar_wait(empty0 + 8 * s, ph ^ 1);
+  unsigned long long *const err_word = a.out_count + (MGX_SC_ERR - MGX_SC_OUTLIERS);
+  if (warp < F3_NP) {
+    // ---- producers: F3_NP warps walk the same tile list; warp w issues the boxes
+    // of planes 3w .. 3w+2, one box per lane (a single thread issuing all 36 boxes
+    // of a tile was measured to be the bottleneck of the whole kernel: ~120
+    // cycles per UTMALDG with its operand set-up); warp 0 also arms the barrier
+    // and writes the tile descriptor
+    const uint32_t T2 = fa.rt[2];
+    const uint32_t SB = T2 * 64;
+    int s = 0;
+    uint32_t ph = 0;
+    bool ok = true;
+    auto next_stage = [&]() {
+      if (++s == S) {
+        s = 0;
+        ph ^= 1;
+      }
+    };
+    // this lane's box: plane p (0..8), row class m (0..3)
+    const int op = warp * (36 / F3_NP) + lane;
+    const bool has_op = lane < 36 / F3_NP;
+    const int bp = op >> 2, bm_ = op & 3;
+    const int bshift = (int)((bp * fa.sh_c) & (G::E - 1)) + (int)((bm_ * fa.sh_b) & (G::E - 1));
+    const uint32_t bdst = (uint32_t)(bp * G::PLANE + G::rowoff(bm_));
+    const CUtensorMap *const bmap = bm_ == 0 ? &tm3 : &tm2;
+    for (uint64_t q = blockIdx.x; q < fa.padded && ok; q += gridDim.x) {
+      const uint32_t sb = (uint32_t)(q / SB), r = (uint32_t)(q % SB);
+      const uint32_t tx = r % T2, r2 = r / T2;
+      const uint32_t ty = (sb % fa.sby) * 8 + (r2 & 7), tz = (sb / fa.sby) * 8 + (r2 >> 3);
+      if (ty >= fa.rt[1] || tz >= fa.rt[0])
+        continue;
+      const uint32_t x0 = tx * G::TX, y0 = ty * G::TY, z0 = tz * G::TZ;
+      ok = mbar_wait(empty0 + 8 * s, ph ^ 1);
+      if (!ok) {
+        if (lane == 0)
+          atomicOr(err_word, 0x100ull);
+        break;
+      }
+      const uint32_t bar = full0 + 8 * s;
+      if (warp == 0 && lane == 0) {
         F3Info &fi = info[s];
 #pragma unroll
         for (int P = 0; P < 3; P++)
@@ -408,49 +441,61 @@ __global__ void __launch_bounds__(F3Cfg<T>::THREADS, 1)
         fi.x0 = x0;
         fi.y0 = y0;
         fi.z0 = z0;
-        const uint32_t bar = full0 + 8 * s;
+        // (boxes of the other producer warps may land first: the phase cannot
+        // complete before this arrival)
         mbar_expect_tx(bar, G::TX_BYTES);
-        const uint32_t dst0 = saddr(tiles + (size_t)s * G::TILE);
-#pragma unroll 1
-        for (int p = 0; p < 9; p++) {
-          const uint32_t R0 = (z0 + p) * ny + y0;
-#pragma unroll
-          for (int m = 0; m < 4; m++) {
-            const uint32_t R = R0 + m;
-            tma_load_2d(dst0 + p * G::PLANE + G::rowoff(m), m == 0 ? &tm3 : &tm2, bar,
-                        (int)((R & 3) * nx + x0), (int)(R >> 2));
-          }
-        }
-        next_stage();
       }
-      // end markers: one for every consumer role's next tile slot
-      for (int e = 0; e < (F3_G > F3_C ? F3_G : F3_C); e++) {
-        mbar_wait(empty0 + 8 * s, ph ^ 1);
-        info[s].x0 = 0xffffffffu;
-        mbar_arrive(full0 + 8 * s);
-        next_stage();
+      if (has_op) {
+        const uint32_t R = (z0 + bp) * ny + y0 + bm_;
+        // start A(p) + B(m) elements before the node: a 16-byte boundary
+        tma_load_2d(saddr(tiles + (size_t)s * G::TILE) + bdst, bmap, bar,
+                    (int)((R & 3) * nx + x0) - bshift, (int)(R >> 2));
       }
+      __syncwarp();
+      next_stage();
     }
+    // end markers: one for every consumer role's next tile slot (on a time-out
+    // the markers are written without waiting, so that every role terminates)
+    if (warp == 0)
+      for (int e = 0; e < (F3_G > F3_C ? F3_G : F3_C); e++) {
+        if (ok && !mbar_wait(empty0 + 8 * s, ph ^ 1)) {
+          ok = false;
+          if (lane == 0)
+            atomicOr(err_word, 0x200ull);
+        }
+        if (lane == 0) {
+          info[s].x0 = 0xffffffffu;
+          mbar_arrive(full0 + 8 * s);
+        }
+        __syncwarp();
+        next_stage();
+      }
   } else {
     const Sink3<T> sink{a, fa.cmax, saddr(s_hist)};
-    const int cw = warp - 1;
+    const int cw = warp - F3_NP;
     if (cw < F3_G * F3_GW) {
       // ---------------------------------- stride-1 pass: group g, warp iw
       const int g = cw / F3_GW, iw = cw % F3_GW;
       const int k = lane, ya = iw & 3, zb0 = (iw >> 2) * 2;
-      const int ro[3] = {G::rowoff(2 * ya), G::rowoff(2 * ya + 1), G::rowoff(2 * ya + 2)};
+      const int ro[3] = {row_term<T>(2 * ya, fa.sh_b), row_term<T>(2 * ya + 1, fa.sh_b),
+                         row_term<T>(2 * ya + 2, fa.sh_b)};
       uint32_t tc[7];
       class_offsets<T>(a, 0, (uint32_t)(zb0 * sz + ya * sy + k), tc);
       int s = g;
       uint32_t ph = 0;
       while (true) {
-        mbar_wait(full0 + 8 * s, ph);
+        if (!mbar_wait(full0 + 8 * s, ph)) {
+          if (lane == 0)
+            atomicOr(err_word, 0x400ull);
+          break;
+        }
         const F3Info &fi = info[s];
         const uint32_t x0 = fi.x0;
         if (x0 == 0xffffffffu)
           break;
+        if (!(fa.dbg & 1))
         march3<T, HALF, 0, 2>((const char *)tiles + (size_t)s * G::TILE, tables, a, sink, k,
-                              ya, zb0, ro, fi.base[0], tc, x0, fi.y0, fi.z0);
+                              ya, zb0, ro, fa.sh_c, fi.base[0], tc, x0, fi.y0, fi.z0);
         __syncwarp();
         if (lane == 0)
           mbar_arrive(empty0 + 8 * s);
@@ -465,27 +510,35 @@ __global__ void __launch_bounds__(F3Cfg<T>::THREADS, 1)
       const int c = cw - F3_G * F3_GW;
       // stride 2: 16 x 2 x 2 blocks, lane = (k, ya), march over both z blocks
       const int k1 = lane & 15, ya1 = lane >> 4;
-      const int ro1[3] = {G::rowoff(4 * ya1), G::rowoff(4 * ya1 + 2), G::rowoff(4 * ya1 + 4)};
+      const int ro1[3] = {row_term<T>(4 * ya1, fa.sh_b), row_term<T>(4 * ya1 + 2, fa.sh_b),
+                          row_term<T>(4 * ya1 + 4, fa.sh_b)};
       uint32_t tc1[7];
       class_offsets<T>(a, 1, (uint32_t)(ya1 * sy + k1), tc1);
       // stride 4: 8 x 1 x 1 blocks, lanes 0..7
-      const int ro2[3] = {G::rowoff(0), G::rowoff(4), G::rowoff(8)};
+      const int ro2[3] = {row_term<T>(0, fa.sh_b), row_term<T>(4, fa.sh_b),
+                          row_term<T>(8, fa.sh_b)};
       uint32_t tc2[7];
       class_offsets<T>(a, 2, (uint32_t)(lane & 7), tc2);
       int s = c % S;
       uint32_t ph = (c / S) & 1;
       while (true) {
-        mbar_wait(full0 + 8 * s, ph);
+        if (!mbar_wait(full0 + 8 * s, ph)) {
+          if (lane == 0)
+            atomicOr(err_word, 0x800ull);
+          break;
+        }
         const F3Info &fi = info[s];
         const uint32_t x0 = fi.x0;
         if (x0 == 0xffffffffu)
           break;
         const char *tile = (const char *)tiles + (size_t)s * G::TILE;
-        march3<T, HALF, 1, 2>(tile, tables, a, sink, k1, ya1, 0, ro1, fi.base[1], tc1, x0,
+        if (!(fa.dbg & 1)) {
+        march3<T, HALF, 1, 2>(tile, tables, a, sink, k1, ya1, 0, ro1, fa.sh_c, fi.base[1], tc1, x0,
                               fi.y0, fi.z0);
         if (lane < 8)
-          march3<T, HALF, 2, 1>(tile, tables, a, sink, lane, 0, 0, ro2, fi.base[2], tc2, x0,
+          march3<T, HALF, 2, 1>(tile, tables, a, sink, lane, 0, 0, ro2, fa.sh_c, fi.base[2], tc2, x0,
                                 fi.y0, fi.z0);
+        }
         __syncwarp();
         if (lane == 0)
           mbar_arrive(empty0 + 8 * s);
@@ -657,15 +710,21 @@ int launch_fwd3(mgx_ctx *ctx, const void *d_in, HierArgs<T> &a, bool *used) {
   fa.rt[1] = (uint32_t)((ny - 1) / G::TY);
   fa.rt[2] = (uint32_t)((nx - 1) / G::TX);
   // The box of the array's very last row is 16-byte granular and may reach up to
-  // 3 elements past the end of the array (only when that row is not the fourth
-  // of its super row, where the tensor bound clips it).  Harmless as long as
-  // those bytes share a page with the last element; else use the LDGSTS kernel.
+  // BX - 65 elements past the end of the array (only when that row is not the
+  // fourth of its super row, where the tensor bound clips it).  Harmless as long
+  // as those bytes share a page with the last element; else use the LDGSTS kernel.
   if ((uint64_t)(fa.rt[2] - 1) * G::TX + G::BX > nx && fa.rt[1] * (uint64_t)G::TY == ny - 1 &&
       fa.rt[0] * (uint64_t)G::TZ == nz - 1 && ((nz * ny) & 3) != 0) {
     const uintptr_t end = (uintptr_t)d_in + N * sizeof(T);
-    if ((end & 4095) == 0 || (end & 4095) > 4096 - 16)
+    if ((end & 4095) == 0 || (end & 4095) > 4096 - 32)
       return MGX_SUCCESS;
   }
+  {
+    const char *e = getenv("MGX_F3_DBG");
+    fa.dbg = e ? (uint32_t)atoi(e) : 0;
+  }
+  fa.sh_b = (uint32_t)(nx % G::E);
+  fa.sh_c = (uint32_t)((ny * nx) % G::E);
   fa.sby = (fa.rt[1] + 7) / 8;
   fa.sbz = (fa.rt[0] + 7) / 8;
   fa.padded = (uint64_t)fa.rt[2] * 64 * fa.sby * fa.sbz;

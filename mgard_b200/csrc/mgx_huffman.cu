@@ -803,6 +803,11 @@ int mgxk_encode_container(mgx_ctx *ctx, uint64_t n, uint8_t *d_out, uint64_t cap
     ctx->err = "longest Huffman codeword exceeds 56 bits"; // GetCodebook.hpp:111
     return MGX_FAILURE;
   }
+  if (ctx->h_scalars[MGX_SC_ERR] & 0xf00ull) {
+    ctx->err = "forward pass: tile pipeline timed out (flags " +
+               std::to_string(ctx->h_scalars[MGX_SC_ERR]) + ")";
+    return MGX_FAILURE;
+  }
   if (ctx->h_scalars[MGX_SC_ERR] & ~8ull) {
     ctx->err = "codebook construction failed";
     return MGX_FAILURE;

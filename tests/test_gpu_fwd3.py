@@ -55,14 +55,15 @@ def test_codes_equal_the_oracle(shape, dtype, rel, tol, kind):
 
 
 @pytest.mark.parametrize("shape,dtype", SHAPES)
-@pytest.mark.parametrize("kind,tol", [("smooth", 1e-3), ("rough", 1e-4), ("rough", 2e-6)])
+@pytest.mark.parametrize("kind,tol", [("smooth", 1e-3), ("rough", 1e-4), ("rough", 2e-5)])
 def test_containers_equal_the_oracle_and_the_ldgsts_kernels(shape, dtype, kind, tol,
                                                             monkeypatch):
     u = smooth_field(shape, dtype) if kind == "smooth" else rough_field(shape, dtype)
     want, wnorm = Oracle("port").compress(u, 1, tol, INF)
     d = torch.from_numpy(u).cuda()
     comp = make(shape, dtype)
-    blob, norm = comp.Compress(d, mg.REL, tol, INF)
+    big = lambda: torch.empty(6 * u.nbytes + (1 << 20), dtype=torch.uint8, device="cuda")
+    blob, norm = comp.Compress(d, mg.REL, tol, INF, out=big())
     got = blob.cpu().numpy()
     assert norm == wnorm
     assert got.size == want.size and np.array_equal(np.delete(got, 7), np.delete(want, 7)), \
@@ -70,10 +71,10 @@ def test_containers_equal_the_oracle_and_the_ldgsts_kernels(shape, dtype, kind, 
     monkeypatch.setenv("MGX_NO_TMA", "1")
     comp_old = make(shape, dtype)
     monkeypatch.delenv("MGX_NO_TMA")
-    blob_old, _ = comp_old.Compress(d, mg.REL, tol, INF)
+    blob_old, _ = comp_old.Compress(d, mg.REL, tol, INF, out=big())
     assert torch.equal(blob, blob_old), "TMA and LDGSTS kernel families disagree"
     # twice in a row on one context (histogram / outlier counters are reset per call)
-    blob2, _ = comp.Compress(d, mg.REL, tol, INF)
+    blob2, _ = comp.Compress(d, mg.REL, tol, INF, out=big())
     assert torch.equal(blob, blob2)
     dec = comp.Decompress(blob, mg.REL, tol, INF, norm).cpu().numpy()
     assert np.abs(dec.astype(np.float64) - u.astype(np.float64)).max() <= tol * norm
