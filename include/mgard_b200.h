@@ -147,6 +147,13 @@ int mgx_subdomain_shape(int D, const uint64_t *shape, int dim, uint64_t size,
 double mgx_local_abs_tol(int dtype, int rel, double norm, double tol, double s,
                          uint64_t num_subdomains);
 
+/* Histogram of the (shifted, outlier-zeroed) symbols of the context's last
+ * mgx_compress / mgx_hier_quantize / mgx_huff_encode call: dict_size uint32 counts
+ * copied to HOST memory.  Replaces reading Huffman's freq workspace
+ * (ParallelHuffman/Histogram.hpp:15-235, HuffmanWorkspace.hpp: freq_subarray);
+ * lets stage A13 be parity-checked on its own. */
+int mgx_last_histogram(mgx_ctx *ctx, uint32_t *h_freq);
+
 /* kernels launched by this context since creation (bench.py's gpu_launches) */
 uint64_t mgx_launch_count(const mgx_ctx *ctx);
 

@@ -147,6 +147,13 @@ class Compressor:
     def max_compressed_bytes(self):
         return int(self.lib.mgx_max_compressed_bytes(self._ctx))
 
+    def LastHistogram(self):
+        """symbol histogram of the last Compress / DecomposeQuantizeFused /
+        LosslessCompress call (numpy uint32[dict])."""
+        h = np.empty(self.config.huff_dict_size, np.uint32)
+        self._check(self.lib.mgx_last_histogram(self._ctx, h.ctypes.data))
+        return h
+
     def launch_count(self):
         return int(self.lib.mgx_launch_count(self._ctx))
 

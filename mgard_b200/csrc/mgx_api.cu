@@ -170,6 +170,15 @@ const char *mgx_last_error(const mgx_ctx *ctx) {
 
 uint64_t mgx_launch_count(const mgx_ctx *ctx) { return ctx ? ctx->launches : 0; }
 
+int mgx_last_histogram(mgx_ctx *ctx, uint32_t *h_freq) {
+  if (!ctx || !ctx->planned || !ctx->d_freq || !h_freq)
+    return MGX_FAILURE;
+  MGX_CUDA(cudaMemcpyAsync(h_freq, ctx->d_freq, (size_t)ctx->dict * 4,
+                           cudaMemcpyDeviceToHost, ctx->stream));
+  MGX_CUDA(cudaStreamSynchronize(ctx->stream));
+  return MGX_SUCCESS;
+}
+
 int mgx_set_timing(mgx_ctx *ctx, int on) {
   if (!ctx)
     return MGX_FAILURE;

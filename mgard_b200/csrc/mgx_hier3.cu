@@ -73,7 +73,7 @@ template <typename T> struct F3 {
 };
 
 constexpr int F3_GW = 8; // stride-1 warps per group (one tile per group at a time)
-constexpr int F3_NP = 3; // producer warps (12 of a tile's 36 boxes each)
+constexpr int F3_NP = 4; // producer warps (9 of a tile's 36 boxes each)
 constexpr int F3_SMEM_MAX = 227 * 1024;
 constexpr int F3_MAX_DICT = 8192;
 
@@ -88,7 +88,7 @@ template <typename T> constexpr int f3_stages() {
 template <typename T> struct F3Cfg {
   static constexpr int S = f3_stages<T>();
   static constexpr int G = sizeof(T) == 4 ? 3 : 2;
-  static constexpr int C = sizeof(T) == 4 ? 5 : 3;
+  static constexpr int C = sizeof(T) == 4 ? 4 : 3;
   static constexpr int WARPS = F3_NP + G * F3_GW + C;
   static constexpr int THREADS = 32 * WARPS;
   static_assert(G <= S && C <= S, "end markers need a stage each");
@@ -97,7 +97,8 @@ template <typename T> struct F3Cfg {
 // per-stage tile descriptor written by the producer
 struct F3Info {
   unsigned long long base[3]; // address of the tile's first symbol of pass P (block 0)
-  uint32_t x0, y0, z0, pad;
+  uint32_t x0, y0, z0;
+  uint32_t seq; // index of the tile in this CTA's sequence (see full_wait)
 };
 
 template <typename T> struct F3Args {
@@ -107,6 +108,7 @@ template <typename T> struct F3Args {
   uint32_t rt[3];       // regular tiles per axis (z, y, x)
   uint32_t sby, sbz;    // super blocks (8 x 8 tiles in y, z)
   uint64_t padded;      // rt[2] * 64 * sby * sbz tile slots
+  uint32_t step[4];     // gridDim.x in the mixed radix (rt[2], 64, sby, sbz) of a slot index
 };
 
 // ------------------------------------------------------------- PTX wrappers
@@ -140,6 +142,34 @@ __device__ __forceinline__ bool mbar_wait(uint32_t bar, uint32_t parity) {
       return false;
   }
   return true;
+}
+// Consumer side of a full barrier.  The stages of the ring are NOT consumed by
+// the same warps in successive rounds (tile j goes to group j mod G and stride-2
+// warp j mod C, stage j mod S), so a fast consumer can reach the barrier of its
+// next tile while the PREVIOUS round of that stage is still loading; a parity
+// wait alone would then return at once (it reads the completed round before that
+// one) and the warp would re-process the stage's old tile.  The producer
+// therefore numbers the tiles: only when the descriptor of tile j is in place --
+// which implies that the previous round was consumed and the barrier is in tile
+// j's phase -- does the parity test mean "tile j has landed".
+__device__ __forceinline__ bool full_wait(uint32_t bar, uint32_t parity,
+                                          const volatile uint32_t *seq, uint32_t j) {
+  for (uint32_t spin = 0; spin < (1u << 24); ++spin) {
+    if (*seq == j) {
+      uint32_t done;
+      asm volatile("{\n\t.reg .pred p;\n\t"
+                   "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                   "selp.u32 %0, 1, 0, p;\n\t}"
+                   : "=r"(done)
+                   : "r"(bar), "r"(parity)
+                   : "memory");
+      if (done)
+        return true;
+    } else {
+      __nanosleep(32);
+    }
+  }
+  return false;
 }
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map,
                                             uint32_t bar, int c0, int c1) {
@@ -383,6 +413,7 @@ __global__ void __launch_bounds__(F3Cfg<T>::THREADS, 1)
     s_hist[i] = 0;
   if (tid == 0) {
     for (int s = 0; s < S; s++) {
+      info[s].seq = 0xffffffffu;
       mbar_init(full0 + 8 * s, 1);
       mbar_init(empty0 + 8 * s, F3_GW + 1);
     }
@@ -395,16 +426,17 @@ __global__ void __launch_bounds__(F3Cfg<T>::THREADS, 1)
   unsigned long long *const err_word = a.out_count + (MGX_SC_ERR - MGX_SC_OUTLIERS);
   if (warp < F3_NP) {
     // ---- producers: F3_NP warps walk the same tile list; warp w issues the boxes
-    // of planes 3w .. 3w+2, one box per lane (a single thread issuing all 36 boxes
+    // of of 36 / F3_NP consecutive (plane, row class) pairs, one box per lane (a single thread issuing all 36 boxes
     // of a tile was measured to be the bottleneck of the whole kernel: ~120
     // cycles per UTMALDG with its operand set-up); warp 0 also arms the barrier
     // and writes the tile descriptor
     const uint32_t T2 = fa.rt[2];
     const uint32_t SB = T2 * 64;
     int s = 0;
-    uint32_t ph = 0;
+    uint32_t ph = 0, seq = 0;
     bool ok = true;
     auto next_stage = [&]() {
+      ++seq;
       if (++s == S) {
         s = 0;
         ph ^= 1;
@@ -417,10 +449,28 @@ __global__ void __launch_bounds__(F3Cfg<T>::THREADS, 1)
     const int bshift = (int)((bp * fa.sh_c) & (G::E - 1)) + (int)((bm_ * fa.sh_b) & (G::E - 1));
     const uint32_t bdst = (uint32_t)(bp * G::PLANE + G::rowoff(bm_));
     const CUtensorMap *const bmap = bm_ == 0 ? &tm3 : &tm2;
-    for (uint64_t q = blockIdx.x; q < fa.padded && ok; q += gridDim.x) {
-      const uint32_t sb = (uint32_t)(q / SB), r = (uint32_t)(q % SB);
-      const uint32_t tx = r % T2, r2 = r / T2;
-      const uint32_t ty = (sb % fa.sby) * 8 + (r2 & 7), tz = (sb / fa.sby) * 8 + (r2 >> 3);
+    // slot index of this CTA's next tile as mixed-radix digits (x tile, slot in the
+    // 8 x 8 super block, super block y, super block z), advanced by gridDim.x per
+    // step without divisions
+    uint32_t tx = blockIdx.x % T2, w = (blockIdx.x / T2) % 64, by = (blockIdx.x / SB) % fa.sby,
+             bz = (blockIdx.x / SB) / fa.sby;
+    for (; bz < fa.sbz && ok; tx += fa.step[0], w += fa.step[1], by += fa.step[2],
+                              bz += fa.step[3]) {
+      if (tx >= T2) {
+        tx -= T2;
+        ++w;
+      }
+      if (w >= 64) {
+        w -= 64;
+        ++by;
+      }
+      if (by >= fa.sby) {
+        by -= fa.sby;
+        ++bz;
+      }
+      if (bz >= fa.sbz)
+        break;
+      const uint32_t ty = by * 8 + (w & 7), tz = bz * 8 + (w >> 3);
       if (ty >= fa.rt[1] || tz >= fa.rt[0])
         continue;
       const uint32_t x0 = tx * G::TX, y0 = ty * G::TY, z0 = tz * G::TZ;
@@ -441,10 +491,13 @@ __global__ void __launch_bounds__(F3Cfg<T>::THREADS, 1)
         fi.x0 = x0;
         fi.y0 = y0;
         fi.z0 = z0;
+        fi.seq = seq;
         // (boxes of the other producer warps may land first: the phase cannot
         // complete before this arrival)
         mbar_expect_tx(bar, G::TX_BYTES);
       }
+      if (fa.dbg & 4)
+        asm volatile("bar.sync 1, %0;" ::"n"(F3_NP * 32) : "memory");
       if (has_op) {
         const uint32_t R = (z0 + bp) * ny + y0 + bm_;
         // start A(p) + B(m) elements before the node: a 16-byte boundary
@@ -465,6 +518,7 @@ __global__ void __launch_bounds__(F3Cfg<T>::THREADS, 1)
         }
         if (lane == 0) {
           info[s].x0 = 0xffffffffu;
+          info[s].seq = seq;
           mbar_arrive(full0 + 8 * s);
         }
         __syncwarp();
@@ -483,8 +537,8 @@ __global__ void __launch_bounds__(F3Cfg<T>::THREADS, 1)
       class_offsets<T>(a, 0, (uint32_t)(zb0 * sz + ya * sy + k), tc);
       int s = g;
       uint32_t ph = 0;
-      while (true) {
-        if (!mbar_wait(full0 + 8 * s, ph)) {
+      for (uint32_t j = g;; j += F3_G) {
+        if (!full_wait(full0 + 8 * s, ph, &info[s].seq, j)) {
           if (lane == 0)
             atomicOr(err_word, 0x400ull);
           break;
@@ -521,8 +575,8 @@ __global__ void __launch_bounds__(F3Cfg<T>::THREADS, 1)
       class_offsets<T>(a, 2, (uint32_t)(lane & 7), tc2);
       int s = c % S;
       uint32_t ph = (c / S) & 1;
-      while (true) {
-        if (!mbar_wait(full0 + 8 * s, ph)) {
+      for (uint32_t j = c;; j += F3_C) {
+        if (!full_wait(full0 + 8 * s, ph, &info[s].seq, j)) {
           if (lane == 0)
             atomicOr(err_word, 0x800ull);
           break;
@@ -729,6 +783,17 @@ int launch_fwd3(mgx_ctx *ctx, const void *d_in, HierArgs<T> &a, bool *used) {
   fa.sbz = (fa.rt[0] + 7) / 8;
   fa.padded = (uint64_t)fa.rt[2] * 64 * fa.sby * fa.sbz;
   fa.cmax = zero_threshold<T>(a.qv);
+  if (getenv("MGX_F3_NOZERO"))
+    fa.cmax = (T)-1;
+  {
+    uint64_t g = std::min<uint64_t>((uint64_t)fa.rt[0] * fa.rt[1] * fa.rt[2], (uint64_t)ctx->num_sms);
+    fa.step[0] = (uint32_t)(g % fa.rt[2]);
+    g /= fa.rt[2];
+    fa.step[1] = (uint32_t)(g % 64);
+    g /= 64;
+    fa.step[2] = (uint32_t)(g % fa.sby);
+    fa.step[3] = (uint32_t)(g / fa.sby);
+  }
   for (int p = 0; p < 12; p++) {
     const int l = a.L - p;
     const uint64_t sy = a.n[2], sz = (uint64_t)a.n[2] * a.n[1];

@@ -4,7 +4,7 @@
 mkdir -p gpurun_out
 (timeout 900 python -m pytest tests/test_gpu_fwd3.py -x -q 2>&1 | tail -15) > gpurun_out/fwd3_tests.log
 tail -6 gpurun_out/fwd3_tests.log
-for v in 0 1; do for t in 1e-3 1e-5; do
+for v in ${AB_VARIANTS:-0 1}; do for t in 1e-3 1e-5; do
 echo "MGX_NO_TMA=$v tol=$t"
 MGX_NO_TMA=$v timeout 300 python bench.py --no-cpu --no-e2e --no-extra --tol $t 2>gpurun_out/bench_err_$v.log | python -c "
 import json,sys
