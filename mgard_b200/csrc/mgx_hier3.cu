@@ -147,29 +147,23 @@ __device__ __forceinline__ bool mbar_wait(uint32_t bar, uint32_t parity) {
 // the same warps in successive rounds (tile j goes to group j mod G and stride-2
 // warp j mod C, stage j mod S), so a fast consumer can reach the barrier of its
 // next tile while the PREVIOUS round of that stage is still loading; a parity
-// wait alone would then return at once (it reads the completed round before that
-// one) and the warp would re-process the stage's old tile.  The producer
-// therefore numbers the tiles: only when the descriptor of tile j is in place --
-// which implies that the previous round was consumed and the barrier is in tile
-// j's phase -- does the parity test mean "tile j has landed".
+// wait alone would then return at once (it would be reading the completed round
+// before that one) and the warp would re-process the stage's old tile -- seen on
+// hardware as double-counted histogram bins and extra empty arrivals.  "Previous
+// round still loading" and "own round complete" show the same parity, so the
+// producer numbers the tiles: once the descriptor of tile j is in place -- which
+// implies that the previous round was consumed and the barrier is in tile j's
+// phase -- the parity test means "tile j has landed".  The descriptor is written
+// when the loads are ISSUED, a microsecond before they land, so polling it with
+// a 200 ns back-off adds no latency and next to no instructions.
 __device__ __forceinline__ bool full_wait(uint32_t bar, uint32_t parity,
                                           const volatile uint32_t *seq, uint32_t j) {
-  for (uint32_t spin = 0; spin < (1u << 24); ++spin) {
-    if (*seq == j) {
-      uint32_t done;
-      asm volatile("{\n\t.reg .pred p;\n\t"
-                   "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-                   "selp.u32 %0, 1, 0, p;\n\t}"
-                   : "=r"(done)
-                   : "r"(bar), "r"(parity)
-                   : "memory");
-      if (done)
-        return true;
-    } else {
-      __nanosleep(32);
-    }
+  for (uint32_t spin = 0; *seq != j; ++spin) {
+    if (spin > (1u << 20))
+      return false;
+    __nanosleep(200);
   }
-  return false;
+  return mbar_wait(bar, parity);
 }
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map,
                                             uint32_t bar, int c0, int c1) {
