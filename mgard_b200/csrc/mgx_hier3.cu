@@ -73,7 +73,16 @@ template <typename T> struct F3 {
 };
 
 constexpr int F3_GW = 8; // stride-1 warps per group (one tile per group at a time)
-constexpr int F3_NP = 4; // producer warps (9 of a tile's 36 boxes each)
+#ifndef F3_NP_
+#define F3_NP_ 4
+#endif
+#ifndef F3_G_
+#define F3_G_ 3
+#endif
+#ifndef F3_C_
+#define F3_C_ 4
+#endif
+constexpr int F3_NP = F3_NP_; // producer warps (36 / F3_NP of a tile's 36 boxes each)
 constexpr int F3_SMEM_MAX = 227 * 1024;
 constexpr int F3_MAX_DICT = 8192;
 
@@ -87,8 +96,8 @@ template <typename T> constexpr int f3_stages() {
 // the stride-1 pass).  fp64 values take two registers: fewer threads, more each.
 template <typename T> struct F3Cfg {
   static constexpr int S = f3_stages<T>();
-  static constexpr int G = sizeof(T) == 4 ? 3 : 2;
-  static constexpr int C = sizeof(T) == 4 ? 4 : 3;
+  static constexpr int G = sizeof(T) == 4 ? F3_G_ : 2;
+  static constexpr int C = sizeof(T) == 4 ? F3_C_ : 3;
   static constexpr int WARPS = F3_NP + G * F3_GW + C;
   static constexpr int THREADS = 32 * WARPS;
   static_assert(G <= S && C <= S, "end markers need a stage each");
@@ -437,8 +446,9 @@ __global__ void __launch_bounds__(F3Cfg<T>::THREADS, 1)
       }
     };
     // this lane's box: plane p (0..8), row class m (0..3)
-    const int op = warp * (36 / F3_NP) + lane;
-    const bool has_op = lane < 36 / F3_NP;
+    constexpr int BPW = (36 + F3_NP - 1) / F3_NP;
+    const int op = min(warp * BPW + lane, 35);
+    const bool has_op = lane < BPW && warp * BPW + lane < 36;
     const int bp = op >> 2, bm_ = op & 3;
     const int bshift = (int)((bp * fa.sh_c) & (G::E - 1)) + (int)((bm_ * fa.sh_b) & (G::E - 1));
     const uint32_t bdst = (uint32_t)(bp * G::PLANE + G::rowoff(bm_));
