@@ -323,137 +323,145 @@ __global__ void __launch_bounds__(ENC_WARPS * 32)
 // symbols (2 B read per symbol, packed words written once).  Everything is
 // warp-granular -- no CTA barrier inside the loop:
 //  * a warp owns one chunk at a time (round-robin over a persistent, fully
-//    resident grid); a lane holds R runs of 8 consecutive symbols, fetched
-//    with 16-byte loads;
-//  * code lengths (and, when the longest code has at most 26 bits, the codes
-//    themselves) come from a packed table in shared memory; run bit offsets
-//    from warp scans;
-//  * the chunk's word offset comes from a decoupled look-back over CHUNKS,
-//    32 predecessors per probe, overlapped with the packing;
-//  * codes are appended MSB first into a zeroed shared-memory image of the
-//    chunk (32-bit units, atomicOr because neighbouring runs share units) which
-//    is then streamed to its final place in the container.  A chunk whose image
-//    would not fit (more than ENC_CAP_BITS bits per symbol on average) is
-//    packed straight into global memory instead.
+//    resident grid of one CTA per SM); a lane holds 8 R CONSECUTIVE symbols (the
+//    reference's 32-symbol "group" for the default chunk of 1024), fetched with R
+//    16-byte loads;
+//  * length pass (length_pass): table look-ups in shared memory, four symbols
+//    merged per 32-bit accumulator, two accumulators per 64-bit run blob; ONE warp
+//    scan per chunk turns the lanes' bit counts into first-bit offsets;
+//  * the chunk's word offset comes from a decoupled look-back over tiles of EW
+//    chunks (scanner warp), overlapped with the packing of the next two tiles;
+//  * a lane appends its blobs in order through LaneSink into a zeroed
+//    shared-memory image of the chunk (at most two atomicOr per lane: the units it
+//    shares with its neighbours), which is then streamed to its final place in
+//    the container.  A chunk whose image would not fit (more than ENC_CAP_BITS bits
+//    per symbol on average) is packed straight into global memory instead.
 constexpr int ENC_CAP_BITS = 10; // image capacity, bits per symbol on average
 constexpr int ENC_IMGS = 3;      // images per packer warp: packers run 2 tiles ahead
 constexpr u64 CODE_MASK = 0x00ffffffffffffffull;
 
-struct BitSink {
-  uint32_t *dst; // unit u of the MSB-first stream lives at dst[u ^ 1]
-  u64 acc;
-  uint32_t unit, fill;
-  __device__ __forceinline__ void begin(uint32_t *d, uint32_t bit) {
-    dst = d;
-    acc = 0;
-    unit = bit >> 5;
-    fill = bit & 31;
-  }
-  __device__ __forceinline__ void put32(u64 code, uint32_t len) { // len <= 32
-    acc |= code << (64 - fill - len); // (a shift by 64 yields 0 on the GPU)
-    fill += len;
-    if (fill >= 32) {
-      atomicOr(&dst[unit ^ 1], (uint32_t)(acc >> 32));
-      acc <<= 32;
-      fill -= 32;
-      ++unit;
-    }
-  }
-  __device__ __forceinline__ void put(u64 cw) {
-    const uint32_t len = (uint32_t)(cw >> 56);
-    const u64 code = cw & CODE_MASK;
-    if (len > 32) {
-      put32(code >> 32, len - 32);
-      put32(code & 0xffffffffull, 32);
-    } else if (len) {
-      put32(code, len);
-    }
-  }
-  __device__ __forceinline__ void end() {
-    if (fill)
-      atomicOr(&dst[unit ^ 1], (uint32_t)(acc >> 32));
-  }
-};
-
-__device__ __forceinline__ uint32_t sym_of(const uint4 &v, int e) {
+__device__ __forceinline__ uint32_t sym_of_dyn(const uint4 &v, int e) {
   const uint32_t w = e < 2 ? v.x : e < 4 ? v.y : e < 6 ? v.z : v.w;
   return (e & 1) ? (w >> 16) : (w & 0xffffu);
 }
 
-// s_tab[s] = len << 26 | (code & 0x3ffffff); codes longer than 26 bits (rare
-// symbols only) are fetched from the global codebook instead.
-template <int R, bool FULL>
-__device__ __forceinline__ void
-pack_runs(uint32_t *dst, const uint4 (&v)[R], const int (&cnt)[R],
-          const uint32_t (&start)[R], const uint32_t *s_tab,
-          const u64 *__restrict__ codebook) {
-  BitSink bs;
-#pragma unroll
-  for (int j = 0; j < R; j++) {
-    bs.begin(dst, start[j]);
-#pragma unroll
-    for (int e = 0; e < 8; e++) {
-      if (FULL || e < cnt[j]) {
-        const uint32_t s = sym_of(v[j], e);
-        const uint32_t t = s_tab[s];
-        if (__builtin_expect(t >= (27u << 26), 0))
-          bs.put(__ldg(&codebook[s]));
-        else
-          bs.put32(t & 0x3ffffffu, t >> 26);
-      }
-    }
-    bs.end();
+// Lane-sequential bit sink: a lane appends the codes of its OWN contiguous run of
+// symbols, MSB first.  Units it fills from their first bit are stored plainly;
+// only the unit it starts in (when it does not start on a unit boundary) and the
+// unit it ends in can be shared with neighbouring lanes and are merged with
+// atomicOr -- at most two shared-memory atomics per lane and chunk, where the
+// per-run placement needed up to three per run of 8 symbols.
+struct LaneSink {
+  uint32_t *dst; // unit u of the MSB-first stream lives at dst[u ^ 1]
+  uint32_t unit, fill, cur;
+  bool shared;
+  __device__ __forceinline__ void begin(uint32_t *d, uint32_t bit) {
+    dst = d;
+    unit = bit >> 5;
+    fill = bit & 31;
+    cur = 0;
+    shared = fill != 0;
   }
+  __device__ __forceinline__ void flush(uint32_t w) {
+    if (shared) {
+      atomicOr(&dst[unit ^ 1], w);
+      shared = false;
+    } else {
+      dst[unit ^ 1] = w;
+    }
+    ++unit;
+  }
+  // append the low nb bits of a (0 < nb <= 64)
+  __device__ __forceinline__ void append(u64 a, uint32_t nb) {
+    const u64 A = a << (64 - nb);
+    const uint32_t w0 = cur | (uint32_t)(A >> (32 + fill));
+    const uint32_t t = fill + nb;
+    if (t >= 32) {
+      flush(w0);
+      const uint32_t w1 = (uint32_t)(A >> fill);
+      if (t >= 64) {
+        flush(w1);
+        cur = (uint32_t)(A << (32 - fill));
+        fill = t - 64;
+      } else {
+        cur = w1;
+        fill = t - 32;
+      }
+    } else {
+      cur = w0;
+      fill = t;
+    }
+  }
+  __device__ __forceinline__ void end() {
+    if (fill)
+      atomicOr(&dst[unit ^ 1], cur);
+  }
+};
+
+__device__ __forceinline__ uint32_t lds_u32(uint32_t saddr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(saddr));
+  return v;
 }
 
-// A run whose codes total at most 64 bits (and none longer than 26) is already
-// merged into one MSB-first blob by the length pass; placing it takes at most
-// three unit-wide ORs and no per-symbol work.
-__device__ __forceinline__ void place64(uint32_t *dst, u64 blob, uint32_t bits,
-                                        uint32_t start) {
-  if (!bits)
-    return;
-  const u64 A = blob << (64 - bits);
-  const uint32_t unit = start >> 5, fill = start & 31;
-  const uint32_t u0 = (uint32_t)(A >> (32 + fill));
-  const uint32_t u1 = (uint32_t)(A >> fill);
-  const uint32_t u2 = fill ? (uint32_t)(A << (32 - fill)) : 0u;
-  if (u0)
-    atomicOr(&dst[unit ^ 1], u0);
-  if (u1)
-    atomicOr(&dst[(unit + 1) ^ 1], u1);
-  if (u2)
-    atomicOr(&dst[(unit + 2) ^ 1], u2);
-}
-
+// Length pass over one lane's 8 R consecutive symbols.  s_tab[s] = len << 26 |
+// code for codes of at most 26 bits, 0xffffffff otherwise.  Four symbols are
+// merged in a 32-bit accumulator, two such halves make the run's 64-bit blob; a
+// half whose lengths add up to more than 32 bits (which includes every marker:
+// its length field reads 63) sends the run to the per-symbol path.
 template <int R, bool FULL>
 __device__ __forceinline__ void
-pack_merged(uint32_t *dst, const uint4 (&v)[R], const int (&cnt)[R],
-            const uint32_t (&start)[R], const u64 (&blob)[R],
-            const uint32_t (&rbits)[R], unsigned slow, const uint32_t *s_tab,
-            const u64 *__restrict__ codebook) {
+length_pass(const uint4 (&v)[R], const int (&cnt)[R], uint32_t tab, u64 (&blob)[R],
+            uint32_t (&rbits)[R], unsigned &slow, unsigned &inexact, uint32_t &tot) {
+  slow = 0;
+  inexact = 0;
+  tot = 0;
 #pragma unroll
   for (int j = 0; j < R; j++) {
-    if (__builtin_expect((slow >> j) & 1u, 0)) {
-      BitSink bs;
-      bs.begin(dst, start[j]);
-#pragma unroll 1
-      for (int e = 0; e < 8; e++) {
-        if (FULL || e < cnt[j]) {
-          const uint32_t w = e < 2 ? v[j].x : e < 4 ? v[j].y : e < 6 ? v[j].z : v[j].w;
-          const uint32_t sy = (e & 1) ? (w >> 16) : (w & 0xffffu);
-          const uint32_t t = s_tab[sy];
-          if (t >= (27u << 26))
-            bs.put(__ldg(&codebook[sy]));
-          else
-            bs.put32(t & 0x3ffffffu, t >> 26);
+    const uint32_t w[4] = {v[j].x, v[j].y, v[j].z, v[j].w};
+    uint32_t acc[2], hb[2];
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      uint32_t a = 0, b = 0;
+#pragma unroll
+      for (int e = 0; e < 4; e++) {
+        const int idx = 4 * h + e;
+        if (FULL || idx < cnt[j]) {
+          const uint32_t ww = w[idx >> 1];
+          // byte offset of the symbol's entry: sym * 4
+          const uint32_t off = (idx & 1) ? ((ww >> 14) & 0x3fffcu) : ((ww << 2) & 0x3fffcu);
+          const uint32_t t = lds_u32(tab + off);
+          const uint32_t len = t >> 26;
+          b += len;
+          a = (a << len) | (t & 0x3ffffffu);
         }
       }
-      bs.end();
-    } else {
-      place64(dst, blob[j], rbits[j], start[j]);
+      acc[h] = a;
+      hb[h] = b;
     }
+    rbits[j] = hb[0] + hb[1];
+    blob[j] = ((u64)acc[0] << hb[1]) | acc[1];
+    if (max(hb[0], hb[1]) > 32u) {
+      slow |= 1u << j;
+      if (max(hb[0], hb[1]) >= 63u) // possibly a marker: the sum is not the bit count
+        inexact |= 1u << j;
+    }
+    tot += rbits[j];
   }
+}
+
+// exact bit count of a run on the per-symbol path (codes longer than 26 bits come
+// from the global codebook)
+__device__ __forceinline__ uint32_t slow_run_bits(const uint4 &v, int cnt, uint32_t tab,
+                                                  const u64 *__restrict__ codebook) {
+  uint32_t rb = 0;
+#pragma unroll 1
+  for (int e = 0; e < cnt; e++) {
+    const uint32_t sy = sym_of_dyn(v, e);
+    const uint32_t t = lds_u32(tab + sy * 4u);
+    rb += t == 0xffffffffu ? (uint32_t)(__ldg(&codebook[sy]) >> 56) : (t >> 26);
+  }
+  return rb;
 }
 
 // Tiles of ENC_WARPS chunks, one per packer warp, plus a ninth "scanner" warp.
@@ -465,26 +473,36 @@ pack_merged(uint32_t *dst, const uint4 (&v)[R], const int (&cnt)[R],
 // the latency of the look-back chain (which couples all resident CTAs) is
 // hidden behind a full tile of work.
 constexpr int ENC_SLOTS = 8;
+// packer warps (= chunks per tile) of the single-pass encoder.  ONE CTA per SM
+// with many warps, not several small CTAs: the look-back chain advances about 32
+// tiles per L2 round trip, so a wave of tiles (one per resident CTA) costs
+// ceil(CTAs / 32) round trips -- measured with 444 CTAs of 8 packers: 5.6 us per
+// wave against 1.5 us of packing, the whole kernel waiting for prefixes.
+template <int R> struct EncCfg {
+  static constexpr int EW = R == 8 ? 16 : 24;
+};
 
 template <int R>
-__global__ void __launch_bounds__((ENC_WARPS + 1) * 32, 3)
+__global__ void __launch_bounds__((EncCfg<R>::EW + 1) * 32, 1)
     k_encode(const uint16_t *__restrict__ sym, uint64_t n, uint32_t dict,
              const u64 *__restrict__ codebook, u64 *__restrict__ chunk_bits,
              u64 *__restrict__ chunk_off, u64 *__restrict__ packed,
              uint64_t cap_words, u64 *__restrict__ state, uint64_t nchunk,
              uint64_t ntiles, u64 *__restrict__ scalars) {
   constexpr int CHUNK = 256 * R;
+  constexpr int EW = EncCfg<R>::EW;
   constexpr int UNITS = CHUNK * ENC_CAP_BITS / 32; // per-warp image, u32 units
   extern __shared__ __align__(16) unsigned char enc_smem[];
-  uint32_t *s_img = (uint32_t *)enc_smem;                  // [ENC_IMGS][ENC_WARPS][UNITS]
-  uint32_t *s_tab = s_img + ENC_IMGS * ENC_WARPS * UNITS;  // dict entries
-  __shared__ uint32_t s_words[ENC_SLOTS][ENC_WARPS];
+  uint32_t *s_img = (uint32_t *)enc_smem;                  // [ENC_IMGS][EW][UNITS]
+  uint32_t *s_tab = s_img + ENC_IMGS * EW * UNITS;  // dict entries
+  __shared__ uint32_t s_words[ENC_SLOTS][EW];
   __shared__ uint32_t s_arrived[ENC_SLOTS];
   __shared__ u64 s_prefix[ENC_SLOTS];
   __shared__ uint32_t s_epoch[ENC_SLOTS];
   for (uint32_t i = threadIdx.x; i < dict; i += blockDim.x) {
     const u64 cw = codebook[i];
-    s_tab[i] = (uint32_t)(cw >> 56) << 26 | (uint32_t)(cw & 0x3ffffffu);
+    s_tab[i] = (cw >> 56) <= 26 ? (uint32_t)(cw >> 56) << 26 | (uint32_t)(cw & 0x3ffffffu)
+                                : 0xffffffffu;
   }
   if (threadIdx.x < ENC_SLOTS) {
     s_arrived[threadIdx.x] = 0;
@@ -492,18 +510,21 @@ __global__ void __launch_bounds__((ENC_WARPS + 1) * 32, 3)
   }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t tab = (uint32_t)__cvta_generic_to_shared(s_tab);
   volatile u64 *vs = state;
   volatile uint32_t *v_arrived = s_arrived, *v_epoch = s_epoch;
   volatile u64 *v_prefix = s_prefix;
+  const uint64_t t_begin = blockIdx.x, t_end = ntiles, t_step = gridDim.x;
+  const u64 region_words = cap_words;
 
-  if (warp == ENC_WARPS) { // ---- scanner ----------------------------------------
+  if (warp == EW) { // ---- scanner ----------------------------------------
     uint32_t iter = 0;
-    for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++iter) {
+    for (uint64_t tile = t_begin; tile < t_end; tile += t_step, ++iter) {
       const int slot = iter & (ENC_SLOTS - 1);
-      while (v_arrived[slot] != ENC_WARPS)
+      while (v_arrived[slot] != EW)
         __nanosleep(40); // leave the issue slots to the packers
       __threadfence_block();
-      u64 agg = lane < ENC_WARPS ? ((volatile uint32_t *)s_words[slot])[lane] : 0;
+      u64 agg = lane < EW ? ((volatile uint32_t *)s_words[slot])[lane] : 0;
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1)
         agg += __shfl_xor_sync(0xffffffffu, agg, o);
@@ -556,12 +577,14 @@ __global__ void __launch_bounds__((ENC_WARPS + 1) * 32, 3)
     while (v_epoch[slot] != it + 1)
       __nanosleep(100); // an issue-bound kernel: do not burn slots spinning
     __threadfence_block();
-    u64 off = v_prefix[slot];
-    for (int w = 0; w < warp; w++)
-      off += ((volatile uint32_t *)s_words[slot])[w];
+    uint32_t before = lane < warp ? ((volatile uint32_t *)s_words[slot])[lane] : 0u;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+      before += __shfl_xor_sync(0xffffffffu, before, o);
+    const u64 off = v_prefix[slot] + before;
     if (lane == 0)
       chunk_off[c] = off;
-    if (off + words > cap_words) {
+    if (off + words > region_words) {
       if (lane == 0)
         atomicOr((unsigned long long *)&scalars[MGX_SC_ERR], 8ull);
       return ~0ull;
@@ -579,69 +602,65 @@ __global__ void __launch_bounds__((ENC_WARPS + 1) * 32, 3)
     const u64 off = finish(it, c, words);
     if (off != ~0ull) {
       const u64 *src =
-          (const u64 *)(s_img + ((it % ENC_IMGS) * ENC_WARPS + warp) * UNITS);
+          (const u64 *)(s_img + ((it % ENC_IMGS) * EW + warp) * UNITS);
       for (uint32_t i = lane; i < words; i += 32)
         packed[off + i] = src[i];
     }
   };
-  for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++iter) {
+  for (uint64_t tile = t_begin; tile < t_end; tile += t_step, ++iter) {
     const int slot = iter & (ENC_SLOTS - 1);
-    uint32_t *img = s_img + ((iter % ENC_IMGS) * ENC_WARPS + warp) * UNITS;
-    const uint64_t c = tile * ENC_WARPS + warp;
+    uint32_t *img = s_img + ((iter % ENC_IMGS) * EW + warp) * UNITS;
+    const uint64_t c = tile * EW + warp;
     const bool have = c < nchunk;
     const uint64_t base = c * CHUNK;
     const bool full = have && base + CHUNK <= n;
     uint4 v[R];
     int cnt[R];
-    uint32_t start[R];
     {
       // pull the chunk this warp packs NEXT into L2 now: a warp works on one
       // chunk at a time, so its 2 B/symbol would otherwise arrive at DRAM
       // latency in front of every tile
-      const uint64_t nb = ((tile + gridDim.x) * ENC_WARPS + warp) * (uint64_t)CHUNK;
+      const uint64_t nb = ((tile + t_step) * EW + warp) * (uint64_t)CHUNK;
       const uint64_t pa = nb + (uint64_t)lane * 64; // 128-byte lines of uint16
       if (lane * 64 < CHUNK && pa < n)
         asm volatile("prefetch.global.L2 [%0];" ::"l"(sym + pa));
     }
+    // a lane owns 8 R CONSECUTIVE symbols (64 bytes for R = 4): R 16-byte loads
 #pragma unroll
     for (int j = 0; j < R; j++) {
-      const uint64_t idx = base + (uint64_t)(j * 32 + lane) * 8;
+      const uint64_t idx = base + (uint64_t)lane * (8 * R) + 8 * j;
       cnt[j] = full ? 8
                     : (!have || idx >= n) ? 0 : (n - idx >= 8 ? 8 : (int)(n - idx));
       v[j] = cnt[j] > 0 ? *(const uint4 *)(sym + idx) : make_uint4(0, 0, 0, 0);
     }
-    uint32_t carry = 0;
+    // length pass: every run of 8 symbols becomes one MSB-first blob
     u64 blob[R];
     uint32_t rbits[R];
-    unsigned slow = 0;
+    unsigned slow, inexact;
+    uint32_t tot;
+    if (full)
+      length_pass<R, true>(v, cnt, tab, blob, rbits, slow, inexact, tot);
+    else
+      length_pass<R, false>(v, cnt, tab, blob, rbits, slow, inexact, tot);
+    if (__builtin_expect(inexact != 0, 0)) {
 #pragma unroll
-    for (int j = 0; j < R; j++) {
-      uint32_t rb = 0, mx = 0;
-      u64 a = 0;
-#pragma unroll
-      for (int e = 0; e < 8; e++)
-        if (full || e < cnt[j]) {
-          const uint32_t t = s_tab[sym_of(v[j], e)];
-          const uint32_t len = t >> 26;
-          rb += len;
-          mx = max(mx, t);
-          a = (a << len) | (t & 0x3ffffffu);
+      for (int j = 0; j < R; j++)
+        if ((inexact >> j) & 1u) {
+          tot -= rbits[j];
+          rbits[j] = slow_run_bits(v[j], cnt[j], tab, codebook);
+          tot += rbits[j];
         }
-      blob[j] = a;
-      rbits[j] = rb;
-      if (rb > 64 || mx >= (27u << 26))
-        slow |= 1u << j;
-      uint32_t incl = rb;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o)
-          incl += t;
-      }
-      start[j] = carry + incl - rb;
-      carry += __shfl_sync(0xffffffffu, incl, 31);
     }
-    const u64 bits = carry;
+    // one scan per chunk: first bit of this lane's symbols
+    uint32_t incl = tot;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o)
+        incl += t;
+    }
+    const uint32_t start = incl - tot;
+    const u64 bits = __shfl_sync(0xffffffffu, incl, 31);
     const uint32_t words = (uint32_t)((bits + 63) >> 6);
     const bool fits = 2 * words <= (uint32_t)UNITS;
     if (lane == 0) {
@@ -651,15 +670,55 @@ __global__ void __launch_bounds__((ENC_WARPS + 1) * 32, 3)
       __threadfence_block();
       atomicAdd(&s_arrived[slot], 1u);
     }
+    // the lane appends its runs in order
+    auto emit = [&](uint32_t *dst) {
+      LaneSink sk;
+      sk.begin(dst, start);
+#pragma unroll
+      for (int j = 0; j < R; j++) {
+        if (__builtin_expect((slow >> j) & 1u, 0)) {
+          // more than 32 bits in a group of four symbols: merge each group in 64
+          // bits; symbol by symbol only when even that overflows or a code is
+          // longer than 26 bits
+#pragma unroll 1
+          for (int h = 0; h < 2; h++) {
+            const int e0 = 4 * h, e1 = min(4 * h + 4, cnt[j]);
+            u64 a = 0;
+            uint32_t b = 0;
+            bool marker = false;
+            for (int e = e0; e < e1; e++) {
+              const uint32_t t = lds_u32(tab + sym_of_dyn(v[j], e) * 4u);
+              marker |= t == 0xffffffffu;
+              b += t >> 26;
+              a = (a << (t >> 26)) | (t & 0x3ffffffu);
+            }
+            if (!marker && b <= 64) {
+              if (b)
+                sk.append(a, b);
+            } else {
+              for (int e = e0; e < e1; e++) {
+                const uint32_t sy = sym_of_dyn(v[j], e);
+                const uint32_t t = lds_u32(tab + sy * 4u);
+                if (t == 0xffffffffu) {
+                  const u64 cw = __ldg(&codebook[sy]);
+                  sk.append(cw & CODE_MASK, (uint32_t)(cw >> 56));
+                } else if (t >> 26) {
+                  sk.append(t & 0x3ffffffu, t >> 26);
+                }
+              }
+            }
+          }
+        } else if (rbits[j]) {
+          sk.append(blob[j], rbits[j]);
+        }
+      }
+      sk.end();
+    };
     if (have && fits) {
       for (uint32_t i = lane; i < 2 * words; i += 32)
         img[i] = 0;
       __syncwarp();
-      if (full)
-        pack_merged<R, true>(img, v, cnt, start, blob, rbits, slow, s_tab, codebook);
-      else
-        pack_merged<R, false>(img, v, cnt, start, blob, rbits, slow, s_tab,
-                              codebook);
+      emit(img);
       __syncwarp();
     }
     if (pendA)
@@ -680,8 +739,7 @@ __global__ void __launch_bounds__((ENC_WARPS + 1) * 32, 3)
         for (uint32_t i = lane; i < words; i += 32)
           packed[off + i] = 0;
         __syncwarp();
-        pack_runs<R, false>((uint32_t *)(packed + off), v, cnt, start, s_tab,
-                            codebook);
+        emit((uint32_t *)(packed + off));
       }
     }
     __syncwarp();
@@ -732,7 +790,7 @@ int mgxk_encode_container(mgx_ctx *ctx, uint64_t n, uint8_t *d_out, uint64_t cap
                           uint64_t *out_bytes) {
   const uint32_t chunk = ctx->chunk, dict = ctx->dict;
   const uint64_t nchunk = (n - 1) / chunk + 1;
-  const uint64_t ntiles = (nchunk + ENC_WARPS - 1) / ENC_WARPS;
+  uint64_t ntiles = (nchunk + ENC_WARPS - 1) / ENC_WARPS;
   HuffHeader h;
   h.n = n;
   h.nchunk = nchunk;
@@ -765,16 +823,18 @@ int mgxk_encode_container(mgx_ctx *ctx, uint64_t n, uint8_t *d_out, uint64_t cap
     // sizes, offsets and packed words in one pass, written straight into the
     // container (the capacity is enforced inside the kernel)
     const int R = (int)(chunk / 256);
+    const int ew = R == 8 ? EncCfg<8>::EW : EncCfg<4>::EW;
+    ntiles = (nchunk + ew - 1) / ew;
+    size_t smem = (size_t)ENC_IMGS * ew * (chunk * ENC_CAP_BITS / 32) * 4 + dict * 4;
     auto kern = R == 1 ? k_encode<1> : R == 2 ? k_encode<2> : R == 4 ? k_encode<4>
                                                                      : k_encode<8>;
-    size_t smem = (size_t)ENC_IMGS * ENC_WARPS * (chunk * ENC_CAP_BITS / 32) * 4 + dict * 4;
     MGX_CUDA(cudaFuncSetAttribute(
         kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     MGX_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(
-        &occ, kern, (ENC_WARPS + 1) * 32, smem));
+        &occ, kern, (ew + 1) * 32, smem));
     unsigned grid = (unsigned)std::min<uint64_t>(
         ntiles, (uint64_t)std::max(occ, 1) * ctx->num_sms);
-    kern<<<grid, (ENC_WARPS + 1) * 32, smem, ctx->stream>>>(
+    kern<<<grid, (ew + 1) * 32, smem, ctx->stream>>>(
         ctx->d_sym, n, dict, (const u64 *)ctx->d_codebook,
         (u64 *)(d_out + h.off_bits), (u64 *)(d_out + h.off_offs),
         (u64 *)(d_out + h.off_packed), (cap - h.off_packed) / 8,
