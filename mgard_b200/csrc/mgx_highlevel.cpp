@@ -1003,7 +1003,8 @@ int x_compress(int D, int dtype, const uint64_t *shape, double tol, double s,
       norm = nrm;
     const void *payload = c.cbuf[b];
     // CR < 1: store the subdomain itself (GPUPipelines.hpp:139-156)
-    if (rc == MGX_OUTPUT_TOO_LARGE || bytes > n_sub * es) {
+    // (>=: the decoder classifies a record of exactly n_sub * es bytes as raw)
+    if (rc == MGX_OUTPUT_TOO_LARGE || bytes >= n_sub * es) {
       payload = d_in;
       bytes = n_sub * es;
     }
@@ -1119,8 +1120,13 @@ int x_decompress(const void *in, size_t in_size, void **out, uint64_t *shape_out
   const int D = (int)md.D, dtype = md.dtype;
   const size_t es = dtype == MGX_F64 ? 8 : 4;
   uint64_t N = 1;
-  for (int d = 0; d < D; d++)
+  for (int d = 0; d < D; d++) {
+    // (only the header's own bytes are covered by its CRC: a zero extent or a
+    // product that does not fit 64 bits must be refused here)
+    if (md.shape[d] == 0 || md.shape[d] > (~0ull / es) / N)
+      return fail(MGX_FAILURE, "bad shape in the header");
     N *= md.shape[d];
+  }
   if (shape_out)
     for (int d = 0; d < D; d++)
       shape_out[d] = md.shape[d];
@@ -1180,6 +1186,8 @@ int x_decompress(const void *in, size_t in_size, void **out, uint64_t *shape_out
     sl.dim = (int)md.dd_dim;
     sl.size = md.dd_size;
     sl.num = (md.shape[sl.dim] - 1) / sl.size + 1;
+    if (sl.num > in_size / 8) // every subdomain record starts with an 8-byte size
+      return fail(MGX_FAILURE, "more subdomains in the header than the stream can hold");
   }
   sl.finish();
 
@@ -1287,6 +1295,19 @@ int x_decompress(const void *in, size_t in_size, void **out, uint64_t *shape_out
 }
 
 } // namespace
+
+// the caller's current device is the caller's business: put it back on return
+struct DeviceRestore {
+  int dev = -1;
+  DeviceRestore() {
+    if (cudaGetDevice(&dev) != cudaSuccess)
+      dev = -1;
+  }
+  ~DeviceRestore() {
+    if (dev >= 0)
+      cudaSetDevice(dev);
+  }
+};
 
 extern "C" {
 
@@ -1432,8 +1453,15 @@ int mgx_x_compress(int D, int dtype, const uint64_t *shape, double tol, double s
   else
     mgx_config_default(&c);
   g_err.clear();
-  return x_compress(D, dtype, shape, tol, s, mode, in, out, out_size, c,
-                    output_pre_allocated);
+  DeviceRestore restore;
+  try {
+    return x_compress(D, dtype, shape, tol, s, mode, in, out, out_size, c,
+                      output_pre_allocated);
+  } catch (const std::exception &e) { // no exception crosses the C ABI
+    return fail(MGX_FAILURE, std::string("compress: ") + e.what());
+  } catch (...) {
+    return fail(MGX_FAILURE, "compress: unknown exception");
+  }
 }
 
 int mgx_x_decompress(const void *in, size_t in_size, void **out,
@@ -1446,8 +1474,15 @@ int mgx_x_decompress(const void *in, size_t in_size, void **out,
   else
     mgx_config_default(&c);
   g_err.clear();
-  return x_decompress(in, in_size, out, shape_out, D_out, dtype_out, c,
-                      output_pre_allocated);
+  DeviceRestore restore;
+  try {
+    return x_decompress(in, in_size, out, shape_out, D_out, dtype_out, c,
+                        output_pre_allocated);
+  } catch (const std::exception &e) {
+    return fail(MGX_FAILURE, std::string("decompress: ") + e.what());
+  } catch (...) {
+    return fail(MGX_FAILURE, "decompress: unknown exception");
+  }
 }
 
 static int backend_ok(const mgx_config *cfg) {

@@ -16,6 +16,7 @@
 //  * decoding uses a 2^12-entry prefix table in shared memory with the
 //    canonical first[]/entry[] search only for longer codes.
 #include <algorithm>
+#include <limits>
 #include <cub/device/device_radix_sort.cuh>
 
 #include "mgx_device.cuh"
@@ -919,6 +920,10 @@ int mgxk_encode_container(mgx_ctx *ctx, uint64_t n, uint8_t *d_out, uint64_t cap
   // outliers in ascending index order (the SERIAL reference's order)
   k_write_outlier_count<<<1, 32, 0, ctx->stream>>>(d_out, off_outc, n_out);
   ctx->launches++;
+  if (n_out > (uint64_t)std::numeric_limits<int>::max()) {
+    ctx->err = "more than 2^31 outliers: the bound is far too tight for this dictionary";
+    return MGX_FAILURE;
+  }
   if (n_out) {
     size_t tmp = 0;
     cub::DeviceRadixSort::SortPairs(nullptr, tmp, (const u64 *)ctx->d_out_idx,
@@ -984,7 +989,7 @@ __global__ void __launch_bounds__(128)
     k_decode(const u64 *__restrict__ packed, const u64 *__restrict__ meta,
              uint64_t nchunk, uint32_t chunk, uint64_t n,
              const u64 *__restrict__ db, const uint32_t *__restrict__ g_lut,
-             uint16_t *__restrict__ sym) {
+             uint16_t *__restrict__ sym, uint32_t dict) {
   __shared__ uint32_t lut[1 << LUT_BITS];
   __shared__ u64 s_first[64], s_entry[64];
   for (uint32_t i = threadIdx.x; i < (1u << LUT_BITS); i += blockDim.x)
@@ -1023,7 +1028,7 @@ __global__ void __launch_bounds__(128)
           ++l;
           v = window >> (64 - l);
         } while (v < s_first[l] && l < 63);
-        s = (uint32_t)keys[s_entry[l] + v - s_first[l]];
+        s = (uint32_t)keys[min(s_entry[l] + v - s_first[l], (u64)dict - 1)];
         len = l;
       }
       stage[k & 7] = (uint16_t)s;
@@ -1092,7 +1097,7 @@ __global__ void __launch_bounds__(DEC_THREADS)
     k_decode_multi(const u64 *__restrict__ packed, const u64 *__restrict__ meta,
                    uint64_t nchunk, uint32_t chunk, uint64_t n,
                    const u64 *__restrict__ db, const u64 *__restrict__ g_mlut,
-                   uint16_t *__restrict__ sym) {
+                   uint16_t *__restrict__ sym, uint32_t dict) {
   __shared__ u64 mlut[1 << LUT_BITS];
   __shared__ u64 s_first[64], s_entry[64];
   __shared__ __align__(8) uint16_t s_ring[DEC_THREADS * DEC_RING];
@@ -1139,7 +1144,7 @@ __global__ void __launch_bounds__(DEC_THREADS)
           ++l;
           v = window >> (64 - l);
         } while (v < s_first[l] && l < 63);
-        ring[k] = (uint16_t)keys[s_entry[l] + v - s_first[l]];
+        ring[k] = (uint16_t)keys[min(s_entry[l] + v - s_first[l], (u64)dict - 1)];
         ++k;
         ++produced;
         pos += l;
@@ -1184,7 +1189,7 @@ __global__ void __launch_bounds__(DEC_THREADS)
 // huffmeta, decodebook bytes, packed words, outlier count
 __global__ void k_parse_header(const uint8_t *in, uint64_t bytes, u64 *out) {
   const char sig[7] = {'M', 'G', 'X', 'H', 'U', 'F', 'F'};
-  for (int i = 0; i < 8; i++)
+  for (int i = 0; i < 9; i++)
     out[i] = 0;
   for (int i = 0; i < 7; i++)
     if (in[i] != (uint8_t)sig[i]) {
@@ -1226,6 +1231,51 @@ __global__ void k_parse_header(const uint8_t *in, uint64_t bytes, u64 *out) {
   out[7] = *(const u64 *)(in + off_outc);
 }
 
+// Payload checks the decoder relies on (only the MGARD header carries a CRC; a
+// corrupt or hostile container must not cause out-of-bounds accesses).  Driven by
+// the parsed header in out[0..7]; flags go to out[8]:
+//   1 chunk metadata points outside the packed words     2 outlier index >= n
+//   4 outlier indices not ascending (legal: the reference's CUDA / OpenMP back ends
+//     append with atomics, OutlierSeparator.hpp:66-97)   8 decodebook key >= dict
+__global__ void __launch_bounds__(256)
+    k_validate_container(const uint8_t *__restrict__ in, uint64_t bytes, uint64_t n_plan,
+                         u64 *__restrict__ out) {
+  if (out[0] != 0)
+    return;
+  const u64 n = out[1], dict = out[2], chunk = out[3], dbs = out[5], ddata = out[6],
+            n_out = out[7];
+  if (n != n_plan || dbs != 8 * (128 + dict))
+    return; // the host rejects these before anything is decoded
+  const u64 nchunk = (n - 1) / chunk + 1;
+  const u64 *meta = (const u64 *)(in + 32);
+  const u64 *keys = (const u64 *)(in + 32 + 16 * nchunk + 8) + 128;
+  const u64 off_outc = 32 + 16 * nchunk + 8 + dbs + 8 + 8 * ddata;
+  unsigned flags = 0;
+  const u64 tid = blockIdx.x * (u64)blockDim.x + threadIdx.x, nth = (u64)gridDim.x * blockDim.x;
+  for (u64 c = tid; c < nchunk; c += nth) {
+    const u64 bits = meta[c], off = meta[nchunk + c];
+    if (bits > chunk * 56 || off > ddata || off + ((bits + 63) >> 6) > ddata)
+      flags |= 1;
+  }
+  for (u64 i = tid; i < dict; i += nth)
+    if (keys[i] >= dict)
+      flags |= 8;
+  if (n_out > n || off_outc + 8 + 16 * n_out > bytes) {
+    flags |= 2;
+  } else {
+    const u64 *idx = (const u64 *)(in + off_outc + 8);
+    for (u64 i = tid; i < n_out; i += nth) {
+      const u64 v = idx[i];
+      if (v >= n)
+        flags |= 2;
+      if (i + 1 < n_out && idx[i + 1] <= v)
+        flags |= 4;
+    }
+  }
+  if (flags)
+    atomicOr((unsigned long long *)&out[8], (unsigned long long)flags);
+}
+
 struct ParsedHeader {
   uint64_t n, nchunk, dbs, ddata, n_out;
   int32_t dict, chunk;
@@ -1246,7 +1296,9 @@ int mgxk_decode_container(mgx_ctx *ctx, const uint8_t *d_in, uint64_t bytes,
   // the section sizes chain through the container (Huffman.hpp:453-518): one
   // single-thread kernel follows the chain, one read-back brings it to the host
   k_parse_header<<<1, 1, 0, ctx->stream>>>(d_in, bytes, (u64 *)ctx->d_scalars);
-  ctx->launches++;
+  k_validate_container<<<ctx->num_sms * 2, 256, 0, ctx->stream>>>(d_in, bytes, n,
+                                                                  (u64 *)ctx->d_scalars);
+  ctx->launches += 2;
   MGX_CUDA(cudaMemcpyAsync(ctx->h_scalars, ctx->d_scalars, MGX_SC_COUNT * 8,
                            cudaMemcpyDeviceToHost, ctx->stream));
   MGX_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -1282,9 +1334,54 @@ int mgxk_decode_container(mgx_ctx *ctx, const uint8_t *d_in, uint64_t bytes,
   p.off_oval = p.off_oidx + 8 * p.n_out;
   if (p.off_oval + 8 * p.n_out > bytes)
     return MGX_FAILURE;
+  if (hs[8] & (1 | 2 | 8)) {
+    ctx->err = "corrupt Huffman container (chunk offsets, outlier indices or decodebook "
+               "out of range)";
+    return MGX_FAILURE;
+  }
   *n_out = p.n_out;
   *d_oidx = (const uint64_t *)(d_in + p.off_oidx);
   *d_oval = (const int64_t *)(d_in + p.off_oval);
+  if (hs[8] & 4) {
+    // outlier list in append order (a stream of the reference's CUDA / OpenMP back
+    // end): the fused inverse looks outliers up by binary search, so sort it
+    if (p.n_out > (uint64_t)std::numeric_limits<int>::max()) {
+      ctx->err = "more than 2^31 unsorted outliers";
+      return MGX_FAILURE;
+    }
+    if (ctx->out_cap < p.n_out) {
+      if (ctx->d_out_idx)
+        cudaFree(ctx->d_out_idx);
+      if (ctx->d_out_val)
+        cudaFree(ctx->d_out_val);
+      ctx->d_out_idx = nullptr;
+      ctx->d_out_val = nullptr;
+      ctx->out_cap = 0;
+      MGX_CUDA(cudaMalloc(&ctx->d_out_idx, p.n_out * 8));
+      MGX_CUDA(cudaMalloc(&ctx->d_out_val, p.n_out * 8));
+      ctx->out_cap = p.n_out;
+    }
+    size_t tmp = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, tmp, (const u64 *)*d_oidx, (u64 *)ctx->d_out_idx,
+                                    (const long long *)*d_oval,
+                                    (long long *)ctx->d_out_val, (int)p.n_out, 0, 64,
+                                    ctx->stream);
+    if (tmp > ctx->sort_tmp_bytes) {
+      if (ctx->d_sort_tmp)
+        cudaFree(ctx->d_sort_tmp);
+      ctx->d_sort_tmp = nullptr;
+      ctx->sort_tmp_bytes = 0;
+      MGX_CUDA(cudaMalloc(&ctx->d_sort_tmp, tmp));
+      ctx->sort_tmp_bytes = tmp;
+    }
+    cub::DeviceRadixSort::SortPairs(ctx->d_sort_tmp, tmp, (const u64 *)*d_oidx,
+                                    (u64 *)ctx->d_out_idx, (const long long *)*d_oval,
+                                    (long long *)ctx->d_out_val, (int)p.n_out, 0, 64,
+                                    ctx->stream);
+    ctx->launches += 4;
+    *d_oidx = ctx->d_out_idx;
+    *d_oval = ctx->d_out_val;
+  }
 
   const u64 *db = (const u64 *)(d_in + p.off_db);
   k_build_lut<<<1, 256, 0, ctx->stream>>>(db, (uint32_t)p.dict,
@@ -1296,14 +1393,14 @@ int mgxk_decode_container(mgx_ctx *ctx, const uint8_t *d_in, uint64_t bytes,
     k_decode_multi<<<mgx_grid_for(p.nchunk, DEC_THREADS, ctx->num_sms * 16),
                      DEC_THREADS, 0, ctx->stream>>>(
         (const u64 *)(d_in + p.off_packed), (const u64 *)(d_in + p.off_meta),
-        p.nchunk, (uint32_t)p.chunk, p.n, db, mlut, ctx->d_sym);
+        p.nchunk, (uint32_t)p.chunk, p.n, db, mlut, ctx->d_sym, (uint32_t)p.dict);
     ctx->launches += 3;
   } else {
     k_decode<<<mgx_grid_for(p.nchunk, 128, ctx->num_sms * 16), 128, 0,
                ctx->stream>>>((const u64 *)(d_in + p.off_packed),
                               (const u64 *)(d_in + p.off_meta), p.nchunk,
                               (uint32_t)p.chunk, p.n, db,
-                              (const uint32_t *)ctx->d_lut, ctx->d_sym);
+                              (const uint32_t *)ctx->d_lut, ctx->d_sym, (uint32_t)p.dict);
     ctx->launches += 2;
   }
   MGX_CUDA(cudaGetLastError());

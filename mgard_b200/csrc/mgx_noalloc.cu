@@ -18,6 +18,7 @@
 // was written by the same call; stale entries of a longer earlier call are
 // never read).  ALL calls on a device share the one array: calls that overlap on
 // the GPU (different streams, or replays of two graphs at once) race.
+#include <atomic>
 #include <cstdio>
 #include <cstring>
 #include <type_traits>
@@ -39,7 +40,7 @@ static __device__ __align__(256) double g_noalloc_scratch[NA_MAX_BLOCKS];
 // name is only a host-side stand-in for the symbol, NOT a device address: the
 // address a kernel may be given comes from cudaGetSymbolAddress, asked once per
 // device with that device current.
-double *g_scratch_addr[NA_MAX_DEVICES] = {};
+std::atomic<double *> g_scratch_addr[NA_MAX_DEVICES]; // device address of the scratch, per device
 
 template <typename T, bool LINF>
 __global__ void __launch_bounds__(NA_THREADS)
@@ -136,18 +137,18 @@ extern "C" int mgx_norm_partial_noalloc(int device, void *cuda_stream,
                 "no such CUDA device (there is no CPU fallback)");
   int rc = MGX_SUCCESS;
   const char *what = nullptr;
-  if (!g_scratch_addr[device]) { // set-up, once per device, that device current
+  if (!g_scratch_addr[device].load(std::memory_order_acquire)) { // set-up, once per device, that device current
     double *p = nullptr;
     const cudaError_t e = cudaGetSymbolAddress((void **)&p, g_noalloc_scratch);
     if (e != cudaSuccess || !p) {
       rc = MGX_FAILURE;
       what = cudaGetErrorString(e);
     } else {
-      g_scratch_addr[device] = p;
+      g_scratch_addr[device].store(p, std::memory_order_release);
     }
   }
   if (!rc) {
-    double *scratch = g_scratch_addr[device];
+    double *scratch = g_scratch_addr[device].load(std::memory_order_acquire);
     cudaStream_t st = (cudaStream_t)cuda_stream;
     const int nblocks = (int)((n + NA_SEG - 1) / NA_SEG);
     if (dtype == MGX_F32) {

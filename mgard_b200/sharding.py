@@ -151,3 +151,217 @@ class ShardedCompressor:
         objs = [None] * world if rank == dst else None
         dist.gather_object(bytes(payload_bytes), objs, dst=dst, group=self.group)
         return frame(objs) if rank == dst else None
+
+
+def serialize_header(shape, dtype_code, ebtype, tol, s, norm, dd_dim, dd_size,
+                     decomposed=True, dict_size=8192, block_size=1024):
+    """the "MGARD" header of a domain-decomposed stream (MetadataBase::Serialize,
+    src/mgard-x/Metadata/Metadata.cpp:259-490; decomposition fields :353-372) through
+    mgx_metadata_serialize -- same bytes mgx_x_compress writes for this domain."""
+    lib = _lib.load()
+    md = _lib.MgxMetadata()
+    md.version[0], md.version[1], md.version[2] = 1, 0, 0
+    md.D = len(shape)
+    for d, n in enumerate(shape):
+        md.shape[d] = int(n)
+    md.dtype = dtype_code
+    md.mode = 0 if ebtype == REL else 1
+    md.linf = 1 if math.isinf(s) else 0
+    md.s, md.norm, md.tol = s, norm, tol
+    md.decomposed = 1 if decomposed else 0
+    md.dd_type = 0
+    md.dd_dim, md.dd_size = int(dd_dim), int(dd_size)
+    md.decomposition = 0
+    md.lossless = 0
+    md.huff_dict_size, md.huff_block_size = dict_size, block_size
+    md.backend = 3
+    n = ctypes.c_uint64()
+    lib.mgx_metadata_serialize(ctypes.byref(md), None, 0, ctypes.byref(n))
+    buf = np.zeros(n.value, dtype=np.uint8)
+    rc = lib.mgx_metadata_serialize(ctypes.byref(md), buf.ctypes.data, buf.size,
+                                    ctypes.byref(n))
+    if rc != 0:
+        from .compressor import MgardError
+        raise MgardError(rc, "mgx_metadata_serialize")
+    return bytes(buf)
+
+
+class ShardedDomain:
+    """The subdomains ONE rank owns of a domain-decomposed field (or, with one
+    shape per rank and no decomposition, its own field of a replicated run).
+
+    ``shapes``: shapes of this rank's subdomains in subdomain order; one Compressor
+    per distinct shape, all on ``stream``.  The only collective is the all-reduce of
+    one fp64 scalar in ``global_norm`` (NCCL between GPUs, gloo in the CPU tests);
+    ``comp_factory`` lets the CPU tests pass a stand-in for the GPU Compressor."""
+
+    def __init__(self, shapes, tdtype, total_elems, num_subdomains, group=None,
+                 device=None, stream=None, dev_id=0, comp_factory=None):
+        import torch
+        self.lib = _lib.load()
+        self.shapes = [tuple(int(x) for x in s) for s in shapes]
+        self.tdtype = tdtype
+        self.dtype_code = 0 if tdtype == torch.float32 else 1
+        self.total_elems = int(total_elems)
+        self.num_subdomains = int(num_subdomains)
+        self.group, self.device, self.stream = group, device, stream
+        self.comps = {}
+        for shp in self.shapes:
+            if shp not in self.comps:
+                if comp_factory is not None:
+                    self.comps[shp] = comp_factory(shp)
+                else:
+                    from .compressor import Compressor, Hierarchy, Config
+                    self.comps[shp] = Compressor(
+                        Hierarchy(shp, tdtype, Config(dev_id=dev_id)), stream=stream)
+        self.last_norm_ms = 0.0
+        self._timing = False
+        self._stage = {}
+        self._dev_in = None
+
+    def comp(self, i):
+        return self.comps[self.shapes[i]]
+
+    def set_timing(self, on):
+        self._timing = bool(on)
+        for c in self.comps.values():
+            c.set_timing(on)
+
+    def launch_count(self):
+        return sum(c.launch_count() for c in self.comps.values())
+
+    def stage_ms(self, pairs):
+        """stage times of the last Compress / Decompress summed over the subdomains"""
+        return {k: sum(st.get(k, 0.0) for st in self._stage.values()) for k, _, _ in pairs}
+
+    def _record(self, i, pairs):
+        if self._timing:
+            c = self.comp(i)
+            self._stage[i] = {k: c.elapsed_ms(a, b) for k, a, b in pairs}
+
+    # ---- the one collective ---------------------------------------------
+    def all_reduce_partial(self, partial, linf):
+        import torch
+        import torch.distributed as dist
+        if not (dist.is_available() and dist.is_initialized()):
+            return float(partial)
+        t = torch.tensor([partial], dtype=torch.float64, device=self.device or "cpu")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX if linf else dist.ReduceOp.SUM,
+                        group=self.group)
+        return float(t.item())
+
+    def global_norm(self, fields, s):
+        """calc_norm_decomposed (ErrorToleranceCalculator.hpp:45-52, 61-123): max |u|
+        or sum u^2 per subdomain, combined over this rank's subdomains, all-reduced,
+        then sqrt( / N) for s != inf."""
+        import time
+        linf = math.isinf(s)
+        t0 = time.perf_counter()
+        parts = [self.comp(i).NormPartial(f, s) for i, f in enumerate(fields)]
+        self.last_norm_ms = (time.perf_counter() - t0) * 1e3
+        local = (max(parts) if linf else sum(parts)) if parts else 0.0
+        part = self.all_reduce_partial(local, linf)
+        return float(self.lib.mgx_finish_norm(self.dtype_code, 1 if linf else 0, part,
+                                              self.total_elems, 1))
+
+    def local_abs_tol(self, ebtype, norm, tol, s):
+        return float(self.lib.mgx_local_abs_tol(
+            self.dtype_code, 1 if ebtype == REL else 0, norm, tol, s,
+            self.num_subdomains))
+
+    # ---- device-resident ---------------------------------------------------
+    def Compress(self, fields, ebtype, tol, s, outs=None):
+        """(payloads of this rank's subdomains, global norm, per-subdomain ABS bound)"""
+        norm = self.global_norm(fields, s) if ebtype == REL else 1.0
+        ltol = self.local_abs_tol(ebtype, norm, tol, s)
+        blobs = []
+        pairs = [("norm", "c_begin", "c_norm"), ("refactor_quantize", "c_norm", "c_refactor"),
+                 ("codebook", "c_refactor", "c_codebook"), ("encode", "c_codebook", "c_sizes"),
+                 ("pack", "c_sizes", "c_pack"), ("outliers_tail", "c_pack", "c_end")]
+        for i, f in enumerate(fields):
+            blob, _ = self.comp(i).Compress(f, ABS, ltol, s, 0.0,
+                                            out=None if outs is None else outs[i])
+            self._record(i, pairs)
+            blobs.append(blob)
+        return blobs, norm, ltol
+
+    def Decompress(self, blobs, ltol, s, outs=None):
+        res = []
+        pairs = [("decode", "d_begin", "d_decode"), ("dequantize", "d_decode", "d_dequant"),
+                 ("recompose", "d_dequant", "d_end")]
+        for i, b in enumerate(blobs):
+            res.append(self.comp(i).Decompress(b, ABS, ltol, s, 0.0,
+                                               out=None if outs is None else outs[i]))
+            self._record(i, pairs)
+        return res
+
+    # ---- host buffers (pinned numpy arrays): every byte crosses PCIe once --------
+    def _staging(self):
+        import torch
+        if self._dev_in is None:
+            self._dev_in = [torch.empty(s, dtype=self.tdtype, device=self.device)
+                            for s in self.shapes]
+            es = 4 if self.dtype_code == 0 else 8
+            self._dev_out = [torch.empty(int(np.prod(s)) * es // 2 + (8 << 20),
+                                         dtype=torch.uint8, device=self.device)
+                             for s in self.shapes]
+        return self._dev_in, self._dev_out
+
+    def CompressHost(self, arrays, ebtype, tol, s, outs):
+        """H2D of every subdomain, norm partials on the copies, all-reduce, compress
+        from the resident copies, D2H of the payloads; returns numpy views of outs"""
+        import torch
+        dev_in, dev_out = self._staging()
+        st = self.stream or torch.cuda.current_stream(self.device)
+        with torch.cuda.stream(st):
+            for d, a in zip(dev_in, arrays):
+                d.copy_(torch.from_numpy(a), non_blocking=True)
+        st.synchronize()
+        blobs, norm, ltol = self.Compress(dev_in, ebtype, tol, s, outs=dev_out)
+        res = []
+        with torch.cuda.stream(st):
+            for b, o in zip(blobs, outs):
+                torch.from_numpy(o[:b.numel()]).copy_(b, non_blocking=True)
+                res.append(o[:b.numel()])
+        st.synchronize()
+        return res
+
+    def DecompressHost(self, hblobs, ltol, s, outs):
+        import torch
+        dev_in, dev_out = self._staging()
+        st = self.stream or torch.cuda.current_stream(self.device)
+        dblobs = []
+        with torch.cuda.stream(st):
+            for o, b in zip(dev_out, hblobs):
+                o[:b.size].copy_(torch.from_numpy(b), non_blocking=True)
+                dblobs.append(o[:b.size])
+        st.synchronize()
+        self.Decompress(dblobs, ltol, s, outs=dev_in)
+        with torch.cuda.stream(st):
+            for d, a in zip(dev_in, outs):
+                torch.from_numpy(a).copy_(d, non_blocking=True)
+        st.synchronize()
+        return outs
+
+    # ---- one self-describing stream from all ranks -----------------------------------
+    def gather_stream(self, blobs, owned, shape, ebtype, tol, s, norm, dd_dim, dd_size,
+                      dst=0):
+        """header + [u64 size][payload] of every subdomain in subdomain order on rank
+        ``dst`` (GPUPipelines.hpp:187-191, Metadata.cpp:353-372): what mgard_x::compress
+        returns for the whole domain, decodable by mgx_x_decompress / mgard_x::decompress
+        on one GPU.  ``owned`` = global indices of this rank's subdomains."""
+        import torch.distributed as dist
+        mine = [(int(i), bytes(b.cpu().numpy().tobytes() if hasattr(b, "cpu") else bytes(b)))
+                for i, b in zip(owned, blobs)]
+        if dist.is_available() and dist.is_initialized():
+            world = dist.get_world_size(self.group)
+            rank = dist.get_rank(self.group)
+            objs = [None] * world if rank == dst else None
+            dist.gather_object(mine, objs, dst=dst, group=self.group)
+            if rank != dst:
+                return None
+            mine = [p for o in objs for p in o]
+        mine.sort(key=lambda p: p[0])
+        assert [i for i, _ in mine] == list(range(self.num_subdomains)), "missing subdomains"
+        head = serialize_header(shape, self.dtype_code, ebtype, tol, s, norm, dd_dim, dd_size)
+        return head + frame([p for _, p in mine])

@@ -128,3 +128,69 @@ def test_two_rank_sharded_compress(shape, dtype, s, ebtype, tol):
     else:
         assert ltol == pytest.approx(tol, rel=1e-6)
         assert err <= tol
+
+
+# ---- several subdomains per rank + one self-describing stream ---------------------
+def domain_worker(rank, world, port, shape, dtype, s, tol, nsub, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        sys.path.insert(0, os.path.dirname(HERE))
+        sys.path.insert(0, HERE)
+        from oracle_lib import smooth_field
+        from mgard_b200 import _lib
+        from mgard_b200.sharding import (ABS, REL, DomainDecomposer, ShardedDomain, unframe)
+        from mgard_b200.highlevel import read_metadata
+        u = smooth_field(shape, dtype, seed=5)
+        dd = DomainDecomposer(shape, nsub)
+        S = dd.num_subdomains
+        per = -(-S // world)
+        owned = [i for i in range(S) if i // per == rank]
+        locals_ = [np.ascontiguousarray(u[dd.subdomain_slice(i)]) for i in owned]
+        tdt = torch.float32 if np.dtype(dtype) == np.float32 else torch.float64
+        dom = ShardedDomain([a.shape for a in locals_], tdt, u.size, S,
+                            comp_factory=lambda shp: OracleCompressor(shp, dtype))
+        blobs, norm, ltol = dom.Compress(locals_, REL, tol, s)
+        stream = dom.gather_stream(blobs, owned, shape, REL, tol, s, norm, dd.dim, dd.size)
+        if rank == 0:
+            md, hb = read_metadata(stream)
+            assert md.decomposed == 1 and md.dd_dim == dd.dim and md.dd_size == dd.size
+            assert md.norm == norm and md.tol == tol and md.D == len(shape)
+            parts = unframe(stream[hb:])
+            assert len(parts) == S
+            # the tolerance a decoder derives from the header is the one that was used
+            lib = _lib.load()
+            assert float(lib.mgx_local_abs_tol(dom.dtype_code, 1, md.norm, md.tol, md.s, S)) == ltol
+            full = np.empty(shape, dtype)
+            for i, p in enumerate(parts):
+                shp, _ = dd.subdomain_shape(i)
+                full[dd.subdomain_slice(i)] = OracleCompressor(shp, dtype).Decompress(
+                    np.frombuffer(p, np.uint8), ABS, ltol, s, 0.0)
+            q.put(("ok", float(np.abs(full.astype(np.float64) - u).max()),
+                   float(np.abs(u.astype(np.float64)).max()), S))
+    except Exception as e:  # pragma: no cover
+        if rank == 0:
+            q.put(("fail", repr(e)))
+        raise
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_ranks_four_subdomains_one_mgard_stream():
+    shape, dtype, tol = (41, 20, 17), np.float32, 1e-3
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = free_port()
+    procs = [ctx.Process(target=domain_worker,
+                         args=(r, 2, port, shape, dtype, INF, tol, 4, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(180)
+        assert p.exitcode == 0
+    res = q.get(timeout=10)
+    assert res[0] == "ok", res
+    _, err, umax, S = res
+    assert S == 4
+    assert err <= tol * umax

@@ -53,6 +53,9 @@ def test_noalloc_norm_matches_the_context_entry_point_twice(tdt, linf):
             # the two entry points only differ in the order of fp64 partial sums
             assert abs(got - want) <= 1e-6 * abs(want), (got, want)
             assert abs(got - want) <= 1e-12 * abs(want), (got, want)
+            # and against a sum that shares no code with the library
+            indep = float((u.double() ** 2).sum().item())
+            assert abs(got - indep) <= 1e-12 * indep, (got, indep)
         # repeated call, same input: bit-identical (fixed summation order)
         assert _noalloc(lib, u, linf, out) == got
 
