@@ -70,6 +70,9 @@ def parse():
                     help="relative bound (default: 1e-3 cfg3, 1e-4 cfg5, 1e-3 cfg4)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-stream-check", action="store_true",
+                    help="N > 1: skip gathering the ranks' records into one MGARD stream and "
+                         "decoding it on rank 0")
     ap.add_argument("--no-extra", action="store_true", help="skip other_configs")
     return ap.parse_args()
 
@@ -622,6 +625,56 @@ def run_reference(args):
 
 
 # ---------------------------------------------------------------------------
+# N ranks -> one "MGARD" stream -> mgx_x_decompress on one GPU
+# ---------------------------------------------------------------------------
+def check_stream(dom, blobs, owned, slabs, wl, tdt, dev, local, rank, norm, ebtype):
+    """Rank 0 gathers every rank's records behind one MGARD header (what
+    mgard_x::compress returns for the whole domain under the MaxDim decomposition),
+    decodes that stream ALONE through mgx_x_decompress and checks the bound on every
+    element against the regenerated field."""
+    import psutil
+    import torch
+    from mgard_b200 import highlevel as hl
+    t0 = time.perf_counter()
+    data = dom.gather_stream(blobs, owned, wl.gshape, ebtype, wl.tol, wl.s, norm,
+                             wl.slab_dim, wl.slab_size)
+    if rank != 0:
+        return None
+    field_bytes = wl.elems() * wl.es
+    out = {"stream_bytes": len(data), "records": len(slabs),
+           "compression_ratio": field_bytes / len(data),
+           "gather_s": time.perf_counter() - t0}
+    avail = psutil.virtual_memory().available
+    if avail < 2 * field_bytes + (16 << 30):
+        out["decoded"] = False
+        out["why"] = "host has %.0f GB free, the decoded field needs %.0f GB" % (
+            avail / 1e9, field_bytes / 1e9)
+        return out
+    t0 = time.perf_counter()
+    back = hl.decompress(np.frombuffer(data, np.uint8), config=hl.Config(dev_id=local))
+    out["decode_s"] = time.perf_counter() - t0
+    assert tuple(back.shape) == tuple(wl.gshape)
+    worst, sq = 0.0, 0.0
+    for lo, hi in slabs:
+        sl = [slice(None)] * len(wl.gshape)
+        sl[wl.slab_dim] = slice(lo, hi)
+        ref = gen_block(wl.kind, wl.gshape, tdt, dev, wl.slab_dim, lo, hi)
+        got = torch.from_numpy(np.ascontiguousarray(back[tuple(sl)])).to(dev)
+        d = got.double() - ref.double()
+        worst = max(worst, float(d.abs().max().item()))
+        sq += float((d * d).sum().item())
+        del ref, got, d
+    if math.isinf(wl.s):
+        ratio = worst / (wl.tol * norm)
+    else:
+        ratio = math.sqrt(sq / wl.elems()) / (wl.tol * norm)
+    out.update({"decoded": True, "decoder": "mgx_x_decompress on rank 0's GPU alone",
+                "err_over_bound": ratio, "ok": bool(ratio <= 1.0),
+                "checked_elements": wl.elems()})
+    return out
+
+
+# ---------------------------------------------------------------------------
 # our arm
 # ---------------------------------------------------------------------------
 def run_ours(args):
@@ -825,6 +878,12 @@ def run_ours(args):
                 / (wl.tol * norm))
         del h_in, h_out, h_back
 
+    # ---- N ranks -> ONE stream, decoded by ONE GPU (outside the timed regions) ----------
+    stream_check = None
+    if world > 1 and not weak and not args.no_stream_check:
+        stream_check = check_stream(dom, blobs, owned, slabs, wl, tdt, dev, local, rank,
+                                    norm, mg.REL)
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -875,6 +934,7 @@ def run_ours(args):
         "error_bound": {"max_err_over_bound": eb_ratio, "ok": bool(eb_ratio <= 1.0),
                         "checked_elements": int(total_elems)},
         "wall_ms_per_step": wall / K,
+        "stream_check": stream_check,
         "other_configs": extra,
     }
     print(json.dumps(line), flush=True)

@@ -193,6 +193,7 @@ class ShardedDomain:
     ``shapes``: shapes of this rank's subdomains in subdomain order; one Compressor
     per distinct shape, all on ``stream``.  The only collective is the all-reduce of
     one fp64 scalar in ``global_norm`` (NCCL between GPUs, gloo in the CPU tests);
+    ``group=False``: this object holds ALL subdomains, no collective at all;
     ``comp_factory`` lets the CPU tests pass a stand-in for the GPU Compressor."""
 
     def __init__(self, shapes, tdtype, total_elems, num_subdomains, group=None,
@@ -243,7 +244,7 @@ class ShardedDomain:
     def all_reduce_partial(self, partial, linf):
         import torch
         import torch.distributed as dist
-        if not (dist.is_available() and dist.is_initialized()):
+        if self.group is False or not (dist.is_available() and dist.is_initialized()):
             return float(partial)
         t = torch.tensor([partial], dtype=torch.float64, device=self.device or "cpu")
         dist.all_reduce(t, op=dist.ReduceOp.MAX if linf else dist.ReduceOp.SUM,
@@ -353,7 +354,7 @@ class ShardedDomain:
         import torch.distributed as dist
         mine = [(int(i), bytes(b.cpu().numpy().tobytes() if hasattr(b, "cpu") else bytes(b)))
                 for i, b in zip(owned, blobs)]
-        if dist.is_available() and dist.is_initialized():
+        if self.group is not False and dist.is_available() and dist.is_initialized():
             world = dist.get_world_size(self.group)
             rank = dist.get_rank(self.group)
             objs = [None] * world if rank == dst else None
