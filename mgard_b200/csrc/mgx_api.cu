@@ -40,6 +40,10 @@ void release_plan(mgx_ctx *ctx) {
   free_dev(ctx->d_coarse0);
   free_dev(ctx->d_coarse1);
   ctx->coarse_bytes = 0;
+  for (int i = 0; i < 2; i++) {
+    free_dev(ctx->d_lvl[i]);
+    ctx->lvl_bytes[i] = 0;
+  }
   ctx->out_cap = 0;
   ctx->planned = false;
 }
@@ -116,6 +120,8 @@ int mgx_create(mgx_ctx **out, int device, void *cuda_stream) {
     ctx->no_ws = e && e[0] == '1';
     e = getenv("MGX_NO_TMA");
     ctx->no_tma = e && e[0] == '1';
+    e = getenv("MGX_INV_TILED");
+    ctx->inv_tiled = e && e[0] == '1';
   }
   cudaDeviceProp prop;
   if (cudaGetDeviceProperties(&prop, device) == cudaSuccess)

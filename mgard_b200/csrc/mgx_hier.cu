@@ -1077,6 +1077,169 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+// ===================== 3-D inverse, one level per launch =======================
+// The tile kernel above keeps three levels in shared memory and pays for it with
+// four CTA barriers per tile, a 2.4x redundant stride-2 pass on the tile halo and
+// ~60 warp-instructions per 32 nodes.  For 3-D fields the levels are run one launch
+// each instead: level l reads the COMPACT nodal array of level l-1 (1/8 of the
+// nodes), the 7/8 of level l's symbols that sit in the seven odd blocks of the
+// reordered layout, and writes the compact nodal array of level l (the caller's
+// buffer for l = L).  No shared memory, no barriers, no halo: 6.25 B per fp32 node
+// at the finest level instead of 6, +1/7 of that for all coarser levels together.
+//
+// In level-l index space the level-(l-1) nodes are the even indices plus the last
+// one.  Block b of an axis = coarse node b (level-l index
+// 2b, or n_l - 1 for the last) and the odd node 2b+1 when 2b+1 < n_l - 1, whose
+// symbol sits at reordered position cn + b.
+template <typename T> struct InvLevel {
+  const T *coarse; // level l-1: cn[0] x cn[1] x cn[2]
+  T *fine;         // level l:   fn[0] x fn[1] x fn[2]
+  uint32_t cn[3], fn[3];
+  uint32_t roff[3];       // ratio tables of level l per axis
+  uint64_t oX, oY, oZ;    // element offsets of the odd x / y / z blocks in sym
+};
+
+template <typename T> struct LvlPlane {
+  T e0, f0, gE, gO;
+};
+
+// x and y lerps of one z plane of a full block: c -> coarse node (bk, bj, bi)
+template <typename T, bool HALF>
+__device__ __forceinline__ void lvl_plane(const T *__restrict__ c, uint64_t csy, T tx,
+                                          T ty, LvlPlane<T> &Q) {
+  const T e0 = __ldg(c), r0 = __ldg(c + 1), e2 = __ldg(c + csy),
+          r2 = __ldg(c + csy + 1);
+  Q.e0 = e0;
+  Q.f0 = mgx_lerp(e0, r0, tx);
+  const T f2 = mgx_lerp(e2, r2, tx);
+  Q.gE = mgx_lerp(e0, e2, ty);
+  Q.gO = mgx_lerp(Q.f0, f2, ty);
+}
+
+constexpr int IL_THREADS = 256;
+
+template <typename T, bool HALF>
+__global__ void __launch_bounds__(IL_THREADS)
+    k_inv_level3(const __grid_constant__ HierArgs<T> a,
+                 const __grid_constant__ InvLevel<T> v, const T *__restrict__ tables) {
+  const uint32_t lane = threadIdx.x & 31, wy = (threadIdx.x >> 5) & 3,
+                 wz = threadIdx.x >> 7;
+  const uint32_t bi = blockIdx.x * 32 + lane, bj = blockIdx.y * 4 + wy,
+                 bk0 = blockIdx.z * 4 + wz * 2;
+  const uint32_t cnz = v.cn[0], cny = v.cn[1], cnx = v.cn[2];
+  const uint32_t fnz = v.fn[0], fny = v.fn[1], fnx = v.fn[2];
+  if (bi >= cnx || bj >= cny || bk0 >= cnz)
+    return;
+  const uint64_t sy = a.n[2], sz = (uint64_t)a.n[2] * a.n[1];
+  const uint64_t csy = cnx, csz = (uint64_t)cnx * cny;
+  const uint64_t fsy = fnx, fsz = (uint64_t)fnx * fny;
+  const bool ex = 2 * bi + 1 < fnx - 1, ey = 2 * bj + 1 < fny - 1;
+  const bool full = ex && ey && bk0 + 1 < cnz && 2 * (bk0 + 1) + 1 < fnz - 1;
+  const bool slow_sym = a.n_out != 0;
+  if (full) {
+    // two full blocks stacked along z: three coarse planes, 14 symbols, 16 nodes
+    T tx = (T)0.5, ty = (T)0.5;
+    if (!HALF) {
+      tx = tables[v.roff[2] + 2 * bi];
+      ty = tables[v.roff[1] + 2 * bj];
+    }
+    const T *c = v.coarse + ((uint64_t)bk0 * csz + (uint64_t)bj * csy + bi);
+    const uint16_t *ob = a.sym + ((uint64_t)bk0 * sz + (uint64_t)bj * sy + bi);
+    T *g = v.fine + ((uint64_t)(2 * bk0) * fsz + (uint64_t)(2 * bj) * fsy + 2 * bi);
+    uint32_t sv[2][7];
+#pragma unroll
+    for (int b = 0; b < 2; b++) {
+      const uint16_t *o = ob + (uint64_t)b * sz;
+      sv[b][0] = __ldg(o + v.oX);
+      sv[b][1] = __ldg(o + v.oY);
+      sv[b][2] = __ldg(o + v.oX + v.oY);
+      sv[b][3] = __ldg(o + v.oZ);
+      sv[b][4] = __ldg(o + v.oZ + v.oX);
+      sv[b][5] = __ldg(o + v.oZ + v.oY);
+      sv[b][6] = __ldg(o + v.oZ + v.oX + v.oY);
+    }
+    LvlPlane<T> A, B;
+    lvl_plane<T, HALF>(c, csy, tx, ty, A);
+#pragma unroll
+    for (int b = 0; b < 2; b++) {
+      lvl_plane<T, HALF>(c + (uint64_t)(b + 1) * csz, csy, tx, ty, B);
+      T tz = (T)0.5;
+      if (!HALF)
+        tz = tables[v.roff[0] + 2 * (bk0 + b)];
+      T cf[7];
+      uint32_t mn = 0xffffffffu;
+#pragma unroll
+      for (int i = 0; i < 7; i++) {
+        cf[i] = mul_rn(a.dq, (T)((int)sv[b][i] - a.shift));
+        mn = min(mn, sv[b][i]);
+      }
+      if (__builtin_expect(slow_sym && mn == 0, 0)) {
+        const uint16_t *o = ob + (uint64_t)b * sz;
+        const uint64_t off[7] = {v.oX, v.oY, v.oX + v.oY, v.oZ, v.oZ + v.oX,
+                                 v.oZ + v.oY, v.oZ + v.oX + v.oY};
+#pragma unroll
+        for (int i = 0; i < 7; i++)
+          if (sv[b][i] == 0)
+            cf[i] = coef_of<T>(a, 0u, o + off[i]);
+      }
+      T *gb = g + (uint64_t)(2 * b) * fsz;
+      gb[0] = A.e0;
+      gb[1] = add_rn(cf[0], A.f0);
+      gb[fsy] = add_rn(cf[1], A.gE);
+      gb[fsy + 1] = add_rn(cf[2], A.gO);
+      gb[fsz] = add_rn(cf[3], mgx_lerp(A.e0, B.e0, tz));
+      gb[fsz + 1] = add_rn(cf[4], mgx_lerp(A.f0, B.f0, tz));
+      gb[fsz + fsy] = add_rn(cf[5], mgx_lerp(A.gE, B.gE, tz));
+      gb[fsz + fsy + 1] = add_rn(cf[6], mgx_lerp(A.gO, B.gO, tz));
+      A = B;
+    }
+    return;
+  }
+  // blocks on the last node of an axis: missing odd halves, last coarse node at n_l - 1
+  for (uint32_t bk = bk0; bk < min(bk0 + 2, cnz); bk++) {
+    const bool ez = 2 * bk + 1 < fnz - 1;
+    const uint32_t fx = bi == cnx - 1 ? fnx - 1 : 2 * bi,
+                   fy = bj == cny - 1 ? fny - 1 : 2 * bj,
+                   fz = bk == cnz - 1 ? fnz - 1 : 2 * bk;
+    T tx = (T)0.5, ty = (T)0.5, tz = (T)0.5;
+    if (!HALF) {
+      if (ex) tx = tables[v.roff[2] + 2 * bi];
+      if (ey) ty = tables[v.roff[1] + 2 * bj];
+      if (ez) tz = tables[v.roff[0] + 2 * bk];
+    }
+    const T *c = v.coarse + ((uint64_t)bk * csz + (uint64_t)bj * csy + bi);
+    const uint64_t dx = ex ? 1 : 0, dy = ey ? csy : 0, dz = ez ? csz : 0;
+    auto plane = [&](const T *r, LvlPlane<T> &Q) {
+      const T e0 = r[0], r0 = r[dx], e2 = r[dy], r2 = r[dy + dx];
+      Q.e0 = e0;
+      Q.f0 = mgx_lerp(e0, r0, tx);
+      const T f2 = mgx_lerp(e2, r2, tx);
+      Q.gE = mgx_lerp(e0, e2, ty);
+      Q.gO = mgx_lerp(Q.f0, f2, ty);
+    };
+    LvlPlane<T> A, B;
+    plane(c, A);
+    const uint16_t *ob = a.sym + ((uint64_t)bk * sz + (uint64_t)bj * sy + bi);
+    auto cf = [&](uint64_t off) {
+      const uint16_t *at = ob + off;
+      return coef_of<T>(a, (uint32_t)__ldg(at), at);
+    };
+    T *gb = v.fine + ((uint64_t)fz * fsz + (uint64_t)fy * fsy + fx);
+    gb[0] = A.e0;
+    if (ex) gb[1] = add_rn(cf(v.oX), A.f0);
+    if (ey) gb[fsy] = add_rn(cf(v.oY), A.gE);
+    if (ex && ey) gb[fsy + 1] = add_rn(cf(v.oX + v.oY), A.gO);
+    if (ez) {
+      plane(c + dz, B);
+      gb[fsz] = add_rn(cf(v.oZ), mgx_lerp(A.e0, B.e0, tz));
+      if (ex) gb[fsz + 1] = add_rn(cf(v.oZ + v.oX), mgx_lerp(A.f0, B.f0, tz));
+      if (ey) gb[fsz + fsy] = add_rn(cf(v.oZ + v.oY), mgx_lerp(A.gE, B.gE, tz));
+      if (ex && ey)
+        gb[fsz + fsy + 1] = add_rn(cf(v.oZ + v.oX + v.oY), mgx_lerp(A.gO, B.gO, tz));
+    }
+  }
+}
+
 typedef TileShape<3, 3, 6> Tile3D;  // 8 x 8 x 64
 typedef TileShape<0, 5, 7> Tile2D;  // 32 x 128
 typedef TileShape<0, 0, 10> Tile1D; // 1024
@@ -1252,6 +1415,58 @@ int launch_inverse(mgx_ctx *ctx, void *d_out, HierArgs<T> &a) {
   return MGX_SUCCESS;
 }
 
+// 3-D: level 0 gathered + dequantised from its box, then one k_inv_level3 per level
+// through two ping-pong compact arrays (level L-1 and level L-2 sized)
+template <typename T, bool HALF>
+int launch_inverse_levels(mgx_ctx *ctx, void *d_out, HierArgs<T> &a) {
+  const int L = a.L;
+  auto elems = [&](int l) {
+    return (uint64_t)a.nl[l][0] * a.nl[l][1] * a.nl[l][2];
+  };
+  const size_t need[2] = {L >= 2 ? elems(L - 2) * sizeof(T) : 0,
+                          L >= 1 ? elems(L - 1) * sizeof(T) : 0};
+  for (int i = 0; i < 2; i++)
+    if (ctx->lvl_bytes[i] < need[i]) {
+      if (ctx->d_lvl[i])
+        cudaFree(ctx->d_lvl[i]);
+      ctx->d_lvl[i] = nullptr;
+      ctx->lvl_bytes[i] = 0;
+      MGX_CUDA(cudaMalloc(&ctx->d_lvl[i], need[i]));
+      ctx->lvl_bytes[i] = need[i];
+    }
+  auto buf = [&](int l) { return l == L ? (T *)d_out : (T *)ctx->d_lvl[(L - l) & 1]; };
+  uint64_t celems = 1;
+  for (int d = 0; d < 3; d++) {
+    a.cdim[d] = a.nl[0][d];
+    celems *= a.cdim[d];
+  }
+  k_coarse_gather<T><<<mgx_grid_for(celems, 256, ctx->num_sms * 8), 256, 0,
+                       ctx->stream>>>(buf(0), a);
+  ctx->launches++;
+  const uint64_t sy = a.n[2], sz = (uint64_t)a.n[2] * a.n[1];
+  for (int l = 1; l <= L; l++) {
+    InvLevel<T> v;
+    v.coarse = buf(l - 1);
+    v.fine = buf(l);
+    for (int d = 0; d < 3; d++) {
+      v.cn[d] = a.nl[l - 1][d];
+      v.fn[d] = a.nl[l][d];
+      v.roff[d] = a.roff[l][d];
+    }
+    v.oX = v.cn[2];
+    v.oY = (uint64_t)v.cn[1] * sy;
+    v.oZ = (uint64_t)v.cn[0] * sz;
+    const dim3 grid((v.cn[2] + 31) / 32, (v.cn[1] + 3) / 4, (v.cn[0] + 3) / 4);
+    if (grid.y > 65535u || grid.z > 65535u)
+      return MGX_FAILURE + 102;
+    k_inv_level3<T, HALF><<<grid, IL_THREADS, 0, ctx->stream>>>(
+        a, v, (const T *)ctx->d_tables);
+    ctx->launches++;
+  }
+  MGX_CUDA(cudaGetLastError());
+  return MGX_SUCCESS;
+}
+
 template <typename T>
 int hier_inverse_t(mgx_ctx *ctx, int rel, double tol_d, double norm_d, void *d_out,
                    const uint64_t *d_oidx, const int64_t *d_oval, uint64_t n_out) {
@@ -1265,6 +1480,9 @@ int hier_inverse_t(mgx_ctx *ctx, int rel, double tol_d, double norm_d, void *d_o
   a.n_out = n_out;
   a.out_count = nullptr;
   a.out_cap = 0;
+  if (a.n[0] > 1 && !ctx->inv_tiled)
+    return tb.ratios_half ? launch_inverse_levels<T, true>(ctx, d_out, a)
+                          : launch_inverse_levels<T, false>(ctx, d_out, a);
   if (a.n[0] > 1)
     return tb.ratios_half ? launch_inverse<T, true, Tile3D>(ctx, d_out, a)
                           : launch_inverse<T, false, Tile3D>(ctx, d_out, a);

@@ -742,7 +742,16 @@ uint64_t footprint(int D, const uint64_t *shape, int dtype, double s, int prefet
   uint64_t ws = n * 2 + (n / 256 + 1) * 24 + n / 8 + (1u << 18);
   if (uses_correction(D, s))
     ws += n * es * 2 + (n * es * 3) / 4;
-  else
+  else if (D == 3) {
+    // level-by-level inverse: compact nodal arrays of levels L-1 and L-2
+    uint64_t c1 = es, c2 = es;
+    for (int d = 0; d < D; d++) {
+      const uint64_t h = shape[d] / 2 + 1;
+      c1 *= h;
+      c2 *= h / 2 + 1;
+    }
+    ws += c1 + c2 + (1u << 16);
+  } else
     ws += (n * es) / 256 + (1u << 16); // coarse lattice of the fused inverse
   return io + ws;
 }

@@ -1086,7 +1086,10 @@ __global__ void __launch_bounds__(256)
   }
 }
 
-constexpr int DEC_THREADS = 128;
+#ifndef MGX_DEC_THREADS
+#define MGX_DEC_THREADS 128
+#endif
+constexpr int DEC_THREADS = MGX_DEC_THREADS;
 constexpr int DEC_RING = 20; // symbols per thread (40 B: 2-way bank conflicts)
 
 // DecodeFunctor, Decode.hpp:14-130: one thread per chunk; the stream is read in

@@ -65,6 +65,7 @@ struct mgx_ctx {
   int fw_minb = 0;          // MGX_FW_MINB=2|3: force the k_level_forward variant (0 = by dtype)
   bool no_sym_recompose = false; // MGX_NO_SYM_RECOMPOSE=1: dequantise to floats first
   bool no_ws = false;       // MGX_NO_WS=1: single-warp Thomas kernels only (A/B)
+  bool inv_tiled = false;   // MGX_INV_TILED=1: 3-D inverse on the three-level tile kernel (A/B)
   bool no_tma = false;      // MGX_NO_TMA=1: 3-D hierarchical forward pass on the LDGSTS kernel (A/B)
 
   // workspaces (allocated on first use, sized for the plan)
@@ -88,6 +89,8 @@ struct mgx_ctx {
   void *d_lut = nullptr;            // decode look-up table
   void *d_coarse0 = nullptr, *d_coarse1 = nullptr; // fused inverse: coarse lattice
   size_t coarse_bytes = 0;
+  void *d_lvl[2] = {nullptr, nullptr}; // 3-D level-by-level inverse: compact levels L-2, L-1
+  size_t lvl_bytes[2] = {0, 0};
   void *d_sort_tmp = nullptr;
   void *d_cb_ws = nullptr;          // codebook workspace when it exceeds shared memory
   size_t cb_ws_bytes = 0;
