@@ -1090,12 +1090,38 @@ __global__ void __launch_bounds__(256)
 #define MGX_DEC_THREADS 128
 #endif
 constexpr int DEC_THREADS = MGX_DEC_THREADS;
-constexpr int DEC_RING = 20; // symbols per thread (40 B: 2-way bank conflicts)
+constexpr int DEC_RING = 20; // symbols per thread (40 B pitch: 2-way bank conflicts; 7 + 8 + 4-store spill)
 
-// DecodeFunctor, Decode.hpp:14-130: one thread per chunk; the stream is read in
-// 32-bit units into a 64-bit bit buffer, up to four symbols come out of one
-// shared-memory look-up, and symbols leave through a small per-thread ring in
-// shared memory as 16-byte stores.
+#ifndef MGX_DEC_SLOTS
+#define MGX_DEC_SLOTS 8
+#endif
+constexpr int DEC_SLOTS = MGX_DEC_SLOTS;
+constexpr int DEC_PERIOD = 16; // iterations between top-ups of the stream ring // 64-bit stream words in flight / staged per thread
+
+// 8-byte asynchronous copy global -> shared (LDGSTS): the data never passes through
+// a register, so no register scoreboard ties one lane's fetch to another lane's use
+__device__ __forceinline__ void cp_async8(void *smem_dst, const void *gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(
+                   (uint32_t)__cvta_generic_to_shared(smem_dst)),
+               "l"(gsrc)
+               : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() {
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+template <int N> __device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+// DecodeFunctor, Decode.hpp:14-130: one thread per chunk.  Each lane walks its own
+// stream at its own pace, so refills are divergent; a refill fed by an ordinary load
+// makes the WHOLE warp wait for that load at the next iteration (the scoreboard is
+// per warp and register), i.e. one L2 / DRAM latency per decoded group.  The stream
+// therefore arrives by cp.async into a per-lane ring of DEC_SLOTS 64-bit words in
+// shared memory, topped up at warp-uniform points one period ahead of use (the
+// cp.async group counter is per warp too); the bit buffer refills 32 bits at a time
+// from that ring, up to four symbols come out of one
+// look-up, and symbols leave through a small per-thread ring as 16-byte stores.
 __global__ void __launch_bounds__(DEC_THREADS)
     k_decode_multi(const u64 *__restrict__ packed, const u64 *__restrict__ meta,
                    uint64_t nchunk, uint32_t chunk, uint64_t n,
@@ -1104,6 +1130,7 @@ __global__ void __launch_bounds__(DEC_THREADS)
   __shared__ u64 mlut[1 << LUT_BITS];
   __shared__ u64 s_first[64], s_entry[64];
   __shared__ __align__(8) uint16_t s_ring[DEC_THREADS * DEC_RING];
+  __shared__ u64 s_words[DEC_SLOTS * DEC_THREADS]; // slot-major: lanes side by side
   for (uint32_t i = threadIdx.x; i < (1u << LUT_BITS); i += blockDim.x)
     mlut[i] = g_mlut[i];
   if (threadIdx.x < 64) {
@@ -1113,33 +1140,72 @@ __global__ void __launch_bounds__(DEC_THREADS)
   __syncthreads();
   const u64 *keys = db + 128;
   uint16_t *ring = s_ring + threadIdx.x * DEC_RING;
+  u64 *words = s_words + threadIdx.x;
   for (uint64_t c = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; c < nchunk;
        c += (uint64_t)gridDim.x * blockDim.x) {
     const u64 *w = packed + meta[nchunk + c];
-    const uint32_t *w32 = (const uint32_t *)w; // unit u = w32[u ^ 1]
     const uint64_t total = meta[c];
-    const uint32_t nunits = (uint32_t)(((total + 63) >> 6) << 1);
+    const uint32_t nwords = (uint32_t)((total + 63) >> 6);
     const uint64_t base = c * chunk;
     const uint32_t count = (uint32_t)min((uint64_t)chunk, n - base);
     uint16_t *dst = sym + base;
-    auto unit = [&](uint32_t u) -> uint32_t { return u < nunits ? w32[u ^ 1] : 0u; };
-    u64 buf = ((u64)unit(0) << 32) | unit(1);
-    uint32_t nbits = 64, next_unit = 2;
-    // the unit the NEXT refill will need is fetched one refill ahead, so its
-    // L2/DRAM latency is not on the decode chain
-    uint32_t ahead = unit(2);
-    uint64_t pos = 0;
-    uint32_t k = 0, produced = 0, written = 0;
+    // The per-lane ring holds stream words [unit / 2, nissued).  Every DEC_PERIOD
+    // iterations -- the same iteration for every lane still decoding -- the copies
+    // issued one period ago are waited for (long landed) and each lane tops its ring
+    // up to DEC_SLOTS words ahead.  A look-up consumes at most LUT_BITS bits, so a lane
+    // uses at most DEC_PERIOD * LUT_BITS / 64 = 3 words per period and always finds
+    // its bits among the words that landed before the last top-up.
+    uint32_t nissued = 0;
+    auto fetch = [&]() {
+      if (nissued < nwords)
+        cp_async8(words + (nissued & (DEC_SLOTS - 1)) * DEC_THREADS, w + nissued);
+      ++nissued;
+    };
+    auto half = [&](uint32_t u) -> uint32_t { // 32-bit unit u of the stream
+      const uint32_t *p32 =
+          (const uint32_t *)(words + ((u >> 1) & (DEC_SLOTS - 1)) * DEC_THREADS);
+      return p32[(u & 1) ^ 1];
+    };
+    u64 buf;
+    uint32_t nbits, unit;
+    auto prime = [&](uint32_t w0, uint32_t r) { // bit cursor at word w0, bit r
+      cp_async_wait<0>();
+      nissued = w0;
+#pragma unroll
+      for (int i = 0; i < DEC_SLOTS; i++)
+        fetch();
+      cp_async_commit();
+      cp_async_wait<0>();
+      buf = (((u64)half(2 * w0) << 32) | half(2 * w0 + 1)) << r;
+      nbits = 64 - r;
+      unit = 2 * w0 + 2;
+    };
+    prime(0, 0);
+    uint32_t it = 0;
+    // two look-ups per iteration: with more than 32 bits in the buffer at the top,
+    // both windows are complete (2 * LUT_BITS <= 32 - 8) and one 32-bit refill
+    // restores the invariant; the symbol ring takes up to 8 new entries on top of
+    // the up to 7 left by the last flush
+    uint32_t produced = 0, written = 0;
     while (produced < count) {
-      const u64 e = mlut[(uint32_t)(buf >> (64 - LUT_BITS))];
-      uint32_t cnt = (uint32_t)(e >> 4) & 7u;
-      uint32_t len = (uint32_t)e & 15u;
-      if (cnt == 0) {
+      if ((it++ & (DEC_PERIOD / 2 - 1)) == 0) {
+        cp_async_wait<0>();
+#pragma unroll
+        for (int i = 0; i < DEC_PERIOD * LUT_BITS / 64; i++)
+          if (nissued < (unit >> 1) + DEC_SLOTS)
+            fetch();
+        cp_async_commit();
+      }
+      const u64 e1 = mlut[(uint32_t)(buf >> (64 - LUT_BITS))];
+      const uint32_t c1 = (uint32_t)(e1 >> 4) & 7u, len1 = (uint32_t)e1 & 15u;
+      uint16_t *r = ring + (produced - written);
+      if (__builtin_expect(c1 == 0, 0)) {
         // first code is longer than the window: canonical search on the raw
         // words (Decode.hpp:60-66), then re-prime the bit buffer
+        uint64_t pos = 32ull * unit - nbits; // bits consumed so far
         const uint32_t wi = (uint32_t)(pos >> 6), used = (uint32_t)(pos & 63);
-        const u64 cur = w[wi];
-        const u64 nxt = ((uint64_t)(wi + 1) * 64 < total) ? w[wi + 1] : 0;
+        const u64 cur = wi < nwords ? w[wi] : 0;
+        const u64 nxt = wi + 1 < nwords ? w[wi + 1] : 0;
         const u64 window = used ? ((cur << used) | (nxt >> (64 - used))) : cur;
         uint32_t l = LUT_BITS;
         u64 v;
@@ -1147,44 +1213,46 @@ __global__ void __launch_bounds__(DEC_THREADS)
           ++l;
           v = window >> (64 - l);
         } while (v < s_first[l] && l < 63);
-        ring[k] = (uint16_t)keys[min(s_entry[l] + v - s_first[l], (u64)dict - 1)];
-        ++k;
+        r[0] = (uint16_t)keys[min(s_entry[l] + v - s_first[l], (u64)dict - 1)];
         ++produced;
         pos += l;
-        const uint32_t u0 = (uint32_t)(pos >> 5), r = (uint32_t)(pos & 31);
-        buf = (((u64)unit(u0) << 32) | unit(u0 + 1)) << r;
-        nbits = 64 - r;
-        next_unit = u0 + 2;
-        ahead = unit(next_unit);
+        prime((uint32_t)(pos >> 6), (uint32_t)(pos & 63));
       } else {
-        cnt = min(cnt, count - produced);
-        ring[k + 0] = (uint16_t)((e >> 8) & 0x1fff);
-        ring[k + 1] = (uint16_t)((e >> 21) & 0x1fff);
-        ring[k + 2] = (uint16_t)((e >> 34) & 0x1fff);
-        ring[k + 3] = (uint16_t)((e >> 47) & 0x1fff);
-        k += cnt;
-        produced += cnt;
-        pos += len;
-        buf <<= len;
-        nbits -= len;
+        const u64 b2 = buf << len1;
+        const u64 e2 = mlut[(uint32_t)(b2 >> (64 - LUT_BITS))];
+        r[0] = (uint16_t)((e1 >> 8) & 0x1fff);
+        r[1] = (uint16_t)((e1 >> 21) & 0x1fff);
+        r[2] = (uint16_t)((e1 >> 34) & 0x1fff);
+        r[3] = (uint16_t)((e1 >> 47) & 0x1fff);
+        // a second window that starts with a long code has count 0 and length 0:
+        // nothing is consumed and the next iteration takes the branch above
+        const uint32_t c2 = (uint32_t)(e2 >> 4) & 7u, len2 = (uint32_t)e2 & 15u;
+        r += c1;
+        r[0] = (uint16_t)((e2 >> 8) & 0x1fff);
+        r[1] = (uint16_t)((e2 >> 21) & 0x1fff);
+        r[2] = (uint16_t)((e2 >> 34) & 0x1fff);
+        r[3] = (uint16_t)((e2 >> 47) & 0x1fff);
+        produced = min(produced + c1 + c2, count);
+        buf = b2 << len2;
+        nbits -= len1 + len2;
       }
       if (nbits <= 32) {
-        buf |= (u64)ahead << (32 - nbits);
+        buf |= (u64)half(unit) << (32 - nbits);
         nbits += 32;
-        ++next_unit;
-        ahead = unit(next_unit);
+        ++unit;
       }
-      if (k >= 8) {
+      if (produced - written >= 8) {
         const uint2 a0 = *reinterpret_cast<const uint2 *>(ring);
         const uint2 a1 = *reinterpret_cast<const uint2 *>(ring + 4);
         *reinterpret_cast<uint4 *>(dst + written) = make_uint4(a0.x, a0.y, a1.x, a1.y);
         *reinterpret_cast<uint2 *>(ring) = *reinterpret_cast<const uint2 *>(ring + 8);
+        *reinterpret_cast<uint2 *>(ring + 4) = *reinterpret_cast<const uint2 *>(ring + 12);
         written += 8;
-        k -= 8;
       }
     }
-    for (uint32_t j = 0; j < k; j++)
+    for (uint32_t j = 0; written + j < produced; j++)
       dst[written + j] = ring[j];
+    cp_async_wait<0>(); // the ring is reused by this thread's next chunk
   }
 }
 
