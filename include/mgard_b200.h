@@ -154,6 +154,13 @@ double mgx_local_abs_tol(int dtype, int rel, double norm, double tol, double s,
  * lets stage A13 be parity-checked on its own. */
 int mgx_last_histogram(mgx_ctx *ctx, uint32_t *h_freq);
 
+/* Chains that the partitioned Thomas solves have had to redo sequentially since the
+ * context's counters were last reset (start of mgx_compress or of a decode; one
+ * synchronising 8-byte read) because a partition's warm-up did not reproduce the sequential
+ * sweep's state bit for bit (mgx_level.cu: k_ipk_part_*; replaces the one-thread-per-
+ * chain Ipk1/2/3Reo, IterativeProcessingKernel3D.hpp:28-1169).  0 in practice. */
+uint64_t mgx_last_redo_count(mgx_ctx *ctx);
+
 /* kernels launched by this context since creation (bench.py's gpu_launches) */
 uint64_t mgx_launch_count(const mgx_ctx *ctx);
 

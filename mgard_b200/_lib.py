@@ -121,6 +121,7 @@ SIGNATURES = {
     "mgx_local_abs_tol": (c_dbl, [c_int, c_int, c_dbl, c_dbl, c_dbl, c_u64]),
     "mgx_launch_count": (c_u64, [c_vp]),
     "mgx_last_histogram": (c_int, [c_vp, c_vp]),
+    "mgx_last_redo_count": (c_u64, [c_vp]),
     "mgx_set_timing": (c_int, [c_vp, c_int]),
     "mgx_elapsed_ms": (c_int, [c_vp, c_int, c_int,
                                ctypes.POINTER(ctypes.c_float)]),

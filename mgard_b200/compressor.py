@@ -154,6 +154,10 @@ class Compressor:
         self._check(self.lib.mgx_last_histogram(self._ctx, h.ctypes.data))
         return h
 
+    def LastRedoCount(self):
+        """chains the partitioned Thomas solves of the last Compress redid sequentially"""
+        return int(self.lib.mgx_last_redo_count(self._ctx))
+
     def launch_count(self):
         return int(self.lib.mgx_launch_count(self._ctx))
 

@@ -120,6 +120,8 @@ int mgx_create(mgx_ctx **out, int device, void *cuda_stream) {
     ctx->no_ws = e && e[0] == '1';
     e = getenv("MGX_NO_TMA");
     ctx->no_tma = e && e[0] == '1';
+    e = getenv("MGX_NO_PART");
+    ctx->no_part = e && e[0] == '1';
     e = getenv("MGX_INV_TILED");
     ctx->inv_tiled = e && e[0] == '1';
   }
@@ -142,6 +144,7 @@ int mgx_create(mgx_ctx **out, int device, void *cuda_stream) {
     delete ctx;
     return MGX_FAILURE;
   }
+  cudaMemsetAsync(ctx->d_scalars, 0, MGX_SC_COUNT * 8, ctx->stream);
   *out = ctx;
   return MGX_SUCCESS;
 }
@@ -175,6 +178,20 @@ const char *mgx_last_error(const mgx_ctx *ctx) {
 }
 
 uint64_t mgx_launch_count(const mgx_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+// chains the partitioned Thomas solves had to redo sequentially since the device
+// scalars were last reset (start of mgx_compress / mgx_hier_quantize / a decode):
+// their warm-up did not reproduce the sequential state bit for bit; 0 in practice
+uint64_t mgx_last_redo_count(mgx_ctx *ctx) {
+  if (!ctx)
+    return 0;
+  unsigned long long v = 0;
+  if (cudaMemcpyAsync(&v, ctx->d_scalars + MGX_SC_REDO, 8, cudaMemcpyDeviceToHost,
+                      ctx->stream) != cudaSuccess ||
+      cudaStreamSynchronize(ctx->stream) != cudaSuccess)
+    return 0;
+  return v;
+}
 
 int mgx_last_histogram(mgx_ctx *ctx, uint32_t *h_freq) {
   if (!ctx || !ctx->planned || !ctx->d_freq || !h_freq)

@@ -65,6 +65,7 @@ struct mgx_ctx {
   int fw_minb = 0;          // MGX_FW_MINB=2|3: force the k_level_forward variant (0 = by dtype)
   bool no_sym_recompose = false; // MGX_NO_SYM_RECOMPOSE=1: dequantise to floats first
   bool no_ws = false;       // MGX_NO_WS=1: single-warp Thomas kernels only (A/B)
+  bool no_part = false;     // MGX_NO_PART=1: no partitioned Thomas solves (A/B)
   bool inv_tiled = false;   // MGX_INV_TILED=1: 3-D inverse on the three-level tile kernel (A/B)
   bool no_tma = false;      // MGX_NO_TMA=1: 3-D hierarchical forward pass on the LDGSTS kernel (A/B)
 
@@ -124,6 +125,7 @@ enum {
   MGX_SC_TICKET = 4,   // dynamic block id for the look-back scan
   MGX_SC_ERR = 5,      // device-side error flags
   MGX_SC_NZ = 6,       // number of non-zero symbols
+  MGX_SC_REDO = 7,     // partitioned Thomas solves: chains redone sequentially
   MGX_SC_COUNT = 16
 };
 

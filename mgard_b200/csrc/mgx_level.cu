@@ -1377,6 +1377,274 @@ LvGeom level_geom(const mgx_ctx *ctx, int l, uint32_t cols_per_chunk) {
   return g;
 }
 
+// ---- partitioned Thomas solves (long, scarce chains) -----------------------------
+// A 2-D 8193^2 level has 4097 chains of 4097 steps: one thread per chain leaves the
+// GPU at ~10 % of its bandwidth.  Both recurrences contract (|am / bm| ~ 0.27 per
+// step), so a chain is cut into P partitions that run concurrently: partition p
+// first runs the recurrence over the PT_W elements BEFORE its range from a zero
+// state, storing nothing; after PT_W steps the influence of the wrong start is
+// 0.27^64 ~ 1e-37 of the neighbouring values -- far below an ulp -- and the state
+// it enters its own range with is, bit for bit, the state the sequential sweep has
+// there.  That is not assumed but CHECKED: the state partition p entered with is
+// compared bitwise with the last state partition p-1 computed; where they differ
+// (a decaying tail after a run of zeros, a 1e+250 next to a 1e-250) partition p
+// repeats its range from its neighbour's state, and the comparison is repeated
+// until every pair agrees (at most P rounds; the first partition is exact, so
+// round r fixes partition r at the latest).  The result then IS the sequential
+// sweep.  Hence: forward sweep out of place (x -> y, x stays readable for the
+// repeats), backward sweep y -> x, and for the accumulating solve a third in-kernel
+// pass acc +-= x over the CTA's own chains once they are final.
+// A CTA owns 32 chains (lanes) x P partitions (warps).
+constexpr int PT_W = 64;       // warm-up steps
+constexpr int PT_MAXP = 16;    // partitions (warps) per CTA
+
+template <typename T> __device__ __forceinline__ bool bits_differ(T a, T b);
+template <> __device__ __forceinline__ bool bits_differ<float>(float a, float b) {
+  return __float_as_uint(a) != __float_as_uint(b);
+}
+template <> __device__ __forceinline__ bool bits_differ<double>(double a, double b) {
+  return __double_as_longlong(a) != __double_as_longlong(b);
+}
+
+// Repeat `sweep(enter) -> last state` for the partitions whose entering state is not
+// the neighbour's last state, until none is left.  nb = index of the neighbour the
+// state comes from (p-1 forward, p+1 backward), has_nb = there is one.
+template <typename T, class Sweep>
+__device__ __forceinline__ void
+part_repair(T (&s_edge)[PT_MAXP][32], uint32_t p, uint32_t lane, bool has_nb,
+            uint32_t nb, bool live, T enter, T last, Sweep sweep,
+            unsigned long long *redo_count) {
+  for (;;) {
+    s_edge[p][lane] = last;
+    __syncthreads();
+    const bool need = has_nb && live && bits_differ(enter, s_edge[nb][lane]);
+    const T from = has_nb ? s_edge[nb][lane] : enter;
+    const int any = __syncthreads_or(need ? 1 : 0);
+    if (!any)
+      break;
+    if (__any_sync(0xffffffffu, need)) {
+      // lanes that agree recompute the same bits from the same state
+      enter = from;
+      last = sweep(enter);
+      if (need)
+        atomicAdd(redo_count, 1ull);
+    }
+  }
+}
+
+// chain element i of lane's chain lives at base[i * inner]
+template <typename T, bool ACC>
+__global__ void __launch_bounds__(PT_MAXP * 32)
+    k_ipk_part_strided(T *__restrict__ x, T *__restrict__ y, const T *__restrict__ am,
+                       const T *__restrict__ bm, const T *__restrict__ abr,
+                       const double *__restrict__ rbm, uint32_t n, uint64_t inner,
+                       uint64_t lines, uint32_t lp, T *__restrict__ acc, int sign,
+                       int fast, unsigned long long *__restrict__ redo_count) {
+  __shared__ T s_edge[PT_MAXP][32];
+  const uint32_t lane = threadIdx.x & 31, p = threadIdx.x >> 5, P = blockDim.x >> 5;
+  uint64_t ln = (uint64_t)blockIdx.x * 32 + lane;
+  const bool active = ln < lines;
+  if (!active)
+    ln = lines - 1; // shadow lanes: compute, never store
+  const uint64_t o = ln / inner, in_ = ln % inner;
+  const uint64_t base = o * n * inner + in_;
+  T *xl = x + base, *yl = y + base;
+  T *al = ACC ? acc + base : nullptr;
+  const uint32_t s = min(p * lp, n), e = min(s + lp, n);
+  // ---- forward: y[i] = x[i] - y[i-1] * abr[i] ----
+  auto fwd = [&](uint32_t lo, uint32_t hi, T prev, bool store) {
+    for (uint32_t i0 = lo; i0 < hi; i0 += 8) {
+      T c[8], f[8];
+#pragma unroll
+      for (int k = 0; k < 8; k++) {
+        const uint32_t i = min(i0 + k, hi - 1);
+        c[k] = xl[(uint64_t)i * inner];
+        f[k] = __ldg(abr + i);
+      }
+#pragma unroll
+      for (int k = 0; k < 8; k++)
+        if (i0 + k < hi) {
+          prev = sub_rn(c[k], mul_rn(prev, f[k]));
+          if (store && active)
+            yl[(uint64_t)(i0 + k) * inner] = prev;
+        }
+    }
+    return prev;
+  };
+  {
+    const T enter = fwd(s > (uint32_t)PT_W ? s - PT_W : 0, s, (T)0, false);
+    const T last = fwd(s, e, enter, true);
+    part_repair<T>(s_edge, p, lane, p > 0, p - 1, s < e, enter, last,
+                   [&](T from) { return fwd(s, e, from, true); }, redo_count);
+  }
+  __syncthreads(); // every y of the CTA's chains is final and visible
+  // ---- backward: x[i] = (y[i] - am[i+1] * x[i+1]) / bm[i+1] ----
+  auto bwd = [&](uint32_t lo, uint32_t hi, T prev, bool store) {
+    // elements hi-1, hi-2, ..., lo
+    while (hi > lo) {
+      const uint32_t cnt = min(8u, hi - lo);
+      T c[8], a1[8], b1[8], res[8];
+      double y1[8];
+#pragma unroll
+      for (int k = 0; k < 8; k++) {
+        const uint32_t i = hi - 1 - min((uint32_t)k, cnt - 1);
+        c[k] = yl[(uint64_t)i * inner];
+        a1[k] = __ldg(am + i + 1);
+        b1[k] = __ldg(bm + i + 1);
+        y1[k] = __ldg(rbm + i + 1);
+      }
+      prev = backward_batch<T, 8>(c, a1, b1, y1, (int)cnt, prev, fast != 0, res);
+      if (store && active) {
+#pragma unroll
+        for (int k = 0; k < 8; k++)
+          if ((uint32_t)k < cnt)
+            xl[(uint64_t)(hi - 1 - k) * inner] = res[k];
+      }
+      hi -= cnt;
+    }
+    return prev;
+  };
+  {
+    const T enter = bwd(e, min(e + (uint32_t)PT_W, n), (T)0, false);
+    const T last = bwd(s, e, enter, true);
+    part_repair<T>(s_edge, p, lane, p + 1 < P && e < n, p + 1, s < e, enter, last,
+                   [&](T from) { return bwd(s, e, from, true); }, redo_count);
+  }
+  if (ACC) {
+    __syncthreads();
+    if (active)
+      for (uint32_t i = s; i < e; i++) {
+        const uint64_t off = (uint64_t)i * inner;
+        al[off] = sign > 0 ? add_rn(al[off], xl[off]) : sub_rn(al[off], xl[off]);
+      }
+  }
+}
+
+// Contiguous chains: lanes = 32 chains, a warp moves 32 x 32 tiles of its partition
+// through shared memory (coalesced rows in, a lane walks its chain's row, coalesced
+// rows out), as k_ipk_contig does for whole chains.  lp and PT_W are multiples of 32.
+template <typename T> struct PartTile {
+  T t[32][33];
+  T ta[32], tb[32];
+  double ty[32];
+};
+
+template <typename T, bool ACC>
+__global__ void __launch_bounds__(PT_MAXP * 32)
+    k_ipk_part_contig(T *__restrict__ x, T *__restrict__ y, const T *__restrict__ am,
+                      const T *__restrict__ bm, const T *__restrict__ abr,
+                      const double *__restrict__ rbm, uint32_t n, uint64_t lines,
+                      uint32_t lp, T *__restrict__ acc, int sign, int fast,
+                      unsigned long long *__restrict__ redo_count) {
+  extern __shared__ __align__(16) unsigned char pt_smem[];
+  __shared__ T s_edge[PT_MAXP][32];
+  const uint32_t lane = threadIdx.x & 31, p = threadIdx.x >> 5, P = blockDim.x >> 5;
+  PartTile<T> &w = reinterpret_cast<PartTile<T> *>(pt_smem)[p];
+  const uint64_t l0 = (uint64_t)blockIdx.x * 32;
+  const uint32_t nl = (uint32_t)min((uint64_t)32, lines - l0);
+  T *xb = x + l0 * n, *yb = y + l0 * n;
+  T *ab = ACC ? acc + l0 * n : nullptr;
+  const uint32_t s = min(p * lp, n), e = min(s + lp, n);
+  // ---- forward over the 32-column tiles [lo, hi) ----
+  auto fwd = [&](uint32_t lo, uint32_t hi, T prev, bool store) {
+    for (uint32_t c0 = lo; c0 < hi; c0 += 32) {
+      const uint32_t ncol = min(32u, n - c0);
+      if (lane < ncol) {
+        for (uint32_t r = 0; r < nl; r++)
+          w.t[r][lane] = xb[(uint64_t)r * n + c0 + lane];
+        w.ta[lane] = __ldg(abr + c0 + lane);
+      }
+      __syncwarp();
+      if (lane < nl) {
+        if (ncol == 32) {
+#pragma unroll 8
+          for (uint32_t j = 0; j < 32; j++) {
+            prev = sub_rn(w.t[lane][j], mul_rn(prev, w.ta[j]));
+            w.t[lane][j] = prev;
+          }
+        } else {
+          for (uint32_t j = 0; j < ncol; j++) {
+            prev = sub_rn(w.t[lane][j], mul_rn(prev, w.ta[j]));
+            w.t[lane][j] = prev;
+          }
+        }
+      }
+      __syncwarp();
+      if (store && lane < ncol)
+        for (uint32_t r = 0; r < nl; r++)
+          yb[(uint64_t)r * n + c0 + lane] = w.t[r][lane];
+      __syncwarp();
+    }
+    return prev;
+  };
+  {
+    const T enter = fwd(s > (uint32_t)PT_W ? s - PT_W : 0, s, (T)0, false);
+    const T last = fwd(s, e, enter, true);
+    part_repair<T>(s_edge, p, lane, p > 0, p - 1, s < e && lane < nl, enter, last,
+                   [&](T from) { return fwd(s, e, from, true); }, redo_count);
+  }
+  __syncthreads();
+  // ---- backward over the tiles of [lo, hi), highest first (lo a multiple of 32) ----
+  auto bwd = [&](uint32_t lo, uint32_t hi, T prev, bool store) {
+    if (hi <= lo)
+      return prev;
+    for (uint32_t c0 = ((hi - 1) / 32) * 32 + 32; c0 > lo;) {
+      c0 -= 32;
+      const uint32_t ncol = min(32u, hi - c0);
+      if (lane < ncol) {
+        for (uint32_t r = 0; r < nl; r++)
+          w.t[r][lane] = yb[(uint64_t)r * n + c0 + lane];
+        w.ta[lane] = __ldg(am + c0 + lane + 1);
+        w.tb[lane] = __ldg(bm + c0 + lane + 1);
+        w.ty[lane] = __ldg(rbm + c0 + lane + 1);
+      }
+      __syncwarp();
+      if (lane < nl) {
+        for (uint32_t j0 = 0; j0 < ncol; j0 += 8) {
+          T c[8], a1[8], b1[8], res[8];
+          double y1[8];
+          const int cnt = (int)min(8u, ncol - j0);
+#pragma unroll
+          for (int k = 0; k < 8; k++) {
+            const uint32_t j = k < cnt ? ncol - 1 - j0 - k : 0;
+            c[k] = w.t[lane][j];
+            a1[k] = w.ta[j];
+            b1[k] = w.tb[j];
+            y1[k] = w.ty[j];
+          }
+          prev = backward_batch<T, 8>(c, a1, b1, y1, cnt, prev, fast != 0, res);
+#pragma unroll
+          for (int k = 0; k < 8; k++)
+            if (k < cnt)
+              w.t[lane][ncol - 1 - j0 - k] = res[k];
+        }
+      }
+      __syncwarp();
+      if (store && lane < ncol)
+        for (uint32_t r = 0; r < nl; r++)
+          xb[(uint64_t)r * n + c0 + lane] = w.t[r][lane];
+      __syncwarp();
+    }
+    return prev;
+  };
+  {
+    const T enter = bwd(e, min(e + (uint32_t)PT_W, n), (T)0, false);
+    const T last = bwd(s, e, enter, true);
+    part_repair<T>(s_edge, p, lane, p + 1 < P && e < n, p + 1, s < e && lane < nl,
+                   enter, last, [&](T from) { return bwd(s, e, from, true); },
+                   redo_count);
+  }
+  if (ACC) {
+    __syncthreads();
+    for (uint32_t c0 = s; c0 < e; c0 += 32)
+      if (c0 + lane < n)
+        for (uint32_t r = 0; r < nl; r++) {
+          const uint64_t off = (uint64_t)r * n + c0 + lane;
+          ab[off] = sign > 0 ? add_rn(ab[off], xb[off]) : sub_rn(ab[off], xb[off]);
+        }
+  }
+}
+
 unsigned task_grid(const LvGeom &g, unsigned warps_per_block) {
   return (unsigned)((g.tasks + warps_per_block - 1) / warps_per_block);
 }
@@ -1465,7 +1733,27 @@ int correction_tail(mgx_ctx *ctx, int l, T *R0, T *R1, T *A, int sign) {
     T *acc = (d == pad) ? A : nullptr;
     // scarce chains: the producer/consumer pair kernels (one pair per 32 lines)
     const bool scarce = lines < (uint64_t)ctx->num_sms * 128 && !ctx->no_ws;
-    if (inner == 1 && scarce) {
+    // long, scarce chains: partitioned solves (bit-identical, checked in-kernel)
+    if (!ctx->no_part && n >= 1024 && lines < (uint64_t)ctx->num_sms * 512) {
+      const uint32_t P = (uint32_t)std::min<uint64_t>(PT_MAXP, n / 256);
+      const uint32_t lp = ((n + P - 1) / P + 31) / 32 * 32;
+      T *other = corr == R0 ? R1 : R0;
+      unsigned long long *redo =
+          (unsigned long long *)(ctx->d_scalars + MGX_SC_REDO);
+      const unsigned grid = (unsigned)((lines + 31) / 32);
+      if (inner == 1) {
+        const size_t smem = (size_t)P * sizeof(PartTile<T>);
+        auto kern = acc ? k_ipk_part_contig<T, true> : k_ipk_part_contig<T, false>;
+        MGX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)(PT_MAXP * sizeof(PartTile<T>))));
+        kern<<<grid, P * 32, smem, ctx->stream>>>(corr, other, am, bm, abr, rbm, n,
+                                                  lines, lp, acc, sign, fast, redo);
+      } else {
+        auto kern = acc ? k_ipk_part_strided<T, true> : k_ipk_part_strided<T, false>;
+        kern<<<grid, P * 32, 0, ctx->stream>>>(corr, other, am, bm, abr, rbm, n, inner,
+                                               lines, lp, acc, sign, fast, redo);
+      }
+    } else if (inner == 1 && scarce) {
       k_ipk_contig_ws<T><<<(unsigned)((lines + 31) / 32), 96, 0, ctx->stream>>>(
           corr, am, bm, abr, rbm, n, lines, acc, sign, fast);
     } else if (inner == 1) {
