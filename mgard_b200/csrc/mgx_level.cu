@@ -1734,8 +1734,8 @@ int correction_tail(mgx_ctx *ctx, int l, T *R0, T *R1, T *A, int sign) {
     // scarce chains: the producer/consumer pair kernels (one pair per 32 lines)
     const bool scarce = lines < (uint64_t)ctx->num_sms * 128 && !ctx->no_ws;
     // long, scarce chains: partitioned solves (bit-identical, checked in-kernel)
-    if (!ctx->no_part && n >= 1024 && lines < (uint64_t)ctx->num_sms * 512) {
-      const uint32_t P = (uint32_t)std::min<uint64_t>(PT_MAXP, n / 256);
+    if (!ctx->no_part && n >= 256 && lines < (uint64_t)ctx->num_sms * 512) {
+      const uint32_t P = (uint32_t)std::min<uint64_t>(PT_MAXP, n / 128);
       const uint32_t lp = ((n + P - 1) / P + 31) / 32 * 32;
       T *other = corr == R0 ? R1 : R0;
       unsigned long long *redo =
