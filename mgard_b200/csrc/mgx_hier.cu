@@ -1116,16 +1116,23 @@ __device__ __forceinline__ void lvl_plane(const T *__restrict__ c, uint64_t csy,
   Q.gO = mgx_lerp(Q.f0, f2, ty);
 }
 
-constexpr int IL_THREADS = 256;
+#ifndef MGX_IL_THREADS
+#define MGX_IL_THREADS 128
+#endif
+#ifndef MGX_IL_MINB
+#define MGX_IL_MINB (1024 / MGX_IL_THREADS)
+#endif
+constexpr int IL_THREADS = MGX_IL_THREADS; // 32 x-blocks x 4 y-blocks x IL_ZW z-pairs
+constexpr int IL_ZW = IL_THREADS / 128;
 
 template <typename T, bool HALF>
-__global__ void __launch_bounds__(IL_THREADS)
+__global__ void __launch_bounds__(IL_THREADS, MGX_IL_MINB)
     k_inv_level3(const __grid_constant__ HierArgs<T> a,
                  const __grid_constant__ InvLevel<T> v, const T *__restrict__ tables) {
   const uint32_t lane = threadIdx.x & 31, wy = (threadIdx.x >> 5) & 3,
                  wz = threadIdx.x >> 7;
   const uint32_t bi = blockIdx.x * 32 + lane, bj = blockIdx.y * 4 + wy,
-                 bk0 = blockIdx.z * 4 + wz * 2;
+                 bk0 = blockIdx.z * (2 * IL_ZW) + wz * 2;
   const uint32_t cnz = v.cn[0], cny = v.cn[1], cnx = v.cn[2];
   const uint32_t fnz = v.fn[0], fny = v.fn[1], fnx = v.fn[2];
   if (bi >= cnx || bj >= cny || bk0 >= cnz)
@@ -1456,7 +1463,8 @@ int launch_inverse_levels(mgx_ctx *ctx, void *d_out, HierArgs<T> &a) {
     v.oX = v.cn[2];
     v.oY = (uint64_t)v.cn[1] * sy;
     v.oZ = (uint64_t)v.cn[0] * sz;
-    const dim3 grid((v.cn[2] + 31) / 32, (v.cn[1] + 3) / 4, (v.cn[0] + 3) / 4);
+    const dim3 grid((v.cn[2] + 31) / 32, (v.cn[1] + 3) / 4,
+                    (v.cn[0] + 2 * IL_ZW - 1) / (2 * IL_ZW));
     if (grid.y > 65535u || grid.z > 65535u)
       return MGX_FAILURE + 102;
     k_inv_level3<T, HALF><<<grid, IL_THREADS, 0, ctx->stream>>>(

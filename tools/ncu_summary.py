@@ -1,4 +1,4 @@
-"""Summarise ncu --set full reports (one kernel launch each) into markdown.
+"""Summarise ncu --set full reports (every kernel launch in them) into markdown.
 
 usage: ncu_summary.py out.md title rep1.ncu-rep [rep2 ...]
 Also prints, per report, 'kernel<TAB>dram_bytes' for profiles/dram_traffic.json."""
@@ -22,6 +22,10 @@ KEEP = [
     "smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio",
     "smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio",
     "smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_mio_throttle_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_lg_throttle_per_issue_active.ratio",
+    "l1tex__throughput.avg.pct_of_peak_sustained_elapsed",
+    "lts__throughput.avg.pct_of_peak_sustained_elapsed",
 ]
 SCALE = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0, "Tbyte": 1e12}
 
@@ -37,19 +41,20 @@ def main():
         rows = list(csv.reader(io.StringIO(txt)))
         if len(rows) < 3:
             continue
-        hdr, units, vals = rows[0], rows[1], rows[-1]
-        name = vals[hdr.index("Kernel Name")]
-        md.append("## %s" % name[:110])
-        dram = 0.0
-        for k in KEEP:
-            if k in hdr:
-                j = hdr.index(k)
-                md.append("- %s = %s %s" % (k, vals[j], units[j]))
-                if k.startswith("dram__bytes"):
-                    dram += float(vals[j]) * SCALE.get(units[j], 1.0)
-        md.append("- dram bytes read+write = %.4g GB" % (dram / 1e9))
-        md.append("")
-        print("%s\t%.0f" % (name.split("(")[0], dram))
+        hdr, units = rows[0], rows[1]
+        for vals in rows[2:]:
+            name = vals[hdr.index("Kernel Name")]
+            md.append("## %s" % name[:110])
+            dram = 0.0
+            for k in KEEP:
+                if k in hdr:
+                    j = hdr.index(k)
+                    md.append("- %s = %s %s" % (k, vals[j], units[j]))
+                    if k.startswith("dram__bytes"):
+                        dram += float(vals[j]) * SCALE.get(units[j], 1.0)
+            md.append("- dram bytes read+write = %.4g GB" % (dram / 1e9))
+            md.append("")
+            print("%s\t%.0f" % (name.split("(")[0], dram))
     with open(out, "w") as f:
         f.write("\n".join(md))
 
