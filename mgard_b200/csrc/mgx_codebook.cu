@@ -83,48 +83,77 @@ __global__ void __launch_bounds__(CB_THREADS, 1)
   // tFreq needs dict+2 entries: P*8+16 >= dict*8+8 always holds
 
   // ---- stable sort by frequency (SortByKey, GetCodebook.hpp:40-51) ----------
-  for (int i = tid; i < P; i += CB_THREADS)
-    A.sortbuf[i] = i < dict ? (((unsigned long long)freq[i] << 16) | (unsigned)i)
-                            : ~0ull;
-  __syncthreads();
-  for (int k = 2; k <= P; k <<= 1)
-    for (int j = k >> 1; j > 0; j >>= 1) {
-      for (int i = tid; i < P; i += CB_THREADS) {
-        int ixj = i ^ j;
-        if (ixj > i) {
-          unsigned long long a = A.sortbuf[i], b = A.sortbuf[ixj];
-          bool up = (i & k) == 0;
-          if ((a > b) == up) {
-            A.sortbuf[i] = b;
-            A.sortbuf[ixj] = a;
+  // Most of the dictionary has count 0: those symbols stay in index order at the
+  // front (what a stable sort gives), only the non-zero ones are sorted, by
+  // (count, index).  Step 1: ordered compaction -- a thread owns `per` consecutive
+  // symbols, an exclusive scan of its non-zero count gives their ranks.
+  {
+    const int per = (dict + CB_THREADS - 1) / CB_THREADS;
+    const int lo = min(tid * per, dict), hi = min(lo + per, dict);
+    int nz = 0;
+    for (int i = lo; i < hi; i++)
+      nz += freq[i] != 0;
+    int incl = nz;
+    for (int off = 1; off < 32; off <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, off);
+      if (lane >= off)
+        incl += t;
+    }
+    if (lane == 31)
+      s_red[warp] = incl;
+    __syncthreads();
+    int before = incl - nz, total = 0;
+    for (int w = 0; w < CB_WARPS; w++) {
+      const int c = s_red[w];
+      if (w < warp)
+        before += c;
+      total += c;
+    }
+    if (tid == 0) {
+      st.n = total;
+      st.fnz = dict - total;
+    }
+    int rz = lo - before; // zero-count symbols before this thread's range
+    for (int i = lo; i < hi; i++) {
+      const uint32_t f = freq[i];
+      if (f) {
+        A.sortbuf[before++] = ((unsigned long long)f << 16) | (unsigned)i;
+      } else {
+        A.ssym[rz] = (uint16_t)i;
+        A.sfreq[rz] = 0;
+        ++rz;
+      }
+    }
+    __syncthreads();
+  }
+  {
+    const int n_ = st.n, fnz_ = st.fnz;
+    int P2 = 1;
+    while (P2 < n_)
+      P2 <<= 1;
+    for (int i = n_ + tid; i < P2; i += CB_THREADS)
+      A.sortbuf[i] = ~0ull;
+    __syncthreads();
+    for (int k = 2; k <= P2; k <<= 1)
+      for (int j = k >> 1; j > 0; j >>= 1) {
+        for (int i = tid; i < P2; i += CB_THREADS) {
+          int ixj = i ^ j;
+          if (ixj > i) {
+            unsigned long long a = A.sortbuf[i], b = A.sortbuf[ixj];
+            bool up = (i & k) == 0;
+            if ((a > b) == up) {
+              A.sortbuf[i] = b;
+              A.sortbuf[ixj] = a;
+            }
           }
         }
+        __syncthreads();
       }
-      __syncthreads();
-    }
-  {
-    // stage through registers: sfreq/ssym do not alias sortbuf, but keep the
-    // read and the write phases apart anyway
-    int cnt0 = 0;
-    for (int i = tid; i < dict; i += CB_THREADS) {
-      unsigned long long k = A.sortbuf[i];
-      A.ssym[i] = (uint16_t)(k & 0xffff);
-      uint32_t f = (uint32_t)(k >> 16);
-      A.sfreq[i] = f;
-      cnt0 += (f == 0);
-    }
     // GetFirstNonzeroIndex (GetCodebook.hpp:53-61) = number of zero counts
-    for (int off = 16; off > 0; off >>= 1)
-      cnt0 += __shfl_xor_sync(0xffffffffu, cnt0, off);
-    if (lane == 0)
-      s_red[warp] = cnt0;
-    __syncthreads();
-    if (tid == 0) {
-      int z = 0;
-      for (int w = 0; w < CB_WARPS; w++)
-        z += s_red[w];
-      st.fnz = z;
-      st.n = dict - z;
+    for (int i = tid; i < n_; i += CB_THREADS) {
+      const unsigned long long k = A.sortbuf[i];
+      A.ssym[fnz_ + i] = (uint16_t)(k & 0xffff);
+      A.sfreq[fnz_ + i] = (uint32_t)(k >> 16);
     }
     __syncthreads();
   }
