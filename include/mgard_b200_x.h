@@ -20,6 +20,16 @@
  *                                       (Metadata.cpp:29-41)
  *   mgx_x_release_cache                 release_cache (compress_x.hpp:166)
  *   mgx_x_pin_memory / _unpin / _check  pin_memory ... (compress_x.hpp:170-176)
+ *
+ * Threading: ONE call at a time per process.  mgx_x_compress / mgx_x_decompress /
+ * mgx_x_release_cache serialise on a process-wide mutex (they share the per-device
+ * context cache, like the reference's static Cache singletons,
+ * CompressionHighLevel.hpp:91-102): concurrent callers are safe but do not overlap.
+ * To drive several GPUs at once use one process per GPU (what bench.py and
+ * mgard_b200/sharding.py do) or the low-level mgx_ctx API, whose contexts are
+ * independent (one context = one device + one stream, one call at a time each).
+ * No exception crosses this boundary: C++ exceptions are caught and returned as
+ * MGX_FAILURE with the text in mgx_x_last_error().
  */
 #ifndef MGARD_B200_X_H
 #define MGARD_B200_X_H
@@ -65,7 +75,8 @@ typedef struct mgx_config {
   uint32_t reorder;              /* recorded in the header (0)                */
   int normalize_coordinates;     /* must be 1 (uniform unit cube)             */
   int auto_pin_host_buffers;     /* cudaHostRegister host buffers for the call */
-  int compress_with_dryrun;
+  int compress_with_dryrun;      /* must be 0: writing the reconstruction back into
+                                    the input (GPUPipelines.hpp:198) is rejected  */
   int auto_cache_release;
   int log_level;
   uint64_t max_larget_level;     /* UINT64_MAX = no limit                     */

@@ -787,6 +787,11 @@ int check_config(const mgx_config &cfg) {
     return fail(MGX_FAILURE, "domain decomposition not supported: MaxDim only");
   if (!cfg.normalize_coordinates)
     return fail(MGX_FAILURE, "normalize_coordinates = false is not supported");
+  // GPUPipelines.hpp:198-202, Compressor.hpp:239-242: the reference then also
+  // decompresses and writes the reconstruction over the caller's INPUT array
+  if (cfg.compress_with_dryrun)
+    return fail(MGX_FAILURE, "compress_with_dryrun (reconstruction written back into "
+                             "the input array) is not supported");
   if (cfg.huff_dict_size == 0 || cfg.huff_block_size == 0)
     return fail(MGX_FAILURE, "huff_dict_size / huff_block_size must be non-zero");
   return MGX_SUCCESS;
