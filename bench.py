@@ -70,6 +70,8 @@ def parse():
                     help="relative bound (default: 1e-3 cfg3, 1e-4 cfg5, 1e-3 cfg4)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-numa", action="store_true",
+                    help="N > 1: do not bind each rank to its GPU's NUMA node")
     ap.add_argument("--no-stream-check", action="store_true",
                     help="N > 1: skip gathering the ranks' records into one MGARD stream and "
                          "decoding it on rank 0")
@@ -698,8 +700,15 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device (there is no CPU fallback)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa = None
+    if world > 1 and not args.no_numa:
+        from mgard_b200.sharding import bind_to_gpu_numa
+        numa = bind_to_gpu_numa(local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        # rank 0's stdout carries ONE JSON line: keep NCCL's version banner off it
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
 
     def barrier():
@@ -868,6 +877,7 @@ def run_ours(args):
                "d2h_bytes_per_step": int(hbytes.item()),
                "h2d_GBs_per_gpu": my_bytes * K / (max(ems, ewall) * 1e-3) / 1e9,
                "decompress": job_bytes * K / (max(edms, edwall) * 1e-3) / 1e9,
+               "rank0_numa_binding": numa,
                "note": "pinned host buffers; wall clock (>= device time) over K calls of "
                        + ("mgx_x_compress / mgx_x_decompress (= mgard_x::compress / "
                           "decompress: MGARD header + records)" if single else

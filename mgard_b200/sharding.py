@@ -153,6 +153,43 @@ class ShardedCompressor:
         return frame(objs) if rank == dst else None
 
 
+def bind_to_gpu_numa(dev_id):
+    """Pin the calling process to the CPUs of the NUMA node the GPU hangs off, so that
+    the pinned host buffers it allocates next (first touch) and the threads that feed
+    the copies are local to the GPU's PCIe root: with 8 ranks per box the host-pointer
+    path is otherwise limited by cross-socket traffic, not by PCIe.  Returns
+    {"numa_node", "cpus"} or None when the topology is not exposed (then nothing is
+    changed)."""
+    import os
+    try:
+        import torch
+        bus = torch.cuda.get_device_properties(dev_id).pci_bus_id
+        dom = torch.cuda.get_device_properties(dev_id).pci_domain_id
+        devn = torch.cuda.get_device_properties(dev_id).pci_device_id
+        path = "/sys/bus/pci/devices/%04x:%02x:%02x.0/numa_node" % (dom, bus, devn)
+        with open(path) as f:
+            node = int(f.read().strip())
+        if node < 0:
+            return None
+        with open("/sys/devices/system/node/node%d/cpulist" % node) as f:
+            txt = f.read().strip()
+        cpus = set()
+        for part in txt.split(","):
+            if "-" in part:
+                a, b = part.split("-")
+                cpus.update(range(int(a), int(b) + 1))
+            elif part:
+                cpus.add(int(part))
+        allowed = os.sched_getaffinity(0)
+        use = cpus & allowed
+        if not use:
+            return None
+        os.sched_setaffinity(0, use)
+        return {"numa_node": node, "cpus": len(use)}
+    except Exception:
+        return None
+
+
 def serialize_header(shape, dtype_code, ebtype, tol, s, norm, dd_dim, dd_size,
                      decomposed=True, dict_size=8192, block_size=1024):
     """the "MGARD" header of a domain-decomposed stream (MetadataBase::Serialize,
