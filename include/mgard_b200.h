@@ -51,6 +51,19 @@ const char *mgx_version(void);
  * (UINT64_MAX = unlimited). */
 int mgx_plan(mgx_ctx *ctx, int D, const uint64_t *shape, int dtype,
              uint32_t dict_size, uint32_t chunk_size, uint64_t max_level);
+
+/* Hierarchy<D,T,Dev>(shape, coords, config) (Hierarchy/Hierarchy.hpp:840-857): a
+ * NON-UNIFORM Cartesian grid.  coords[d] -> shape[d] strictly increasing node
+ * coordinates of dimension d in HOST memory, in the data type T; per-level spacing
+ * follows coord_to_dist / reduce_dist for Cartesian_Grid_Non_Uniform
+ * (Hierarchy.hpp:22-61, 86-140: pairs of cells merged, last cell split in half when
+ * the node count is even).  coords == NULL: uniform grid on the unit cube
+ * (normalize_coordinates != 0, the default of mgx_plan) or with unit spacing
+ * (normalize_coordinates == 0: create_uniform_coords, Hierarchy.hpp:762-782; the L2
+ * norm is then sqrt(sum u^2) without the 1/N, NormCalculator.hpp:64). */
+int mgx_plan_grid(mgx_ctx *ctx, int D, const uint64_t *shape, int dtype,
+                  uint32_t dict_size, uint32_t chunk_size, uint64_t max_level,
+                  const void *const *coords, int normalize_coordinates);
 /* l_target and the (l_target+1) x D level shapes (Hierarchy.hpp:277-309). */
 int mgx_levels(const mgx_ctx *ctx, int *l_target, uint64_t *level_shapes);
 /* bytes a caller must provide to mgx_compress / mgx_huff_encode in the worst

@@ -9,7 +9,7 @@
 // Served: uniform Cartesian grids, D <= 5, float / double, REL / ABS,
 // L-inf / L2 / s-norm, Huffman lossless, MultiDim decomposition, MaxDim domain
 // decomposition, host or device buffers.  Anything else a Config can ask for
-// (non-uniform coords, Huffman_Zstd / LZ4, SingleDim / Hybrid, Block / Variable,
+// (Huffman_Zstd / LZ4, SingleDim / Hybrid, Block / Variable,
 // ZFP, CPU back ends) is answered with the reference's failure codes -- there
 // is no CPU fallback.
 #ifndef MGARD_B200_COMPRESS_X_HPP
@@ -146,17 +146,33 @@ compress(DIM D, data_type dtype, std::vector<SIZE> shape, double tol, double s,
                   compressed_size, Config(), output_pre_allocated);
 }
 
-// Non-uniform grids (coords overloads, compress_x.hpp:74-100) are row N2 of the
-// scope table: refused until they are built.
+// Non-uniform grids (coords overloads, compress_x.hpp:74-100): coords[d] points to
+// shape[d] node coordinates of the field's data type.
 inline compress_status_type
-compress(DIM, data_type, std::vector<SIZE>, double, double, error_bound_type,
-         const void *, void *&, size_t &, std::vector<const Byte *>, Config, bool) {
-  return compress_status_type::Failure;
+compress(DIM D, data_type dtype, std::vector<SIZE> shape, double tol, double s,
+         error_bound_type mode, const void *original_data, void *&compressed_data,
+         size_t &compressed_size, std::vector<const Byte *> coords, Config config,
+         bool output_pre_allocated) {
+  if (config.compressor != compressor_type::MGARD)
+    return compress_status_type::Failure;
+  if (shape.size() != D || coords.size() != D)
+    return compress_status_type::Failure;
+  const mgx_config c = detail::to_c(config);
+  const void *cp[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  for (DIM d = 0; d < D && d < 5; d++)
+    cp[d] = coords[d];
+  return detail::status(mgx_x_compress_coords(
+      D, dtype == data_type::Double ? MGX_F64 : dtype == data_type::Float ? MGX_F32 : -1,
+      shape.data(), tol, s, (int)mode, original_data, &compressed_data,
+      &compressed_size, cp, &c, output_pre_allocated));
 }
 inline compress_status_type
-compress(DIM, data_type, std::vector<SIZE>, double, double, error_bound_type,
-         const void *, void *&, size_t &, std::vector<const Byte *>, bool) {
-  return compress_status_type::Failure;
+compress(DIM D, data_type dtype, std::vector<SIZE> shape, double tol, double s,
+         error_bound_type mode, const void *original_data, void *&compressed_data,
+         size_t &compressed_size, std::vector<const Byte *> coords,
+         bool output_pre_allocated) {
+  return compress(D, dtype, shape, tol, s, mode, original_data, compressed_data,
+                  compressed_size, coords, Config(), output_pre_allocated);
 }
 
 // ---- decompress (compress_x.hpp:108-160) -----------------------------------------

@@ -73,7 +73,7 @@ typedef struct mgx_config {
   uint32_t huff_dict_size;       /* 8192                                      */
   uint32_t huff_block_size;      /* 1024                                      */
   uint32_t reorder;              /* recorded in the header (0)                */
-  int normalize_coordinates;     /* must be 1 (uniform unit cube)             */
+  int normalize_coordinates;     /* uniform grids: unit cube (1) or unit spacing (0) */
   int auto_pin_host_buffers;     /* cudaHostRegister host buffers for the call */
   int compress_with_dryrun;      /* must be 0: writing the reconstruction back into
                                     the input (GPUPipelines.hpp:198) is rejected  */
@@ -95,6 +95,18 @@ void mgx_config_default(mgx_config *cfg); /* Config::Config(), Config.cpp:31-66 
 int mgx_x_compress(int D, int dtype, const uint64_t *shape, double tol, double s,
                    int mode, const void *in, void **out, size_t *out_size,
                    const mgx_config *cfg, int output_pre_allocated);
+
+/* compress(..., coords, config, output_pre_allocated) -- the NON-UNIFORM overloads,
+ * compress_x.hpp:74-100: coords[d] -> shape[d] strictly increasing node coordinates
+ * of dimension d in HOST memory, in the data type of the field
+ * (CompressionHighLevel.hpp:687-740 reinterprets the byte pointers as float* /
+ * double*).  The coordinates are written into the header as doubles
+ * (Metadata.hpp:138-153); mgx_x_decompress rebuilds the hierarchy from them, narrowed
+ * to float as the reference does (CompressionHighLevel.hpp:443-450). */
+int mgx_x_compress_coords(int D, int dtype, const uint64_t *shape, double tol, double s,
+                          int mode, const void *in, void **out, size_t *out_size,
+                          const void *const *coords, const mgx_config *cfg,
+                          int output_pre_allocated);
 
 /* decompress(in, in_size, out, shape, dtype, config, output_pre_allocated)
  * -- compress_x.hpp:137-141.  shape_out (5 entries), D_out, dtype_out may be
@@ -143,6 +155,16 @@ int mgx_metadata_serialize(const mgx_metadata *m, uint8_t *out, uint64_t cap,
 int mgx_metadata_parse(const uint8_t *in, uint64_t bytes, mgx_metadata *m,
                        uint64_t *header_bytes);
 /* bytes of the whole header given its first 13 bytes (DeserializeSize) */
+/* Non-uniform grids (Metadata.hpp:130-154, Metadata.cpp:303-321, 557-580): the
+ * header of a stream compressed with node coordinates carries them as doubles
+ * (Domain.geometry = EXPLICIT_CUBE), all dimensions back to back.
+ * mgx_metadata_serialize_coords: as mgx_metadata_serialize, with m->nonuniform != 0
+ * and coords -> sum(shape) doubles.  mgx_metadata_coords: copies them out of a
+ * stream's header (*count = 0 for a uniform grid). */
+int mgx_metadata_serialize_coords(const mgx_metadata *m, const double *coords,
+                                  uint8_t *out, uint64_t cap, uint64_t *bytes);
+int mgx_metadata_coords(const uint8_t *in, uint64_t bytes, double *coords,
+                        uint64_t cap, uint64_t *count);
 int mgx_metadata_size(const uint8_t *in, uint64_t bytes, uint64_t *header_bytes);
 uint32_t mgx_crc32(const void *data, uint64_t bytes);
 

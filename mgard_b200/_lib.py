@@ -54,6 +54,12 @@ SIGNATURES = {
     "mgx_x_compress": (c_int, [c_int, c_int, ctypes.POINTER(c_u64), c_dbl, c_dbl,
                                c_int, c_vp, ctypes.POINTER(c_vp), _szp, _cfgp,
                                c_int]),
+    "mgx_x_compress_coords": (c_int, [c_int, c_int, ctypes.POINTER(c_u64), c_dbl, c_dbl,
+                                      c_int, c_vp, ctypes.POINTER(c_vp), _szp,
+                                      ctypes.POINTER(c_vp), _cfgp, c_int]),
+    "mgx_metadata_serialize_coords": (c_int, [ctypes.POINTER(MgxMetadata), c_vp, c_vp,
+                                              c_u64, ctypes.POINTER(c_u64)]),
+    "mgx_metadata_coords": (c_int, [c_vp, c_u64, c_vp, c_u64, ctypes.POINTER(c_u64)]),
     "mgx_x_decompress": (c_int, [c_vp, ctypes.c_size_t, ctypes.POINTER(c_vp),
                                  ctypes.POINTER(c_u64), ctypes.POINTER(c_int),
                                  ctypes.POINTER(c_int), _cfgp, c_int]),
@@ -82,6 +88,8 @@ SIGNATURES = {
     "mgx_version": (ctypes.c_char_p, []),
     "mgx_plan": (c_int, [c_vp, c_int, ctypes.POINTER(c_u64), c_int, c_u32,
                          c_u32, c_u64]),
+    "mgx_plan_grid": (c_int, [c_vp, c_int, ctypes.POINTER(c_u64), c_int, c_u32,
+                              c_u32, c_u64, ctypes.POINTER(c_vp), c_int]),
     "mgx_levels": (c_int, [c_vp, ctypes.POINTER(c_int), ctypes.POINTER(c_u64)]),
     "mgx_max_compressed_bytes": (c_u64, [c_vp]),
     "mgx_norm_partial": (c_int, [c_vp, c_vp, c_int, ctypes.POINTER(c_dbl)]),

@@ -60,15 +60,27 @@ def infer_orthogonal_projection(D, s):
 
 
 class Hierarchy:
-    """Level structure of a uniform Cartesian grid (shape slowest->fastest)."""
+    """Level structure of a Cartesian grid (shape slowest->fastest): uniform
+    (Hierarchy(shape, config), Hierarchy.hpp:814-837), or NON-UNIFORM when ``coords``
+    gives one strictly increasing array of node coordinates per dimension
+    (Hierarchy(shape, coords, config), Hierarchy.hpp:840-857)."""
 
-    def __init__(self, shape, dtype=torch.float32, config=None):
+    def __init__(self, shape, dtype=torch.float32, config=None, coords=None):
         self.shape = tuple(int(s) for s in shape)
         self.dtype = dtype
         self.config = config or Config()
         if len(self.shape) > 5:
             raise MgardError(3)
         self.dtype_code = _dtype_code(dtype)
+        self.coords = None
+        if coords is not None:
+            npdt = np.float32 if self.dtype_code == 0 else np.float64
+            if len(coords) != len(self.shape):
+                raise MgardError(1, "one coordinate array per dimension")
+            self.coords = [np.ascontiguousarray(c, npdt) for c in coords]
+            for c, n in zip(self.coords, self.shape):
+                if c.shape != (n,):
+                    raise MgardError(1, "coordinate array length != dimension")
 
     def total_num_elems(self):
         return int(np.prod(self.shape))
@@ -115,10 +127,13 @@ class Compressor:
         self.config = config or self.config
         D = len(hierarchy.shape)
         shp = (ctypes.c_uint64 * D)(*hierarchy.shape)
-        self._check(self.lib.mgx_plan(self._ctx, D, shp, hierarchy.dtype_code,
-                                      self.config.huff_dict_size,
-                                      self.config.huff_block_size,
-                                      self.config.max_larget_level))
+        cptr = None
+        if hierarchy.coords is not None:
+            cptr = (ctypes.c_void_p * D)(*[c.ctypes.data for c in hierarchy.coords])
+        self._check(self.lib.mgx_plan_grid(
+            self._ctx, D, shp, hierarchy.dtype_code, self.config.huff_dict_size,
+            self.config.huff_block_size, self.config.max_larget_level, cptr,
+            1 if self.config.normalize_coordinates else 0))
         self.D = D
         self.N = hierarchy.total_num_elems()
         self.tdtype = (torch.float32 if hierarchy.dtype_code == 0

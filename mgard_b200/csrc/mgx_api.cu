@@ -226,6 +226,13 @@ int mgx_elapsed_ms(mgx_ctx *ctx, int from_tick, int to_tick, float *ms) {
 
 int mgx_plan(mgx_ctx *ctx, int D, const uint64_t *shape, int dtype,
              uint32_t dict_size, uint32_t chunk_size, uint64_t max_level) {
+  return mgx_plan_grid(ctx, D, shape, dtype, dict_size, chunk_size, max_level, nullptr,
+                       1);
+}
+
+int mgx_plan_grid(mgx_ctx *ctx, int D, const uint64_t *shape, int dtype,
+                  uint32_t dict_size, uint32_t chunk_size, uint64_t max_level,
+                  const void *const *coords, int normalize_coordinates) {
   if (!ctx)
     return MGX_FAILURE;
   if (dtype != MGX_F32 && dtype != MGX_F64)
@@ -249,12 +256,33 @@ int mgx_plan(mgx_ctx *ctx, int D, const uint64_t *shape, int dtype,
   ctx->chunk = chunk_size;
   const void *src;
   size_t bytes;
+  if (coords) {
+    // node coordinates must increase strictly (Hierarchy(shape, coords, config))
+    for (int d = 0; d < D; d++) {
+      if (!coords[d]) {
+        ctx->err = "coordinate array missing";
+        return MGX_FAILURE;
+      }
+      for (uint64_t i = 0; i + 1 < shape[d]; i++) {
+        const double a = dtype == MGX_F32 ? (double)((const float *)coords[d])[i]
+                                          : ((const double *)coords[d])[i];
+        const double b = dtype == MGX_F32 ? (double)((const float *)coords[d])[i + 1]
+                                          : ((const double *)coords[d])[i + 1];
+        if (!(b > a)) {
+          ctx->err = "node coordinates must be strictly increasing";
+          return MGX_FAILURE;
+        }
+      }
+    }
+  }
+  ctx->nonuniform = coords != nullptr;
+  ctx->normalize = normalize_coordinates != 0;
   if (dtype == MGX_F32) {
-    mgx_build_tables<float>(ctx->lv, &ctx->tbf);
+    mgx_build_tables<float>(ctx->lv, &ctx->tbf, coords, ctx->normalize);
     src = ctx->tbf.buf.data();
     bytes = ctx->tbf.buf.size() * 4;
   } else {
-    mgx_build_tables<double>(ctx->lv, &ctx->tbd);
+    mgx_build_tables<double>(ctx->lv, &ctx->tbd, coords, ctx->normalize);
     src = ctx->tbd.buf.data();
     bytes = ctx->tbd.buf.size() * 8;
   }
@@ -541,7 +569,7 @@ int mgx_compress(mgx_ctx *ctx, const void *d_in, int rel, double tol, double s,
     int rc = mgx_norm_partial(ctx, d_in, linf, &partial);
     if (rc)
       return rc;
-    norm = mgx_finish_norm(ctx->dtype, linf, partial, N, 1);
+    norm = mgx_finish_norm(ctx->dtype, linf, partial, N, ctx->normalize ? 1 : 0);
     if (norm_inout)
       *norm_inout = norm;
   }

@@ -54,9 +54,11 @@ int mgx_build_levels(int D, const uint64_t *shape, uint64_t max_level,
 }
 
 template <typename T>
-void mgx_build_tables(const MgxLevels &lv, MgxHostTables<T> *tb) {
+void mgx_build_tables(const MgxLevels &lv, MgxHostTables<T> *tb,
+                      const void *const *coords, bool normalize) {
   const int L = lv.L;
   const int pad = MGX_MAX_D - lv.D;
+  const bool nonuniform = coords != nullptr;
   tb->buf.clear();
   tb->ratios_half = true;
   std::memset(&tb->off, 0, sizeof(tb->off));
@@ -66,24 +68,49 @@ void mgx_build_tables(const MgxLevels &lv, MgxHostTables<T> *tb) {
   };
   T vol[MGX_MAX_L][MGX_MAX_D], volr[MGX_MAX_L][MGX_MAX_D];
   for (int d = pad; d < MGX_MAX_D; d++) {
-    // create_uniform_coords (normalize_coordinates) + coord_to_dist,
-    // Hierarchy.hpp:762-782, 22-61
+    // create_uniform_coords (0..1 with normalize_coordinates, else 0..n-1) or the
+    // caller's node coordinates, then coord_to_dist; Hierarchy.hpp:762-782, 22-61
     uint64_t n = lv.shape[d];
     std::vector<T> coord(n);
-    for (uint64_t i = 0; i < n; i++)
-      coord[i] = (T)i / (n - 1);
+    if (nonuniform) {
+      const T *c = (const T *)coords[d - pad];
+      for (uint64_t i = 0; i < n; i++)
+        coord[i] = c[i];
+    } else {
+      for (uint64_t i = 0; i < n; i++)
+        coord[i] = normalize ? (T)i / (n - 1) : (T)i;
+    }
     D_(L, d).assign(n, (T)0);
     for (uint64_t i = 0; i + 1 < n; i++)
       D_(L, d)[i] = coord[i + 1] - coord[i];
-    // reduce_dist, uniform branch, Hierarchy.hpp:115-126
+    // non-uniform grids split the last cell in half when the node count is even
+    // (Hierarchy.hpp:42-48); uniform grids keep every level's spacing uniform
+    auto split_last = [](std::vector<T> &h) {
+      const uint64_t dof = h.size();
+      if (dof != 2 && dof % 2 == 0) {
+        const T last = h[dof - 2];
+        h[dof - 2] = last / (T)2.0;
+        h[dof - 1] = last / (T)2.0;
+      }
+    };
+    if (nonuniform)
+      split_last(D_(L, d));
+    // reduce_dist, Hierarchy.hpp:86-140
     for (int l = L - 1; l >= 0; l--) {
       uint64_t dof = lv.n[l + 1][d], dof2 = lv.n[l][d];
-      T total = 0;
-      for (uint64_t i = 0; i + 1 < dof; i++)
-        total += D_(l + 1, d)[i];
       D_(l, d).assign(dof2, (T)0);
-      for (uint64_t i = 0; i + 1 < dof2; i++)
-        D_(l, d)[i] = total / (dof2 - 1);
+      if (nonuniform) {
+        // merge each pair of fine cells, then split the last cell again
+        for (uint64_t i = 0; i + 1 < dof2; i++)
+          D_(l, d)[i] = D_(l + 1, d)[2 * i] + D_(l + 1, d)[2 * i + 1];
+        split_last(D_(l, d));
+      } else {
+        T total = 0;
+        for (uint64_t i = 0; i + 1 < dof; i++)
+          total += D_(l + 1, d)[i];
+        for (uint64_t i = 0; i + 1 < dof2; i++)
+          D_(l, d)[i] = total / (dof2 - 1);
+      }
     }
   }
   for (int l = 0; l <= L; l++)
@@ -151,9 +178,10 @@ void mgx_build_tables(const MgxLevels &lv, MgxHostTables<T> *tb) {
   }
 }
 
-template void mgx_build_tables<float>(const MgxLevels &, MgxHostTables<float> *);
-template void mgx_build_tables<double>(const MgxLevels &,
-                                       MgxHostTables<double> *);
+template void mgx_build_tables<float>(const MgxLevels &, MgxHostTables<float> *,
+                                      const void *const *, bool);
+template void mgx_build_tables<double>(const MgxLevels &, MgxHostTables<double> *,
+                                       const void *const *, bool);
 
 // ---- host-only entry points of the C ABI ---------------------------------------
 #include <cmath>

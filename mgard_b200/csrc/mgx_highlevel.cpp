@@ -85,6 +85,18 @@ struct PbWriter {
     varint(m.b.size());
     b.insert(b.end(), m.b.begin(), m.b.end());
   }
+  void put_packed_double(uint32_t field, const double *v, size_t n) {
+    if (!n)
+      return;
+    key(field, 2);
+    varint(n * 8);
+    for (size_t i = 0; i < n; i++) {
+      uint64_t bits;
+      memcpy(&bits, &v[i], 8);
+      for (int k = 0; k < 8; k++)
+        b.push_back((uint8_t)(bits >> (8 * k)));
+    }
+  }
   void put_packed_uint(uint32_t field, const uint64_t *v, size_t n) {
     if (!n)
       return;
@@ -176,7 +188,9 @@ void put_version(PbWriter &h, uint32_t field, const uint32_t v[3]) {
   h.put_message(field, m);
 }
 
-std::vector<uint8_t> header_bytes(const mgx_metadata &md) {
+// coords: node coordinates of all dimensions back to back (sum of shape doubles) for
+// a non-uniform grid (Domain.geometry = EXPLICIT_CUBE, Metadata.cpp:303-321), else null
+std::vector<uint8_t> header_bytes(const mgx_metadata &md, const double *coords = nullptr) {
   PbWriter h;
   put_version(h, 2, md.version);
   put_version(h, 3, md.file_version);
@@ -185,6 +199,15 @@ std::vector<uint8_t> header_bytes(const mgx_metadata &md) {
     grid.put_uint(1, md.D);
     grid.put_packed_uint(2, md.shape, md.D);
     dom.put_message(2, grid); // topology CARTESIAN_GRID = 0, geometry UNIT_CUBE = 0
+    if (md.nonuniform && coords) {
+      uint64_t total = 0;
+      for (uint32_t d = 0; d < md.D; d++)
+        total += md.shape[d];
+      PbWriter cube;
+      cube.put_packed_double(2, coords, total);
+      dom.put_uint(3, 1); // EXPLICIT_CUBE
+      dom.put_message(4, cube);
+    }
     h.put_message(4, dom);
   }
   { // Dataset
@@ -329,7 +352,8 @@ bool parse_scalars(PbReader r, uint64_t *u, double *d, uint32_t nf) {
   return true;
 }
 
-int parse_header(const uint8_t *p, uint64_t n, mgx_metadata &md) {
+int parse_header(const uint8_t *p, uint64_t n, mgx_metadata &md,
+                 std::vector<double> *coords = nullptr) {
   memset(&md, 0, sizeof(md));
   md.linf = 1; // proto3 default ErrorControl.norm == L_INFINITY
   md.mode = MGX_EB_ABS;
@@ -374,6 +398,34 @@ int parse_header(const uint8_t *p, uint64_t n, mgx_metadata &md) {
           uint64_t x;
           ok = m.varint(x);
           md.nonuniform = x == 1;
+        } else if (f2 == 4 && w2 == 2) { // ExplicitCubeGeometry
+          PbReader cube;
+          ok = m.sub(cube);
+          uint32_t f3, w3;
+          while (ok && !cube.done()) {
+            if (!cube.next(f3, w3)) {
+              ok = false;
+              break;
+            }
+            uint64_t bits;
+            double v;
+            if (f3 == 2 && w3 == 2) { // packed doubles
+              PbReader pk;
+              ok = cube.sub(pk);
+              while (ok && !pk.done()) {
+                ok = pk.fixed64(bits);
+                memcpy(&v, &bits, 8);
+                if (ok && coords)
+                  coords->push_back(v);
+              }
+            } else if (f3 == 2 && w3 == 1) {
+              ok = cube.fixed64(bits);
+              memcpy(&v, &bits, 8);
+              if (ok && coords)
+                coords->push_back(v);
+            } else
+              ok = cube.skip(w3);
+          }
         } else
           ok = m.skip(w2);
       }
@@ -439,6 +491,14 @@ int parse_header(const uint8_t *p, uint64_t n, mgx_metadata &md) {
     return fail(MGX_FAILURE, "MGARD file format version mismatch.");
   if (md.D != shape_count)
     return fail(MGX_FAILURE, "grid shape does not match given dimension.");
+  if (md.nonuniform && coords) {
+    uint64_t total = 0;
+    for (uint32_t d = 0; d < md.D && d < 5; d++)
+      total += md.shape[d];
+    if (coords->size() != total)
+      return fail(MGX_FAILURE,
+                  "mismatch between number of node coordinates and grid shape.");
+  }
   if (norm_kind == PB_L_INFINITY) {
     md.linf = 1;
     md.s = std::numeric_limits<double>::infinity();
@@ -525,6 +585,8 @@ struct PlanEntry {
   uint64_t max_level;
   mgx_ctx *ctx;
   uint64_t stamp;
+  bool normalize = true;
+  bool nonuniform = false; // never reused (Hierarchy::can_reuse, Hierarchy.hpp:797-807)
 };
 
 struct DeviceCache {
@@ -605,16 +667,21 @@ void cache_release(DeviceCache &c) {
   c.ready = false;
 }
 
+// coords: node coordinates of THIS (sub)domain per dimension (host, type T), or null
 int cache_ctx(DeviceCache &c, int D, const uint64_t *shape, int dtype,
-              const mgx_config &cfg, mgx_ctx **out) {
-  for (auto &p : c.plans)
-    if (p.dtype == dtype && p.dict == cfg.huff_dict_size &&
-        p.chunk == cfg.huff_block_size && p.max_level == cfg.max_larget_level &&
-        p.shape.size() == (size_t)D && std::equal(p.shape.begin(), p.shape.end(), shape)) {
-      p.stamp = ++c.stamp;
-      *out = p.ctx;
-      return MGX_SUCCESS;
-    }
+              const mgx_config &cfg, mgx_ctx **out,
+              const void *const *coords = nullptr) {
+  const bool normalize = cfg.normalize_coordinates != 0;
+  if (!coords)
+    for (auto &p : c.plans)
+      if (!p.nonuniform && p.normalize == normalize && p.dtype == dtype &&
+          p.dict == cfg.huff_dict_size && p.chunk == cfg.huff_block_size &&
+          p.max_level == cfg.max_larget_level && p.shape.size() == (size_t)D &&
+          std::equal(p.shape.begin(), p.shape.end(), shape)) {
+        p.stamp = ++c.stamp;
+        *out = p.ctx;
+        return MGX_SUCCESS;
+      }
   if (c.plans.size() >= 2) { // evict the least recently used plan
     size_t victim = c.plans[0].stamp < c.plans[1].stamp ? 0 : 1;
     c.retired_launches += mgx_launch_count(c.plans[victim].ctx);
@@ -625,19 +692,35 @@ int cache_ctx(DeviceCache &c, int D, const uint64_t *shape, int dtype,
   int rc = mgx_create(&ctx, c.dev, c.compute);
   if (rc)
     return fail(rc, "mgx_create failed");
-  rc = mgx_plan(ctx, D, shape, dtype, cfg.huff_dict_size, cfg.huff_block_size,
-                cfg.max_larget_level);
+  rc = mgx_plan_grid(ctx, D, shape, dtype, cfg.huff_dict_size, cfg.huff_block_size,
+                     cfg.max_larget_level, coords, normalize ? 1 : 0);
   if (rc) {
     std::string msg = mgx_last_error(ctx);
     mgx_destroy(ctx);
     return fail(rc, "mgx_plan: " + msg);
   }
-  c.plans.push_back({std::vector<uint64_t>(shape, shape + D), dtype,
-                     cfg.huff_dict_size, cfg.huff_block_size, cfg.max_larget_level,
-                     ctx, ++c.stamp});
+  PlanEntry e{std::vector<uint64_t>(shape, shape + D), dtype, cfg.huff_dict_size,
+              cfg.huff_block_size, cfg.max_larget_level, ctx, ++c.stamp};
+  e.normalize = normalize;
+  e.nonuniform = coords != nullptr;
+  c.plans.push_back(e);
   *out = ctx;
   return MGX_SUCCESS;
 }
+
+// coordinates of subdomain i: the decomposed dimension's array starts at the slab's
+// first row (DomainDecomposer.hpp:259-289)
+struct SubCoords {
+  const void *p[5];
+  const void *const *get(const void *const *coords, int D, int dim, uint64_t off,
+                         size_t es) {
+    if (!coords)
+      return nullptr;
+    for (int d = 0; d < D; d++)
+      p[d] = d == dim ? (const void *)((const char *)coords[d] + off * es) : coords[d];
+    return p;
+  }
+};
 
 int ensure_buffer(void *&p, size_t &have, size_t want) {
   if (have >= want)
@@ -785,8 +868,6 @@ int check_config(const mgx_config &cfg) {
     return fail(MGX_FAILURE, "decomposition type not supported: MultiDim only");
   if (cfg.domain_decomposition != MGX_DD_MAXDIM)
     return fail(MGX_FAILURE, "domain decomposition not supported: MaxDim only");
-  if (!cfg.normalize_coordinates)
-    return fail(MGX_FAILURE, "normalize_coordinates = false is not supported");
   // GPUPipelines.hpp:198-202, Compressor.hpp:239-242: the reference then also
   // decompresses and writes the reconstruction over the caller's INPUT array
   if (cfg.compress_with_dryrun)
@@ -815,7 +896,8 @@ void put_u64_le(uint8_t *p, uint64_t v) {
 // ---- compress ------------------------------------------------------------------
 int x_compress(int D, int dtype, const uint64_t *shape, double tol, double s,
                int mode, const void *in, void **out, size_t *out_size,
-               const mgx_config &cfg, int prealloc) {
+               const mgx_config &cfg, int prealloc,
+               const void *const *coords = nullptr) {
   if (D > 5)
     return fail(MGX_TOO_MANY_DIMENSIONS, "more than 5 dimensions");
   if (dtype != MGX_F32 && dtype != MGX_F64)
@@ -913,7 +995,20 @@ int x_compress(int D, int dtype, const uint64_t *shape, double tol, double s,
   md.huff_block_size = cfg.huff_block_size;
   md.reorder = cfg.reorder;
   md.backend = 3; // X_CUDA
-  std::vector<uint8_t> head = header_bytes(md);
+  // non-uniform grid: the node coordinates travel in the header as doubles
+  // (Metadata.hpp:138-153)
+  std::vector<double> hcoords;
+  if (coords) {
+    md.nonuniform = 1;
+    for (int d = 0; d < D; d++) {
+      if (!coords[d])
+        return fail(MGX_FAILURE, "coordinate array missing");
+      for (uint64_t i = 0; i < shape[d]; i++)
+        hcoords.push_back(dtype == MGX_F32 ? (double)((const float *)coords[d])[i]
+                                           : ((const double *)coords[d])[i]);
+    }
+  }
+  std::vector<uint8_t> head = header_bytes(md, coords ? hcoords.data() : nullptr);
   const uint64_t M = PREAMBLE + head.size();
   if (cap < M)
     return fail(MGX_OUTPUT_TOO_LARGE, "output buffer smaller than the header");
@@ -970,7 +1065,9 @@ int x_compress(int D, int dtype, const uint64_t *shape, double tol, double s,
         uint64_t sh[5], off;
         sl.sub_shape(i, sh, &off);
         mgx_ctx *ctx;
-        if ((rc = cache_ctx(c, D, sh, dtype, cfg, &ctx)))
+        SubCoords sc;
+        if ((rc = cache_ctx(c, D, sh, dtype, cfg, &ctx,
+                            sc.get(coords, D, sl.decomposed ? sl.dim : -1, off, es))))
           return rc;
         if (!in_place)
           X_CUDA(cudaStreamWaitEvent(c.compute, c.ev_in[b], 0));
@@ -981,7 +1078,7 @@ int x_compress(int D, int dtype, const uint64_t *shape, double tol, double s,
         X_CUDA(cudaEventRecord(c.ev_free[b], c.compute));
         acc = linf ? std::max(acc, part) : acc + part;
       }
-      norm = mgx_finish_norm(dtype, linf, acc, N, 1);
+      norm = mgx_finish_norm(dtype, linf, acc, N, cfg.normalize_coordinates ? 1 : 0);
     }
     local_tol = mgx_local_abs_tol(dtype, rel, norm, tolT, sT, sl.num);
     local_rel = 0; // ABS inside every subdomain (:126-129)
@@ -1000,7 +1097,9 @@ int x_compress(int D, int dtype, const uint64_t *shape, double tol, double s,
     sl.sub_shape(i, sh, &off);
     const uint64_t n_sub = sl.elems(i);
     mgx_ctx *ctx;
-    if ((rc = cache_ctx(c, D, sh, dtype, cfg, &ctx)))
+    SubCoords sc;
+    if ((rc = cache_ctx(c, D, sh, dtype, cfg, &ctx,
+                        sc.get(coords, D, sl.decomposed ? sl.dim : -1, off, es))))
       return rc;
     if (!in_place)
       X_CUDA(cudaStreamWaitEvent(c.compute, c.ev_in[b], 0));
@@ -1045,7 +1144,7 @@ int x_compress(int D, int dtype, const uint64_t *shape, double tol, double s,
 
   // header with the final norm (:230-262)
   md.norm = dtype == MGX_F32 ? (double)(float)norm : norm;
-  head = header_bytes(md);
+  head = header_bytes(md, coords ? hcoords.data() : nullptr);
   std::vector<uint8_t> pre(PREAMBLE + head.size());
   memcpy(pre.data(), SIGNATURE, 5);
   put_u64_le(pre.data() + 5, head.size());
@@ -1116,8 +1215,41 @@ int x_decompress(const void *in, size_t in_size, void **out, uint64_t *shape_out
     return fail(MGX_TOO_MANY_DIMENSIONS, "more than 5 dimensions");
   if (md.D < 1)
     return fail(MGX_FAILURE, "header without a shape");
-  if (md.nonuniform)
-    return fail(MGX_FAILURE, "non-uniform grids are not supported");
+  // non-uniform grid: node coordinates from the header.  The reference narrows them
+  // to float whatever the data type ("coords[d][i] = (float)m.coords[d][i]",
+  // CompressionHighLevel.hpp:443-450); reproduced so that both decoders rebuild the
+  // same hierarchy from the same stream.
+  std::vector<std::vector<unsigned char>> tcoords;
+  const void *cptr[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  if (md.nonuniform) {
+    std::vector<double> hc;
+    mgx_metadata md2;
+    rc = parse_header(hb.data() + PREAMBLE, M - PREAMBLE, md2, &hc);
+    if (rc)
+      return rc;
+    uint64_t total = 0;
+    for (uint32_t d = 0; d < md.D; d++)
+      total += md.shape[d];
+    if (hc.size() != total)
+      return fail(MGX_FAILURE,
+                  "mismatch between number of node coordinates and grid shape.");
+    tcoords.resize(md.D);
+    uint64_t at = 0;
+    for (uint32_t d = 0; d < md.D; d++) {
+      const uint64_t n = md.shape[d];
+      tcoords[d].resize(n * (md.dtype == MGX_F64 ? 8 : 4));
+      for (uint64_t i = 0; i < n; i++) {
+        const float f = (float)hc[at + i];
+        if (md.dtype == MGX_F64)
+          ((double *)tcoords[d].data())[i] = (double)f;
+        else
+          ((float *)tcoords[d].data())[i] = f;
+      }
+      at += n;
+      cptr[d] = tcoords[d].data();
+    }
+  }
+  const void *const *coords = md.nonuniform ? cptr : nullptr;
   // MetadataBase::InitializeConfig (Metadata.cpp:129-149)
   mgx_config cfg = cfg_in;
   cfg.domain_decomposition = md.dd_type;
@@ -1279,7 +1411,9 @@ int x_decompress(const void *in, size_t in_size, void **out, uint64_t *shape_out
     const double CR = (double)n_sub * es / (double)rec_bytes[i];
     if (CR > 1.0) {
       mgx_ctx *ctx;
-      if ((rc = cache_ctx(c, D, sh, dtype, cfg, &ctx)))
+      SubCoords sc;
+      if ((rc = cache_ctx(c, D, sh, dtype, cfg, &ctx,
+                          sc.get(coords, D, sl.decomposed ? sl.dim : -1, off, es))))
         return rc;
       rc = mgx_decompress(ctx, (const uint8_t *)c.cbuf[b], rec_bytes[i], local_rel,
                           local_tol, sT, normT, d_out);
@@ -1357,9 +1491,39 @@ uint32_t mgx_crc32(const void *data, uint64_t bytes) {
 
 int mgx_metadata_serialize(const mgx_metadata *m, uint8_t *out, uint64_t cap,
                            uint64_t *bytes) {
+  return mgx_metadata_serialize_coords(m, nullptr, out, cap, bytes);
+}
+
+int mgx_metadata_coords(const uint8_t *in, uint64_t bytes, double *coords, uint64_t cap,
+                        uint64_t *count) {
+  if (!count)
+    return MGX_FAILURE;
+  uint64_t total = 0;
+  int rc = mgx_metadata_size(in, bytes, &total);
+  if (rc)
+    return rc;
+  if (bytes < total)
+    return fail(MGX_FAILURE, "stream shorter than its header");
+  mgx_metadata md;
+  std::vector<double> c;
+  rc = parse_header(in + PREAMBLE, total - PREAMBLE, md, &c);
+  if (rc)
+    return rc;
+  *count = md.nonuniform ? c.size() : 0;
+  if (*count && (!coords || cap < *count))
+    return MGX_OUTPUT_TOO_LARGE;
+  if (*count)
+    memcpy(coords, c.data(), c.size() * 8);
+  return MGX_SUCCESS;
+}
+
+int mgx_metadata_serialize_coords(const mgx_metadata *m, const double *coords,
+                                  uint8_t *out, uint64_t cap, uint64_t *bytes) {
   if (!m || !bytes || m->D < 1 || m->D > 5)
     return MGX_FAILURE;
-  std::vector<uint8_t> head = header_bytes(*m);
+  if (m->nonuniform && !coords)
+    return fail(MGX_FAILURE, "a non-uniform grid needs its node coordinates");
+  std::vector<uint8_t> head = header_bytes(*m, coords);
   *bytes = PREAMBLE + head.size();
   if (!out || cap < *bytes)
     return MGX_OUTPUT_TOO_LARGE;
@@ -1472,6 +1636,30 @@ int mgx_x_compress(int D, int dtype, const uint64_t *shape, double tol, double s
     return x_compress(D, dtype, shape, tol, s, mode, in, out, out_size, c,
                       output_pre_allocated);
   } catch (const std::exception &e) { // no exception crosses the C ABI
+    return fail(MGX_FAILURE, std::string("compress: ") + e.what());
+  } catch (...) {
+    return fail(MGX_FAILURE, "compress: unknown exception");
+  }
+}
+
+int mgx_x_compress_coords(int D, int dtype, const uint64_t *shape, double tol, double s,
+                          int mode, const void *in, void **out, size_t *out_size,
+                          const void *const *coords, const mgx_config *cfg,
+                          int output_pre_allocated) {
+  std::lock_guard<std::mutex> lock(g_mu);
+  mgx_config c;
+  if (cfg)
+    c = *cfg;
+  else
+    mgx_config_default(&c);
+  g_err.clear();
+  if (!coords)
+    return fail(MGX_FAILURE, "coords missing");
+  DeviceRestore restore;
+  try {
+    return x_compress(D, dtype, shape, tol, s, mode, in, out, out_size, c,
+                      output_pre_allocated, coords);
+  } catch (const std::exception &e) {
     return fail(MGX_FAILURE, std::string("compress: ") + e.what());
   } catch (...) {
     return fail(MGX_FAILURE, "compress: unknown exception");

@@ -41,7 +41,8 @@ template <typename T> struct MgxHostTables {
 int mgx_build_levels(int D, const uint64_t *shape, uint64_t max_level,
                      MgxLevels *lv);
 template <typename T>
-void mgx_build_tables(const MgxLevels &lv, MgxHostTables<T> *tb);
+void mgx_build_tables(const MgxLevels &lv, MgxHostTables<T> *tb,
+                      const void *const *coords = nullptr, bool normalize = true);
 
 // ---- context ---------------------------------------------------------------
 struct mgx_ctx {
@@ -62,6 +63,8 @@ struct mgx_ctx {
   void *d_tables = nullptr; // T[] copy of tb.buf
   double *d_rcp = nullptr;  // 1.0 / tb.buf[k] in double, same offsets
   bool fast_div = true;
+  bool nonuniform = false;  // planned with caller-supplied node coordinates
+  bool normalize = true;    // Config::normalize_coordinates of the plan
   int fw_minb = 0;          // MGX_FW_MINB=2|3: force the k_level_forward variant (0 = by dtype)
   bool no_sym_recompose = false; // MGX_NO_SYM_RECOMPOSE=1: dequantise to floats first
   bool no_ws = false;       // MGX_NO_WS=1: single-warp Thomas kernels only (A/B)

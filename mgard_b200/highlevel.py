@@ -44,10 +44,11 @@ def _check(rc):
         raise MgardError(rc, _lib.load().mgx_x_last_error().decode())
 
 
-def compress(data, tol, s, mode, config=None, out=None):
+def compress(data, tol, s, mode, config=None, out=None, coords=None):
     """-> compressed stream (numpy uint8 array for host input, torch uint8 CUDA
     tensor for device input).  ``out``: optional pre-allocated buffer of the
-    same kind (output_pre_allocated = true)."""
+    same kind (output_pre_allocated = true).  ``coords``: one array of node
+    coordinates per dimension -> the non-uniform overload (compress_x.hpp:74-100)."""
     lib = _lib.load()
     cfg = config if config is not None else Config()
     shape = tuple(int(v) for v in data.shape)
@@ -71,10 +72,43 @@ def compress(data, tol, s, mode, config=None, out=None):
         in_ptr, out_ptr, cap = data.ctypes.data, out.ctypes.data, out.size
     p = ctypes.c_void_p(out_ptr)
     size = ctypes.c_size_t(cap)
-    _check(lib.mgx_x_compress(D, code, shp, float(tol), float(s), int(mode),
-                              ctypes.c_void_p(in_ptr), ctypes.byref(p),
-                              ctypes.byref(size), ctypes.byref(cfg), 1))
+    if coords is not None:
+        npdt = np.float64 if code == 1 else np.float32
+        arrs = [np.ascontiguousarray(c, npdt) for c in coords]
+        if len(arrs) != D or any(a.shape != (n_,) for a, n_ in zip(arrs, shape)):
+            raise MgardError(1, "one coordinate array of the dimension's length per "
+                                "dimension")
+        cptr = (ctypes.c_void_p * D)(*[a.ctypes.data for a in arrs])
+        _check(lib.mgx_x_compress_coords(
+            D, code, shp, float(tol), float(s), int(mode), ctypes.c_void_p(in_ptr),
+            ctypes.byref(p), ctypes.byref(size), cptr, ctypes.byref(cfg), 1))
+    else:
+        _check(lib.mgx_x_compress(D, code, shp, float(tol), float(s), int(mode),
+                                  ctypes.c_void_p(in_ptr), ctypes.byref(p),
+                                  ctypes.byref(size), ctypes.byref(cfg), 1))
     return out[:size.value]
+
+
+def read_coords(stream):
+    """node coordinates stored in a stream's header: list of float64 arrays, one per
+    dimension, or None for a uniform grid"""
+    lib = _lib.load()
+    buf = np.frombuffer(bytes(stream), dtype=np.uint8)
+    md, hb = read_metadata(buf[:min(buf.size, 1 << 26)])
+    if not md.nonuniform:
+        return None
+    total = sum(int(md.shape[d]) for d in range(md.D))
+    out = np.empty(total, np.float64)
+    cnt = ctypes.c_uint64()
+    _check(lib.mgx_metadata_coords(ctypes.c_void_p(buf.ctypes.data), buf.size,
+                                   ctypes.c_void_p(out.ctypes.data), total,
+                                   ctypes.byref(cnt)))
+    res, at = [], 0
+    for d in range(md.D):
+        n_ = int(md.shape[d])
+        res.append(out[at:at + n_].copy())
+        at += n_
+    return res
 
 
 def read_metadata(stream_head):

@@ -204,6 +204,11 @@ def serialize_header(shape, dtype_code, ebtype, tol, s, norm, dd_dim, dd_size,
     md.dtype = dtype_code
     md.mode = 0 if ebtype == REL else 1
     md.linf = 1 if math.isinf(s) else 0
+    if dtype_code == 0:
+        # the templated reference entry takes tol, s and the norm as T
+        # (CompressionHighLevel.hpp:311): what is recorded is their float value
+        tol, norm = float(np.float32(tol)), float(np.float32(norm))
+        s = s if math.isinf(s) else float(np.float32(s))
     md.s, md.norm, md.tol = s, norm, tol
     md.decomposed = 1 if decomposed else 0
     md.dd_type = 0
@@ -297,7 +302,11 @@ class ShardedDomain:
         t0 = time.perf_counter()
         parts = [self.comp(i).NormPartial(f, s) for i, f in enumerate(fields)]
         self.last_norm_ms = (time.perf_counter() - t0) * 1e3
-        local = (max(parts) if linf else sum(parts)) if parts else 0.0
+        # plain left-to-right fp64 adds like the reference's loop over subdomains
+        # (ErrorToleranceCalculator.hpp:86-123); Python >= 3.12's sum() compensates
+        local = 0.0
+        for v in parts:
+            local = max(local, v) if linf else local + v
         part = self.all_reduce_partial(local, linf)
         return float(self.lib.mgx_finish_norm(self.dtype_code, 1 if linf else 0, part,
                                               self.total_elems, 1))

@@ -42,6 +42,22 @@ int mgxo_levels(int D, const uint64_t *shape, uint64_t max_level,
   return (int)L;
 }
 
+/* Grid of the hierarchies built from now on (mgxo_set_grid): the caller's node
+ * coordinates -- Hierarchy(shape, coords, config), Hierarchy.hpp:840-857, data
+ * structure Cartesian_Grid_Non_Uniform -- or a uniform grid on the unit cube /
+ * with unit spacing (Config::normalize_coordinates).  Test infrastructure: process
+ * wide, not thread safe. */
+static int mgxo_grid_nonuniform = 0;
+static int mgxo_grid_normalize = 1;
+static const void *mgxo_grid_coords[MGXO_MAX_D] = {0};
+
+void mgxo_set_grid(int D, const void *const *coords, int normalize_coordinates) {
+  mgxo_grid_nonuniform = coords != NULL;
+  mgxo_grid_normalize = normalize_coordinates != 0;
+  for (int d = 0; d < MGXO_MAX_D; d++)
+    mgxo_grid_coords[d] = (coords && d < D) ? coords[d] : NULL;
+}
+
 #define CAT_(a, b) a##b
 #define CAT(a, b) CAT_(a, b)
 

@@ -30,6 +30,11 @@ int mgxo_levels(int D, const uint64_t *shape, uint64_t max_level,
 
 /* In-place multilevel decomposition / recomposition into the reordered,
  * level-blocked layout (DataRefactoring.hpp:24-317). */
+/* Grid used by every call that follows: coords[d] -> shape[d] node coordinates in
+ * the data type of that call (float for *_f32, double for *_f64), or NULL for a
+ * uniform grid (unit cube if normalize_coordinates, else unit spacing). */
+void mgxo_set_grid(int D, const void *const *coords, int normalize_coordinates);
+
 int mgxo_decompose_f32(int D, const uint64_t *shape, float *v, int orthogonal);
 int mgxo_decompose_f64(int D, const uint64_t *shape, double *v, int orthogonal);
 int mgxo_recompose_f32(int D, const uint64_t *shape, float *v, int orthogonal);

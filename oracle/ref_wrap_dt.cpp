@@ -60,13 +60,28 @@ namespace {
 constexpr DIM D = REF_D;
 using T = REF_T;
 
+// grid of the hierarchies built from now on (ref_set_grid_<D><t>): the caller's node
+// coordinates -> Hierarchy(shape, coords, config), or uniform with / without
+// Config::normalize_coordinates
+bool g_nonuniform = false;
+bool g_normalize = true;
+std::vector<T *> g_coords(D, nullptr);
+
 Config make_config(uint32_t dict_size, uint32_t chunk_size) {
   Config config;
   config.huff_dict_size = dict_size;
   config.huff_block_size = chunk_size;
   config.lossless = lossless_type::Huffman;
   config.log_level = log::ERR;
+  config.normalize_coordinates = g_normalize;
   return config;
+}
+
+template <typename Dev>
+Hierarchy<D, T, Dev> make_hierarchy(std::vector<SIZE> shp, Config config) {
+  if (g_nonuniform)
+    return Hierarchy<D, T, Dev>(shp, g_coords, config);
+  return Hierarchy<D, T, Dev>(shp, config);
 }
 
 std::vector<SIZE> make_shape(const uint64_t *shape) {
@@ -87,7 +102,7 @@ int do_compress(const uint64_t *shape, const T *in, int rel, double tol,
   DeviceRuntime<Dev>::Initialize();
   Config config = make_config(dict, chunk);
   std::vector<SIZE> shp = make_shape(shape);
-  Hierarchy<D, T, Dev> hierarchy(shp, config);
+  Hierarchy<D, T, Dev> hierarchy = make_hierarchy<Dev>(shp, config);
   Compressor<D, T, Dev> compressor;
   compressor.Adapt(hierarchy, config, 0);
   DeviceRuntime<Dev>::SyncQueue(0);
@@ -113,7 +128,7 @@ int do_decompress(const uint64_t *shape, const uint8_t *in, uint64_t bytes,
   DeviceRuntime<Dev>::Initialize();
   Config config = make_config(dict, chunk);
   std::vector<SIZE> shp = make_shape(shape);
-  Hierarchy<D, T, Dev> hierarchy(shp, config);
+  Hierarchy<D, T, Dev> hierarchy = make_hierarchy<Dev>(shp, config);
   Compressor<D, T, Dev> compressor;
   compressor.Adapt(hierarchy, config, 0);
   DeviceRuntime<Dev>::SyncQueue(0);
@@ -140,7 +155,7 @@ int do_bench(const uint64_t *shape, const T *in, int rel, double tol, double s,
   DeviceRuntime<Dev>::Initialize();
   Config config = make_config(8192, 1024);
   std::vector<SIZE> shp = make_shape(shape);
-  Hierarchy<D, T, Dev> hierarchy(shp, config);
+  Hierarchy<D, T, Dev> hierarchy = make_hierarchy<Dev>(shp, config);
   Compressor<D, T, Dev> compressor;
   compressor.Adapt(hierarchy, config, 0);
   DeviceRuntime<Dev>::SyncQueue(0);
@@ -184,13 +199,22 @@ int do_bench(const uint64_t *shape, const T *in, int rel, double tol, double s,
 
 extern "C" {
 
+// grid for the calls that follow: coords[d] -> shape[d] node coordinates (T), kept
+// alive by the caller; NULL -> uniform grid
+void FN(ref_set_grid_)(const void *const *coords, int normalize_coordinates) {
+  g_nonuniform = coords != nullptr;
+  g_normalize = normalize_coordinates != 0;
+  for (DIM d = 0; d < D; d++)
+    g_coords[d] = coords ? (T *)coords[d] : nullptr;
+}
+
 // DataRefactor::Decompose / Recompose (DataRefactoring/DataRefactor.hpp:73-130)
 int FN(ref_decompose_)(const uint64_t *shape, T *data, int orthogonal) {
   using Dev = SERIAL;
   DeviceRuntime<Dev>::Initialize();
   Config config = make_config(8192, 1024);
   std::vector<SIZE> shp = make_shape(shape);
-  Hierarchy<D, T, Dev> hierarchy(shp, config);
+  Hierarchy<D, T, Dev> hierarchy = make_hierarchy<Dev>(shp, config);
   data_refactoring::DataRefactor<D, T, Dev> refactor(hierarchy, config);
   Array<D, T, Dev> arr(shp);
   arr.load(data);
@@ -206,7 +230,7 @@ int FN(ref_recompose_)(const uint64_t *shape, T *data, int orthogonal) {
   DeviceRuntime<Dev>::Initialize();
   Config config = make_config(8192, 1024);
   std::vector<SIZE> shp = make_shape(shape);
-  Hierarchy<D, T, Dev> hierarchy(shp, config);
+  Hierarchy<D, T, Dev> hierarchy = make_hierarchy<Dev>(shp, config);
   data_refactoring::DataRefactor<D, T, Dev> refactor(hierarchy, config);
   Array<D, T, Dev> arr(shp);
   arr.load(data);
@@ -226,7 +250,7 @@ int FN(ref_quantize_)(const uint64_t *shape, const T *coeff, int rel,
   DeviceRuntime<Dev>::Initialize();
   Config config = make_config(dict, 1024);
   std::vector<SIZE> shp = make_shape(shape);
-  Hierarchy<D, T, Dev> hierarchy(shp, config);
+  Hierarchy<D, T, Dev> hierarchy = make_hierarchy<Dev>(shp, config);
   LinearQuantizer<D, T, QUANTIZED_INT, Dev> quantizer(hierarchy, config);
   Array<D, T, Dev> arr(shp);
   arr.load(coeff);
@@ -250,7 +274,7 @@ int FN(ref_dequantize_)(const uint64_t *shape, const int64_t *codes, int rel,
   DeviceRuntime<Dev>::Initialize();
   Config config = make_config(dict, 1024);
   std::vector<SIZE> shp = make_shape(shape);
-  Hierarchy<D, T, Dev> hierarchy(shp, config);
+  Hierarchy<D, T, Dev> hierarchy = make_hierarchy<Dev>(shp, config);
   LinearQuantizer<D, T, QUANTIZED_INT, Dev> quantizer(hierarchy, config);
   Array<D, T, Dev> arr(shp);
   Array<D, QUANTIZED_INT, Dev> q(shp);

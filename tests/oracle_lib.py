@@ -74,6 +74,41 @@ def port():
     return _port
 
 
+import contextlib
+
+
+@contextlib.contextmanager
+def grid(coords=None, normalize=True, dtype=None):
+    """Grid of every hierarchy the oracles build inside the block: ``coords`` = one
+    1-D array of node coordinates per dimension (-> Hierarchy(shape, coords, config),
+    a NON-UNIFORM grid; converted to ``dtype``, the data type of the calls), or None
+    for a uniform grid with Config::normalize_coordinates = ``normalize``."""
+    arrs, ptrs, D = None, None, 0
+    if coords is not None:
+        assert dtype is not None
+        arrs = [np.ascontiguousarray(c, dtype) for c in coords]
+        D = len(arrs)
+        ptrs = (c_vp * D)(*[a.ctypes.data for a in arrs])
+
+    def apply(p, D_, norm_, dt):
+        port().mgxo_set_grid(D_, p, int(norm_))
+        if have_ref():
+            for d in range(1, 6):
+                for t in ("f", "d"):
+                    fn = getattr(ref(), "ref_set_grid_%d%s" % (d, t), None)
+                    if fn is None:
+                        continue
+                    mine = p is not None and d == D_ and t == (
+                        "f" if np.dtype(dt) == np.float32 else "d")
+                    fn(p if mine else None, int(norm_))
+
+    apply(ptrs, D, normalize, dtype)
+    try:
+        yield arrs
+    finally:
+        apply(None, 0, True, None)
+
+
 class Oracle:
     """Uniform python face over either library."""
 
@@ -244,6 +279,25 @@ def fresh(kind, method, *args, **kwargs):
         code = ("import pickle,sys; sys.path.insert(0,%r); import oracle_lib as o;"
                 "k,m,a,kw=pickle.load(open(%r,'rb'));"
                 "r=getattr(o.Oracle(k),m)(*a,**kw);"
+                "pickle.dump(r,open(%r,'wb'))" % (os.path.dirname(__file__), pin, pout))
+        subprocess.check_call([sys.executable, "-c", code])
+        with open(pout, "rb") as f:
+            return pickle.load(f)
+
+
+def fresh_in_grid(kind, coords, dtype, normalize, method, *args, **kwargs):
+    """fresh() inside ``grid(coords, normalize, dtype)``"""
+    import pickle
+    import sys
+    import tempfile
+    with tempfile.TemporaryDirectory() as td:
+        pin, pout = os.path.join(td, "in.pkl"), os.path.join(td, "out.pkl")
+        with open(pin, "wb") as f:
+            pickle.dump((kind, coords, dtype, normalize, method, args, kwargs), f)
+        code = ("import pickle,sys; sys.path.insert(0,%r); import oracle_lib as o;"
+                "k,c,dt,nz,m,a,kw=pickle.load(open(%r,'rb'));\n"
+                "with o.grid(c, nz, dt):\n"
+                "    r=getattr(o.Oracle(k),m)(*a,**kw)\n"
                 "pickle.dump(r,open(%r,'wb'))" % (os.path.dirname(__file__), pin, pout))
         subprocess.check_call([sys.executable, "-c", code])
         with open(pout, "rb") as f:

@@ -74,4 +74,10 @@ def test_sharded_stream_equals_the_single_call_stream(shape, dtype, s, tol, nsub
     md1, _ = hl.read_metadata(bytes(single[:4096]))
     assert md1.decomposed and md1.dd_dim == dd.dim and md1.dd_size == dd.size, \
         (md1.decomposed, md1.dd_dim, md1.dd_size, dd.dim, dd.size)
+    md0, _ = hl.read_metadata(stream[:4096])
+    for f, _t in md0._fields_:
+        a, b = getattr(md0, f), getattr(md1, f)
+        a = list(a) if hasattr(a, "__len__") else a
+        b = list(b) if hasattr(b, "__len__") else b
+        assert a == b, "header field %s: sharded %r, single call %r" % (f, a, b)
     assert bytes(single) == stream, "sharded stream differs from mgx_x_compress"
