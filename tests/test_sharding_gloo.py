@@ -156,7 +156,9 @@ def domain_worker(rank, world, port, shape, dtype, s, tol, nsub, q):
         if rank == 0:
             md, hb = read_metadata(stream)
             assert md.decomposed == 1 and md.dd_dim == dd.dim and md.dd_size == dd.size
-            assert md.norm == norm and md.tol == tol and md.D == len(shape)
+            as_t = (lambda x: float(np.float32(x))) if np.dtype(dtype) == np.float32 \
+                else float
+            assert md.norm == as_t(norm) and md.tol == as_t(tol) and md.D == len(shape)
             parts = unframe(stream[hb:])
             assert len(parts) == S
             # the tolerance a decoder derives from the header is the one that was used
