@@ -637,40 +637,48 @@ __global__ void __launch_bounds__(HIER_THREADS)
   const uint32_t nz = a.n[0], ny = a.n[1], nx = a.n[2];
   const uint32_t RZ = fa.rt[0] * 8, RY = fa.rt[1] * 8, RX = fa.rt[2] * 64;
   // deep nodes of the regular region, then slabs z >= RZ, y >= RY, x >= RX
-  const uint64_t nd = (uint64_t)fa.rt[0] * fa.rt[1] * (RX / 8);
-  const uint64_t nA = (uint64_t)(nz - RZ) * ny * nx;
-  const uint64_t nB = (uint64_t)RZ * (ny - RY) * nx;
-  const uint64_t nC = (uint64_t)RZ * RY * (nx - RX);
-  const uint64_t total = nd + nA + nB + nC;
-  for (uint64_t i = blockIdx.x * (uint64_t)HIER_THREADS + threadIdx.x; i < total;
-       i += (uint64_t)gridDim.x * HIER_THREADS) {
+  // (N < 2^32 is a launch condition: every count below fits 32 bits, and 32-bit
+  // divisions are a fraction of the cost of 64-bit ones on this per-node path)
+  const uint32_t nd = fa.rt[0] * fa.rt[1] * (RX / 8);
+  const uint32_t nA = (nz - RZ) * ny * nx;
+  const uint32_t nB = RZ * (ny - RY) * nx;
+  const uint32_t nC = RZ * RY * (nx - RX);
+  const uint32_t total = nd + nA + nB + nC;
+  const uint32_t stride = gridDim.x * HIER_THREADS;
+  for (uint32_t i = blockIdx.x * HIER_THREADS + threadIdx.x; i < total;) {
     uint32_t gx, gy, gz;
     if (i < nd) {
       const uint32_t per = RX / 8;
-      gx = (uint32_t)(i % per) * 8;
-      const uint64_t r = i / per;
-      gy = (uint32_t)(r % fa.rt[1]) * 8;
-      gz = (uint32_t)(r / fa.rt[1]) * 8;
+      gx = (i % per) * 8;
+      const uint32_t r = i / per;
+      gy = (r % fa.rt[1]) * 8;
+      gz = (r / fa.rt[1]) * 8;
     } else if (i < nd + nA) {
-      const uint64_t j = i - nd;
-      gx = (uint32_t)(j % nx);
-      gy = (uint32_t)((j / nx) % ny);
-      gz = RZ + (uint32_t)(j / ((uint64_t)nx * ny));
+      const uint32_t j = i - nd;
+      gx = j % nx;
+      gy = (j / nx) % ny;
+      gz = RZ + j / (nx * ny);
     } else if (i < nd + nA + nB) {
-      const uint64_t j = i - nd - nA;
+      const uint32_t j = i - nd - nA;
       const uint32_t wy = ny - RY;
-      gx = (uint32_t)(j % nx);
-      gy = RY + (uint32_t)((j / nx) % wy);
-      gz = (uint32_t)(j / ((uint64_t)nx * wy));
+      gx = j % nx;
+      gy = RY + (j / nx) % wy;
+      gz = j / (nx * wy);
     } else {
-      const uint64_t j = i - nd - nA - nB;
+      const uint32_t j = i - nd - nA - nB;
       const uint32_t wx = nx - RX;
-      gx = RX + (uint32_t)(j % wx);
-      gy = (uint32_t)((j / wx) % RY);
-      gz = (uint32_t)(j / ((uint64_t)wx * RY));
+      gx = RX + j % wx;
+      gy = (j / wx) % RY;
+      gz = j / (wx * RY);
     }
+    // (the last block's i + stride may wrap around 2^32: stop on overflow)
+    const uint32_t next = i + stride;
+    const bool last = next < i;
+    i = next;
     element_generic<T, HALF, TS>(u, (const T *)nullptr, tables, a, gx, gy, gz, 0, 0, 0, 0,
                                  0, 0, sink);
+    if (last)
+      break;
   }
   __syncthreads();
   for (uint32_t i = threadIdx.x; i < a.dict; i += HIER_THREADS) {
