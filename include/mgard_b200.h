@@ -205,7 +205,10 @@ enum mgx_tick_id {
  * the caller synchronises.  Scratch is a 16 KB static __device__ array that
  * every GPU loading the library holds until exit.  Limit: n <= 2^31 elements
  * (2048 blocks x 2^20), larger n returns MGX_OUTPUT_TOO_LARGE.  All calls on a
- * device share the scratch: calls that overlap on the GPU race.  On failure a
+ * device share the scratch: calls that overlap on the GPU race.  The first call
+ * on a device resolves the scratch address and loads the kernels' module: make
+ * one eager call per device before calling under stream capture
+ * (tests/test_zz_no_alloc.py replays it from a CUDA graph).  On failure a
  * message is copied into err (if err != NULL, capacity err_cap). */
 int mgx_norm_partial_noalloc(int device, void *cuda_stream, const void *d_in,
                              int dtype, uint64_t n, int linf, double *d_partial,

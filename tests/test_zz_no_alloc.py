@@ -73,3 +73,31 @@ def test_noalloc_norm_rejects_sizes_beyond_the_scratch():
     rc = lib.mgx_norm_partial_noalloc(0, None, small.data_ptr(), 7, 1 << 31, 1,
                                       out.data_ptr(), err, 256)
     assert rc == 4 and b"dtype" in err.value
+
+
+def test_noalloc_norm_replays_from_a_cuda_graph():
+    """captured once (after one eager call on the device), replayed twice on changing
+    input: what a caller under CUDA graph capture does"""
+    lib = _lib.load()
+    dev = torch.device("cuda", 0)
+    g = torch.Generator(device="cpu").manual_seed(9)
+    u = (torch.randn((64, 70, 130), generator=g, dtype=torch.float64) + 0.5).to(torch.float32).to(dev)
+    out = torch.zeros(1, dtype=torch.float64, device=dev)
+    eager = _noalloc(lib, u, 0, out)  # resolves the scratch address, loads the module
+    s = torch.cuda.Stream(device=dev)
+    graph = torch.cuda.CUDAGraph()
+    err = ctypes.create_string_buffer(256)
+    s.wait_stream(torch.cuda.current_stream(dev))
+    with torch.cuda.graph(graph, stream=s):
+        rc = lib.mgx_norm_partial_noalloc(
+            0, ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream), u.data_ptr(), 0,
+            u.numel(), 0, out.data_ptr(), err, 256)
+    assert rc == 0, err.value.decode()
+    out.fill_(-1.0)
+    graph.replay()
+    torch.cuda.synchronize()
+    assert float(out.item()) == eager
+    u.mul_(2.0)  # exact in floating point: the sum of squares is exactly 4 x
+    graph.replay()
+    torch.cuda.synchronize()
+    assert float(out.item()) == 4.0 * eager
