@@ -1397,6 +1397,11 @@ LvGeom level_geom(const mgx_ctx *ctx, int l, uint32_t cols_per_chunk) {
 // A CTA owns 32 chains (lanes) x P partitions (warps).
 constexpr int PT_W = 64;       // warm-up steps
 constexpr int PT_MAXP = 16;    // partitions (warps) per CTA
+#ifndef MGX_PT_MIN_STRIDED
+#define MGX_PT_MIN_STRIDED 1024
+#endif
+constexpr uint32_t PT_MIN_CONTIG = 512;  // shortest chains worth partitioning (measured)
+constexpr uint32_t PT_MIN_STRIDED = MGX_PT_MIN_STRIDED;
 
 template <typename T> __device__ __forceinline__ bool bits_differ(T a, T b);
 template <> __device__ __forceinline__ bool bits_differ<float>(float a, float b) {
@@ -1452,14 +1457,21 @@ __global__ void __launch_bounds__(PT_MAXP * 32)
   T *al = ACC ? acc + base : nullptr;
   const uint32_t s = min(p * lp, n), e = min(s + lp, n);
   // ---- forward: y[i] = x[i] - y[i-1] * abr[i] ----
+  // (the rows of the NEXT batch of 8 are requested before the current batch's
+  // dependent chain runs: one memory latency per sweep instead of one per batch)
   auto fwd = [&](uint32_t lo, uint32_t hi, T prev, bool store) {
+    if (lo >= hi)
+      return prev;
+    T c[8], cn[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++)
+      c[k] = xl[(uint64_t)min(lo + k, hi - 1) * inner];
     for (uint32_t i0 = lo; i0 < hi; i0 += 8) {
-      T c[8], f[8];
+      T f[8];
 #pragma unroll
       for (int k = 0; k < 8; k++) {
-        const uint32_t i = min(i0 + k, hi - 1);
-        c[k] = xl[(uint64_t)i * inner];
-        f[k] = __ldg(abr + i);
+        cn[k] = xl[(uint64_t)min(i0 + 8 + k, hi - 1) * inner];
+        f[k] = __ldg(abr + min(i0 + k, hi - 1));
       }
 #pragma unroll
       for (int k = 0; k < 8; k++)
@@ -1468,6 +1480,9 @@ __global__ void __launch_bounds__(PT_MAXP * 32)
           if (store && active)
             yl[(uint64_t)(i0 + k) * inner] = prev;
         }
+#pragma unroll
+      for (int k = 0; k < 8; k++)
+        c[k] = cn[k];
     }
     return prev;
   };
@@ -1480,15 +1495,24 @@ __global__ void __launch_bounds__(PT_MAXP * 32)
   __syncthreads(); // every y of the CTA's chains is final and visible
   // ---- backward: x[i] = (y[i] - am[i+1] * x[i+1]) / bm[i+1] ----
   auto bwd = [&](uint32_t lo, uint32_t hi, T prev, bool store) {
-    // elements hi-1, hi-2, ..., lo
+    // elements hi-1, hi-2, ..., lo; the next batch's rows are requested first
+    if (hi <= lo)
+      return prev;
+    T c[8], cn[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++)
+      c[k] = yl[(uint64_t)(hi - 1 - min((uint32_t)k, hi - lo - 1)) * inner];
     while (hi > lo) {
       const uint32_t cnt = min(8u, hi - lo);
-      T c[8], a1[8], b1[8], res[8];
+      const uint32_t nhi = hi - cnt; // next batch: nhi-1, nhi-2, ...
+      T a1[8], b1[8], res[8];
       double y1[8];
 #pragma unroll
       for (int k = 0; k < 8; k++) {
+        const uint32_t left = nhi > lo ? nhi - lo : 1u;
+        const uint32_t in = nhi > lo ? nhi - 1 - min((uint32_t)k, left - 1) : lo;
+        cn[k] = yl[(uint64_t)in * inner];
         const uint32_t i = hi - 1 - min((uint32_t)k, cnt - 1);
-        c[k] = yl[(uint64_t)i * inner];
         a1[k] = __ldg(am + i + 1);
         b1[k] = __ldg(bm + i + 1);
         y1[k] = __ldg(rbm + i + 1);
@@ -1500,7 +1524,10 @@ __global__ void __launch_bounds__(PT_MAXP * 32)
           if ((uint32_t)k < cnt)
             xl[(uint64_t)(hi - 1 - k) * inner] = res[k];
       }
-      hi -= cnt;
+#pragma unroll
+      for (int k = 0; k < 8; k++)
+        c[k] = cn[k];
+      hi = nhi;
     }
     return prev;
   };
@@ -1513,9 +1540,19 @@ __global__ void __launch_bounds__(PT_MAXP * 32)
   if (ACC) {
     __syncthreads();
     if (active)
-      for (uint32_t i = s; i < e; i++) {
-        const uint64_t off = (uint64_t)i * inner;
-        al[off] = sign > 0 ? add_rn(al[off], xl[off]) : sub_rn(al[off], xl[off]);
+      for (uint32_t i0 = s; i0 < e; i0 += 8) { // 16 independent loads in flight
+        T av[8], xv[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+          const uint64_t off = (uint64_t)min(i0 + k, e - 1) * inner;
+          av[k] = al[off];
+          xv[k] = xl[off];
+        }
+#pragma unroll
+        for (int k = 0; k < 8; k++)
+          if (i0 + k < e)
+            al[(uint64_t)(i0 + k) * inner] =
+                sign > 0 ? add_rn(av[k], xv[k]) : sub_rn(av[k], xv[k]);
       }
   }
 }
@@ -1734,7 +1771,8 @@ int correction_tail(mgx_ctx *ctx, int l, T *R0, T *R1, T *A, int sign) {
     // scarce chains: the producer/consumer pair kernels (one pair per 32 lines)
     const bool scarce = lines < (uint64_t)ctx->num_sms * 128 && !ctx->no_ws;
     // long, scarce chains: partitioned solves (bit-identical, checked in-kernel)
-    if (!ctx->no_part && n >= 256 && lines < (uint64_t)ctx->num_sms * 512) {
+    if (!ctx->no_part && n >= (inner == 1 ? PT_MIN_CONTIG : PT_MIN_STRIDED) &&
+        lines < (uint64_t)ctx->num_sms * 512) {
       const uint32_t P = (uint32_t)std::min<uint64_t>(PT_MAXP, n / 128);
       const uint32_t lp = ((n + P - 1) / P + 31) / 32 * 32;
       T *other = corr == R0 ? R1 : R0;
