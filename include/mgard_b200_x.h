@@ -111,6 +111,21 @@ int mgx_x_compress_coords(int D, int dtype, const uint64_t *shape, double tol, d
 /* decompress(in, in_size, out, shape, dtype, config, output_pre_allocated)
  * -- compress_x.hpp:137-141.  shape_out (5 entries), D_out, dtype_out may be
  * NULL. */
+/* compress on SEVERAL GPUs of this process (no counterpart in the reference, whose
+ * compress drives one device, Config::dev_id; this is the subdomain loop of
+ * compress_pipeline_gpu, GPUPipelines.hpp:89-205, dealt to `num_devices` devices).
+ * `in` and `*out` are HOST buffers.  The domain is cut into at least num_devices
+ * MaxDim subdomains (DomainDecomposer.hpp:192-223), devices[k] takes the k-th
+ * contiguous block of them on its own host thread, the norm of a REL bound is
+ * combined over all subdomains (calc_norm_decomposed,
+ * ErrorToleranceCalculator.hpp:61-123) and every subdomain is compressed with the
+ * same ABS bound.  The stream is what mgx_x_compress writes for that decomposition,
+ * byte for byte: any single GPU (or stock MGARD-X) decodes it. */
+int mgx_x_compress_multi(int D, int dtype, const uint64_t *shape, double tol, double s,
+                         int mode, const void *in, void **out, size_t *out_size,
+                         const int *devices, int num_devices, const mgx_config *cfg,
+                         int output_pre_allocated);
+
 int mgx_x_decompress(const void *in, size_t in_size, void **out,
                      uint64_t *shape_out, int *D_out, int *dtype_out,
                      const mgx_config *cfg, int output_pre_allocated);

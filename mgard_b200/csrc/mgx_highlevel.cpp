@@ -20,7 +20,9 @@
 #include <cstring>
 #include <limits>
 #include <map>
+#include <condition_variable>
 #include <mutex>
+#include <thread>
 #include <string>
 #include <vector>
 
@@ -32,7 +34,9 @@ std::string g_err;
 std::mutex g_mu; // the reference's cache is process-global and not
                  // thread-safe; calls are serialised here instead
 
+std::mutex g_err_mu; // mgx_x_compress_multi reports from several threads
 int fail(int rc, const std::string &msg) {
+  std::lock_guard<std::mutex> lock(g_err_mu);
   g_err = msg;
   return rc;
 }
@@ -1165,6 +1169,308 @@ int x_compress(int D, int dtype, const uint64_t *shape, double tol, double s,
   return MGX_SUCCESS;
 }
 
+// ---- compress on several GPUs of one process ------------------------------------
+// One host thread per device, MaxDim subdomains dealt to the devices in contiguous
+// blocks.  The only coupling between the devices is the scalar of a REL bound: every
+// thread leaves the partials of its subdomains in a shared array, a barrier, and
+// every thread adds them up in subdomain order (the same fp64 result on all of them,
+// and the same one x_compress gets).  The ABS bound per subdomain is a host-side
+// argument of mgx_compress, so the scalar passes through the host anyway: an 8-byte
+// read per subdomain and a host barrier replace the all-reduce of the N-process
+// path.  Payloads stay on their device until every size is known, then rank-ordered
+// records are copied behind the header: the stream is byte-identical to the one
+// x_compress writes for the same decomposition.
+struct HostBarrier {
+  std::mutex m;
+  std::condition_variable cv;
+  int n, waiting = 0, gen = 0;
+  explicit HostBarrier(int n_) : n(n_) {}
+  void wait() {
+    std::unique_lock<std::mutex> l(m);
+    const int g = gen;
+    if (++waiting == n) {
+      waiting = 0;
+      ++gen;
+      cv.notify_all();
+    } else {
+      cv.wait(l, [&] { return gen != g; });
+    }
+  }
+};
+
+struct MultiShared {
+  Slabs sl;
+  int D, dtype, rel, linf, ndev;
+  double tolT, sT;
+  uint64_t N;
+  const void *in;
+  mgx_config cfg;
+  std::vector<double> part;      // per subdomain: max |u| or sum u^2
+  std::vector<void *> d_payload; // per subdomain: record payload on its device
+  std::vector<uint64_t> bytes;
+  double norm = 1, local_tol = 0;
+  int local_rel = 0;
+  std::vector<int> rc;
+  std::vector<std::string> msg;
+};
+
+void multi_worker(MultiShared &S, HostBarrier &bar, int k, int dev, DeviceCache *cp) {
+  DeviceCache &c = *cp;
+  const size_t es = S.sl.es;
+  const uint64_t per = (S.sl.num + S.ndev - 1) / S.ndev;
+  const uint64_t lo = std::min<uint64_t>((uint64_t)k * per, S.sl.num),
+                 hi = std::min<uint64_t>(lo + per, S.sl.num);
+  auto bail = [&](int rc, const std::string &m) {
+    if (!S.rc[k]) {
+      S.rc[k] = rc;
+      S.msg[k] = m;
+    }
+  };
+  bool ok = cudaSetDevice(dev) == cudaSuccess;
+  if (!ok)
+    bail(MGX_FAILURE, "cudaSetDevice failed");
+  uint64_t max_elems = 0;
+  for (uint64_t i = lo; i < hi; i++)
+    max_elems = std::max(max_elems, S.sl.elems(i));
+  const size_t pay_cap = max_elems * es + (max_elems / S.cfg.huff_block_size + 2) * 16 +
+                         (size_t)(128 + S.cfg.huff_dict_size) * 8 + 4096;
+  if (ok && hi > lo) {
+    if (ensure_buffer(c.sub[0], c.sub_bytes[0], max_elems * es) ||
+        ensure_buffer(c.cbuf[0], c.cbuf_bytes[0], pay_cap)) {
+      bail(MGX_FAILURE, "out of device memory");
+      ok = false;
+    }
+  }
+  auto load = [&](uint64_t i) -> bool { // OriginalToSubdomain, synchronous
+    if (copy_slab(S.sl, i, c.sub[0], (void *)S.in, true, c.copy_in) ||
+        cudaStreamSynchronize(c.copy_in) != cudaSuccess) {
+      bail(MGX_FAILURE, "host -> device copy failed");
+      return false;
+    }
+    return true;
+  };
+  auto ctx_of = [&](uint64_t i, mgx_ctx **ctx) -> bool {
+    uint64_t sh[5], off;
+    S.sl.sub_shape(i, sh, &off);
+    const int r = cache_ctx(c, S.D, sh, S.dtype, S.cfg, ctx);
+    if (r)
+      bail(r, "plan failed");
+    return r == 0;
+  };
+  // ---- global norm (calc_norm_decomposed, ErrorToleranceCalculator.hpp:61-123)
+  if (S.rel && S.sl.decomposed) {
+    for (uint64_t i = lo; ok && i < hi; i++) {
+      mgx_ctx *ctx;
+      if (!(ok = load(i) && ctx_of(i, &ctx)))
+        break;
+      const int r = mgx_norm_partial(ctx, c.sub[0], S.linf, &S.part[i]);
+      if (r) {
+        bail(r, std::string("norm: ") + mgx_last_error(ctx));
+        ok = false;
+      }
+    }
+    bar.wait();
+    bool all_ok = true;
+    for (int j = 0; j < S.ndev; j++)
+      all_ok = all_ok && S.rc[j] == 0;
+    if (!all_ok)
+      ok = false;
+    if (k == 0 && all_ok) {
+      double acc = 0;
+      for (uint64_t i = 0; i < S.sl.num; i++)
+        acc = S.linf ? std::max(acc, S.part[i]) : acc + S.part[i];
+      S.norm = mgx_finish_norm(S.dtype, S.linf, acc, S.N,
+                               S.cfg.normalize_coordinates ? 1 : 0);
+      S.local_tol = mgx_local_abs_tol(S.dtype, S.rel, S.norm, S.tolT, S.sT, S.sl.num);
+    }
+    bar.wait();
+  }
+  // ---- compress this device's subdomains, payloads stay on the device
+  for (uint64_t i = lo; ok && i < hi; i++) {
+    mgx_ctx *ctx;
+    if (!(ok = load(i) && ctx_of(i, &ctx)))
+      break;
+    const uint64_t n_sub = S.sl.elems(i);
+    uint64_t bytes = 0;
+    double nrm = S.local_rel ? 0.0 : S.norm;
+    int r = mgx_compress(ctx, c.sub[0], S.local_rel, S.local_tol, S.sT, &nrm,
+                         (uint8_t *)c.cbuf[0], pay_cap, &bytes);
+    if (r != MGX_SUCCESS && r != MGX_OUTPUT_TOO_LARGE) {
+      bail(r, std::string("compress: ") + mgx_last_error(ctx));
+      ok = false;
+      break;
+    }
+    if (!S.sl.decomposed && S.rel)
+      S.norm = nrm;
+    const void *payload = c.cbuf[0];
+    if (r == MGX_OUTPUT_TOO_LARGE || bytes >= n_sub * es) { // raw fallback
+      payload = c.sub[0];
+      bytes = n_sub * es;
+    }
+    void *keep = nullptr;
+    if (cudaMalloc(&keep, bytes) != cudaSuccess ||
+        cudaMemcpy(keep, payload, bytes, cudaMemcpyDeviceToDevice) != cudaSuccess) {
+      cudaGetLastError();
+      bail(MGX_FAILURE, "out of device memory for a payload");
+      ok = false;
+      break;
+    }
+    S.d_payload[i] = keep;
+    S.bytes[i] = bytes;
+  }
+}
+
+int x_compress_multi(int D, int dtype, const uint64_t *shape, double tol, double s,
+                     int mode, const void *in, void **out, size_t *out_size,
+                     const int *devices, int ndev, const mgx_config &cfg, int prealloc) {
+  if (D > 5)
+    return fail(MGX_TOO_MANY_DIMENSIONS, "more than 5 dimensions");
+  if (dtype != MGX_F32 && dtype != MGX_F64)
+    return fail(MGX_BAD_DATA_TYPE, "data type not supported");
+  if (D < 1 || !shape || !in || !out || !out_size || !devices || ndev < 1 || ndev > 64)
+    return fail(MGX_FAILURE, "bad argument");
+  int rc = check_config(cfg);
+  if (rc)
+    return rc;
+  if (locate(in).device)
+    return fail(MGX_FAILURE, "mgx_x_compress_multi takes host buffers");
+  for (int a = 0; a < ndev; a++)
+    for (int b = a + 1; b < ndev; b++)
+      if (devices[a] == devices[b])
+        return fail(MGX_FAILURE, "a device is listed twice");
+  MultiShared S;
+  S.D = D;
+  S.dtype = dtype;
+  S.ndev = ndev;
+  S.cfg = cfg;
+  S.in = in;
+  const size_t es = dtype == MGX_F64 ? 8 : 4;
+  S.tolT = dtype == MGX_F32 ? (double)(float)tol : tol;
+  S.sT = dtype == MGX_F32 ? (double)(float)s : s;
+  S.rel = mode == MGX_EB_REL;
+  S.linf = std::isinf(S.sT) ? 1 : 0;
+  S.N = 1;
+  for (int d = 0; d < D; d++) {
+    if (shape[d] == 0)
+      return fail(MGX_FAILURE, "empty dimension");
+    S.N *= shape[d];
+  }
+  // devices first (streams, caches), the smallest free memory bounds a subdomain
+  std::vector<DeviceCache *> caches(ndev);
+  uint64_t avail = ~0ull;
+  for (int k = 0; k < ndev; k++) {
+    if ((rc = cache_get(devices[k], &caches[k])))
+      return rc;
+    avail = std::min(avail, available_bytes(*caches[k], cfg));
+  }
+  // at least one subdomain per device (DomainDecomposer.hpp:192-223 halving rule),
+  // further halved until one fits the memory
+  Slabs &sl = S.sl;
+  if ((rc = decide_slabs(D, shape, dtype, S.sT, avail, &sl)))
+    return rc;
+  if (sl.num < (uint64_t)ndev) {
+    int dim = 0;
+    uint64_t size = 0, num = 1;
+    mgx_max_dim_decomposition(D, shape, (uint64_t)ndev, &dim, &size, &num);
+    if (num > 1) {
+      sl.decomposed = true;
+      sl.dim = dim;
+      sl.size = size;
+      sl.num = num;
+      sl.finish();
+    }
+  }
+  S.part.assign(sl.num, 0.0);
+  S.d_payload.assign(sl.num, nullptr);
+  S.bytes.assign(sl.num, 0);
+  S.rc.assign(ndev, 0);
+  S.msg.assign(ndev, "");
+  S.local_rel = S.rel;
+  S.local_tol = S.tolT;
+  if (sl.decomposed) {
+    S.local_rel = 0; // ABS inside every subdomain (CompressionHighLevel.hpp:126-129)
+    if (!S.rel)
+      S.local_tol = mgx_local_abs_tol(dtype, 0, 1.0, S.tolT, S.sT, sl.num);
+  }
+  ScopedPin pin_in;
+  pin_in.pin(in, S.N * es, cfg.auto_pin_host_buffers);
+  {
+    HostBarrier bar(ndev);
+    std::vector<std::thread> th;
+    for (int k = 0; k < ndev; k++)
+      th.emplace_back(multi_worker, std::ref(S), std::ref(bar), k, devices[k], caches[k]);
+    for (auto &t : th)
+      t.join();
+  }
+  struct FreePayloads {
+    MultiShared &S;
+    const int *devices;
+    ~FreePayloads() {
+      const uint64_t per = (S.sl.num + S.ndev - 1) / S.ndev;
+      for (uint64_t i = 0; i < S.sl.num; i++)
+        if (S.d_payload[i]) {
+          cudaSetDevice(devices[i / per]);
+          cudaFree(S.d_payload[i]);
+        }
+    }
+  } freer{S, devices};
+  for (int k = 0; k < ndev; k++)
+    if (S.rc[k])
+      return fail(S.rc[k], "device " + std::to_string(devices[k]) + ": " + S.msg[k]);
+
+  mgx_metadata md;
+  memset(&md, 0, sizeof(md));
+  md.version[0] = FILE_VERSION_MAJOR;
+  md.D = D;
+  for (int d = 0; d < D; d++)
+    md.shape[d] = shape[d];
+  md.dtype = dtype;
+  md.mode = S.rel ? MGX_EB_REL : MGX_EB_ABS;
+  md.linf = S.linf;
+  md.s = S.sT;
+  md.tol = S.tolT;
+  md.norm = dtype == MGX_F32 ? (double)(float)S.norm : S.norm;
+  md.decomposed = sl.decomposed;
+  md.dd_type = MGX_DD_MAXDIM;
+  md.dd_dim = sl.dim;
+  md.dd_size = sl.decomposed ? sl.size : shape[0];
+  md.decomposition = MGX_DC_MULTIDIM;
+  md.lossless = MGX_LL_HUFFMAN;
+  md.huff_dict_size = cfg.huff_dict_size;
+  md.huff_block_size = cfg.huff_block_size;
+  md.reorder = cfg.reorder;
+  md.backend = 3; // X_CUDA
+  std::vector<uint8_t> head = header_bytes(md);
+  uint64_t total = PREAMBLE + head.size();
+  for (uint64_t i = 0; i < sl.num; i++)
+    total += 8 + S.bytes[i];
+  if (!prealloc) {
+    *out = malloc(total);
+    if (!*out)
+      return fail(MGX_FAILURE, "out of host memory");
+  } else if (!*out || *out_size < total) {
+    return fail(MGX_OUTPUT_TOO_LARGE, "output too large");
+  }
+  uint8_t *o = (uint8_t *)*out;
+  memcpy(o, SIGNATURE, 5);
+  put_u64_le(o + 5, head.size());
+  const uint32_t crc = mgx_crc32(head.data(), head.size());
+  for (int i = 0; i < 4; i++)
+    o[13 + i] = (uint8_t)(crc >> (8 * i));
+  memcpy(o + PREAMBLE, head.data(), head.size());
+  uint64_t offset = PREAMBLE + head.size();
+  const uint64_t per = (sl.num + ndev - 1) / ndev;
+  for (uint64_t i = 0; i < sl.num; i++) {
+    put_u64_le(o + offset, S.bytes[i]);
+    offset += 8;
+    X_CUDA(cudaSetDevice(devices[i / per]));
+    X_CUDA(cudaMemcpy(o + offset, S.d_payload[i], S.bytes[i], cudaMemcpyDeviceToHost));
+    offset += S.bytes[i];
+  }
+  *out_size = offset;
+  return MGX_SUCCESS;
+}
+
 // ---- decompress ------------------------------------------------------------------
 int fetch_header(const void *in, size_t in_size, const PtrLoc &loc,
                  std::vector<uint8_t> *buf) {
@@ -1659,6 +1965,28 @@ int mgx_x_compress_coords(int D, int dtype, const uint64_t *shape, double tol, d
   try {
     return x_compress(D, dtype, shape, tol, s, mode, in, out, out_size, c,
                       output_pre_allocated, coords);
+  } catch (const std::exception &e) {
+    return fail(MGX_FAILURE, std::string("compress: ") + e.what());
+  } catch (...) {
+    return fail(MGX_FAILURE, "compress: unknown exception");
+  }
+}
+
+int mgx_x_compress_multi(int D, int dtype, const uint64_t *shape, double tol, double s,
+                         int mode, const void *in, void **out, size_t *out_size,
+                         const int *devices, int num_devices, const mgx_config *cfg,
+                         int output_pre_allocated) {
+  std::lock_guard<std::mutex> lock(g_mu);
+  mgx_config c;
+  if (cfg)
+    c = *cfg;
+  else
+    mgx_config_default(&c);
+  g_err.clear();
+  DeviceRestore restore;
+  try {
+    return x_compress_multi(D, dtype, shape, tol, s, mode, in, out, out_size, devices,
+                            num_devices, c, output_pre_allocated);
   } catch (const std::exception &e) {
     return fail(MGX_FAILURE, std::string("compress: ") + e.what());
   } catch (...) {

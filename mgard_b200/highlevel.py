@@ -89,6 +89,30 @@ def compress(data, tol, s, mode, config=None, out=None, coords=None):
     return out[:size.value]
 
 
+def compress_multi(data, tol, s, mode, devices, config=None):
+    """mgx_x_compress_multi: host array -> "MGARD" stream (numpy uint8), the MaxDim
+    subdomains compressed on the listed GPUs of this process, one host thread each."""
+    lib = _lib.load()
+    cfg = config if config is not None else Config()
+    data = np.ascontiguousarray(data)
+    shape = tuple(int(v) for v in data.shape)
+    D = len(shape)
+    shp = (ctypes.c_uint64 * max(D, 1))(*shape)
+    code = _dtype_code(data)
+    devs = (ctypes.c_int * len(devices))(*[int(d) for d in devices])
+    p = ctypes.c_void_p()
+    size = ctypes.c_size_t(0)
+    _check(lib.mgx_x_compress_multi(D, code, shp, float(tol), float(s), int(mode),
+                                    ctypes.c_void_p(data.ctypes.data), ctypes.byref(p),
+                                    ctypes.byref(size), devs, len(devices),
+                                    ctypes.byref(cfg), 0))
+    try:
+        return np.ctypeslib.as_array(
+            ctypes.cast(p, ctypes.POINTER(ctypes.c_uint8)), (size.value,)).copy()
+    finally:
+        ctypes.CDLL(None).free(p)
+
+
 def read_coords(stream):
     """node coordinates stored in a stream's header: list of float64 arrays, one per
     dimension, or None for a uniform grid"""
