@@ -1087,8 +1087,12 @@ __global__ void __launch_bounds__(128)
 // Multi-symbol prefix table: entry for a 12-bit window = up to four complete
 // codes found in it (smooth fields spend 1-2 bits on most symbols, so one
 // look-up usually yields 3-4 symbols).
-//   bits 0..3 total length, bits 4..6 count (0 = first code longer than the
-//   window), then four 13-bit symbols from bit 8 (dictionaries up to 8192).
+//   four 13-bit symbols in the low 13 bits of the four 16-bit fields (dictionaries
+//   up to 8192; unused fields are 0, so an entry can be OR-ed into a register of
+//   packed symbols as it is once its spare bits are masked off); spare bits:
+//   13..15 = total length bits 0..2, 29 = total length bit 3, 61..63 = count
+//   (0 = first code longer than the window).
+constexpr u64 MLUT_SYMS = 0x1fff1fff1fff1fffull;
 __global__ void __launch_bounds__(256)
     k_build_mlut(const uint32_t *__restrict__ lut1, u64 *__restrict__ mlut) {
   for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < (1u << LUT_BITS);
@@ -1101,12 +1105,17 @@ __global__ void __launch_bounds__(256)
       const uint32_t len = t >> 16;
       if (len == 0 || len > LUT_BITS - pos)
         break; // not fully inside the window
-      e |= (u64)(t & 0x1fffu) << (8 + 13 * cnt);
+      e |= (u64)(t & 0x1fffu) << (16 * cnt);
       pos += len;
       ++cnt;
     }
-    mlut[idx] = e | pos | ((u64)cnt << 4);
+    mlut[idx] = e | ((u64)(pos & 7u) << 13) | ((u64)((pos >> 3) & 1u) << 29) |
+                ((u64)cnt << 61);
   }
+}
+__device__ __forceinline__ uint32_t mlut_len(u64 e) {
+  const uint32_t lo = (uint32_t)e;
+  return ((lo >> 13) & 7u) | ((lo >> 26) & 8u);
 }
 
 #ifndef MGX_DEC_THREADS
@@ -1145,6 +1154,7 @@ template <int N> __device__ __forceinline__ void cp_async_wait() {
 // cp.async group counter is per warp too); the bit buffer refills 32 bits at a time
 // from that ring, up to four symbols come out of one
 // look-up, and symbols leave through a small per-thread ring as 16-byte stores.
+template <bool REGS>
 __global__ void __launch_bounds__(DEC_THREADS)
     k_decode_multi(const u64 *__restrict__ packed, const u64 *__restrict__ meta,
                    uint64_t nchunk, uint32_t chunk, uint64_t n,
@@ -1152,8 +1162,10 @@ __global__ void __launch_bounds__(DEC_THREADS)
                    uint16_t *__restrict__ sym, uint32_t dict) {
   __shared__ u64 mlut[1 << LUT_BITS];
   __shared__ u64 s_first[64], s_entry[64];
-  __shared__ __align__(8) uint16_t s_ring[DEC_THREADS * DEC_RING];
   __shared__ u64 s_words[DEC_SLOTS * DEC_THREADS]; // slot-major: lanes side by side
+  // REGS = false: symbols leave through a per-thread ring in shared memory
+  __shared__ __align__(8) uint16_t s_ring[REGS ? 4 : DEC_THREADS * DEC_RING];
+  uint16_t *ring = s_ring + (REGS ? 0 : threadIdx.x * DEC_RING);
   for (uint32_t i = threadIdx.x; i < (1u << LUT_BITS); i += blockDim.x)
     mlut[i] = g_mlut[i];
   if (threadIdx.x < 64) {
@@ -1162,7 +1174,6 @@ __global__ void __launch_bounds__(DEC_THREADS)
   }
   __syncthreads();
   const u64 *keys = db + 128;
-  uint16_t *ring = s_ring + threadIdx.x * DEC_RING;
   u64 *words = s_words + threadIdx.x;
   for (uint64_t c = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; c < nchunk;
        c += (uint64_t)gridDim.x * blockDim.x) {
@@ -1205,11 +1216,53 @@ __global__ void __launch_bounds__(DEC_THREADS)
     };
     prime(0, 0);
     uint32_t it = 0;
-    // two look-ups per iteration: with more than 32 bits in the buffer at the top,
+    // Two look-ups per iteration: with more than 32 bits in the buffer at the top,
     // both windows are complete (2 * LUT_BITS <= 32 - 8) and one 32-bit refill
-    // restores the invariant; the symbol ring takes up to 8 new entries on top of
-    // the up to 7 left by the last flush
+    // restores the invariant.  Two symbol sinks, chosen by the stream's bits per
+    // symbol (measured at 1025^3: 1.61 / 1.71 ms at 1.5 bits, 4.41 / 4.06 ms at 7.4):
+    // REGS: a0 | a1 hold the 8 symbols of the next 16-byte store, a2 what spills
+    // over; a look-up's four 16-bit fields are OR-ed in at symbol position k with
+    // two 64-bit shifts -- no shared-memory traffic for symbols (8 two-byte stores
+    // per iteration with bank conflicts otherwise), more ALU work;
+    // ring: 20 entries per thread in shared memory, flushed 8 at a time.
     uint32_t produced = 0, written = 0;
+    u64 a0 = 0, a1 = 0, a2 = 0;
+    auto insert = [&](u64 v, uint32_t k) { // k = 0..7 (REGS) / 0..11 (ring)
+      if constexpr (REGS) {
+        const uint32_t b = (k & 3u) << 4;
+        const u64 lo = v << b;
+        const u64 hi = (v >> 1) >> (63u - b);
+        if (k & 4u) {
+          a1 |= lo;
+          a2 |= hi;
+        } else {
+          a0 |= lo;
+          a1 |= hi;
+        }
+      } else {
+        uint16_t *r = ring + k;
+        r[0] = (uint16_t)v;
+        r[1] = (uint16_t)(v >> 16);
+        r[2] = (uint16_t)(v >> 32);
+        r[3] = (uint16_t)(v >> 48);
+      }
+    };
+    auto flush8 = [&]() {
+      if constexpr (REGS) {
+        *reinterpret_cast<uint4 *>(dst + written) = make_uint4(
+            (uint32_t)a0, (uint32_t)(a0 >> 32), (uint32_t)a1, (uint32_t)(a1 >> 32));
+        a0 = a2;
+        a1 = 0;
+        a2 = 0;
+      } else {
+        const uint2 x0 = *reinterpret_cast<const uint2 *>(ring);
+        const uint2 x1 = *reinterpret_cast<const uint2 *>(ring + 4);
+        *reinterpret_cast<uint4 *>(dst + written) = make_uint4(x0.x, x0.y, x1.x, x1.y);
+        *reinterpret_cast<uint2 *>(ring) = *reinterpret_cast<const uint2 *>(ring + 8);
+        *reinterpret_cast<uint2 *>(ring + 4) = *reinterpret_cast<const uint2 *>(ring + 12);
+      }
+      written += 8;
+    };
     while (produced < count) {
       if ((it++ & (DEC_PERIOD / 2 - 1)) == 0) {
         cp_async_wait<0>();
@@ -1220,8 +1273,7 @@ __global__ void __launch_bounds__(DEC_THREADS)
         cp_async_commit();
       }
       const u64 e1 = mlut[(uint32_t)(buf >> (64 - LUT_BITS))];
-      const uint32_t c1 = (uint32_t)(e1 >> 4) & 7u, len1 = (uint32_t)e1 & 15u;
-      uint16_t *r = ring + (produced - written);
+      const uint32_t c1 = (uint32_t)(e1 >> 61), len1 = mlut_len(e1);
       if (__builtin_expect(c1 == 0, 0)) {
         // first code is longer than the window: canonical search on the raw
         // words (Decode.hpp:60-66), then re-prime the bit buffer
@@ -1236,26 +1288,23 @@ __global__ void __launch_bounds__(DEC_THREADS)
           ++l;
           v = window >> (64 - l);
         } while (v < s_first[l] && l < 63);
-        r[0] = (uint16_t)keys[min(s_entry[l] + v - s_first[l], (u64)dict - 1)];
+        insert(keys[min(s_entry[l] + v - s_first[l], (u64)dict - 1)] & 0xffffu,
+               produced - written);
         ++produced;
         pos += l;
         prime((uint32_t)(pos >> 6), (uint32_t)(pos & 63));
       } else {
         const u64 b2 = buf << len1;
         const u64 e2 = mlut[(uint32_t)(b2 >> (64 - LUT_BITS))];
-        r[0] = (uint16_t)((e1 >> 8) & 0x1fff);
-        r[1] = (uint16_t)((e1 >> 21) & 0x1fff);
-        r[2] = (uint16_t)((e1 >> 34) & 0x1fff);
-        r[3] = (uint16_t)((e1 >> 47) & 0x1fff);
+        insert(e1 & MLUT_SYMS, produced - written);
+        produced += c1;
+        if (REGS && produced - written >= 8)
+          flush8(); // three registers hold 12 symbols, the ring 20
         // a second window that starts with a long code has count 0 and length 0:
         // nothing is consumed and the next iteration takes the branch above
-        const uint32_t c2 = (uint32_t)(e2 >> 4) & 7u, len2 = (uint32_t)e2 & 15u;
-        r += c1;
-        r[0] = (uint16_t)((e2 >> 8) & 0x1fff);
-        r[1] = (uint16_t)((e2 >> 21) & 0x1fff);
-        r[2] = (uint16_t)((e2 >> 34) & 0x1fff);
-        r[3] = (uint16_t)((e2 >> 47) & 0x1fff);
-        produced = min(produced + c1 + c2, count);
+        const uint32_t c2 = (uint32_t)(e2 >> 61), len2 = mlut_len(e2);
+        insert(e2 & MLUT_SYMS, produced - written);
+        produced = min(produced + c2, count);
         buf = b2 << len2;
         nbits -= len1 + len2;
       }
@@ -1264,18 +1313,13 @@ __global__ void __launch_bounds__(DEC_THREADS)
         nbits += 32;
         ++unit;
       }
-      if (produced - written >= 8) {
-        const uint2 a0 = *reinterpret_cast<const uint2 *>(ring);
-        const uint2 a1 = *reinterpret_cast<const uint2 *>(ring + 4);
-        *reinterpret_cast<uint4 *>(dst + written) = make_uint4(a0.x, a0.y, a1.x, a1.y);
-        *reinterpret_cast<uint2 *>(ring) = *reinterpret_cast<const uint2 *>(ring + 8);
-        *reinterpret_cast<uint2 *>(ring + 4) = *reinterpret_cast<const uint2 *>(ring + 12);
-        written += 8;
-      }
+      if (produced - written >= 8)
+        flush8();
     }
     for (uint32_t j = 0; written + j < produced; j++)
-      dst[written + j] = ring[j];
-    cp_async_wait<0>(); // the ring is reused by this thread's next chunk
+      dst[written + j] = REGS ? (uint16_t)((j < 4 ? a0 >> (16 * j) : a1 >> (16 * (j - 4))))
+                              : ring[j];
+    cp_async_wait<0>(); // the word ring is reused by this thread's next chunk
   }
 }
 
@@ -1484,8 +1528,12 @@ int mgxk_decode_container(mgx_ctx *ctx, const uint8_t *d_in, uint64_t bytes,
   if (p.dict <= 8192 && p.chunk % 8 == 0) {
     u64 *mlut = (u64 *)((uint8_t *)ctx->d_lut + 4096 * 4);
     k_build_mlut<<<16, 256, 0, ctx->stream>>>((const uint32_t *)ctx->d_lut, mlut);
-    k_decode_multi<<<mgx_grid_for(p.nchunk, DEC_THREADS, ctx->num_sms * 16),
-                     DEC_THREADS, 0, ctx->stream>>>(
+    // symbol sink by the stream's density: above ~3 bits per symbol the look-ups
+    // yield few symbols each and the shared-memory ring costs more than it saves
+    const bool regs = p.ddata * 64 > p.n * 3;
+    auto kern = regs ? k_decode_multi<true> : k_decode_multi<false>;
+    kern<<<mgx_grid_for(p.nchunk, DEC_THREADS, ctx->num_sms * 16), DEC_THREADS, 0,
+           ctx->stream>>>(
         (const u64 *)(d_in + p.off_packed), (const u64 *)(d_in + p.off_meta),
         p.nchunk, (uint32_t)p.chunk, p.n, db, mlut, ctx->d_sym, (uint32_t)p.dict);
     ctx->launches += 3;
