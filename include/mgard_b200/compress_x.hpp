@@ -7,9 +7,9 @@
 // links -lmgard_b200.
 //
 // Served: uniform Cartesian grids, D <= 5, float / double, REL / ABS,
-// L-inf / L2 / s-norm, Huffman lossless, MultiDim decomposition, MaxDim domain
-// decomposition, host or device buffers.  Anything else a Config can ask for
-// (Huffman_Zstd / LZ4, SingleDim / Hybrid, Block / Variable,
+// L-inf / L2 / s-norm, Huffman lossless, MultiDim decomposition, MaxDim and Block
+// domain decomposition, host or device buffers.  Anything else a Config can ask for
+// (Huffman_Zstd / LZ4, SingleDim / Hybrid, Variable,
 // ZFP, CPU back ends) is answered with the reference's failure codes -- there
 // is no CPU fallback.
 #ifndef MGARD_B200_COMPRESS_X_HPP
@@ -115,6 +115,7 @@ inline mgx_config to_c(const Config &c) {
   m.log_level = c.log_level;
   m.max_larget_level = c.max_larget_level;
   m.max_memory_footprint = c.max_memory_footprint;
+  m.block_size = c.block_size;
   return m;
 }
 inline compress_status_type status(int rc) {

@@ -67,7 +67,7 @@ enum mgx_decomp_type { MGX_DC_MULTIDIM = 0, MGX_DC_SINGLEDIM = 1, MGX_DC_HYBRID 
 typedef struct mgx_config {
   int dev_type;                  /* mgx_device_type; AUTO and CUDA are served */
   int dev_id;
-  int domain_decomposition;      /* mgx_dd_type; MaxDim only                  */
+  int domain_decomposition;      /* mgx_dd_type; MaxDim or Block              */
   int decomposition;             /* mgx_decomp_type; MultiDim only            */
   int lossless;                  /* mgx_lossless; Huffman only                */
   uint32_t huff_dict_size;       /* 8192                                      */
@@ -81,6 +81,7 @@ typedef struct mgx_config {
   int log_level;
   uint64_t max_larget_level;     /* UINT64_MAX = no limit                     */
   uint64_t max_memory_footprint; /* UINT64_MAX = no limit (bytes)             */
+  uint64_t block_size;           /* Block decomposition: edge of a block (256) */
 } mgx_config;
 
 void mgx_config_default(mgx_config *cfg); /* Config::Config(), Config.cpp:31-66 */

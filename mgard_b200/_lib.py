@@ -28,7 +28,7 @@ class MgxConfig(ctypes.Structure):
                 ("auto_pin_host_buffers", c_int),
                 ("compress_with_dryrun", c_int), ("auto_cache_release", c_int),
                 ("log_level", c_int), ("max_larget_level", c_u64),
-                ("max_memory_footprint", c_u64)]
+                ("max_memory_footprint", c_u64), ("block_size", c_u64)]
 
 
 class MgxMetadata(ctypes.Structure):

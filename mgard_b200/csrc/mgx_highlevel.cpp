@@ -716,12 +716,13 @@ int cache_ctx(DeviceCache &c, int D, const uint64_t *shape, int dtype,
 // first row (DomainDecomposer.hpp:259-289)
 struct SubCoords {
   const void *p[5];
-  const void *const *get(const void *const *coords, int D, int dim, uint64_t off,
+  // offs: first node of the subdomain per dimension
+  const void *const *get(const void *const *coords, int D, const uint64_t *offs,
                          size_t es) {
     if (!coords)
       return nullptr;
     for (int d = 0; d < D; d++)
-      p[d] = d == dim ? (const void *)((const char *)coords[d] + off * es) : coords[d];
+      p[d] = (const void *)((const char *)coords[d] + offs[d] * es);
     return p;
   }
 };
@@ -744,35 +745,65 @@ struct Slabs {
   uint64_t shape[5] = {};
   size_t es = 4;
   bool decomposed = false;
+  int type = MGX_DD_MAXDIM; // MGX_DD_MAXDIM: slabs along `dim`; MGX_DD_BLOCK: cubes
   int dim = 0;
-  uint64_t size = 0, num = 1;
-  uint64_t outer = 1, inner = 1; // products of the dims before / after `dim`
+  uint64_t size = 0, num = 1; // rows per slab / edge of a block; subdomain count
+  uint64_t outer = 1, inner = 1; // MaxDim: products of the dims before / after `dim`
+  uint64_t nb[5] = {1, 1, 1, 1, 1}; // Block: blocks per dimension
 
+  bool block() const { return decomposed && type == MGX_DD_BLOCK; }
   void finish() {
     outer = inner = 1;
+    if (block()) {
+      num = 1;
+      for (int d = 0; d < D; d++) {
+        nb[d] = (shape[d] - 1) / size + 1;
+        num *= nb[d];
+      }
+      return;
+    }
     for (int d = 0; d < dim; d++)
       outer *= shape[d];
     for (int d = dim + 1; d < D; d++)
       inner *= shape[d];
   }
-  void sub_shape(uint64_t id, uint64_t *out, uint64_t *off) const {
-    if (!decomposed) {
-      for (int d = 0; d < D; d++)
-        out[d] = shape[d];
-      *off = 0;
+  // shape of subdomain `id` and its offset per dimension
+  // (DomainDecomposer::subdomain_shape / dim_subdomain_offset, :95-160)
+  void sub_box(uint64_t id, uint64_t *out, uint64_t *offs) const {
+    for (int d = 0; d < D; d++) {
+      out[d] = shape[d];
+      offs[d] = 0;
+    }
+    if (!decomposed)
+      return;
+    if (block()) {
+      for (int d = D - 1; d >= 0; d--) { // last dimension fastest
+        const uint64_t bid = id % nb[d];
+        id /= nb[d];
+        offs[d] = bid * size;
+        out[d] = bid < shape[d] / size ? size : shape[d] % size;
+      }
       return;
     }
-    mgx_subdomain_shape(D, shape, dim, size, id, out, off);
+    uint64_t off = 0;
+    mgx_subdomain_shape(D, shape, dim, size, id, out, &off);
+    offs[dim] = off;
+  }
+  // MaxDim view: row offset along `dim`
+  void sub_shape(uint64_t id, uint64_t *out, uint64_t *off) const {
+    uint64_t offs[5];
+    sub_box(id, out, offs);
+    *off = block() ? 0 : offs[dim];
   }
   uint64_t elems(uint64_t id) const {
-    uint64_t s[5], off, n = 1;
-    sub_shape(id, s, &off);
+    uint64_t s[5], offs[5], n = 1;
+    sub_box(id, s, offs);
     for (int d = 0; d < D; d++)
       n *= s[d];
     return n;
   }
-  // a slab is one contiguous range of the dense array
-  bool contiguous() const { return !decomposed || outer == 1; }
+  // a subdomain is one contiguous range of the dense array
+  bool contiguous() const { return !decomposed || (!block() && outer == 1); }
 };
 
 // DomainDecomposer::copy_subdomain (DomainDecomposer.hpp:628-820) for MaxDim:
@@ -780,6 +811,43 @@ struct Slabs {
 // or device memory.
 int copy_slab(const Slabs &sl, uint64_t id, void *slab, void *whole, bool to_slab,
               cudaStream_t stream) {
+  if (sl.block()) {
+    // a D-dimensional box: one pitched copy per index of the dimensions before the
+    // last two (DomainDecomposer.hpp:714-790)
+    uint64_t b[5], o[5];
+    sl.sub_box(id, b, o);
+    const int D = sl.D;
+    const size_t width = (size_t)b[D - 1] * sl.es;
+    const size_t pitch = (size_t)sl.shape[D - 1] * sl.es;
+    const uint64_t rows = D >= 2 ? b[D - 2] : 1;
+    uint64_t planes = 1;
+    for (int d = 0; d + 2 < D; d++)
+      planes *= b[d];
+    for (uint64_t p = 0; p < planes; p++) {
+      // multi-index of plane p over dims 0 .. D-3, row-major
+      uint64_t rem = p, woff = 0;
+      uint64_t idxs[5] = {0, 0, 0, 0, 0};
+      for (int d = D - 3; d >= 0; d--) {
+        idxs[d] = rem % b[d];
+        rem /= b[d];
+      }
+      uint64_t st = 1;
+      for (int d = D - 1; d >= 0; d--) {
+        const uint64_t i = o[d] + (d + 2 < D ? idxs[d] : 0);
+        woff += i * st;
+        st *= sl.shape[d];
+      }
+      char *w = (char *)whole + (size_t)woff * sl.es;
+      char *a = (char *)slab + (size_t)p * rows * width;
+      if (to_slab)
+        X_CUDA(cudaMemcpy2DAsync(a, width, w, pitch, width, rows, cudaMemcpyDefault,
+                                 stream));
+      else
+        X_CUDA(cudaMemcpy2DAsync(w, pitch, a, width, width, rows, cudaMemcpyDefault,
+                                 stream));
+    }
+    return MGX_SUCCESS;
+  }
   uint64_t s[5], off;
   sl.sub_shape(id, s, &off);
   const size_t width = (size_t)s[sl.dim] * sl.inner * sl.es;
@@ -844,11 +912,42 @@ uint64_t footprint(int D, const uint64_t *shape, int dtype, double s, int prefet
 }
 
 int decide_slabs(int D, const uint64_t *shape, int dtype, double s,
-                 uint64_t available, Slabs *sl) {
+                 uint64_t available, Slabs *sl, const mgx_config *cfg = nullptr) {
   sl->D = D;
   sl->es = dtype == MGX_F64 ? 8 : 4;
   for (int d = 0; d < D; d++)
     sl->shape[d] = shape[d];
+  if (cfg && cfg->domain_decomposition == MGX_DD_BLOCK) {
+    // generate_block_domain_decomposition_strategy (DomainDecomposer.hpp:226-251):
+    // cubes of Config::block_size, halved (rounding up) until one fits the device
+    uint64_t size = cfg->block_size ? cfg->block_size : 256;
+    for (;;) {
+      uint64_t chunk[5], n = 1;
+      for (int d = 0; d < D; d++) {
+        chunk[d] = size;
+        n *= (shape[d] - 1) / size + 1;
+      }
+      if (footprint(D, chunk, dtype, s, n > 1) < available)
+        break;
+      if (size <= 1)
+        return fail(MGX_FAILURE, "dataset cannot be decomposed to fit the device");
+      size = (size - 1) / 2 + 1;
+    }
+    sl->decomposed = true;
+    sl->type = MGX_DD_BLOCK;
+    sl->dim = 0;
+    sl->size = size;
+    sl->finish();
+    for (uint64_t i = 0; i < sl->num; i++) {
+      uint64_t b[5], o[5];
+      sl->sub_box(i, b, o);
+      for (int d = 0; d < D; d++)
+        if (b[d] < 3)
+          return fail(MGX_FAILURE, "block decomposition leaves a block with fewer "
+                                   "than 3 nodes along a dimension");
+    }
+    return MGX_SUCCESS;
+  }
   int dec = 0, dim = 0;
   uint64_t size = 0, num = 1;
   int rc = mgx_max_dim_by_memory(D, shape, dtype, s, available, &dec, &dim, &size, &num);
@@ -870,8 +969,9 @@ int check_config(const mgx_config &cfg) {
     return fail(MGX_FAILURE, "lossless type not supported: Huffman only");
   if (cfg.decomposition != MGX_DC_MULTIDIM)
     return fail(MGX_FAILURE, "decomposition type not supported: MultiDim only");
-  if (cfg.domain_decomposition != MGX_DD_MAXDIM)
-    return fail(MGX_FAILURE, "domain decomposition not supported: MaxDim only");
+  if (cfg.domain_decomposition != MGX_DD_MAXDIM &&
+      cfg.domain_decomposition != MGX_DD_BLOCK)
+    return fail(MGX_FAILURE, "domain decomposition not supported: MaxDim and Block only");
   // GPUPipelines.hpp:198-202, Compressor.hpp:239-242: the reference then also
   // decompresses and writes the reconstruction over the caller's INPUT array
   if (cfg.compress_with_dryrun)
@@ -933,7 +1033,7 @@ int x_compress(int D, int dtype, const uint64_t *shape, double tol, double s,
   DeviceCache &c = *cp;
 
   Slabs sl;
-  rc = decide_slabs(D, shape, dtype, sT, available_bytes(c, cfg), &sl);
+  rc = decide_slabs(D, shape, dtype, sT, available_bytes(c, cfg), &sl, &cfg);
   if (rc)
     return rc;
 
@@ -990,7 +1090,7 @@ int x_compress(int D, int dtype, const uint64_t *shape, double tol, double s,
   md.tol = tolT;
   md.norm = 1;
   md.decomposed = sl.decomposed;
-  md.dd_type = MGX_DD_MAXDIM;
+  md.dd_type = sl.type;
   md.dd_dim = sl.dim;
   md.dd_size = sl.decomposed ? sl.size : shape[0];
   md.decomposition = MGX_DC_MULTIDIM;
@@ -1068,10 +1168,12 @@ int x_compress(int D, int dtype, const uint64_t *shape, double tol, double s,
           return rc;
         uint64_t sh[5], off;
         sl.sub_shape(i, sh, &off);
+    uint64_t offs[5];
+    sl.sub_box(i, sh, offs);
         mgx_ctx *ctx;
         SubCoords sc;
         if ((rc = cache_ctx(c, D, sh, dtype, cfg, &ctx,
-                            sc.get(coords, D, sl.decomposed ? sl.dim : -1, off, es))))
+                            sc.get(coords, D, offs, es))))
           return rc;
         if (!in_place)
           X_CUDA(cudaStreamWaitEvent(c.compute, c.ev_in[b], 0));
@@ -1099,11 +1201,13 @@ int x_compress(int D, int dtype, const uint64_t *shape, double tol, double s,
       return rc;
     uint64_t sh[5], off;
     sl.sub_shape(i, sh, &off);
+    uint64_t offs[5];
+    sl.sub_box(i, sh, offs);
     const uint64_t n_sub = sl.elems(i);
     mgx_ctx *ctx;
     SubCoords sc;
     if ((rc = cache_ctx(c, D, sh, dtype, cfg, &ctx,
-                        sc.get(coords, D, sl.decomposed ? sl.dim : -1, off, es))))
+                        sc.get(coords, D, offs, es))))
       return rc;
     if (!in_place)
       X_CUDA(cudaStreamWaitEvent(c.compute, c.ev_in[b], 0));
@@ -1334,6 +1438,8 @@ int x_compress_multi(int D, int dtype, const uint64_t *shape, double tol, double
     return rc;
   if (locate(in).device)
     return fail(MGX_FAILURE, "mgx_x_compress_multi takes host buffers");
+  if (cfg.domain_decomposition != MGX_DD_MAXDIM)
+    return fail(MGX_FAILURE, "mgx_x_compress_multi: MaxDim decomposition only");
   for (int a = 0; a < ndev; a++)
     for (int b = a + 1; b < ndev; b++)
       if (devices[a] == devices[b])
@@ -1633,15 +1739,25 @@ int x_decompress(const void *in, size_t in_size, void **out, uint64_t *shape_out
     sl.shape[d] = md.shape[d];
   sl.decomposed = md.decomposed != 0;
   if (sl.decomposed) {
-    if (md.dd_type != MGX_DD_MAXDIM || md.dd_dim >= (uint32_t)D || md.dd_size == 0)
+    if ((md.dd_type != MGX_DD_MAXDIM && md.dd_type != MGX_DD_BLOCK) ||
+        md.dd_dim >= (uint32_t)D || md.dd_size == 0)
       return fail(MGX_FAILURE, "bad domain decomposition in the header");
+    sl.type = md.dd_type;
     sl.dim = (int)md.dd_dim;
     sl.size = md.dd_size;
     sl.num = (md.shape[sl.dim] - 1) / sl.size + 1;
-    if (sl.num > in_size / 8) // every subdomain record starts with an 8-byte size
-      return fail(MGX_FAILURE, "more subdomains in the header than the stream can hold");
   }
   sl.finish();
+  if (sl.decomposed && sl.num > in_size / 8) // a record starts with an 8-byte size
+    return fail(MGX_FAILURE, "more subdomains in the header than the stream can hold");
+  if (sl.block())
+    for (uint64_t i = 0; i < sl.num; i++) {
+      uint64_t b[5], o[5];
+      sl.sub_box(i, b, o);
+      for (int d = 0; d < D; d++)
+        if (b[d] < 3)
+          return fail(MGX_FAILURE, "bad block decomposition in the header");
+    }
 
   const int rel = md.mode == MGX_EB_REL;
   const double sT = dtype == MGX_F32 ? (double)(float)md.s : md.s;
@@ -1706,6 +1822,8 @@ int x_decompress(const void *in, size_t in_size, void **out, uint64_t *shape_out
       return rc;
     uint64_t sh[5], off;
     sl.sub_shape(i, sh, &off);
+    uint64_t offs[5];
+    sl.sub_box(i, sh, offs);
     const uint64_t n_sub = sl.elems(i);
     void *d_out = in_place ? (void *)((char *)*out + (size_t)off * sl.inner * es)
                            : c.sub[b];
@@ -1719,7 +1837,7 @@ int x_decompress(const void *in, size_t in_size, void **out, uint64_t *shape_out
       mgx_ctx *ctx;
       SubCoords sc;
       if ((rc = cache_ctx(c, D, sh, dtype, cfg, &ctx,
-                          sc.get(coords, D, sl.decomposed ? sl.dim : -1, off, es))))
+                          sc.get(coords, D, offs, es))))
         return rc;
       rc = mgx_decompress(ctx, (const uint8_t *)c.cbuf[b], rec_bytes[i], local_rel,
                           local_tol, sT, normT, d_out);
@@ -1779,6 +1897,7 @@ void mgx_config_default(mgx_config *cfg) {
   cfg->normalize_coordinates = 1;
   cfg->auto_pin_host_buffers = 1;
   cfg->compress_with_dryrun = 0;
+  cfg->block_size = 256;
   cfg->auto_cache_release = 0;
   cfg->log_level = 1;
   cfg->max_larget_level = std::numeric_limits<uint64_t>::max();

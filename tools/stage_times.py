@@ -47,13 +47,19 @@ def main():
     ap.add_argument("--s", type=float, default=float("inf"))
     ap.add_argument("--tol", type=float, default=1e-3)
     ap.add_argument("--abs", action="store_true")
+    ap.add_argument("--field", default="smooth", choices=["smooth", "nyx"],
+                    help="nyx: bench.py's NYX-shaped generator (3-D only)")
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=2)
     a = ap.parse_args()
     dt = torch.float32 if a.dtype == "f32" else torch.float64
     shape = tuple(a.shape)
     dev = torch.device("cuda", 0)
-    u = field(shape, dt, dev)
+    if a.field == "nyx":
+        import bench
+        u = bench.gen_block("nyx", shape, dt, dev)
+    else:
+        u = field(shape, dt, dev)
     comp = mg.Compressor(mg.Hierarchy(shape, dt))
     comp.set_timing(True)
     eb = mg.ABS if a.abs else mg.REL
