@@ -127,6 +127,15 @@ int mgx_x_compress_multi(int D, int dtype, const uint64_t *shape, double tol, do
                          const int *devices, int num_devices, const mgx_config *cfg,
                          int output_pre_allocated);
 
+/* decompress on SEVERAL GPUs of this process (counterpart of mgx_x_compress_multi):
+ * devices[k] decodes the k-th contiguous block of subdomain records of a
+ * domain-decomposed stream on its own host thread, straight into the caller's host
+ * array.  `in` and `*out` are HOST buffers. */
+int mgx_x_decompress_multi(const void *in, size_t in_size, void **out,
+                           uint64_t *shape_out, int *D_out, int *dtype_out,
+                           const int *devices, int num_devices, const mgx_config *cfg,
+                           int output_pre_allocated);
+
 int mgx_x_decompress(const void *in, size_t in_size, void **out,
                      uint64_t *shape_out, int *D_out, int *dtype_out,
                      const mgx_config *cfg, int output_pre_allocated);

@@ -63,6 +63,10 @@ SIGNATURES = {
     "mgx_x_compress_multi": (c_int, [c_int, c_int, ctypes.POINTER(c_u64), c_dbl, c_dbl,
                                      c_int, c_vp, ctypes.POINTER(c_vp), _szp,
                                      ctypes.POINTER(c_int), c_int, _cfgp, c_int]),
+    "mgx_x_decompress_multi": (c_int, [c_vp, ctypes.c_size_t, ctypes.POINTER(c_vp),
+                                       ctypes.POINTER(c_u64), ctypes.POINTER(c_int),
+                                       ctypes.POINTER(c_int), ctypes.POINTER(c_int),
+                                       c_int, _cfgp, c_int]),
     "mgx_x_decompress": (c_int, [c_vp, ctypes.c_size_t, ctypes.POINTER(c_vp),
                                  ctypes.POINTER(c_u64), ctypes.POINTER(c_int),
                                  ctypes.POINTER(c_int), _cfgp, c_int]),

@@ -1601,8 +1601,11 @@ int fetch_header(const void *in, size_t in_size, const PtrLoc &loc,
   return MGX_SUCCESS;
 }
 
+// rec_lo / rec_hi: only the subdomain records [rec_lo, rec_hi) are decoded (the
+// several-GPU entry hands every device its block of records)
 int x_decompress(const void *in, size_t in_size, void **out, uint64_t *shape_out,
-                 int *D_out, int *dtype_out, const mgx_config &cfg_in, int prealloc) {
+                 int *D_out, int *dtype_out, const mgx_config &cfg_in, int prealloc,
+                 uint64_t rec_lo = 0, uint64_t rec_hi = ~0ull) {
   if (!in || !out)
     return fail(MGX_FAILURE, "bad argument");
   if (cfg_in.dev_type != MGX_DEV_AUTO && cfg_in.dev_type != MGX_DEV_CUDA)
@@ -1814,11 +1817,13 @@ int x_decompress(const void *in, size_t in_size, void **out, uint64_t *shape_out
     return MGX_SUCCESS;
   };
 
-  if ((rc = fetch(0, 0)))
+  const uint64_t first = std::min<uint64_t>(rec_lo, sl.num),
+                 last = std::min<uint64_t>(rec_hi, sl.num);
+  if (first < last && (rc = fetch(first, 0)))
     return rc;
-  for (uint64_t i = 0; i < sl.num; i++) {
-    const int b = (int)(i & 1);
-    if (i + 1 < sl.num && (rc = fetch(i + 1, b ^ 1)))
+  for (uint64_t i = first; i < last; i++) {
+    const int b = (int)((i - first) & 1);
+    if (i + 1 < last && (rc = fetch(i + 1, b ^ 1)))
       return rc;
     uint64_t sh[5], off;
     sl.sub_shape(i, sh, &off);
@@ -1863,6 +1868,104 @@ int x_decompress(const void *in, size_t in_size, void **out, uint64_t *shape_out
   guard.armed = false;
   if (cfg.auto_cache_release)
     cache_release(c);
+  return MGX_SUCCESS;
+}
+
+// decompress on several GPUs of one process: devices[k] decodes the k-th contiguous
+// block of subdomain records on its own host thread, straight into the caller's host
+// array (the counterpart of x_compress_multi; any stream with a domain decomposition)
+int x_decompress_multi(const void *in, size_t in_size, void **out, uint64_t *shape_out,
+                       int *D_out, int *dtype_out, const int *devices, int ndev,
+                       const mgx_config &cfg, int prealloc) {
+  if (!in || !out || !devices || ndev < 1 || ndev > 64)
+    return fail(MGX_FAILURE, "bad argument");
+  if (locate(in).device)
+    return fail(MGX_FAILURE, "mgx_x_decompress_multi takes host buffers");
+  for (int a = 0; a < ndev; a++)
+    for (int b = a + 1; b < ndev; b++)
+      if (devices[a] == devices[b])
+        return fail(MGX_FAILURE, "a device is listed twice");
+  mgx_metadata md;
+  uint64_t M = 0;
+  int rc = mgx_metadata_parse((const uint8_t *)in, in_size, &md, &M);
+  if (rc)
+    return rc;
+  if (md.D < 1 || md.D > 5)
+    return fail(MGX_FAILURE, "bad shape in the header");
+  const size_t es = md.dtype == MGX_F64 ? 8 : 4;
+  uint64_t N = 1, num = 1;
+  for (uint32_t d = 0; d < md.D; d++) {
+    if (md.shape[d] == 0 || md.shape[d] > (~0ull / es) / N)
+      return fail(MGX_FAILURE, "bad shape in the header");
+    N *= md.shape[d];
+  }
+  if (md.decomposed) {
+    if (md.dd_size == 0 || md.dd_dim >= md.D)
+      return fail(MGX_FAILURE, "bad domain decomposition in the header");
+    if (md.dd_type == MGX_DD_BLOCK) {
+      for (uint32_t d = 0; d < md.D; d++)
+        num *= (md.shape[d] - 1) / md.dd_size + 1;
+    } else {
+      num = (md.shape[md.dd_dim] - 1) / md.dd_size + 1;
+    }
+  }
+  bool allocated_here = false;
+  if (!prealloc) {
+    *out = malloc(N * es);
+    if (!*out)
+      return fail(MGX_FAILURE, "out of host memory");
+    allocated_here = true;
+  } else if (!*out) {
+    return fail(MGX_FAILURE, "output_pre_allocated without a buffer");
+  }
+  std::vector<DeviceCache *> caches(ndev);
+  for (int k = 0; k < ndev; k++)
+    if ((rc = cache_get(devices[k], &caches[k]))) {
+      if (allocated_here) {
+        free(*out);
+        *out = nullptr;
+      }
+      return rc;
+    }
+  ScopedPin pin_in, pin_out; // once, here: the workers must not unpin under each other
+  pin_in.pin(in, in_size, cfg.auto_pin_host_buffers);
+  pin_out.pin(*out, N * es, cfg.auto_pin_host_buffers);
+  const uint64_t per = (num + ndev - 1) / ndev;
+  std::vector<int> rcs(ndev, 0);
+  {
+    std::vector<std::thread> th;
+    for (int k = 0; k < ndev; k++) {
+      const uint64_t lo = std::min<uint64_t>((uint64_t)k * per, num),
+                     hi = std::min<uint64_t>(lo + per, num);
+      if (lo >= hi)
+        continue;
+      th.emplace_back([&, k, lo, hi]() {
+        mgx_config c = cfg;
+        c.dev_id = devices[k];
+        c.auto_pin_host_buffers = 0;
+        c.auto_cache_release = 0;
+        void *o = *out;
+        rcs[k] = x_decompress(in, in_size, &o, nullptr, nullptr, nullptr, c, 1, lo, hi);
+      });
+    }
+    for (auto &t : th)
+      t.join();
+  }
+  for (int k = 0; k < ndev; k++)
+    if (rcs[k]) {
+      if (allocated_here) {
+        free(*out);
+        *out = nullptr;
+      }
+      return rcs[k]; // the message of the (last) failing worker is in g_err
+    }
+  if (shape_out)
+    for (uint32_t d = 0; d < md.D; d++)
+      shape_out[d] = md.shape[d];
+  if (D_out)
+    *D_out = (int)md.D;
+  if (dtype_out)
+    *dtype_out = md.dtype;
   return MGX_SUCCESS;
 }
 
@@ -2110,6 +2213,28 @@ int mgx_x_compress_multi(int D, int dtype, const uint64_t *shape, double tol, do
     return fail(MGX_FAILURE, std::string("compress: ") + e.what());
   } catch (...) {
     return fail(MGX_FAILURE, "compress: unknown exception");
+  }
+}
+
+int mgx_x_decompress_multi(const void *in, size_t in_size, void **out,
+                           uint64_t *shape_out, int *D_out, int *dtype_out,
+                           const int *devices, int num_devices, const mgx_config *cfg,
+                           int output_pre_allocated) {
+  std::lock_guard<std::mutex> lock(g_mu);
+  mgx_config c;
+  if (cfg)
+    c = *cfg;
+  else
+    mgx_config_default(&c);
+  g_err.clear();
+  DeviceRestore restore;
+  try {
+    return x_decompress_multi(in, in_size, out, shape_out, D_out, dtype_out, devices,
+                              num_devices, c, output_pre_allocated);
+  } catch (const std::exception &e) {
+    return fail(MGX_FAILURE, std::string("decompress: ") + e.what());
+  } catch (...) {
+    return fail(MGX_FAILURE, "decompress: unknown exception");
   }
 }
 

@@ -113,6 +113,23 @@ def compress_multi(data, tol, s, mode, devices, config=None):
         ctypes.CDLL(None).free(p)
 
 
+def decompress_multi(stream, devices, config=None):
+    """mgx_x_decompress_multi: host stream -> numpy array, the subdomain records
+    decoded on the listed GPUs of this process, one host thread each."""
+    lib = _lib.load()
+    cfg = config if config is not None else Config()
+    stream = np.ascontiguousarray(stream)
+    md, _ = read_metadata(bytes(stream[:min(stream.size, 1 << 26)]))
+    shape = tuple(int(md.shape[d]) for d in range(md.D))
+    out = np.empty(shape, dtype=np.float64 if md.dtype == 1 else np.float32)
+    devs = (ctypes.c_int * len(devices))(*[int(d) for d in devices])
+    p = ctypes.c_void_p(out.ctypes.data)
+    _check(lib.mgx_x_decompress_multi(ctypes.c_void_p(stream.ctypes.data), stream.size,
+                                      ctypes.byref(p), None, None, None, devs,
+                                      len(devices), ctypes.byref(cfg), 1))
+    return out
+
+
 def read_coords(stream):
     """node coordinates stored in a stream's header: list of float64 arrays, one per
     dimension, or None for a uniform grid"""

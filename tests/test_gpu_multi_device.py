@@ -35,6 +35,15 @@ def test_one_device_equals_the_plain_call(shape, dtype, s, tol, mode):
     a = hl.compress_multi(u, tol, s, mode, [0])
     b = np.asarray(hl.compress(u, tol, s, mode))
     assert a.size == b.size and np.array_equal(a, b)
+    assert np.array_equal(hl.decompress_multi(a, [0]), hl.decompress(b))
+
+
+def test_one_device_decodes_a_decomposed_stream_like_the_plain_call():
+    u = smooth_field((70, 20, 24), np.float32, seed=4)
+    stream = np.asarray(_single_call_with_slabs(u, 1e-3, INF, hl.REL, 18, 0))
+    md, _ = hl.read_metadata(bytes(stream[:4096]))
+    assert md.decomposed
+    assert np.array_equal(hl.decompress_multi(stream, [0]), hl.decompress(stream))
 
 
 @pytest.mark.parametrize("shape,dtype,s,tol,mode", [
@@ -54,6 +63,9 @@ def test_two_devices_equal_the_single_call_stream(shape, dtype, s, tol, mode):
                                                 int(md.dd_dim)))
     assert multi.size == single.size and np.array_equal(multi, single)
     back = hl.decompress(multi)
+    # the records decoded on two devices, one host thread each: the same array
+    assert np.array_equal(hl.decompress_multi(multi, [0, 1]), back)
+    assert np.array_equal(hl.decompress_multi(multi, [1]), back)
     err = back.astype(np.float64) - u
     bound = tol * (md.norm if mode == hl.REL else 1.0)
     assert (np.abs(err).max() if np.isinf(s) else np.sqrt((err ** 2).mean())) <= bound
