@@ -16,7 +16,10 @@
 
 namespace {
 
-constexpr int CB_THREADS = 1024;
+#ifndef MGX_CB_THREADS
+#define MGX_CB_THREADS 1024
+#endif
+constexpr int CB_THREADS = MGX_CB_THREADS;
 constexpr int CB_WARPS = CB_THREADS / 32;
 
 struct CbState {
