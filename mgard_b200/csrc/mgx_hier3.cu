@@ -118,6 +118,7 @@ template <typename T> struct F3Args {
   uint32_t sby, sbz;    // super blocks (8 x 8 tiles in y, z)
   uint64_t padded;      // rt[2] * 64 * sby * sbz tile slots
   uint32_t step[4];     // gridDim.x in the mixed radix (rt[2], 64, sby, sbz) of a slot index
+  uint32_t chunk;       // tiles per draw of the tile counter (power of two)
 };
 
 // ------------------------------------------------------------- PTX wrappers
@@ -192,10 +193,86 @@ __device__ __forceinline__ void stg_u16(uint16_t *p, uint32_t v) {
 // Sink of the TMA kernels: like Sink<T> of mgx_hier_common.cuh, but the modal
 // symbol dict/2 is never counted (restored by k_hist_fix) and a group of seven
 // coefficients that all quantise to zero takes a four-instruction test.
+// Outliers are staged per consumer warp in shared memory (F3_OCAP entries of 16 bytes,
+// slots handed out by a shared-memory atomic) and moved to the global list by the whole
+// warp after it has released a tile: one global atomic per flush.  An atomicAdd on the
+// global counter per outlier, with the two stores waiting for its result, put a
+// device-wide round trip on the consumer warp's critical path for every coefficient
+// group that held one: 60 000 outliers of the NYX field at 1e-5 doubled the kernel time.
+#ifndef F3_CHUNK_MAX_
+#define F3_CHUNK_MAX_ 32
+#endif
+// tiles per draw of the device-wide tile counter: a power of two <= 32 (one lane decodes
+// one tile), about 1/8 of a CTA's share of the tiles (F3Args::chunk)
+constexpr uint32_t F3_CHUNK_MAX = F3_CHUNK_MAX_;
+constexpr uint32_t F3_CHUNKQ = 16; // ring of published draws (see the producer loop)
+static_assert((F3_CHUNK_MAX & (F3_CHUNK_MAX - 1)) == 0 && F3_CHUNK_MAX <= 32, "");
+constexpr uint32_t F3_OCAP = 32;
+constexpr uint32_t F3_OFLUSH = 12; // flush at a tile boundary from this fill level
+
+template <typename T>
+__device__ __noinline__ void f3_outlier_direct(const HierArgs<T> &a, uint64_t opos,
+                                               long long q) {
+  const unsigned long long slot = atomicAdd(a.out_count, 1ull);
+  if (slot < a.out_cap) {
+    a.out_idx[slot] = opos;
+    a.out_val[slot] = q;
+  }
+}
+
 template <typename T> struct Sink3 {
   const HierArgs<T> &a;
   T cmax;
   uint32_t hist_saddr;
+  uint32_t obuf_saddr; // this warp's F3_OCAP staged outliers (index, value)
+  uint32_t ocnt_saddr; // entries handed out since the last flush (may exceed F3_OCAP)
+
+  // symbol of a coefficient whose candidate left [0, dict): 0 and an entry of the
+  // outlier list (hier_slow_symbol of mgx_hier_common.cuh; OutlierSeparator.hpp:17-44)
+  __device__ __forceinline__ uint32_t outlier(T c, uint64_t opos) const {
+    const T r = add_rn((T)0.5, fabs(mul_rn(c, a.qv)));
+    long long q = (long long)r;
+    q = (c < (T)0 ? -q : q) + (long long)a.shift;
+    if (q >= 0 && q < (long long)a.dict)
+      return (uint32_t)q;
+    uint32_t slot;
+    asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(slot) : "r"(ocnt_saddr) : "memory");
+    if (slot < F3_OCAP)
+      asm volatile("st.shared.v2.u64 [%0], {%1, %2};" ::"r"(obuf_saddr + slot * 16u),
+                   "l"((unsigned long long)opos), "l"(q)
+                   : "memory");
+    else
+      f3_outlier_direct<T>(a, opos, q); // staging area full: the direct way
+    return 0;
+  }
+  // whole warp, converged, after __syncwarp(): move the staged entries to the list
+  __device__ __forceinline__ void flush(int lane, uint32_t level) const {
+    uint32_t n;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(n) : "r"(ocnt_saddr) : "memory");
+    if (n < level)
+      return;
+    n = min(n, F3_OCAP);
+    unsigned long long base = 0;
+    if (lane == 0)
+      base = atomicAdd(a.out_count, (unsigned long long)n);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if ((uint32_t)lane < n) {
+      unsigned long long idx;
+      long long q;
+      asm volatile("ld.shared.v2.u64 {%0, %1}, [%2];"
+                   : "=l"(idx), "=l"(q)
+                   : "r"(obuf_saddr + (uint32_t)lane * 16u)
+                   : "memory");
+      if (base + lane < a.out_cap) {
+        a.out_idx[base + lane] = idx;
+        a.out_val[base + lane] = q;
+      }
+    }
+    __syncwarp();
+    if (lane == 0)
+      asm volatile("st.shared.u32 [%0], %1;" ::"r"(ocnt_saddr), "r"(0u) : "memory");
+    __syncwarp();
+  }
 
   __device__ __forceinline__ uint32_t quant(T c) const {
     const T r = add_rn((T)0.5, fabs(mul_rn(c, a.qv)));
@@ -211,10 +288,8 @@ template <typename T> struct Sink3 {
     if (__builtin_expect(worst >= a.dict, 0)) {
 #pragma unroll
       for (int i = 0; i < 7; i++)
-        if (sv[i] >= a.dict) {
-          const T r = add_rn((T)0.5, fabs(mul_rn(c[i], a.qv)));
-          sv[i] = hier_slow_symbol<T>(c[i], r, a, (uint64_t)(dst[i] - a.sym));
-        }
+        if (sv[i] >= a.dict)
+          sv[i] = outlier(c[i], (uint64_t)(dst[i] - a.sym));
     }
 #pragma unroll
     for (int i = 0; i < 7; i++) {
@@ -226,7 +301,15 @@ template <typename T> struct Sink3 {
   __device__ __forceinline__ void put7(const T (&c)[7], uint16_t *const (&dst)[7]) const {
     const T m = fmax(fmax(fmax(fabs(c[0]), fabs(c[1])), fmax(fabs(c[2]), fabs(c[3]))),
                      fmax(fmax(fabs(c[4]), fabs(c[5])), fabs(c[6])));
-    if (m <= cmax) { // (false for NaN)
+#ifndef MGX_F3_LANE_ZERO_TEST
+    // one branch for the whole warp: a lane of zeros next to a lane of codes takes the
+    // long path too (slow7 of seven zeros stores the same seven modal symbols), so every
+    // symbol store is issued once, by all lanes, and covers whole 32-byte sectors
+    const bool zero = __ballot_sync(__activemask(), !(m <= cmax)) == 0;
+#else
+    const bool zero = m <= cmax; // (false for NaN)
+#endif
+    if (zero) {
 #pragma unroll
       for (int i = 0; i < 7; i++)
         stg_u16(dst[i], (uint32_t)a.shift);
@@ -410,7 +493,17 @@ __global__ void __launch_bounds__(F3Cfg<T>::THREADS, 1)
   uint32_t *s_hist = (uint32_t *)(smem + (size_t)S * G::TILE);
   F3Info *info = (F3Info *)(s_hist + a.dict);
   unsigned long long *bars = (unsigned long long *)(info + S);
+  // outlier staging of the consumer warps: F3_OCAP 16-byte entries each, then the counts
+  constexpr int CW = F3Cfg<T>::WARPS - F3_NP;
+  unsigned char *obuf = (unsigned char *)(((uintptr_t)(bars + 2 * S) + 15) & ~(uintptr_t)15);
+  uint32_t *ocnt = (uint32_t *)(obuf + (size_t)CW * F3_OCAP * 16);
+  unsigned long long *chunkq =
+      (unsigned long long *)(((uintptr_t)(ocnt + CW) + 7) & ~(uintptr_t)7);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (tid < CW)
+    ocnt[tid] = 0;
+  if (tid < F3_CHUNKQ)
+    chunkq[tid] = ~0ull;
   const uint32_t full0 = saddr(bars), empty0 = saddr(bars + S);
   for (uint32_t i = tid; i < a.dict; i += F3_THREADS)
     s_hist[i] = 0;
@@ -434,7 +527,6 @@ __global__ void __launch_bounds__(F3Cfg<T>::THREADS, 1)
     // cycles per UTMALDG with its operand set-up); warp 0 also arms the barrier
     // and writes the tile descriptor
     const uint32_t T2 = fa.rt[2];
-    const uint32_t SB = T2 * 64;
     int s = 0;
     uint32_t ph = 0, seq = 0;
     bool ok = true;
@@ -453,9 +545,11 @@ __global__ void __launch_bounds__(F3Cfg<T>::THREADS, 1)
     const int bshift = (int)((bp * fa.sh_c) & (G::E - 1)) + (int)((bm_ * fa.sh_b) & (G::E - 1));
     const uint32_t bdst = (uint32_t)(bp * G::PLANE + G::rowoff(bm_));
     const CUtensorMap *const bmap = bm_ == 0 ? &tm3 : &tm2;
+#ifdef MGX_F3_STATIC_TILES
     // slot index of this CTA's next tile as mixed-radix digits (x tile, slot in the
     // 8 x 8 super block, super block y, super block z), advanced by gridDim.x per
     // step without divisions
+    const uint32_t SB = T2 * 64;
     uint32_t tx = blockIdx.x % T2, w = (blockIdx.x / T2) % 64, by = (blockIdx.x / SB) % fa.sby,
              bz = (blockIdx.x / SB) / fa.sby;
     for (; bz < fa.sbz && ok; tx += fa.step[0], w += fa.step[1], by += fa.step[2],
@@ -477,6 +571,67 @@ __global__ void __launch_bounds__(F3Cfg<T>::THREADS, 1)
       const uint32_t ty = by * 8 + (w & 7), tz = bz * 8 + (w >> 3);
       if (ty >= fa.rt[1] || tz >= fa.rt[0])
         continue;
+#else
+    // Tiles are handed out by a device-wide counter, fa.chunk consecutive tiles of the
+    // super-block order per draw (x tile fastest, then the <= 8 x 8 (y, z) tiles of a
+    // super block, then super blocks along y, then z).  The cost of a tile depends on
+    // its data (all-zero groups, outliers) and on the SM's distance to the memory
+    // partitions: a fixed tile list per CTA left the first CTAs idle for a quarter of
+    // the kernel.  Warp 0 draws one chunk ahead and publishes {chunk number, first
+    // tile} through a ring; the other producer warps cannot fall more than
+    // S + 1 tiles, i.e. F3_CHUNKQ - 1 draws, behind (warp 0 waits for the stage of tile
+    // i - S).  One draw costs the producers about 0.4 us (the decode below): 4 tiles per
+    // draw were no faster than the fixed lists, 32 are 11 % faster.
+    const uint32_t ntile = (uint32_t)a.ntiles;
+    const uint32_t rowsz = fa.rt[1] * T2 * 8; // tiles of a full row of super blocks
+    unsigned long long *const tile_ctr = a.out_count + (MGX_SC_TILE - MGX_SC_OUTLIERS);
+    uint32_t drawn = 0;
+    if (warp == 0 && lane == 0)
+      drawn = (uint32_t)atomicAdd(tile_ctr, (unsigned long long)fa.chunk);
+    for (uint32_t chunk = 0; ok; chunk++) {
+      uint32_t t0;
+      if (warp == 0) {
+        t0 = __shfl_sync(0xffffffffu, drawn, 0);
+        if (lane == 0) {
+          chunkq[chunk % F3_CHUNKQ] = ((unsigned long long)chunk << 32) | t0;
+          if (t0 < ntile) // next draw: its round trip overlaps this chunk's tiles
+            drawn = (uint32_t)atomicAdd(tile_ctr, (unsigned long long)fa.chunk);
+        }
+      } else {
+        unsigned long long e;
+        uint32_t spins = 0;
+        do {
+          e = *(volatile unsigned long long *)&chunkq[chunk % F3_CHUNKQ];
+        } while ((uint32_t)(e >> 32) != chunk && ++spins < (1u << 26));
+        if ((uint32_t)(e >> 32) != chunk) {
+          ok = false;
+          if (lane == 0)
+            atomicOr(err_word, 0x100ull);
+          break;
+        }
+        t0 = (uint32_t)e;
+      }
+      if (t0 >= ntile)
+        break;
+      // lane j decodes tile t0 + j (five divisions: once per chunk, not per tile --
+      // the producer warps have about 1000 cycles per tile and spend them on the boxes)
+      uint32_t dx, dy, dz;
+      {
+        const uint32_t v = min(t0 + (lane & (fa.chunk - 1)), ntile - 1);
+        const uint32_t bz = v / rowsz, r = v - bz * rowsz;
+        const uint32_t hz = min(8u, fa.rt[0] - 8 * bz), fb = 8 * hz * T2;
+        const uint32_t by = r / fb, r2 = r - by * fb;
+        const uint32_t hy = min(8u, fa.rt[1] - 8 * by);
+        const uint32_t q = r2 / T2;
+        dx = r2 - q * T2;
+        dz = bz * 8 + q / hy;
+        dy = by * 8 + q % hy;
+      }
+      const uint32_t nin = min(fa.chunk, ntile - t0);
+      for (uint32_t j = 0; j < nin && ok; j++) {
+      const uint32_t tx = __shfl_sync(0xffffffffu, dx, j), ty = __shfl_sync(0xffffffffu, dy, j),
+                     tz = __shfl_sync(0xffffffffu, dz, j);
+#endif
       const uint32_t x0 = tx * G::TX, y0 = ty * G::TY, z0 = tz * G::TZ;
       ok = mbar_wait(empty0 + 8 * s, ph ^ 1);
       if (!ok) {
@@ -511,6 +666,9 @@ __global__ void __launch_bounds__(F3Cfg<T>::THREADS, 1)
       __syncwarp();
       next_stage();
     }
+#ifndef MGX_F3_STATIC_TILES
+    }
+#endif
     // end markers: one for every consumer role's next tile slot (on a time-out
     // the markers are written without waiting, so that every role terminates)
     if (warp == 0)
@@ -529,8 +687,9 @@ __global__ void __launch_bounds__(F3Cfg<T>::THREADS, 1)
         next_stage();
       }
   } else {
-    const Sink3<T> sink{a, fa.cmax, saddr(s_hist)};
     const int cw = warp - F3_NP;
+    const Sink3<T> sink{a, fa.cmax, saddr(s_hist), saddr(obuf) + (uint32_t)cw * F3_OCAP * 16u,
+                        saddr(ocnt + cw)};
     if (cw < F3_G * F3_GW) {
       // ---------------------------------- stride-1 pass: group g, warp iw
       const int g = cw / F3_GW, iw = cw % F3_GW;
@@ -557,6 +716,7 @@ __global__ void __launch_bounds__(F3Cfg<T>::THREADS, 1)
         __syncwarp();
         if (lane == 0)
           mbar_arrive(empty0 + 8 * s);
+        sink.flush(lane, F3_OFLUSH);
         s += F3_G;
         if (s >= S) {
           s -= S;
@@ -600,6 +760,7 @@ __global__ void __launch_bounds__(F3Cfg<T>::THREADS, 1)
         __syncwarp();
         if (lane == 0)
           mbar_arrive(empty0 + 8 * s);
+        sink.flush(lane, F3_OFLUSH);
         s += F3_C;
         while (s >= S) {
           s -= S;
@@ -607,6 +768,8 @@ __global__ void __launch_bounds__(F3Cfg<T>::THREADS, 1)
         }
       }
     }
+    __syncwarp();
+    sink.flush(lane, 1);
   }
   // flush the CTA histogram (the bin of dict/2 is restored by k_hist_fix)
   __syncthreads();
@@ -806,6 +969,14 @@ int launch_fwd3(mgx_ctx *ctx, const void *d_in, HierArgs<T> &a, bool *used) {
     fa.step[2] = (uint32_t)(g % fa.sby);
     fa.step[3] = (uint32_t)(g / fa.sby);
   }
+  {
+    // tiles per draw: about 1/8 of a CTA's share, so that the last draws level the CTAs
+    const uint64_t nt = (uint64_t)fa.rt[0] * fa.rt[1] * fa.rt[2];
+    const uint64_t share = nt / (std::min<uint64_t>(nt, (uint64_t)ctx->num_sms) * 8);
+    fa.chunk = 1;
+    while (fa.chunk * 2 <= share && fa.chunk * 2 <= F3_CHUNK_MAX)
+      fa.chunk *= 2;
+  }
   for (int p = 0; p < 12; p++) {
     const int l = a.L - p;
     const uint64_t sy = a.n[2], sz = (uint64_t)a.n[2] * a.n[1];
@@ -842,12 +1013,20 @@ int launch_fwd3(mgx_ctx *ctx, const void *d_in, HierArgs<T> &a, bool *used) {
       return MGX_SUCCESS; // fall back to the LDGSTS kernel
   }
   constexpr int S = F3Cfg<T>::S;
+  constexpr size_t OSTAGE =
+      16 + (size_t)(F3Cfg<T>::WARPS - F3_NP) * (F3_OCAP * 16 + 4) + 8 + F3_CHUNKQ * 8;
+  static_assert(F3_CHUNKQ > F3Cfg<T>::S + 2,
+                "the ring of draws must outlast the lag between producer warps");
+  static_assert((size_t)S * G::TILE + F3_MAX_DICT * 4 + S * sizeof(F3Info) + 2 * S * 8 + OSTAGE <=
+                    (size_t)F3_SMEM_MAX,
+                "stages + histogram + outlier staging exceed the CTA's shared memory");
   const size_t smem = (size_t)S * G::TILE + (size_t)ctx->dict * 4 + S * sizeof(F3Info) +
-                      2 * S * 8;
+                      2 * S * 8 + OSTAGE;
   auto kern = k_fwd3<T, HALF>;
   MGX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)smem));
   const unsigned grid = (unsigned)std::min<uint64_t>(a.ntiles, (uint64_t)ctx->num_sms);
+  MGX_CUDA(cudaMemsetAsync(ctx->d_scalars + MGX_SC_TILE, 0, 8, ctx->stream)); // tile counter
   kern<<<grid, F3Cfg<T>::THREADS, smem, ctx->stream>>>(ctx->d_freq, (const T *)ctx->d_tables, a,
                                                 fa, tm3, tm2);
   ctx->launches++;

@@ -129,6 +129,7 @@ enum {
   MGX_SC_ERR = 5,      // device-side error flags
   MGX_SC_NZ = 6,       // number of non-zero symbols
   MGX_SC_REDO = 7,     // partitioned Thomas solves: chains redone sequentially
+  MGX_SC_TILE = 8,     // k_fwd3: next tile of the device-wide tile list
   MGX_SC_COUNT = 16
 };
 

@@ -49,6 +49,8 @@ def main():
     ap.add_argument("--abs", action="store_true")
     ap.add_argument("--field", default="smooth", choices=["smooth", "nyx"],
                     help="nyx: bench.py's NYX-shaped generator (3-D only)")
+    ap.add_argument("--compress-only", action="store_true",
+                    help="diagnostic builds whose streams do not decode")
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=2)
     a = ap.parse_args()
@@ -75,10 +77,12 @@ def main():
               "refactor_quantize": comp.elapsed_ms("c_norm", "c_refactor"),
               "codebook": comp.elapsed_ms("c_refactor", "c_codebook"),
               "encode": comp.elapsed_ms("c_codebook", "c_end")}
-        comp.Decompress(blob, eb, a.tol, a.s, norm, out=back)
-        d = comp.elapsed_ms("d_begin", "d_end")
-        st["decode"] = comp.elapsed_ms("d_begin", "d_decode")
-        st["dequant_recompose"] = comp.elapsed_ms("d_decode", "d_end")
+        d = 0.0
+        if not a.compress_only:
+            comp.Decompress(blob, eb, a.tol, a.s, norm, out=back)
+            d = comp.elapsed_ms("d_begin", "d_end")
+            st["decode"] = comp.elapsed_ms("d_begin", "d_decode")
+            st["dequant_recompose"] = comp.elapsed_ms("d_decode", "d_end")
         if it >= a.warmup:
             cs.append(c)
             ds.append(d)
