@@ -74,15 +74,14 @@ template <typename T> struct F3 {
 
 constexpr int F3_GW = 8; // stride-1 warps per group (one tile per group at a time)
 #ifndef F3_NP_
-#define F3_NP_ 4
+#define F3_NP_ 8
 #endif
 #ifndef F3_G_
-#define F3_G_ 3
+#define F3_G_ 2
 #endif
 #ifndef F3_C_
 #define F3_C_ 4
 #endif
-constexpr int F3_NP = F3_NP_; // producer warps (36 / F3_NP of a tile's 36 boxes each)
 constexpr int F3_SMEM_MAX = 227 * 1024;
 constexpr int F3_MAX_DICT = 8192;
 
@@ -91,14 +90,20 @@ template <typename T> constexpr int f3_stages() {
              ? 8
              : (F3_SMEM_MAX - F3_MAX_DICT * 4 - 1024) / F3<T>::TILE;
 }
-// roles per CTA: F3_NP producer warps, G groups of 8 stride-1 warps, C warps for the
-// stride-2 / stride-4 passes (about 1.6 warp-tiles of work per tile against 8 for
-// the stride-1 pass).  fp64 values take two registers: fewer threads, more each.
+// roles per CTA: NP producer warps (36 / NP of a tile's 36 boxes each), G groups of 8
+// stride-1 warps, C warps for the stride-2 / stride-4 passes (about 1.6 warp-tiles of
+// work per tile against 8 for the stride-1 pass).  fp32: (8, 2, 4) = 28 warps.  With
+// the tiles drawn from a counter the CTA waits for its boxes, not for its consumers:
+// 8 producer warps deliver a tile in 0.83 us where 4 needed 1.0 (loads alone), and 896
+// threads get 72 registers each where 1024 got 64 -- at 29 warps and more the smooth
+// field's long path is 25 % slower.  fp64 values take two registers: fewer threads,
+// more each.
 template <typename T> struct F3Cfg {
   static constexpr int S = f3_stages<T>();
+  static constexpr int NP = sizeof(T) == 4 ? F3_NP_ : 4;
   static constexpr int G = sizeof(T) == 4 ? F3_G_ : 2;
   static constexpr int C = sizeof(T) == 4 ? F3_C_ : 3;
-  static constexpr int WARPS = F3_NP + G * F3_GW + C;
+  static constexpr int WARPS = NP + G * F3_GW + C;
   static constexpr int THREADS = 32 * WARPS;
   static_assert(G <= S && C <= S, "end markers need a stage each");
 };
@@ -494,6 +499,7 @@ __global__ void __launch_bounds__(F3Cfg<T>::THREADS, 1)
   F3Info *info = (F3Info *)(s_hist + a.dict);
   unsigned long long *bars = (unsigned long long *)(info + S);
   // outlier staging of the consumer warps: F3_OCAP 16-byte entries each, then the counts
+  constexpr int F3_NP = F3Cfg<T>::NP;
   constexpr int CW = F3Cfg<T>::WARPS - F3_NP;
   unsigned char *obuf = (unsigned char *)(((uintptr_t)(bars + 2 * S) + 15) & ~(uintptr_t)15);
   uint32_t *ocnt = (uint32_t *)(obuf + (size_t)CW * F3_OCAP * 16);
@@ -521,8 +527,8 @@ __global__ void __launch_bounds__(F3Cfg<T>::THREADS, 1)
 
   unsigned long long *const err_word = a.out_count + (MGX_SC_ERR - MGX_SC_OUTLIERS);
   if (warp < F3_NP) {
-    // ---- producers: F3_NP warps walk the same tile list; warp w issues the boxes
-    // of of 36 / F3_NP consecutive (plane, row class) pairs, one box per lane (a single thread issuing all 36 boxes
+    // ---- producers: F3_NP warps walk the same tile list; warp w issues 36 / F3_NP of
+    // the tile's 36 (plane, row class) boxes, one box per lane (a single thread issuing all 36 boxes
     // of a tile was measured to be the bottleneck of the whole kernel: ~120
     // cycles per UTMALDG with its operand set-up); warp 0 also arms the barrier
     // and writes the tile descriptor
@@ -539,8 +545,14 @@ __global__ void __launch_bounds__(F3Cfg<T>::THREADS, 1)
     };
     // this lane's box: plane p (0..8), row class m (0..3)
     constexpr int BPW = (36 + F3_NP - 1) / F3_NP;
+#ifdef F3_BOX_BLOCKED
     const int op = min(warp * BPW + lane, 35);
     const bool has_op = lane < BPW && warp * BPW + lane < 36;
+#else
+    // box o goes to warp o mod NP: 5, 5, 5, 5, 4, 4, 4, 4 boxes for NP = 8
+    const int op = min(lane * F3_NP + warp, 35);
+    const bool has_op = lane < BPW && lane * F3_NP + warp < 36;
+#endif
     const int bp = op >> 2, bm_ = op & 3;
     const int bshift = (int)((bp * fa.sh_c) & (G::E - 1)) + (int)((bm_ * fa.sh_b) & (G::E - 1));
     const uint32_t bdst = (uint32_t)(bp * G::PLANE + G::rowoff(bm_));
@@ -1014,7 +1026,7 @@ int launch_fwd3(mgx_ctx *ctx, const void *d_in, HierArgs<T> &a, bool *used) {
   }
   constexpr int S = F3Cfg<T>::S;
   constexpr size_t OSTAGE =
-      16 + (size_t)(F3Cfg<T>::WARPS - F3_NP) * (F3_OCAP * 16 + 4) + 8 + F3_CHUNKQ * 8;
+      16 + (size_t)(F3Cfg<T>::WARPS - F3Cfg<T>::NP) * (F3_OCAP * 16 + 4) + 8 + F3_CHUNKQ * 8;
   static_assert(F3_CHUNKQ > F3Cfg<T>::S + 2,
                 "the ring of draws must outlast the lag between producer warps");
   static_assert((size_t)S * G::TILE + F3_MAX_DICT * 4 + S * sizeof(F3Info) + 2 * S * 8 + OSTAGE <=
