@@ -82,6 +82,9 @@ constexpr int F3_GW = 8; // stride-1 warps per group (one tile per group at a ti
 #ifndef F3_C_
 #define F3_C_ 4
 #endif
+#ifndef F3_NP64_
+#define F3_NP64_ 5
+#endif
 constexpr int F3_SMEM_MAX = 227 * 1024;
 constexpr int F3_MAX_DICT = 8192;
 
@@ -97,10 +100,11 @@ template <typename T> constexpr int f3_stages() {
 // 8 producer warps deliver a tile in 0.83 us where 4 needed 1.0 (loads alone), and 896
 // threads get 72 registers each where 1024 got 64 -- at 29 warps and more the smooth
 // field's long path is 25 % slower.  fp64 values take two registers: fewer threads,
-// more each.
+// more each -- (5, 2, 3) = 24 warps with 80 registers (641^3: 0.69 ms with 4 producer
+// warps, 0.66 with 5, 0.69 with 6 or 8).
 template <typename T> struct F3Cfg {
   static constexpr int S = f3_stages<T>();
-  static constexpr int NP = sizeof(T) == 4 ? F3_NP_ : 4;
+  static constexpr int NP = sizeof(T) == 4 ? F3_NP_ : F3_NP64_;
   static constexpr int G = sizeof(T) == 4 ? F3_G_ : 2;
   static constexpr int C = sizeof(T) == 4 ? F3_C_ : 3;
   static constexpr int WARPS = NP + G * F3_GW + C;
