@@ -94,3 +94,55 @@ def test_unaligned_input_pointer_takes_the_ldgsts_kernel():
     blob, _ = comp.Compress(view, mg.REL, 1e-3, INF)
     got = blob.cpu().numpy()
     assert got.size == want.size and np.array_equal(np.delete(got, 7), np.delete(want, 7))
+
+
+# ---- tile draws of several tiles, staged outliers ------------------------------------
+def spiky_field(shape, dtype, seed=11):
+    """smooth field with narrow peaks of 1e3 x its amplitude: the coefficients around a
+    peak leave the dictionary, hundreds of outliers in a few tiles (more than the 32
+    slots a warp stages) next to tiles with none"""
+    rng = np.random.default_rng(seed)
+    u = smooth_field(shape, np.float64)
+    for _ in range(24):
+        c = [int(rng.integers(4, n - 4)) for n in shape]
+        sl = tuple(slice(ci - 3, ci + 4) for ci in c)
+        u[sl] += 1e3 * rng.standard_normal(u[sl].shape)
+    return u.astype(dtype)
+
+
+@pytest.mark.parametrize("shape,dtype,draw", [
+    ((210, 210, 530), np.float32, 4),    # 26 x 26 x 8 regular tiles: draws of 4
+    ((137, 330, 1100), np.float32, 8),   # 17 x 41 x 17 tiles, ragged super blocks: draws of 8
+    ((130, 265, 330), np.float64, 2),    # fp64: 16 x 33 x 5 tiles, draws of 2
+])
+def test_drawn_tiles_and_outlier_staging_match_the_ldgsts_kernels(shape, dtype, draw,
+                                                                  monkeypatch):
+    """k_fwd3 with tiles drawn several at a time from the device-wide counter and with
+    outlier-dense tiles: container bytes equal to the LDGSTS kernel family (one tile
+    list per CTA, one global atomic per outlier), which the small cases pin to the
+    oracle; twice in a row on one context (tile counter and outlier counter reset)."""
+    u = spiky_field(shape, dtype)
+    d = torch.from_numpy(u).cuda()
+    tol = 1e-6
+    big = lambda: torch.empty(3 * u.nbytes + (1 << 20), dtype=torch.uint8, device="cuda")
+    comp = make(shape, dtype)
+    blob, norm = comp.Compress(d, mg.REL, tol, INF, out=big())
+    blob = blob.clone()
+    monkeypatch.setenv("MGX_NO_TMA", "1")
+    comp_old = make(shape, dtype)
+    monkeypatch.delenv("MGX_NO_TMA")
+    blob_old, norm_old = comp_old.Compress(d, mg.REL, tol, INF, out=big())
+    assert norm == norm_old
+    assert torch.equal(blob, blob_old), "TMA and LDGSTS kernel families disagree"
+    blob2, _ = comp.Compress(d, mg.REL, tol, INF, out=big())
+    assert torch.equal(blob, blob2)
+    # the outlier list is not empty, and the stream decodes within the bound
+    n = u.size
+    nchunk = (n - 1) // 1024 + 1
+    host = blob.cpu().numpy()
+    off_ddata = 32 + 16 * nchunk + 8 + 8 * (128 + 8192)
+    ddata = int(host[off_ddata:off_ddata + 8].view(np.uint64)[0])
+    n_out = int(host[off_ddata + 8 + 8 * ddata:off_ddata + 16 + 8 * ddata].view(np.uint64)[0])
+    assert n_out > 1000, n_out
+    dec = comp.Decompress(blob, mg.REL, tol, INF, norm).cpu().numpy()
+    assert np.abs(dec.astype(np.float64) - u.astype(np.float64)).max() <= tol * norm
