@@ -26,11 +26,14 @@
 //   box A(p) + B(m) elements early (A(p) = p*ny*nx mod E, B(m) = m*nx mod E, no
 //   wrap) makes the staged address of a node the SUM of a plane term and a row
 //   term.  36 UTMALDG per tile replace 5 300 per-element LDGSTS.
-// * one CTA per SM, no CTA barrier in steady state: a producer warp issues the
+// * one CTA per SM, no CTA barrier in steady state: NP producer warps issue the
 //   boxes into a ring of S tile buffers (mbarrier full/empty pairs); G groups of
 //   8 warps run the stride-1 pass of one tile each; C further warps run the
 //   stride-2 and stride-4 passes of the same tiles.  Tiles are read-only for all
 //   roles, so a tile needs no synchronisation between its passes.
+// * the CTAs draw their tiles from a device-wide counter, several consecutive
+//   tiles per draw (see the producer loop); outliers are staged per warp in shared
+//   memory and leave for the global list with one atomic per flush (Sink3).
 // * with ratio 0.5 (uniform grids) lerp(a, b) = (a - RN(a/2)) + RN(b/2): the two
 //   halves of every node are formed once and shared by all the interpolations
 //   that use it -- same roundings as the reference's four-operation lerp
@@ -39,8 +42,8 @@
 //   exact threshold found on the host) writes the symbol dict/2 seven times and
 //   skips conversion, range test and histogram; the bin of dict/2 is never
 //   counted in the kernels and is restored afterwards as N - sum(other bins).
-// * tiles are walked in super blocks of (all x) x 8 x 8 tiles so that the halo
-//   planes shared by neighbouring tiles are still in L2 when they are re-read.
+// * the tile order runs through super blocks of (all x) x 8 x 8 tiles so that the
+//   halo planes shared by neighbouring tiles are still in L2 when they are re-read.
 //
 // Nodes outside the structured passes (multiples of 8 on every axis, and the
 // nodes of the clipped tiles that touch the last node of an axis) go through
