@@ -75,8 +75,8 @@ typedef struct mgx_config {
   uint32_t reorder;              /* recorded in the header (0)                */
   int normalize_coordinates;     /* uniform grids: unit cube (1) or unit spacing (0) */
   int auto_pin_host_buffers;     /* cudaHostRegister host buffers for the call */
-  int compress_with_dryrun;      /* must be 0: writing the reconstruction back into
-                                    the input (GPUPipelines.hpp:198) is rejected  */
+  int compress_with_dryrun;      /* 1: the reconstruction is written over the INPUT
+                                    array (GPUPipelines.hpp:198-202); one-GPU entries */
   int auto_cache_release;
   int log_level;
   uint64_t max_larget_level;     /* UINT64_MAX = no limit                     */

@@ -972,11 +972,6 @@ int check_config(const mgx_config &cfg) {
   if (cfg.domain_decomposition != MGX_DD_MAXDIM &&
       cfg.domain_decomposition != MGX_DD_BLOCK)
     return fail(MGX_FAILURE, "domain decomposition not supported: MaxDim and Block only");
-  // GPUPipelines.hpp:198-202, Compressor.hpp:239-242: the reference then also
-  // decompresses and writes the reconstruction over the caller's INPUT array
-  if (cfg.compress_with_dryrun)
-    return fail(MGX_FAILURE, "compress_with_dryrun (reconstruction written back into "
-                             "the input array) is not supported");
   if (cfg.huff_dict_size == 0 || cfg.huff_block_size == 0)
     return fail(MGX_FAILURE, "huff_dict_size / huff_block_size must be non-zero");
   return MGX_SUCCESS;
@@ -1231,6 +1226,19 @@ int x_compress(int D, int dtype, const uint64_t *shape, double tol, double s,
     }
     if (offset + 8 > cap || bytes > cap - offset - 8)
       return fail(MGX_OUTPUT_TOO_LARGE, "output too large");
+    // dry run (Compressor.hpp:239-242: Dequantize + Recompose after Serialize;
+    // GPUPipelines.hpp:198-202: SubdomainToOriginal): the reconstruction replaces the
+    // caller's INPUT array.  It is what mgx_x_decompress returns for this record -- a
+    // subdomain stored raw (CR < 1) is its own reconstruction and stays as it is.
+    if (cfg.compress_with_dryrun && payload != d_in) {
+      void *recon = in_place ? (void *)d_in : c.sub[b];
+      int r2 = mgx_decompress(ctx, (const uint8_t *)c.cbuf[b], bytes, local_rel, local_tol,
+                              sT, nrm, recon);
+      if (r2)
+        return fail(r2, std::string("dry run: ") + mgx_last_error(ctx));
+      if (!in_place && (r2 = copy_slab(sl, i, c.sub[b], (void *)in, false, c.compute)))
+        return r2;
+    }
     put_u64_le(size_le, bytes);
     if (out_loc.device)
       X_CUDA(cudaMemcpy(obase + offset, size_le, 8, cudaMemcpyHostToDevice));
@@ -1436,6 +1444,9 @@ int x_compress_multi(int D, int dtype, const uint64_t *shape, double tol, double
   int rc = check_config(cfg);
   if (rc)
     return rc;
+  // (the one-GPU pipeline does it, x_compress below "dry run")
+  if (cfg.compress_with_dryrun)
+    return fail(MGX_FAILURE, "compress_with_dryrun is not supported by the multi-GPU entry");
   if (locate(in).device)
     return fail(MGX_FAILURE, "mgx_x_compress_multi takes host buffers");
   if (cfg.domain_decomposition != MGX_DD_MAXDIM)

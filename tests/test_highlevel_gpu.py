@@ -193,6 +193,45 @@ def test_max_dim_decomposition(shape, dtype, s, mode, where):
     check_bound(u, back.cpu().numpy() if where == "device" else back, rel, tol, s)
 
 
+@pytest.mark.parametrize("shape,dtype,s,mode,decomposed", [
+    ((33, 40, 65), np.float32, INF, hl.REL, False),
+    ((129, 70), np.float64, 0.0, hl.ABS, False),
+    ((24, 60, 190), np.float64, INF, hl.REL, True),     # slabs along dim 2: strided copies back
+    ((600, 257), np.float32, 0.0, hl.REL, True),        # slabs along dim 0
+])
+@pytest.mark.parametrize("where", ["device", "host"])
+def test_compress_with_dryrun_leaves_the_reconstruction_in_the_input(shape, dtype, s, mode,
+                                                                     decomposed, where):
+    """Config::compress_with_dryrun (Compressor.hpp:239-242: Dequantize + Recompose after
+    Serialize; GPUPipelines.hpp:198-202: SubdomainToOriginal): after the call the INPUT
+    array holds what decompress returns for the stream, bit for bit; the stream itself is
+    the one a plain compress writes."""
+    u = smooth_field(shape, dtype)
+    tol = 1e-3
+    cfg = budget_for_halvings(shape, dtype, s, 3)[0] if decomposed else hl.Config()
+    plain = hl.compress(torch.from_numpy(u).cuda() if where == "device" else u.copy(),
+                        tol, s, mode, config=cfg)
+    cfg.compress_with_dryrun = 1
+    x = torch.from_numpy(u).cuda() if where == "device" else u.copy()
+    stream = hl.compress(x, tol, s, mode, config=cfg)
+    as_np = lambda t: t.cpu().numpy() if hasattr(t, "cpu") else np.asarray(t)
+    assert np.array_equal(as_np(stream), as_np(plain))
+    md, recs = records(stream)
+    assert bool(md.decomposed) == decomposed
+    back = as_np(hl.decompress(stream))
+    got = as_np(x)
+    assert not np.array_equal(got, u), "the input was not touched"
+    assert np.array_equal(got.view(np.uint8), back.view(np.uint8))
+    check_bound(u, got, int(mode == hl.REL), tol, s)
+
+
+def test_dryrun_is_refused_by_the_multi_gpu_entry():
+    u = smooth_field((40, 30, 50), np.float32)
+    with pytest.raises(hl.MgardError):
+        hl.compress_multi(u, 1e-3, INF, hl.REL, [0],
+                          config=hl.Config(compress_with_dryrun=1))
+
+
 def test_raw_fallback_when_a_subdomain_does_not_compress():
     """CR < 1 -> the record is the raw subdomain (GPUPipelines.hpp:139-156) and
     decompress copies it back (:407-421)."""
