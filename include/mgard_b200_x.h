@@ -69,7 +69,7 @@ typedef struct mgx_config {
   int dev_id;
   int domain_decomposition;      /* mgx_dd_type; MaxDim or Block              */
   int decomposition;             /* mgx_decomp_type; MultiDim only            */
-  int lossless;                  /* mgx_lossless; Huffman only                */
+  int lossless;                  /* mgx_lossless; Huffman or Huffman_Zstd     */
   uint32_t huff_dict_size;       /* 8192                                      */
   uint32_t huff_block_size;      /* 1024                                      */
   uint32_t reorder;              /* recorded in the header (0)                */
@@ -82,6 +82,7 @@ typedef struct mgx_config {
   uint64_t max_larget_level;     /* UINT64_MAX = no limit                     */
   uint64_t max_memory_footprint; /* UINT64_MAX = no limit (bytes)             */
   uint64_t block_size;           /* Block decomposition: edge of a block (256) */
+  int zstd_compress_level;       /* Huffman_Zstd: level of ZSTD_compress (3)   */
 } mgx_config;
 
 void mgx_config_default(mgx_config *cfg); /* Config::Config(), Config.cpp:31-66 */
@@ -145,6 +146,10 @@ int mgx_x_pin_memory(void *ptr, uint64_t bytes, const mgx_config *cfg);
 int mgx_x_check_memory_pinned(void *ptr, const mgx_config *cfg);
 int mgx_x_unpin_memory(void *ptr, const mgx_config *cfg);
 const char *mgx_x_last_error(void);
+
+/* 1 when libzstd.so.1 was found on this machine (lossless = Huffman_Zstd runs
+ * ZSTD_compress / ZSTD_decompress on the host, Lossless/Zstd.hpp:72-141), else 0. */
+int mgx_x_have_zstd(void);
 /* kernels launched by the high-level path's contexts since the cache was made */
 uint64_t mgx_x_launch_count(void);
 

@@ -28,7 +28,8 @@ class MgxConfig(ctypes.Structure):
                 ("auto_pin_host_buffers", c_int),
                 ("compress_with_dryrun", c_int), ("auto_cache_release", c_int),
                 ("log_level", c_int), ("max_larget_level", c_u64),
-                ("max_memory_footprint", c_u64), ("block_size", c_u64)]
+                ("max_memory_footprint", c_u64), ("block_size", c_u64),
+                ("zstd_compress_level", c_int)]
 
 
 class MgxMetadata(ctypes.Structure):
@@ -75,6 +76,7 @@ SIGNATURES = {
     "mgx_x_check_memory_pinned": (c_int, [c_vp, _cfgp]),
     "mgx_x_unpin_memory": (c_int, [c_vp, _cfgp]),
     "mgx_x_last_error": (ctypes.c_char_p, []),
+    "mgx_x_have_zstd": (c_int, []),
     "mgx_x_launch_count": (c_u64, []),
     "mgx_metadata_serialize": (c_int, [ctypes.POINTER(MgxMetadata), c_vp, c_u64,
                                        ctypes.POINTER(c_u64)]),

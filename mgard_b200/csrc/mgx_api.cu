@@ -308,7 +308,11 @@ int mgx_plan_grid(mgx_ctx *ctx, int D, const uint64_t *shape, int dtype,
       }
     }
     MGX_CUDA(cudaMalloc(&ctx->d_rcp, cnt * 8));
-    MGX_CUDA(cudaMemcpy(ctx->d_rcp, rcp.data(), cnt * 8, cudaMemcpyHostToDevice));
+    // (on the context's stream, synchronised below: a cudaMemcpy from pageable memory
+    // returns once the bytes are staged, and a non-blocking stream does not wait for it)
+    MGX_CUDA(cudaMemcpyAsync(ctx->d_rcp, rcp.data(), cnt * 8, cudaMemcpyHostToDevice,
+                             ctx->stream));
+    MGX_CUDA(cudaStreamSynchronize(ctx->stream));
   }
   const uint64_t N = ctx->lv.N;
   const uint64_t nchunk = (N - 1) / chunk_size + 1;

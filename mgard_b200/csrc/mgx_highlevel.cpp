@@ -13,6 +13,7 @@
 //   * at most two planned contexts are kept (full slab + leftover), the same
 //     working set the reference's hierarchy cache holds for MaxDim.
 #include <cuda_runtime.h>
+#include <dlfcn.h>
 
 #include <algorithm>
 #include <cmath>
@@ -39,6 +40,42 @@ int fail(int rc, const std::string &msg) {
   std::lock_guard<std::mutex> lock(g_err_mu);
   g_err = msg;
   return rc;
+}
+
+// ---- libzstd, bound at run time -----------------------------------------------
+// The second lossless stage of lossless_type::Huffman_Zstd is the host library's
+// ZSTD_compress / ZSTD_decompress over the serialised Huffman container
+// (Lossless/Zstd.hpp:72-141).  The image ships libzstd.so.1 without its headers:
+// the five entry points used are declared here and resolved with dlopen, and a
+// machine without the library refuses Huffman_Zstd with an error text.
+struct ZstdApi {
+  size_t (*compressBound)(size_t) = nullptr;
+  size_t (*compress)(void *, size_t, const void *, size_t, int) = nullptr;
+  size_t (*decompress)(void *, size_t, const void *, size_t) = nullptr;
+  unsigned (*isError)(size_t) = nullptr;
+  const char *(*getErrorName)(size_t) = nullptr;
+  bool ok = false;
+};
+const ZstdApi &zstd_api() {
+  static ZstdApi api;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void *h = dlopen("libzstd.so.1", RTLD_NOW | RTLD_LOCAL);
+    if (!h)
+      h = dlopen("libzstd.so", RTLD_NOW | RTLD_LOCAL);
+    if (!h)
+      return;
+    api.compressBound = (size_t(*)(size_t))dlsym(h, "ZSTD_compressBound");
+    api.compress =
+        (size_t(*)(void *, size_t, const void *, size_t, int))dlsym(h, "ZSTD_compress");
+    api.decompress =
+        (size_t(*)(void *, size_t, const void *, size_t))dlsym(h, "ZSTD_decompress");
+    api.isError = (unsigned (*)(size_t))dlsym(h, "ZSTD_isError");
+    api.getErrorName = (const char *(*)(size_t))dlsym(h, "ZSTD_getErrorName");
+    api.ok = api.compressBound && api.compress && api.decompress && api.isError &&
+             api.getErrorName;
+  });
+  return api;
 }
 
 // ---- CRC-32 (IEEE 802.3, reflected 0xEDB88320) == zlib crc32_z --------------
@@ -602,6 +639,7 @@ struct DeviceCache {
   size_t sub_bytes[2] = {0, 0};
   void *cbuf[2] = {nullptr, nullptr};
   size_t cbuf_bytes[2] = {0, 0};
+  std::vector<uint8_t> zin, zout[2]; // host side of the Zstd stage
   uint64_t stamp = 0;
   uint64_t retired_launches = 0;
   bool ready = false;
@@ -965,8 +1003,10 @@ int check_config(const mgx_config &cfg) {
   if (cfg.dev_type != MGX_DEV_AUTO && cfg.dev_type != MGX_DEV_CUDA)
     return fail(MGX_BACKEND_UNAVAILABLE,
                 "only the CUDA backend is built (no CPU fallback by design)");
-  if (cfg.lossless != MGX_LL_HUFFMAN)
-    return fail(MGX_FAILURE, "lossless type not supported: Huffman only");
+  if (cfg.lossless != MGX_LL_HUFFMAN && cfg.lossless != MGX_LL_HUFFMAN_ZSTD)
+    return fail(MGX_FAILURE, "lossless type not supported: Huffman and Huffman_Zstd only");
+  if (cfg.lossless == MGX_LL_HUFFMAN_ZSTD && !zstd_api().ok)
+    return fail(MGX_FAILURE, "Huffman_Zstd needs libzstd.so.1 on this machine");
   if (cfg.decomposition != MGX_DC_MULTIDIM)
     return fail(MGX_FAILURE, "decomposition type not supported: MultiDim only");
   if (cfg.domain_decomposition != MGX_DD_MAXDIM &&
@@ -1089,7 +1129,7 @@ int x_compress(int D, int dtype, const uint64_t *shape, double tol, double s,
   md.dd_dim = sl.dim;
   md.dd_size = sl.decomposed ? sl.size : shape[0];
   md.decomposition = MGX_DC_MULTIDIM;
-  md.lossless = MGX_LL_HUFFMAN;
+  md.lossless = cfg.lossless;
   md.huff_dict_size = cfg.huff_dict_size;
   md.huff_block_size = cfg.huff_block_size;
   md.reorder = cfg.reorder;
@@ -1218,9 +1258,29 @@ int x_compress(int D, int dtype, const uint64_t *shape, double tol, double s,
     if (!sl.decomposed && rel)
       norm = nrm;
     const void *payload = c.cbuf[b];
+    const uint64_t huff_bytes = bytes; // the Huffman container in c.cbuf[b]
+    bool raw = rc == MGX_OUTPUT_TOO_LARGE || bytes >= n_sub * es;
+    if (!raw && cfg.lossless == MGX_LL_HUFFMAN_ZSTD) {
+      // Lossless.hpp:188-192, Zstd.hpp:72-104: the record is [size_t n][ZSTD frame of
+      // the n bytes of the serialised Huffman container]; libzstd runs on the host
+      const ZstdApi &z = zstd_api();
+      X_CUDA(cudaEventSynchronize(c.ev_out[b])); // the previous record left zout[b]
+      c.zin.resize(bytes);
+      X_CUDA(cudaMemcpy(c.zin.data(), c.cbuf[b], bytes, cudaMemcpyDeviceToHost));
+      const size_t bound = z.compressBound(bytes);
+      c.zout[b].resize(8 + bound);
+      const size_t zs = z.compress(c.zout[b].data() + 8, bound, c.zin.data(), bytes,
+                                   cfg.zstd_compress_level);
+      if (z.isError(zs))
+        return fail(MGX_FAILURE, std::string("ZSTD_compress: ") + z.getErrorName(zs));
+      put_u64_le(c.zout[b].data(), bytes);
+      payload = c.zout[b].data();
+      bytes = 8 + zs;
+      raw = bytes >= n_sub * es;
+    }
     // CR < 1: store the subdomain itself (GPUPipelines.hpp:139-156)
     // (>=: the decoder classifies a record of exactly n_sub * es bytes as raw)
-    if (rc == MGX_OUTPUT_TOO_LARGE || bytes >= n_sub * es) {
+    if (raw) {
       payload = d_in;
       bytes = n_sub * es;
     }
@@ -1230,10 +1290,10 @@ int x_compress(int D, int dtype, const uint64_t *shape, double tol, double s,
     // GPUPipelines.hpp:198-202: SubdomainToOriginal): the reconstruction replaces the
     // caller's INPUT array.  It is what mgx_x_decompress returns for this record -- a
     // subdomain stored raw (CR < 1) is its own reconstruction and stays as it is.
-    if (cfg.compress_with_dryrun && payload != d_in) {
+    if (cfg.compress_with_dryrun && !raw) {
       void *recon = in_place ? (void *)d_in : c.sub[b];
-      int r2 = mgx_decompress(ctx, (const uint8_t *)c.cbuf[b], bytes, local_rel, local_tol,
-                              sT, nrm, recon);
+      int r2 = mgx_decompress(ctx, (const uint8_t *)c.cbuf[b], huff_bytes, local_rel,
+                              local_tol, sT, nrm, recon);
       if (r2)
         return fail(r2, std::string("dry run: ") + mgx_last_error(ctx));
       if (!in_place && (r2 = copy_slab(sl, i, c.sub[b], (void *)in, false, c.compute)))
@@ -1447,6 +1507,8 @@ int x_compress_multi(int D, int dtype, const uint64_t *shape, double tol, double
   // (the one-GPU pipeline does it, x_compress below "dry run")
   if (cfg.compress_with_dryrun)
     return fail(MGX_FAILURE, "compress_with_dryrun is not supported by the multi-GPU entry");
+  if (cfg.lossless != MGX_LL_HUFFMAN)
+    return fail(MGX_FAILURE, "the multi-GPU entry writes Huffman streams only");
   if (locate(in).device)
     return fail(MGX_FAILURE, "mgx_x_compress_multi takes host buffers");
   if (cfg.domain_decomposition != MGX_DD_MAXDIM)
@@ -1855,7 +1917,39 @@ int x_decompress(const void *in, size_t in_size, void **out, uint64_t *shape_out
       if ((rc = cache_ctx(c, D, sh, dtype, cfg, &ctx,
                           sc.get(coords, D, offs, es))))
         return rc;
-      rc = mgx_decompress(ctx, (const uint8_t *)c.cbuf[b], rec_bytes[i], local_rel,
+      uint64_t huff_bytes = rec_bytes[i];
+      if (md.lossless == MGX_LL_HUFFMAN_ZSTD) {
+        // Zstd.hpp:106-141: [size_t n][ZSTD frame] -> the n bytes of the Huffman
+        // container, decoded by libzstd on the host and sent back to the device
+        const ZstdApi &z = zstd_api();
+        if (rec_bytes[i] < 8)
+          return fail(MGX_FAILURE, "Zstd record shorter than its size field");
+        X_CUDA(cudaEventSynchronize(c.ev_in[b]));
+        c.zin.resize(rec_bytes[i]);
+        X_CUDA(cudaMemcpy(c.zin.data(), c.cbuf[b], rec_bytes[i], cudaMemcpyDeviceToHost));
+        uint64_t n = 0;
+        for (int k = 0; k < 8; k++)
+          n |= (uint64_t)c.zin[k] << (8 * k);
+        // a Huffman container is smaller than the field plus its fixed sections
+        if (n > n_sub * es + 16 * (n_sub / cfg.huff_block_size + 2) +
+                    8ull * (128 + cfg.huff_dict_size) + 4096)
+          return fail(MGX_FAILURE, "Zstd record announces an impossible size");
+        c.zout[b].resize(n);
+        const size_t got = z.decompress(c.zout[b].data(), n, c.zin.data() + 8,
+                                        rec_bytes[i] - 8);
+        if (z.isError(got))
+          return fail(MGX_FAILURE, std::string("ZSTD_decompress: ") + z.getErrorName(got));
+        if (got != n)
+          return fail(MGX_FAILURE, "Zstd frame shorter than announced");
+        if ((rc = ensure_buffer(c.cbuf[b], c.cbuf_bytes[b], n)))
+          return rc;
+        // on the compute stream: a cudaMemcpy from pageable memory returns once the
+        // bytes are STAGED, and the kernels' stream does not wait for the legacy one
+        X_CUDA(cudaMemcpyAsync(c.cbuf[b], c.zout[b].data(), n, cudaMemcpyHostToDevice,
+                               c.compute));
+        huff_bytes = n;
+      }
+      rc = mgx_decompress(ctx, (const uint8_t *)c.cbuf[b], huff_bytes, local_rel,
                           local_tol, sT, normT, d_out);
       if (rc)
         return fail(rc, std::string("decompress: ") + mgx_last_error(ctx));
@@ -1903,6 +1997,8 @@ int x_decompress_multi(const void *in, size_t in_size, void **out, uint64_t *sha
     return rc;
   if (md.D < 1 || md.D > 5)
     return fail(MGX_FAILURE, "bad shape in the header");
+  if (md.lossless != MGX_LL_HUFFMAN)
+    return fail(MGX_FAILURE, "the multi-GPU entry reads Huffman streams only");
   const size_t es = md.dtype == MGX_F64 ? 8 : 4;
   uint64_t N = 1, num = 1;
   for (uint32_t d = 0; d < md.D; d++) {
@@ -2005,6 +2101,7 @@ void mgx_config_default(mgx_config *cfg) {
   cfg->domain_decomposition = MGX_DD_MAXDIM;
   cfg->decomposition = MGX_DC_MULTIDIM;
   cfg->lossless = MGX_LL_HUFFMAN;
+  cfg->zstd_compress_level = 3; // Config.cpp:44
   cfg->huff_dict_size = 8192;
   cfg->huff_block_size = 1024;
   cfg->reorder = 0;
@@ -2311,6 +2408,8 @@ int mgx_x_unpin_memory(void *ptr, const mgx_config *cfg) {
 }
 
 const char *mgx_x_last_error(void) { return g_err.c_str(); }
+
+int mgx_x_have_zstd(void) { return zstd_api().ok ? 1 : 0; }
 
 uint64_t mgx_x_launch_count(void) {
   std::lock_guard<std::mutex> lock(g_mu);

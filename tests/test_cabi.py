@@ -137,3 +137,15 @@ def test_max_dim_decomposition(shape, devices, want):
     assert total == shape[dd.dim]
     with pytest.raises(IndexError):
         dd.subdomain_shape(dd.num_subdomains)
+
+
+def test_libzstd_is_found_at_run_time_and_the_config_carries_its_level():
+    """lossless_type::Huffman_Zstd binds libzstd.so.1 with dlopen (this image ships the
+    library without headers); Config::zstd_compress_level defaults to 3 (Config.cpp:44)"""
+    from mgard_b200 import _lib, highlevel as hl
+    lib = _lib.load()
+    assert lib.mgx_x_have_zstd() in (0, 1)
+    if os.path.exists("/usr/lib/x86_64-linux-gnu/libzstd.so.1"):
+        assert lib.mgx_x_have_zstd() == 1
+    cfg = hl.Config()
+    assert cfg.zstd_compress_level == 3 and cfg.lossless == 0

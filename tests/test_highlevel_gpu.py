@@ -232,6 +232,65 @@ def test_dryrun_is_refused_by_the_multi_gpu_entry():
                           config=hl.Config(compress_with_dryrun=1))
 
 
+def _restream(stream, payloads):
+    """the stream's header followed by the given record payloads"""
+    stream = np.asarray(stream)
+    _, pos = hl.read_metadata(bytes(stream[:4096]))
+    parts = [stream[:pos].tobytes()]
+    for p in payloads:
+        parts.append(struct.pack("<Q", len(p)))
+        parts.append(bytes(p))
+    return np.frombuffer(b"".join(parts), np.uint8).copy()
+
+
+@pytest.mark.parametrize("shape,dtype,s,mode,decomposed", [
+    ((33, 40, 65), np.float32, INF, hl.REL, False),
+    ((257, 130), np.float64, 0.0, hl.ABS, False),
+    ((24, 60, 190), np.float64, INF, hl.REL, True),
+])
+@pytest.mark.parametrize("where", ["device", "host"])
+def test_huffman_zstd_second_stage(shape, dtype, s, mode, decomposed, where):
+    """lossless_type::Huffman_Zstd (Lossless.hpp:188-192, 250-253; Zstd.hpp:72-141): every
+    record is [u64 n][ZSTD frame of the n bytes of the Huffman container].  The frames
+    are read back with ANOTHER zstd implementation (pyarrow's) and must hold the records
+    of the plain Huffman stream; frames written by that other implementation at level 19
+    and spliced into the stream decode to the same field."""
+    pa = pytest.importorskip("pyarrow")
+    if not _lib.load().mgx_x_have_zstd():
+        pytest.skip("no libzstd.so.1 on this machine")
+    u = smooth_field(shape, dtype)
+    tol = 1e-3
+    cfg = budget_for_halvings(shape, dtype, s, 3)[0] if decomposed else hl.Config()
+    as_np = lambda t: t.cpu().numpy() if hasattr(t, "cpu") else np.asarray(t)
+    x = torch.from_numpy(u).cuda() if where == "device" else u
+    plain = as_np(hl.compress(x, tol, s, mode, config=cfg))
+    cfg.lossless = 2  # Huffman_Zstd
+    stream = as_np(hl.compress(x, tol, s, mode, config=cfg))
+    md0, recs0 = records(plain)
+    md, recs = records(stream)
+    assert md0.lossless == 0 and md.lossless == 2 and bool(md.decomposed) == decomposed
+    assert len(recs) == len(recs0)
+    codec = pa.Codec("zstd", compression_level=19)
+    other = []
+    for r, r0 in zip(recs, recs0):
+        n = int(r[:8].view(np.uint64)[0])
+        assert n == r0.size and r.size < r0.size + 64
+        body = codec.decompress(r[8:].tobytes(), decompressed_size=n, asbytes=True)
+        assert body == r0.tobytes(), "the frame does not hold the Huffman container"
+        other.append(struct.pack("<Q", n) + codec.compress(r0.tobytes(), asbytes=True))
+    want = as_np(hl.decompress(plain))
+    got = as_np(hl.decompress(torch.from_numpy(stream).cuda() if where == "device" else stream))
+    assert np.array_equal(got.view(np.uint8), want.view(np.uint8))
+    foreign = _restream(stream, other)
+    got2 = as_np(hl.decompress(foreign))
+    assert np.array_equal(got2.view(np.uint8), want.view(np.uint8))
+    check_bound(u, got, int(mode == hl.REL), tol, s)
+    # a truncated frame is refused
+    bad = _restream(stream, [bytes(r[:-5]) for r in recs])
+    with pytest.raises(hl.MgardError):
+        hl.decompress(bad)
+
+
 def test_raw_fallback_when_a_subdomain_does_not_compress():
     """CR < 1 -> the record is the raw subdomain (GPUPipelines.hpp:139-156) and
     decompress copies it back (:407-421)."""
@@ -265,7 +324,7 @@ def test_status_codes():
     assert call(D=6) == 3           # NotSupportHigherNumberOfDimensionsFailure
     assert call(dtype=7) == 4       # NotSupportDataTypeFailure
     assert call(cfg=hl.Config(dev_type=hl.OPENMP)) == 5   # BackendNotAvailable
-    assert call(cfg=hl.Config(lossless=2)) == 1           # Huffman_Zstd: Failure
+    assert call(cfg=hl.Config(lossless=1)) == 1           # Huffman_LZ4: Failure
     assert call(cap=64) == 2        # OutputTooLargeFailure
     assert call(cap=300) == 2
     assert b"too large" in lib.mgx_x_last_error()
