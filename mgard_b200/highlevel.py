@@ -13,6 +13,8 @@ from .compressor import MgardError
 
 REL, ABS = 0, 1          # error_bound_type (Utilities/Types.h:34)
 AUTO, SERIAL, OPENMP, CUDA, HIP, SYCL = range(6)   # device_type
+# lossless_type (Types.h:36-56): Huffman and Huffman_Zstd are built
+HUFFMAN, HUFFMAN_LZ4, HUFFMAN_ZSTD, CPU_LOSSLESS = range(4)
 
 
 def Config(**kw):

@@ -189,7 +189,11 @@ def fill_header(Header, c):
     h.bitplane_encoding.SetInParent()
     en = h.encoding
     en.preprocessor = 0
-    en.compressor = 3                                     # X_HUFFMAN
+    # X_HUFFMAN, or X_HUFFMAN_ZSTD for lossless_type::Huffman_Zstd (:431-444; both
+    # carry the dictionary and block sizes); the numbers come from the .proto
+    comp = en.DESCRIPTOR.fields_by_name["compressor"].enum_type
+    en.compressor = comp.values_by_name[
+        "X_HUFFMAN_ZSTD" if c.get("lossless") == "zstd" else "X_HUFFMAN"].number
     en.huffman_dictionary_size = c["dict"]
     en.huffman_block_size = c["block"]
     h.device.backend = 3                                  # X_CUDA
@@ -218,6 +222,9 @@ CASES = {
     "f32_1d_abs_linf": dict(shape=[100000], dtype="f32", mode="ABS", s=math.inf,
                             tol=f32(0.5), norm=1.0, decomposed=False, dd_dim=0,
                             dd_size=100000, dict=64, block=256),
+    "f32_3d_rel_zstd": dict(shape=[257, 130, 65], dtype="f32", mode="REL", s=math.inf,
+                            tol=f32(1e-4), norm=f32(2.5), decomposed=True, dd_dim=0,
+                            dd_size=129, dict=8192, block=1024, lossless="zstd"),
     "f64_4d_abs_negs": dict(shape=[5, 6, 7, 300], dtype="f64", mode="ABS", s=-0.5,
                             tol=2.5e-7, norm=1.0, decomposed=True, dd_dim=3,
                             dd_size=150, dict=8192, block=1024),

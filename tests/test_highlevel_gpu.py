@@ -264,7 +264,7 @@ def test_huffman_zstd_second_stage(shape, dtype, s, mode, decomposed, where):
     as_np = lambda t: t.cpu().numpy() if hasattr(t, "cpu") else np.asarray(t)
     x = torch.from_numpy(u).cuda() if where == "device" else u
     plain = as_np(hl.compress(x, tol, s, mode, config=cfg))
-    cfg.lossless = 2  # Huffman_Zstd
+    cfg.lossless = hl.HUFFMAN_ZSTD
     stream = as_np(hl.compress(x, tol, s, mode, config=cfg))
     md0, recs0 = records(plain)
     md, recs = records(stream)
@@ -324,7 +324,7 @@ def test_status_codes():
     assert call(D=6) == 3           # NotSupportHigherNumberOfDimensionsFailure
     assert call(dtype=7) == 4       # NotSupportDataTypeFailure
     assert call(cfg=hl.Config(dev_type=hl.OPENMP)) == 5   # BackendNotAvailable
-    assert call(cfg=hl.Config(lossless=1)) == 1           # Huffman_LZ4: Failure
+    assert call(cfg=hl.Config(lossless=hl.HUFFMAN_LZ4)) == 1   # not built: Failure
     assert call(cap=64) == 2        # OutputTooLargeFailure
     assert call(cap=300) == 2
     assert b"too large" in lib.mgx_x_last_error()

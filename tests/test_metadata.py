@@ -34,7 +34,7 @@ def make_md(c):
     md.dd_type = 0
     md.dd_dim, md.dd_size = c["dd_dim"], c["dd_size"]
     md.decomposition = 0
-    md.lossless = 0
+    md.lossless = 2 if c.get("lossless") == "zstd" else 0
     md.huff_dict_size, md.huff_block_size = c["dict"], c["block"]
     md.backend = 3
     return md
@@ -83,7 +83,8 @@ def test_parse_golden(name):
     assert bool(md.decomposed) == c["decomposed"]
     assert (md.dd_dim, md.dd_size) == (c["dd_dim"], c["dd_size"])
     assert (md.huff_dict_size, md.huff_block_size) == (c["dict"], c["block"])
-    assert md.backend == 3 and md.lossless == 0 and md.decomposition == 0
+    assert md.lossless == (2 if c.get("lossless") == "zstd" else 0)
+    assert md.backend == 3 and md.decomposition == 0
     assert (md.version[0], md.file_version[0]) == (1, 0)
 
 
