@@ -5,6 +5,7 @@
 // (SERIAL back-end, Q=uint64, S=int64, H=uint64 exactly as instantiated by
 //  CompressionLowLevel/Compressor.h:47-48).  Compiled by oracle/Makefile into
 // oracle/_ref/libmgardx_ref.so.
+#include <dlfcn.h>
 #include <cstdint>
 #include <cstring>
 #include <vector>
@@ -67,13 +68,45 @@ int ref_huffman_decompress(const uint8_t *in, uint64_t bytes, uint64_t n,
   }
 }
 
-// zstd is referenced unconditionally by Lossless/Zstd.hpp and Lossless/CPU.hpp
-// but never called on the Huffman path; stub the five symbols so the oracle has
-// no run-time dependency outside libstdc++/libgomp.
-size_t ZSTD_compress(void *, size_t, const void *, size_t, int) { return 0; }
-size_t ZSTD_decompress(void *, size_t, const void *, size_t) { return 0; }
-size_t ZSTD_compressBound(size_t n) { return n; }
-unsigned ZSTD_isError(size_t) { return 1; }
-const char *ZSTD_getErrorName(size_t) { return "zstd stubbed out in oracle"; }
+// zstd is referenced unconditionally by Lossless/Zstd.hpp and Lossless/CPU.hpp.  The
+// image has the run-time library (libzstd.so.1) but not its headers: the five symbols
+// forward to it through dlopen, so that the reference's own Huffman_Zstd writer and
+// reader run in the oracle (ref_set_lossless(2)); without the library they report an
+// error and the Huffman path, which never calls them, is unaffected.
+static void *zstd_handle() {
+  static void *h = dlopen("libzstd.so.1", RTLD_NOW | RTLD_LOCAL);
+  return h;
+}
+static void *zstd_raw(const char *name) {
+  void *h = zstd_handle();
+  return h ? dlsym(h, name) : nullptr;
+}
+#define zstd_sym(F, name) ((F)zstd_raw(name))
+size_t ZSTD_compress(void *d, size_t dc, const void *s, size_t sc, int level) {
+  auto f = zstd_sym(size_t (*)(void *, size_t, const void *, size_t, int), "ZSTD_compress");
+  return f ? f(d, dc, s, sc, level) : (size_t)-1;
+}
+size_t ZSTD_decompress(void *d, size_t dc, const void *s, size_t sc) {
+  auto f = zstd_sym(size_t (*)(void *, size_t, const void *, size_t), "ZSTD_decompress");
+  return f ? f(d, dc, s, sc) : (size_t)-1;
+}
+size_t ZSTD_compressBound(size_t n) {
+  auto f = zstd_sym(size_t (*)(size_t), "ZSTD_compressBound");
+  return f ? f(n) : n;
+}
+unsigned ZSTD_isError(size_t c) {
+  auto f = zstd_sym(unsigned (*)(size_t), "ZSTD_isError");
+  return f ? f(c) : 1u;
+}
+const char *ZSTD_getErrorName(size_t c) {
+  auto f = zstd_sym(const char *(*)(size_t), "ZSTD_getErrorName");
+  return f ? f(c) : "libzstd.so.1 not found";
+}
+
+// lossless_type of the Config the wrappers build (0 Huffman, 2 Huffman_Zstd)
+static int g_ref_lossless = 0;
+void ref_set_lossless(int t) { g_ref_lossless = t; }
+int ref_get_lossless(void) { return g_ref_lossless; }
+int ref_have_zstd(void) { return zstd_handle() != nullptr; }
 
 } // extern "C"

@@ -88,3 +88,38 @@ def test_openmp_backend_matches_serial_size():
     a, _ = r.compress(u, 1, 1e-3, INF, backend=0)
     b, _ = r.compress(u, 1, 1e-3, INF, backend=1)
     assert a.size == b.size
+
+
+@pytest.mark.parametrize("shape,dtype,s,rel,tol", [
+    ((33, 40, 65), np.float32, float("inf"), 1, 1e-3),
+    ((129, 70), np.float64, 0.0, 0, 1e-4),
+])
+def test_reference_huffman_zstd_record_is_a_size_and_a_zstd_frame(shape, dtype, s, rel, tol):
+    """lossless_type::Huffman_Zstd run by the REFERENCE's own writer and reader
+    (Lossless.hpp:188-192, Zstd.hpp:72-141; its ZSTD_* calls forwarded to the machine's
+    libzstd.so.1 by oracle/ref_wrap_huff.cpp): the record is [u64 n][ZSTD frame], the
+    frame -- read with another zstd implementation -- is the n bytes of the plain
+    Huffman container, and the reference decodes it to the same field.  This is the
+    layout mgx_highlevel.cpp writes and reads (tests/test_highlevel_gpu.py)."""
+    pa = pytest.importorskip("pyarrow")
+    o = Oracle("ref")
+    if not o.lib.ref_have_zstd():
+        pytest.skip("no libzstd.so.1 on this machine")
+    u = smooth_field(shape, dtype)
+    plain, norm = o.compress(u, rel, tol, s)
+    back_plain = o.decompress(plain, shape, dtype, rel, tol, s, norm)
+    o.lib.ref_set_lossless(2)
+    try:
+        rec, norm_z = o.compress(u, rel, tol, s)
+        back = o.decompress(rec, shape, dtype, rel, tol, s, norm_z)
+    finally:
+        o.lib.ref_set_lossless(0)
+    assert norm_z == norm
+    n = int(rec[:8].view(np.uint64)[0])
+    assert n == plain.size
+    assert rec[8:12].tobytes() == bytes.fromhex("28b52ffd")   # zstd frame magic
+    body = np.frombuffer(pa.Codec("zstd").decompress(rec[8:].tobytes(), decompressed_size=n,
+                                                     asbytes=True), np.uint8)
+    # (byte 7 of the Huffman container is a pad byte the reference leaves uninitialised)
+    assert np.array_equal(np.delete(body, 7), np.delete(plain, 7))
+    assert np.array_equal(back, back_plain)
