@@ -103,9 +103,10 @@ inline mgx_config to_c(const Config &c) {
   m.domain_decomposition = (int)c.domain_decomposition;
   m.decomposition = (int)c.decomposition;
   // lossless types past CPU_Lossless have no C-side name: anything that is not
-  // Huffman or Huffman_Zstd is refused by the library
+  // Huffman, Huffman_LZ4 or Huffman_Zstd is refused by the library
   m.lossless = (int)c.lossless;
   m.zstd_compress_level = c.zstd_compress_level;
+  m.lz4_block_size = (uint32_t)c.lz4_block_size;
   m.huff_dict_size = (uint32_t)c.huff_dict_size;
   m.huff_block_size = (uint32_t)c.huff_block_size;
   m.reorder = (uint32_t)c.reorder;

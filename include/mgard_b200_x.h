@@ -69,7 +69,7 @@ typedef struct mgx_config {
   int dev_id;
   int domain_decomposition;      /* mgx_dd_type; MaxDim or Block              */
   int decomposition;             /* mgx_decomp_type; MultiDim only            */
-  int lossless;                  /* mgx_lossless; Huffman or Huffman_Zstd     */
+  int lossless;                  /* mgx_lossless; Huffman, Huffman_LZ4, Huffman_Zstd */
   uint32_t huff_dict_size;       /* 8192                                      */
   uint32_t huff_block_size;      /* 1024                                      */
   uint32_t reorder;              /* recorded in the header (0)                */
@@ -83,6 +83,7 @@ typedef struct mgx_config {
   uint64_t max_memory_footprint; /* UINT64_MAX = no limit (bytes)             */
   uint64_t block_size;           /* Block decomposition: edge of a block (256) */
   int zstd_compress_level;       /* Huffman_Zstd: level of ZSTD_compress (3)   */
+  uint32_t lz4_block_size;       /* Huffman_LZ4: bytes per LZ4 block (1 << 15) */
 } mgx_config;
 
 void mgx_config_default(mgx_config *cfg); /* Config::Config(), Config.cpp:31-66 */
@@ -150,6 +151,18 @@ const char *mgx_x_last_error(void);
 /* 1 when libzstd.so.1 was found on this machine (lossless = Huffman_Zstd runs
  * ZSTD_compress / ZSTD_decompress on the host, Lossless/Zstd.hpp:72-141), else 0. */
 int mgx_x_have_zstd(void);
+
+/* lossless = Huffman_LZ4: the reference's portable LZ4 container
+ * (Lossless/LZ4/LZ4.hpp:28-36: "MGXLZ4P\0" | n | chunk_size | nchunks |
+ * comp_bytes[nchunks] | packed_bytes | packed[], every chunk an LZ4 block) written
+ * and read on the host with liblz4.so.1 (dlopen).  mgx_x_have_lz4: 1 when the
+ * library was found.  The two helpers are the stage on host buffers (out = NULL or
+ * too small: MGX_OUTPUT_TOO_LARGE with the size needed in *out_bytes). */
+int mgx_x_have_lz4(void);
+int mgx_x_lz4_wrap(const uint8_t *in, uint64_t n, uint64_t chunk_size, uint8_t *out,
+                   uint64_t cap, uint64_t *out_bytes);
+int mgx_x_lz4_unwrap(const uint8_t *in, uint64_t bytes, uint8_t *out, uint64_t cap,
+                     uint64_t *out_bytes);
 /* kernels launched by the high-level path's contexts since the cache was made */
 uint64_t mgx_x_launch_count(void);
 

@@ -29,7 +29,7 @@ class MgxConfig(ctypes.Structure):
                 ("compress_with_dryrun", c_int), ("auto_cache_release", c_int),
                 ("log_level", c_int), ("max_larget_level", c_u64),
                 ("max_memory_footprint", c_u64), ("block_size", c_u64),
-                ("zstd_compress_level", c_int)]
+                ("zstd_compress_level", c_int), ("lz4_block_size", c_u32)]
 
 
 class MgxMetadata(ctypes.Structure):
@@ -77,6 +77,11 @@ SIGNATURES = {
     "mgx_x_unpin_memory": (c_int, [c_vp, _cfgp]),
     "mgx_x_last_error": (ctypes.c_char_p, []),
     "mgx_x_have_zstd": (c_int, []),
+    "mgx_x_have_lz4": (c_int, []),
+    "mgx_x_lz4_wrap": (c_int, [ctypes.c_void_p, c_u64, c_u64, ctypes.c_void_p, c_u64,
+                               ctypes.POINTER(c_u64)]),
+    "mgx_x_lz4_unwrap": (c_int, [ctypes.c_void_p, c_u64, ctypes.c_void_p, c_u64,
+                                 ctypes.POINTER(c_u64)]),
     "mgx_x_launch_count": (c_u64, []),
     "mgx_metadata_serialize": (c_int, [ctypes.POINTER(MgxMetadata), c_vp, c_u64,
                                        ctypes.POINTER(c_u64)]),

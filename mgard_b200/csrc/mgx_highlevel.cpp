@@ -78,6 +78,114 @@ const ZstdApi &zstd_api() {
   return api;
 }
 
+// ---- liblz4, bound at run time; the reference's portable LZ4 container -----------
+// lossless_type::Huffman_LZ4 is, in this reference, its own nvcomp-free LZ4 stage
+// (Lossless/LZ4/LZ4.hpp:28-36): "MGXLZ4P\0" | n | chunk_size | nchunks |
+// comp_bytes[nchunks] | packed_bytes | packed[] (all size_t), every chunk of
+// chunk_size input bytes an independent LZ4 BLOCK, decoded by output length
+// (LZ4Kernels.hpp:202-262).  The blocks here come from liblz4's LZ4_compress_default
+// and go through LZ4_decompress_safe: the same block format, not the same match
+// finder -- the reference's decoder reads these blocks and this one reads the
+// reference's (tests/test_oracle_vs_ref.py), the compressed sizes differ.
+struct Lz4Api {
+  int (*compress_default)(const char *, char *, int, int) = nullptr;
+  int (*decompress_safe)(const char *, char *, int, int) = nullptr;
+  int (*compressBound)(int) = nullptr;
+  bool ok = false;
+};
+const Lz4Api &lz4_api() {
+  static Lz4Api api;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void *h = dlopen("liblz4.so.1", RTLD_NOW | RTLD_LOCAL);
+    if (!h)
+      h = dlopen("liblz4.so", RTLD_NOW | RTLD_LOCAL);
+    if (!h)
+      return;
+    api.compress_default =
+        (int (*)(const char *, char *, int, int))dlsym(h, "LZ4_compress_default");
+    api.decompress_safe =
+        (int (*)(const char *, char *, int, int))dlsym(h, "LZ4_decompress_safe");
+    api.compressBound = (int (*)(int))dlsym(h, "LZ4_compressBound");
+    api.ok = api.compress_default && api.decompress_safe && api.compressBound;
+  });
+  return api;
+}
+const uint8_t LZ4_SIGNATURE[8] = {'M', 'G', 'X', 'L', 'Z', '4', 'P', 0};
+void put_u64_at(uint8_t *p, uint64_t v) {
+  for (int k = 0; k < 8; k++)
+    p[k] = (uint8_t)(v >> (8 * k));
+}
+uint64_t get_u64_at(const uint8_t *p) {
+  uint64_t v = 0;
+  for (int k = 0; k < 8; k++)
+    v |= (uint64_t)p[k] << (8 * k);
+  return v;
+}
+// -> out = the container of in[0, n)
+int lz4_wrap(const uint8_t *in, uint64_t n, uint64_t chunk, std::vector<uint8_t> &out) {
+  const Lz4Api &z = lz4_api();
+  if (!z.ok)
+    return fail(MGX_FAILURE, "Huffman_LZ4 needs liblz4.so.1 on this machine");
+  if (n == 0 || chunk == 0 || chunk > 0x7E000000ull)
+    return fail(MGX_FAILURE, "LZ4 stage: bad size or chunk size");
+  const uint64_t nchunks = (n - 1) / chunk + 1;
+  const uint64_t head = 8 + 8 * 3 + 8 * nchunks + 8;
+  const uint64_t bound = (uint64_t)z.compressBound((int)chunk);
+  out.resize(head + nchunks * bound);
+  uint64_t packed = 0;
+  for (uint64_t c = 0; c < nchunks; c++) {
+    const uint64_t len = std::min<uint64_t>(chunk, n - c * chunk);
+    const int got = z.compress_default((const char *)in + c * chunk,
+                                       (char *)out.data() + head + packed, (int)len,
+                                       (int)bound);
+    if (got <= 0)
+      return fail(MGX_FAILURE, "LZ4_compress_default failed");
+    put_u64_at(out.data() + 32 + 8 * c, (uint64_t)got);
+    packed += (uint64_t)got;
+  }
+  memcpy(out.data(), LZ4_SIGNATURE, 8);
+  put_u64_at(out.data() + 8, n);
+  put_u64_at(out.data() + 16, chunk);
+  put_u64_at(out.data() + 24, nchunks);
+  put_u64_at(out.data() + 32 + 8 * nchunks, packed);
+  out.resize(head + packed);
+  return MGX_SUCCESS;
+}
+// -> out = the bytes a container holds (at most `limit` of them)
+int lz4_unwrap(const uint8_t *in, uint64_t bytes, uint64_t limit, std::vector<uint8_t> &out) {
+  const Lz4Api &z = lz4_api();
+  if (!z.ok)
+    return fail(MGX_FAILURE, "Huffman_LZ4 needs liblz4.so.1 on this machine");
+  if (bytes < 40 || memcmp(in, LZ4_SIGNATURE, 8) != 0)
+    return fail(MGX_FAILURE, "LZ4 signature mismatch.");
+  const uint64_t n = get_u64_at(in + 8), chunk = get_u64_at(in + 16),
+                 nchunks = get_u64_at(in + 24);
+  if (n == 0 || n > limit || chunk == 0 || chunk > 0x7E000000ull ||
+      nchunks != (n - 1) / chunk + 1 || nchunks > (bytes - 40) / 8)
+    return fail(MGX_FAILURE, "LZ4 container: bad header");
+  const uint64_t head = 8 + 8 * 3 + 8 * nchunks + 8;
+  const uint64_t packed = get_u64_at(in + 32 + 8 * nchunks);
+  if (packed != bytes - head)
+    return fail(MGX_FAILURE, "LZ4 container: size mismatch");
+  out.resize(n);
+  uint64_t pos = 0;
+  for (uint64_t c = 0; c < nchunks; c++) {
+    const uint64_t cb = get_u64_at(in + 32 + 8 * c);
+    const uint64_t len = std::min<uint64_t>(chunk, n - c * chunk);
+    if (cb == 0 || cb > packed - pos || cb > 0x7FFFFFFFull)
+      return fail(MGX_FAILURE, "LZ4 container: bad chunk size");
+    const int got = z.decompress_safe((const char *)in + head + pos,
+                                      (char *)out.data() + c * chunk, (int)cb, (int)len);
+    if (got < 0 || (uint64_t)got != len)
+      return fail(MGX_FAILURE, "LZ4 container: a chunk does not decode to its length");
+    pos += cb;
+  }
+  if (pos != packed)
+    return fail(MGX_FAILURE, "LZ4 container: trailing bytes");
+  return MGX_SUCCESS;
+}
+
 // ---- CRC-32 (IEEE 802.3, reflected 0xEDB88320) == zlib crc32_z --------------
 uint32_t g_crc_table[256];
 bool g_crc_ready = false;
@@ -1003,10 +1111,16 @@ int check_config(const mgx_config &cfg) {
   if (cfg.dev_type != MGX_DEV_AUTO && cfg.dev_type != MGX_DEV_CUDA)
     return fail(MGX_BACKEND_UNAVAILABLE,
                 "only the CUDA backend is built (no CPU fallback by design)");
-  if (cfg.lossless != MGX_LL_HUFFMAN && cfg.lossless != MGX_LL_HUFFMAN_ZSTD)
-    return fail(MGX_FAILURE, "lossless type not supported: Huffman and Huffman_Zstd only");
+  if (cfg.lossless != MGX_LL_HUFFMAN && cfg.lossless != MGX_LL_HUFFMAN_ZSTD &&
+      cfg.lossless != MGX_LL_HUFFMAN_LZ4)
+    return fail(MGX_FAILURE,
+                "lossless type not supported: Huffman, Huffman_LZ4 and Huffman_Zstd only");
   if (cfg.lossless == MGX_LL_HUFFMAN_ZSTD && !zstd_api().ok)
     return fail(MGX_FAILURE, "Huffman_Zstd needs libzstd.so.1 on this machine");
+  if (cfg.lossless == MGX_LL_HUFFMAN_LZ4 && !lz4_api().ok)
+    return fail(MGX_FAILURE, "Huffman_LZ4 needs liblz4.so.1 on this machine");
+  if (cfg.lossless == MGX_LL_HUFFMAN_LZ4 && cfg.lz4_block_size == 0)
+    return fail(MGX_FAILURE, "lz4_block_size must be non-zero");
   if (cfg.decomposition != MGX_DC_MULTIDIM)
     return fail(MGX_FAILURE, "decomposition type not supported: MultiDim only");
   if (cfg.domain_decomposition != MGX_DD_MAXDIM &&
@@ -1276,6 +1390,17 @@ int x_compress(int D, int dtype, const uint64_t *shape, double tol, double s,
       put_u64_le(c.zout[b].data(), bytes);
       payload = c.zout[b].data();
       bytes = 8 + zs;
+      raw = bytes >= n_sub * es;
+    } else if (!raw && cfg.lossless == MGX_LL_HUFFMAN_LZ4) {
+      // Lossless.hpp:182-186: the serialised Huffman container goes through the
+      // portable LZ4 stage (lz4_wrap above), on the host like the Zstd one
+      X_CUDA(cudaEventSynchronize(c.ev_out[b]));
+      c.zin.resize(bytes);
+      X_CUDA(cudaMemcpy(c.zin.data(), c.cbuf[b], bytes, cudaMemcpyDeviceToHost));
+      if ((rc = lz4_wrap(c.zin.data(), bytes, cfg.lz4_block_size, c.zout[b])))
+        return rc;
+      payload = c.zout[b].data();
+      bytes = c.zout[b].size();
       raw = bytes >= n_sub * es;
     }
     // CR < 1: store the subdomain itself (GPUPipelines.hpp:139-156)
@@ -1948,6 +2073,21 @@ int x_decompress(const void *in, size_t in_size, void **out, uint64_t *shape_out
         X_CUDA(cudaMemcpyAsync(c.cbuf[b], c.zout[b].data(), n, cudaMemcpyHostToDevice,
                                c.compute));
         huff_bytes = n;
+      } else if (md.lossless == MGX_LL_HUFFMAN_LZ4) {
+        // LZ4.hpp:183-262: container -> the bytes of the Huffman container
+        X_CUDA(cudaEventSynchronize(c.ev_in[b]));
+        c.zin.resize(rec_bytes[i]);
+        X_CUDA(cudaMemcpy(c.zin.data(), c.cbuf[b], rec_bytes[i], cudaMemcpyDeviceToHost));
+        const uint64_t limit = n_sub * es + 16 * (n_sub / cfg.huff_block_size + 2) +
+                               8ull * (128 + cfg.huff_dict_size) + 4096;
+        if ((rc = lz4_unwrap(c.zin.data(), rec_bytes[i], limit, c.zout[b])))
+          return rc;
+        const uint64_t n = c.zout[b].size();
+        if ((rc = ensure_buffer(c.cbuf[b], c.cbuf_bytes[b], n)))
+          return rc;
+        X_CUDA(cudaMemcpyAsync(c.cbuf[b], c.zout[b].data(), n, cudaMemcpyHostToDevice,
+                               c.compute));
+        huff_bytes = n;
       }
       rc = mgx_decompress(ctx, (const uint8_t *)c.cbuf[b], huff_bytes, local_rel,
                           local_tol, sT, normT, d_out);
@@ -2102,6 +2242,7 @@ void mgx_config_default(mgx_config *cfg) {
   cfg->decomposition = MGX_DC_MULTIDIM;
   cfg->lossless = MGX_LL_HUFFMAN;
   cfg->zstd_compress_level = 3; // Config.cpp:44
+  cfg->lz4_block_size = 1u << 15;
   cfg->huff_dict_size = 8192;
   cfg->huff_block_size = 1024;
   cfg->reorder = 0;
@@ -2410,6 +2551,38 @@ int mgx_x_unpin_memory(void *ptr, const mgx_config *cfg) {
 const char *mgx_x_last_error(void) { return g_err.c_str(); }
 
 int mgx_x_have_zstd(void) { return zstd_api().ok ? 1 : 0; }
+
+int mgx_x_have_lz4(void) { return lz4_api().ok ? 1 : 0; }
+
+int mgx_x_lz4_wrap(const uint8_t *in, uint64_t n, uint64_t chunk_size, uint8_t *out,
+                   uint64_t cap, uint64_t *out_bytes) {
+  if (!in || !out_bytes)
+    return fail(MGX_FAILURE, "bad argument");
+  std::vector<uint8_t> tmp;
+  int rc = lz4_wrap(in, n, chunk_size, tmp);
+  if (rc)
+    return rc;
+  *out_bytes = tmp.size();
+  if (!out || cap < tmp.size())
+    return MGX_OUTPUT_TOO_LARGE;
+  memcpy(out, tmp.data(), tmp.size());
+  return MGX_SUCCESS;
+}
+
+int mgx_x_lz4_unwrap(const uint8_t *in, uint64_t bytes, uint8_t *out, uint64_t cap,
+                     uint64_t *out_bytes) {
+  if (!in || !out_bytes)
+    return fail(MGX_FAILURE, "bad argument");
+  std::vector<uint8_t> tmp;
+  int rc = lz4_unwrap(in, bytes, ~0ull >> 1, tmp);
+  if (rc)
+    return rc;
+  *out_bytes = tmp.size();
+  if (!out || cap < tmp.size())
+    return MGX_OUTPUT_TOO_LARGE;
+  memcpy(out, tmp.data(), tmp.size());
+  return MGX_SUCCESS;
+}
 
 uint64_t mgx_x_launch_count(void) {
   std::lock_guard<std::mutex> lock(g_mu);

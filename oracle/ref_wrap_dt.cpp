@@ -55,7 +55,7 @@
 
 using namespace mgard_x;
 
-extern "C" int ref_get_lossless(void); // ref_wrap_huff.cpp: 0 Huffman, 2 Huffman_Zstd
+extern "C" int ref_get_lossless(void); // ref_wrap_huff.cpp: 0 Huffman, 1 Huffman_LZ4, 2 Huffman_Zstd
 
 namespace {
 
@@ -73,8 +73,9 @@ Config make_config(uint32_t dict_size, uint32_t chunk_size) {
   Config config;
   config.huff_dict_size = dict_size;
   config.huff_block_size = chunk_size;
-  config.lossless = ref_get_lossless() == 2 ? lossless_type::Huffman_Zstd
-                                            : lossless_type::Huffman;
+  config.lossless = ref_get_lossless() == 2   ? lossless_type::Huffman_Zstd
+                    : ref_get_lossless() == 1 ? lossless_type::Huffman_LZ4
+                                              : lossless_type::Huffman;
   config.log_level = log::ERR;
   config.normalize_coordinates = g_normalize;
   return config;

@@ -103,7 +103,7 @@ const char *ZSTD_getErrorName(size_t c) {
   return f ? f(c) : "libzstd.so.1 not found";
 }
 
-// lossless_type of the Config the wrappers build (0 Huffman, 2 Huffman_Zstd)
+// lossless_type of the Config the wrappers build (0 Huffman, 1 Huffman_LZ4, 2 Huffman_Zstd)
 static int g_ref_lossless = 0;
 void ref_set_lossless(int t) { g_ref_lossless = t; }
 int ref_get_lossless(void) { return g_ref_lossless; }

@@ -122,8 +122,8 @@ int main() {
     EXPECT(mgard_x::compress(3, mgard_x::data_type::Float, shape, 1e-3, inf,
                              mgard_x::error_bound_type::REL, in.data(), q, n, cpu,
                              false) == mgard_x::compress_status_type::BackendNotAvailableFailure);
-    mgard_x::Config lz4 = config; // (Huffman and Huffman_Zstd are the lossless types built)
-    lz4.lossless = mgard_x::lossless_type::Huffman_LZ4;
+    mgard_x::Config lz4 = config; // (Huffman, Huffman_LZ4, Huffman_Zstd are the types built)
+    lz4.lossless = mgard_x::lossless_type::CPU_Lossless;
     EXPECT(mgard_x::compress(3, mgard_x::data_type::Float, shape, 1e-3, inf,
                              mgard_x::error_bound_type::REL, in.data(), q, n, lz4,
                              false) == mgard_x::compress_status_type::Failure);

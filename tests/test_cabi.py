@@ -149,3 +149,45 @@ def test_libzstd_is_found_at_run_time_and_the_config_carries_its_level():
         assert lib.mgx_x_have_zstd() == 1
     cfg = hl.Config()
     assert cfg.zstd_compress_level == 3 and cfg.lossless == 0
+
+
+@pytest.mark.parametrize("n,chunk", [(1, 32768), (32768, 32768), (32769, 32768),
+                                     (200001, 4096), (70000, 65536)])
+def test_lz4_container_round_trip_and_checks(n, chunk):
+    """mgx_x_lz4_wrap / mgx_x_lz4_unwrap on host buffers (the reference's portable LZ4
+    container, Lossless/LZ4/LZ4.hpp:28-36): layout, round trip, corrupt input refused"""
+    from mgard_b200 import _lib
+    lib = _lib.load()
+    if not lib.mgx_x_have_lz4():
+        pytest.skip("no liblz4.so.1 on this machine")
+    rng = np.random.default_rng(n)
+    # half compressible, half noise
+    data = np.where(rng.random(n) < 0.5, 7, rng.integers(0, 256, n)).astype(np.uint8)
+    nb = ctypes.c_uint64()
+    assert lib.mgx_x_lz4_wrap(data.ctypes.data, n, chunk, None, 0, ctypes.byref(nb)) == 2
+    box = np.zeros(nb.value, np.uint8)
+    assert lib.mgx_x_lz4_wrap(data.ctypes.data, n, chunk, box.ctypes.data, box.size,
+                              ctypes.byref(nb)) == 0 and nb.value == box.size
+    nchunks = (n - 1) // chunk + 1
+    assert box[:8].tobytes() == b"MGXLZ4P\x00"
+    assert [int(v) for v in box[8:32].view(np.uint64)] == [n, chunk, nchunks]
+    sizes = box[32:32 + 8 * nchunks].view(np.uint64)
+    packed = int(box[32 + 8 * nchunks:40 + 8 * nchunks].view(np.uint64)[0])
+    assert int(sizes.sum()) == packed == box.size - (40 + 8 * nchunks)
+    out = np.zeros(n, np.uint8)
+    assert lib.mgx_x_lz4_unwrap(box.ctypes.data, box.size, out.ctypes.data, n,
+                                ctypes.byref(nb)) == 0 and nb.value == n
+    assert np.array_equal(out, data)
+    # corrupt: signature, a chunk size, truncation, announced size
+    for mutate in ("sig", "chunk", "trunc", "n"):
+        bad = box.copy()
+        if mutate == "sig":
+            bad[3] ^= 1
+        elif mutate == "chunk":
+            bad[32:40] = np.array([int(sizes[0]) + 3], np.uint64).view(np.uint8)
+        elif mutate == "trunc":
+            bad = bad[:-2].copy()
+        else:
+            bad[8:16] = np.array([n + chunk + 1], np.uint64).view(np.uint8)
+        assert lib.mgx_x_lz4_unwrap(bad.ctypes.data, bad.size, out.ctypes.data, n,
+                                    ctypes.byref(nb)) != 0, mutate

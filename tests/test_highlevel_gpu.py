@@ -291,6 +291,50 @@ def test_huffman_zstd_second_stage(shape, dtype, s, mode, decomposed, where):
         hl.decompress(bad)
 
 
+@pytest.mark.xfail(strict=False, reason="written after the round's GPU minutes were spent: "
+                   "the host stage is pinned against the reference on the CPU "
+                   "(tests/test_oracle_vs_ref.py, tests/test_cabi.py) and the pipeline code "
+                   "is the Zstd one's, but this test has not run on a GPU yet")
+@pytest.mark.parametrize("shape,dtype,s,mode,decomposed", [
+    ((33, 40, 65), np.float32, INF, hl.REL, False),
+    ((24, 60, 190), np.float64, INF, hl.REL, True),
+])
+@pytest.mark.parametrize("where", ["device", "host"])
+def test_huffman_lz4_second_stage(shape, dtype, s, mode, decomposed, where):
+    """lossless_type::Huffman_LZ4 (Lossless.hpp:182-186, LZ4/LZ4.hpp:28-36): every record is
+    the reference's portable LZ4 container of the Huffman container; the records unwrap
+    to those of the plain Huffman stream and the stream decodes to the same field."""
+    lib = _lib.load()
+    if not lib.mgx_x_have_lz4():
+        pytest.skip("no liblz4.so.1 on this machine")
+    u = smooth_field(shape, dtype)
+    tol = 1e-3
+    cfg = budget_for_halvings(shape, dtype, s, 3)[0] if decomposed else hl.Config()
+    as_np = lambda t: t.cpu().numpy() if hasattr(t, "cpu") else np.asarray(t)
+    x = torch.from_numpy(u).cuda() if where == "device" else u
+    plain = as_np(hl.compress(x, tol, s, mode, config=cfg))
+    cfg.lossless = hl.HUFFMAN_LZ4
+    stream = as_np(hl.compress(x, tol, s, mode, config=cfg))
+    md0, recs0 = records(plain)
+    md, recs = records(stream)
+    assert md.lossless == hl.HUFFMAN_LZ4 and len(recs) == len(recs0)
+    nb = ctypes.c_uint64()
+    for r, r0 in zip(recs, recs0):
+        r = np.ascontiguousarray(r)
+        assert r[:8].tobytes() == b"MGXLZ4P\x00"
+        out = np.zeros(r0.size, np.uint8)
+        assert lib.mgx_x_lz4_unwrap(r.ctypes.data, r.size, out.ctypes.data, out.size,
+                                    ctypes.byref(nb)) == 0 and nb.value == r0.size
+        assert np.array_equal(out, r0)
+    want = as_np(hl.decompress(plain))
+    got = as_np(hl.decompress(torch.from_numpy(stream).cuda() if where == "device" else stream))
+    assert np.array_equal(got.view(np.uint8), want.view(np.uint8))
+    check_bound(u, got, int(mode == hl.REL), tol, s)
+    bad = _restream(stream, [bytes(r[:-5]) for r in recs])
+    with pytest.raises(hl.MgardError):
+        hl.decompress(bad)
+
+
 def test_raw_fallback_when_a_subdomain_does_not_compress():
     """CR < 1 -> the record is the raw subdomain (GPUPipelines.hpp:139-156) and
     decompress copies it back (:407-421)."""
@@ -324,7 +368,7 @@ def test_status_codes():
     assert call(D=6) == 3           # NotSupportHigherNumberOfDimensionsFailure
     assert call(dtype=7) == 4       # NotSupportDataTypeFailure
     assert call(cfg=hl.Config(dev_type=hl.OPENMP)) == 5   # BackendNotAvailable
-    assert call(cfg=hl.Config(lossless=hl.HUFFMAN_LZ4)) == 1   # not built: Failure
+    assert call(cfg=hl.Config(lossless=hl.CPU_LOSSLESS)) == 1  # not built: Failure
     assert call(cap=64) == 2        # OutputTooLargeFailure
     assert call(cap=300) == 2
     assert b"too large" in lib.mgx_x_last_error()

@@ -123,3 +123,45 @@ def test_reference_huffman_zstd_record_is_a_size_and_a_zstd_frame(shape, dtype, 
     # (byte 7 of the Huffman container is a pad byte the reference leaves uninitialised)
     assert np.array_equal(np.delete(body, 7), np.delete(plain, 7))
     assert np.array_equal(back, back_plain)
+
+
+@pytest.mark.parametrize("shape,dtype,s,rel,tol", [
+    ((33, 40, 65), np.float32, float("inf"), 1, 1e-3),
+    ((129, 70), np.float64, 0.0, 0, 1e-4),
+])
+def test_reference_huffman_lz4_container_both_ways(shape, dtype, s, rel, tol):
+    """lossless_type::Huffman_LZ4 = the reference's portable LZ4 container
+    (Lossless/LZ4/LZ4.hpp:28-36, LZ4Kernels.hpp:202-262) around the serialised Huffman
+    container.  The library's host reader (liblz4 blocks, mgx_x_lz4_unwrap) decodes the
+    REFERENCE's container to its plain Huffman container, and the REFERENCE decodes the
+    container the library's writer (mgx_x_lz4_wrap) makes of that Huffman container to
+    the same field; the block format is shared, the match finder is not (sizes differ)."""
+    import ctypes
+    from mgard_b200 import _lib
+    my = _lib.load()
+    if not my.mgx_x_have_lz4():
+        pytest.skip("no liblz4.so.1 on this machine")
+    o = Oracle("ref")
+    u = smooth_field(shape, dtype)
+    plain, norm = o.compress(u, rel, tol, s)
+    want = o.decompress(plain, shape, dtype, rel, tol, s, norm)
+    nb = ctypes.c_uint64()
+    o.lib.ref_set_lossless(1)
+    try:
+        rec, _ = o.compress(u, rel, tol, s)
+        assert rec[:8].tobytes() == b"MGXLZ4P\x00"
+        n, chunk, nchunks = (int(v) for v in rec[8:32].view(np.uint64))
+        assert n == plain.size and chunk == 1 << 15 and nchunks == (n - 1) // chunk + 1
+        out = np.zeros(n, np.uint8)
+        assert my.mgx_x_lz4_unwrap(rec.ctypes.data, rec.size, out.ctypes.data, out.size,
+                                   ctypes.byref(nb)) == 0 and nb.value == n
+        # (byte 7 of the Huffman container is a pad byte the reference leaves uninitialised)
+        assert np.array_equal(np.delete(out, 7), np.delete(plain, 7))
+        mine = np.zeros(2 * n + 4096, np.uint8)
+        assert my.mgx_x_lz4_wrap(plain.ctypes.data, n, chunk, mine.ctypes.data, mine.size,
+                                 ctypes.byref(nb)) == 0
+        mine = mine[:nb.value].copy()
+        assert np.array_equal(o.decompress(mine, shape, dtype, rel, tol, s, norm), want)
+        assert np.array_equal(o.decompress(rec, shape, dtype, rel, tol, s, norm), want)
+    finally:
+        o.lib.ref_set_lossless(0)
